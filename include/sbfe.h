@@ -1,0 +1,141 @@
+/* sbfe.h - C ABI of the B200-native SpeechBrain feature frontend ("sbfe").
+ *
+ * One shared library (speechbrain_b200/csrc/libsbfe.so) of hand-written sm_100a
+ * kernels.  The reference (SpeechBrain, pure Python on torch) has no FFI; the
+ * drop-in boundary on its side is the Python classes named below, and each entry
+ * point here is what the replacement class binds (ctypes stubs: INTEGRATION.md).
+ *
+ * Conventions
+ *  - every pointer named d_* is a DEVICE pointer owned by the caller; h_* is host.
+ *  - all tensors are contiguous float32 unless a stride argument is given.
+ *  - `stream` is a cudaStream_t passed as void*; every call only enqueues work:
+ *    no allocation, no synchronisation, no global mutable state (thread-safe).
+ *  - return value: 0 ok; <0 invalid argument (SBFE_E_*); >0 a cudaError_t.
+ *  - frame count T = 1 + L / hop (zero centre padding of n_fft/2 per side).
+ */
+#ifndef SBFE_H_
+#define SBFE_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SBFE_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define SBFE_API __attribute__((visibility("default")))
+#else
+#define SBFE_API
+#endif
+
+#define SBFE_E_INVAL (-1)    /* bad size / null pointer / unsupported combination */
+#define SBFE_E_TOOBIG (-2)   /* a dimension exceeds what the kernels index */
+#define SBFE_E_NOSPACE (-3)  /* workspace too small */
+
+/* Utterance-maximum keys: order-preserving uint32 encoding of a float so that
+ * atomicMax works for negative dB values.  0 == "no value yet". */
+typedef uint32_t sbfe_maxkey_t;
+
+/* STFT + mel filterbank configuration.
+ * Mirrors STFT.__init__ (speechbrain/processing/features.py:101-131) and
+ * Filterbank.__init__ (:415-488) after the host has turned them into tables. */
+typedef struct sbfe_fbank_desc {
+  int32_t n_fft;        /* DFT size; bins = n_fft/2 + 1 */
+  int32_t hop;          /* hop in samples */
+  int32_t n_mels;       /* number of filters M */
+  int32_t log_mel;      /* 1: amplitude_to_DB (without the top_db clamp), 0: linear */
+  float multiplier;     /* 10 for power spectrogram, else 20           (:451-454) */
+  float amin;           /* clamp before the log                        (:701) */
+  float db_offset;      /* multiplier * log10(max(amin, ref_value))    (:446,702) */
+  float floor_db;       /* value emitted when x <= amin (= multiplier*log10(amin) - db_offset,
+                           rounded on the host like torch does; -100 by default) */
+  const float* h_window;     /* HOST [n_fft]: window, zero-padded/centred to n_fft */
+  const float* d_window;     /* DEVICE copy of the same */
+  /* filterbank matrix [bins, M] in compressed-column form: filter m covers bins
+   * [mel_start[m], mel_start[m]+mel_count[m]) with weights
+   * d_mel_weight[mel_offset[m] ...]  (triangular: <= ~2*band/df entries;
+   * gaussian: all bins). */
+  const int32_t* d_mel_start;   /* [M] */
+  const int32_t* d_mel_count;   /* [M] */
+  const int32_t* d_mel_offset;  /* [M] */
+  const float* d_mel_weight;    /* [nnz] */
+} sbfe_fbank_desc;
+
+SBFE_API int sbfe_abi_version(void);
+SBFE_API const char* sbfe_error_string(int code);
+
+/* Number of frames torch.stft(center=True) yields for L samples (features.py:161). */
+SBFE_API int64_t sbfe_num_frames(int64_t n_samples, int32_t hop);
+
+/* Scratch bytes sbfe_fbank_forward needs for shapes [B, L] (0 on the fused
+ * n_fft == 400 path; power spectrogram [B,T,bins] otherwise). */
+SBFE_API int64_t sbfe_fbank_workspace_bytes(const sbfe_fbank_desc* desc, int64_t B, int64_t L);
+
+/* Fbank hot path = STFT.forward + spectral_magnitude(power=1) + Filterbank.forward
+ * up to (not including) the per-utterance top_db clamp
+ * (lobes/features.py:138-140; processing/features.py:133-188, 327-356, 490-551,
+ * 691-702).  wav [B, L] (row stride wav_stride) -> out [B, T, M]; d_utt_max[b]
+ * receives the key of max_{t,m} out[b] (must be zeroed by the caller first). */
+SBFE_API int sbfe_fbank_forward(const sbfe_fbank_desc* desc, const float* d_wav, int64_t B, int64_t L,
+                       int64_t wav_stride, float* d_out, sbfe_maxkey_t* d_utt_max,
+                       void* d_workspace, int64_t workspace_bytes, void* stream);
+
+/* STFT.forward for [B, L] input (processing/features.py:133-188):
+ * out [B, T, bins, 2] (re, im), or, with power_only != 0, [B, T, bins] = re^2+im^2. */
+SBFE_API int sbfe_stft_forward(const sbfe_fbank_desc* desc, const float* d_wav, int64_t B, int64_t L,
+                      int64_t wav_stride, float* d_out, int32_t power_only, void* stream);
+
+/* spectral_magnitude (processing/features.py:327-356) on n complex pairs. */
+SBFE_API int sbfe_spectral_magnitude(const float* d_stft, int64_t n, float power, int32_t take_log,
+                            float eps, float* d_out, void* stream);
+
+/* Filterbank.forward on a spectrogram [B, T, bins] (processing/features.py:490-551,
+ * 691-702), again without the top_db clamp; d_utt_max may be NULL. */
+SBFE_API int sbfe_filterbank_forward(const sbfe_fbank_desc* desc, const float* d_spec, int64_t B,
+                            int64_t T, float* d_out, sbfe_maxkey_t* d_utt_max, void* stream);
+
+/* Post stage, any subset of (in this order):
+ *   top_db clamp  x = max(x, max_b - top_db)          (features.py:706-710)
+ *   DCT           x @ d_dct[F_in, n_dct]              (features.py:764-786)
+ *   Deltas x2     [x, d(x), d(d(x))], window 5        (features.py:820-852; lobes:141-144)
+ *   ContextWindow out[t, f*C + c] = x[t + c - left, f] (features.py:897-937)
+ * x [B, T, F_in] -> out [B, T, F_out], F_out = (n_dct or F_in) * (3 if deltas) * (left+right+1 if context).
+ * d_utt_max NULL => no clamp; d_dct NULL => no DCT; out may alias x only when
+ * no DCT/deltas/context is requested (pure clamp). */
+SBFE_API int sbfe_post_forward(const float* d_x, int64_t B, int64_t T, int32_t F_in,
+                      const sbfe_maxkey_t* d_utt_max, float top_db, const float* d_dct,
+                      int32_t n_dct, int32_t deltas, int32_t delta_window, int32_t context,
+                      int32_t left, int32_t right, float* d_out, void* stream);
+
+/* InputNormalization statistics (processing/features.py:1020-1031, 1120-1145).
+ * x [B, T, F], d_lengths [B] relative lengths; n_b = rint(lengths[b] * T) frames.
+ * Writes mean[B, F] and std[B, F] (unbiased, floored at eps; mean_norm == 0 -> 0,
+ * std_norm == 0 -> 1).  With d_utt_max != NULL the top_db clamp is applied to x
+ * on the fly (fused frontend).  Workspace: sbfe_norm_workspace_bytes(B, T, F). */
+SBFE_API int64_t sbfe_norm_workspace_bytes(int64_t B, int64_t T, int32_t F);
+SBFE_API int sbfe_norm_stats(const float* d_x, const float* d_lengths, int64_t B, int64_t T, int32_t F,
+                    int32_t mean_norm, int32_t std_norm, float eps,
+                    const sbfe_maxkey_t* d_utt_max, float top_db, float* d_mean, float* d_std,
+                    void* d_workspace, int64_t workspace_bytes, void* stream);
+
+/* batch / global statistics (processing/features.py:1083-1114):
+ * d_cur[2F+1] = {sum_b mean_b, sum_b std_b, B} (the all-reduce payload).  */
+SBFE_API int sbfe_norm_reduce(const float* d_mean, const float* d_std, int64_t B, int32_t F,
+                     float* d_cur, void* stream);
+/* running update: glob = first ? cur/n : (1-w)*glob + w*cur/n, n = d_cur[2F]. */
+SBFE_API int sbfe_norm_update(const float* d_cur, int32_t F, int32_t first, float weight,
+                     float* d_glob_mean, float* d_glob_std, void* stream);
+
+/* out = (x - mean) / std (processing/features.py:1035, 1088, 1116).
+ * per_utt != 0: mean/std are [B, F]; else [F] shared.  In place when out == x.
+ * d_utt_max != NULL applies the top_db clamp to x first. */
+SBFE_API int sbfe_norm_apply(const float* d_x, int64_t B, int64_t T, int32_t F, const float* d_mean,
+                    const float* d_std, int32_t per_utt, const sbfe_maxkey_t* d_utt_max,
+                    float top_db, float* d_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SBFE_H_ */

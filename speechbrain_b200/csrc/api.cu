@@ -1,0 +1,152 @@
+// extern "C" entry points of libsbfe.so (declared in include/sbfe.h).
+// Validation + dispatch only; kernels live in fbank400.cu / generic.cu /
+// post.cu / norm.cu.  Nothing here allocates, synchronises or keeps state.
+#include "common.cuh"
+
+namespace sbfe {
+int launch_fbank400(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
+                    sbfe_maxkey_t*, cudaStream_t);
+int launch_stft_generic(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
+                        int, cudaStream_t);
+int launch_spectral_magnitude(const float*, int64_t, float, int, float, float*, cudaStream_t);
+int launch_mel_db(const sbfe_fbank_desc*, const float*, int64_t, int64_t, float*, sbfe_maxkey_t*,
+                  cudaStream_t);
+int launch_post(const float*, int64_t, int64_t, int, const sbfe_maxkey_t*, float, const float*,
+                int, int, int, int, int, int, float*, cudaStream_t);
+int64_t norm_workspace_bytes(int64_t, int64_t, int);
+int launch_norm_stats(const float*, const float*, int64_t, int64_t, int, int, int, float,
+                      const sbfe_maxkey_t*, float, float*, float*, void*, int64_t, cudaStream_t);
+int launch_norm_reduce(const float*, const float*, int64_t, int, float*, cudaStream_t);
+int launch_norm_update(const float*, int, int, float, float*, float*, cudaStream_t);
+int launch_norm_apply(const float*, int64_t, int64_t, int, const float*, const float*, int,
+                      const sbfe_maxkey_t*, float, float*, cudaStream_t);
+
+static bool desc_ok(const sbfe_fbank_desc* d, bool need_mel) {
+  if (!d || d->n_fft < 2 || (d->n_fft & 1) || d->hop < 1 || !d->d_window || !d->h_window)
+    return false;
+  if (need_mel && (d->n_mels < 1 || !d->d_mel_start || !d->d_mel_count || !d->d_mel_offset ||
+                   !d->d_mel_weight))
+    return false;
+  return true;
+}
+// the fused kernel covers n_fft == 400 with any hop <= 400 and M that fits its tile
+static bool fused_ok(const sbfe_fbank_desc* d) {
+  return d->n_fft == 400 && d->hop <= 400 && d->n_mels <= 384;
+}
+}  // namespace sbfe
+
+using namespace sbfe;
+
+extern "C" {
+
+int sbfe_abi_version(void) { return SBFE_ABI_VERSION; }
+
+const char* sbfe_error_string(int code) {
+  if (code == 0) return "ok";
+  if (code == SBFE_E_INVAL) return "sbfe: invalid argument";
+  if (code == SBFE_E_TOOBIG) return "sbfe: dimension too large for the kernels";
+  if (code == SBFE_E_NOSPACE) return "sbfe: workspace too small";
+  if (code > 0) return cudaGetErrorString((cudaError_t)code);
+  return "sbfe: unknown error";
+}
+
+int64_t sbfe_num_frames(int64_t n_samples, int32_t hop) {
+  return hop > 0 && n_samples >= 0 ? 1 + n_samples / hop : -1;
+}
+
+int64_t sbfe_fbank_workspace_bytes(const sbfe_fbank_desc* d, int64_t B, int64_t L) {
+  if (!d || d->hop < 1 || B < 0 || L < 0) return SBFE_E_INVAL;
+  if (fused_ok(d)) return 0;
+  return B * (1 + L / d->hop) * (int64_t)(d->n_fft / 2 + 1) * (int64_t)sizeof(float);
+}
+
+int sbfe_fbank_forward(const sbfe_fbank_desc* d, const float* d_wav, int64_t B, int64_t L,
+                       int64_t wav_stride, float* d_out, sbfe_maxkey_t* d_utt_max, void* d_ws,
+                       int64_t ws_bytes, void* stream) {
+  if (!desc_ok(d, true) || B < 0 || L < 0 || wav_stride < L) return SBFE_E_INVAL;
+  if (B == 0) return 0;
+  if (!d_wav || !d_out) return SBFE_E_INVAL;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (fused_ok(d)) return launch_fbank400(d, d_wav, B, L, wav_stride, d_out, d_utt_max, s);
+  if (!d_ws || ws_bytes < sbfe_fbank_workspace_bytes(d, B, L)) return SBFE_E_NOSPACE;
+  int rc = launch_stft_generic(d, d_wav, B, L, wav_stride, (float*)d_ws, 1, s);
+  if (rc) return rc;
+  return launch_mel_db(d, (const float*)d_ws, B, 1 + L / d->hop, d_out, d_utt_max, s);
+}
+
+int sbfe_stft_forward(const sbfe_fbank_desc* d, const float* d_wav, int64_t B, int64_t L,
+                      int64_t wav_stride, float* d_out, int32_t power_only, void* stream) {
+  if (!desc_ok(d, false) || B < 0 || L < 0 || wav_stride < L) return SBFE_E_INVAL;
+  if (B == 0) return 0;
+  if (!d_wav || !d_out) return SBFE_E_INVAL;
+  return launch_stft_generic(d, d_wav, B, L, wav_stride, d_out, power_only, (cudaStream_t)stream);
+}
+
+int sbfe_spectral_magnitude(const float* d_stft, int64_t n, float power, int32_t take_log,
+                            float eps, float* d_out, void* stream) {
+  if (n < 0 || (n > 0 && (!d_stft || !d_out))) return SBFE_E_INVAL;
+  return launch_spectral_magnitude(d_stft, n, power, take_log, eps, d_out, (cudaStream_t)stream);
+}
+
+int sbfe_filterbank_forward(const sbfe_fbank_desc* d, const float* d_spec, int64_t B, int64_t T,
+                            float* d_out, sbfe_maxkey_t* d_utt_max, void* stream) {
+  if (!d || d->n_fft < 2 || d->n_mels < 1 || !d->d_mel_start || !d->d_mel_count ||
+      !d->d_mel_offset || !d->d_mel_weight || B < 0 || T < 0)
+    return SBFE_E_INVAL;
+  if (B == 0 || T == 0) return 0;
+  if (!d_spec || !d_out) return SBFE_E_INVAL;
+  return launch_mel_db(d, d_spec, B, T, d_out, d_utt_max, (cudaStream_t)stream);
+}
+
+int sbfe_post_forward(const float* d_x, int64_t B, int64_t T, int32_t F_in,
+                      const sbfe_maxkey_t* d_utt_max, float top_db, const float* d_dct,
+                      int32_t n_dct, int32_t deltas, int32_t delta_window, int32_t context,
+                      int32_t left, int32_t right, float* d_out, void* stream) {
+  if (B < 0 || T < 0 || F_in < 1 || left < 0 || right < 0) return SBFE_E_INVAL;
+  if (d_dct && (n_dct < 1 || n_dct > F_in)) return SBFE_E_INVAL;
+  if (B == 0 || T == 0) return 0;
+  if (!d_x || !d_out) return SBFE_E_INVAL;
+  return launch_post(d_x, B, T, F_in, d_utt_max, top_db, d_dct, n_dct, deltas, delta_window,
+                     context, left, right, d_out, (cudaStream_t)stream);
+}
+
+int64_t sbfe_norm_workspace_bytes(int64_t B, int64_t T, int32_t F) {
+  if (B < 0 || T < 0 || F < 0) return SBFE_E_INVAL;
+  return norm_workspace_bytes(B, T, F);
+}
+
+int sbfe_norm_stats(const float* d_x, const float* d_lengths, int64_t B, int64_t T, int32_t F,
+                    int32_t mean_norm, int32_t std_norm, float eps,
+                    const sbfe_maxkey_t* d_utt_max, float top_db, float* d_mean, float* d_std,
+                    void* d_ws, int64_t ws_bytes, void* stream) {
+  if (B < 0 || T < 0 || F < 0) return SBFE_E_INVAL;
+  if (B == 0 || F == 0) return 0;
+  if (!d_x || !d_lengths || !d_mean || !d_std || !d_ws) return SBFE_E_INVAL;
+  return launch_norm_stats(d_x, d_lengths, B, T, F, mean_norm, std_norm, eps, d_utt_max, top_db,
+                           d_mean, d_std, d_ws, ws_bytes, (cudaStream_t)stream);
+}
+
+int sbfe_norm_reduce(const float* d_mean, const float* d_std, int64_t B, int32_t F, float* d_cur,
+                     void* stream) {
+  if (B < 0 || F < 1 || !d_mean || !d_std || !d_cur) return SBFE_E_INVAL;
+  return launch_norm_reduce(d_mean, d_std, B, F, d_cur, (cudaStream_t)stream);
+}
+
+int sbfe_norm_update(const float* d_cur, int32_t F, int32_t first, float weight,
+                     float* d_glob_mean, float* d_glob_std, void* stream) {
+  if (F < 1 || !d_cur || !d_glob_mean || !d_glob_std) return SBFE_E_INVAL;
+  return launch_norm_update(d_cur, F, first, weight, d_glob_mean, d_glob_std,
+                            (cudaStream_t)stream);
+}
+
+int sbfe_norm_apply(const float* d_x, int64_t B, int64_t T, int32_t F, const float* d_mean,
+                    const float* d_std, int32_t per_utt, const sbfe_maxkey_t* d_utt_max,
+                    float top_db, float* d_out, void* stream) {
+  if (B < 0 || T < 0 || F < 0) return SBFE_E_INVAL;
+  if (B == 0 || T == 0 || F == 0) return 0;
+  if (!d_x || !d_out || !d_mean || !d_std) return SBFE_E_INVAL;
+  return launch_norm_apply(d_x, B, T, F, d_mean, d_std, per_utt, d_utt_max, top_db, d_out,
+                           (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,52 @@
+// Shared device helpers for the sbfe kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/sbfe.h"
+
+namespace sbfe {
+
+// Order-preserving float -> uint32 key (0 is reserved for "empty").
+__device__ __forceinline__ uint32_t max_key_encode(float v) {
+  const uint32_t u = __float_as_uint(v);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float max_key_decode(uint32_t k) {
+  const uint32_t u = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k;
+  return __uint_as_float(u);
+}
+// floor for the top_db clamp of utterance b; -inf when clamping is off
+__device__ __forceinline__ float clamp_floor(const sbfe_maxkey_t* utt_max, int64_t b,
+                                             float top_db) {
+  if (utt_max == nullptr) return -INFINITY;
+  return max_key_decode(utt_max[b]) - top_db;
+}
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// amplitude_to_DB without the top_db clamp (processing/features.py:701-702).
+// log10 through the MUFU lg2 unit: |err| <= ~2^-22 * |log2 x| -> < 3e-5 dB.
+struct DbParams {
+  float scale;     // multiplier * log10(2)
+  float amin;
+  float offset;    // multiplier * log10(max(amin, ref))
+  float floor_db;  // exact host-rounded value for x <= amin
+  int log_mel;
+};
+__device__ __forceinline__ float to_db(float x, const DbParams& p) {
+  if (!p.log_mel) return x;
+  // !(x > amin) also catches NaN-free zero/negative inputs exactly like clamp()
+  return (x > p.amin) ? fmaf(__log2f(x), p.scale, -p.offset) : p.floor_db;
+}
+
+inline int check_last(void) {
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : (int)e;
+}
+
+}  // namespace sbfe

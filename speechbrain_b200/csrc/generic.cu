@@ -1,0 +1,153 @@
+// General (any n_fft / hop) kernels: direct-DFT STFT, spectral magnitude and the
+// mel projection on a materialised spectrogram.  They back the stand-alone
+// STFT / spectral_magnitude / Filterbank modules and Fbank/MFCC with
+// n_fft != 400; the default hot path is fbank400.cu.
+//   STFT.forward        speechbrain/processing/features.py:133-188
+//   spectral_magnitude  speechbrain/processing/features.py:327-356
+//   Filterbank.forward  speechbrain/processing/features.py:490-551, 701-702
+#include <cmath>
+
+#include "common.cuh"
+
+namespace sbfe {
+
+constexpr int kGenFrames = 4;     // frames per CTA
+constexpr int kGenThreads = 256;
+
+// smem: twiddle table cs[n_fft] (cos, -sin) + kGenFrames windowed frames.
+__global__ void __launch_bounds__(kGenThreads)
+stft_generic_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, int64_t T,
+                    const float* __restrict__ window, int n_fft, int hop,
+                    float* __restrict__ out, int power_only, unsigned tiles) {
+  extern __shared__ __align__(16) float smem[];
+  float2* s_cs = reinterpret_cast<float2*>(smem);
+  float* s_fr = smem + 2 * n_fft;
+  const int bins = n_fft / 2 + 1;
+  const int64_t b = blockIdx.x / tiles;
+  const int64_t t0 = (int64_t)(blockIdx.x - b * tiles) * kGenFrames;
+  const float* w = wav + b * wav_stride;
+  for (int j = threadIdx.x; j < n_fft; j += kGenThreads) {
+    float s, c;
+    sincospif(2.0f * (float)j / (float)n_fft, &s, &c);
+    s_cs[j] = make_float2(c, -s);
+  }
+  for (int i = threadIdx.x; i < kGenFrames * n_fft; i += kGenThreads) {
+    const int f = i / n_fft, n = i - f * n_fft;
+    const int64_t g = (t0 + f) * hop - n_fft / 2 + n;
+    s_fr[i] = (g >= 0 && g < L) ? __ldg(w + g) * __ldg(window + n) : 0.f;
+  }
+  __syncthreads();
+  for (int p = threadIdx.x; p < kGenFrames * bins; p += kGenThreads) {
+    const int f = p / bins, k = p - f * bins;
+    if (t0 + f >= T) continue;
+    const float* x = s_fr + f * n_fft;
+    float re = 0.f, im = 0.f;
+    int idx = 0;
+    for (int n = 0; n < n_fft; ++n) {
+      const float2 cs = s_cs[idx];
+      re = fmaf(x[n], cs.x, re);
+      im = fmaf(x[n], cs.y, im);
+      idx += k;
+      if (idx >= n_fft) idx -= n_fft;
+    }
+    const int64_t o = ((b * T + t0 + f) * bins + k);
+    if (power_only) {
+      out[o] = re * re + im * im;
+    } else {
+      reinterpret_cast<float2*>(out)[o] = make_float2(re, im);
+    }
+  }
+}
+
+int launch_stft_generic(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64_t L,
+                        int64_t wav_stride, float* out, int power_only, cudaStream_t stream) {
+  const int64_t T = 1 + L / d->hop;
+  const int64_t tiles = (T + kGenFrames - 1) / kGenFrames;
+  if (tiles * B > 0x7fffffff) return SBFE_E_TOOBIG;
+  if (d->n_fft > 4096) return SBFE_E_TOOBIG;
+  const size_t smem = (size_t)(2 + kGenFrames) * d->n_fft * sizeof(float);
+  cudaError_t e = cudaFuncSetAttribute(stft_generic_kernel,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return (int)e;
+  stft_generic_kernel<<<(unsigned)(tiles * B), kGenThreads, smem, stream>>>(
+      wav, L, wav_stride, T, d->d_window, d->n_fft, d->hop, out, power_only, (unsigned)tiles);
+  return check_last();
+}
+
+__global__ void spectral_magnitude_kernel(const float2* __restrict__ in, int64_t n, float power,
+                                          int take_log, float eps, float* __restrict__ out) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const float2 v = in[i];
+    float s = v.x * v.x + v.y * v.y;
+    if (power < 1.f) s += eps;
+    if (power != 1.f) s = powf(s, power);
+    out[i] = take_log ? logf(s + eps) : s;
+  }
+}
+
+int launch_spectral_magnitude(const float* in, int64_t n, float power, int take_log, float eps,
+                              float* out, cudaStream_t stream) {
+  if (n == 0) return 0;
+  int64_t blocks = (n + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  spectral_magnitude_kernel<<<(unsigned)blocks, 256, 0, stream>>>(
+      reinterpret_cast<const float2*>(in), n, power, take_log, eps, out);
+  return check_last();
+}
+
+constexpr int kMelFrames = 8;
+constexpr int kMelThreads = 256;
+
+__global__ void __launch_bounds__(kMelThreads)
+mel_db_kernel(const float* __restrict__ spec, int64_t T, int bins, int M,
+              const int32_t* __restrict__ mel_start, const int32_t* __restrict__ mel_count,
+              const int32_t* __restrict__ mel_offset, const float* __restrict__ mel_weight,
+              DbParams db, float* __restrict__ out, sbfe_maxkey_t* utt_max, unsigned tiles) {
+  extern __shared__ __align__(16) float s_spec[];  // [kMelFrames][bins]
+  const int64_t b = blockIdx.x / tiles;
+  const int64_t t0 = (int64_t)(blockIdx.x - b * tiles) * kMelFrames;
+  const int64_t left = T - t0;
+  const int nf = left < kMelFrames ? (int)left : kMelFrames;
+  const float* src = spec + (b * T + t0) * bins;
+  for (int i = threadIdx.x; i < nf * bins; i += kMelThreads) s_spec[i] = __ldg(src + i);
+  __syncthreads();
+  float vmax = -INFINITY;
+  float* dst = out + (b * T + t0) * M;
+  for (int p = threadIdx.x; p < nf * M; p += kMelThreads) {
+    const int f = p / M, m = p - f * M;
+    const int start = mel_start[m], cnt = mel_count[m];
+    const float* wt = mel_weight + mel_offset[m];
+    const float* x = s_spec + f * bins + start;
+    float acc = 0.f;
+    for (int i = 0; i < cnt; ++i) acc = fmaf(__ldg(wt + i), x[i], acc);
+    const float v = to_db(acc, db);
+    dst[p] = v;
+    vmax = fmaxf(vmax, v);
+  }
+  vmax = warp_max(vmax);
+  if ((threadIdx.x & 31) == 0 && vmax > -INFINITY && utt_max != nullptr)
+    atomicMax(utt_max + b, max_key_encode(vmax));
+}
+
+int launch_mel_db(const sbfe_fbank_desc* d, const float* spec, int64_t B, int64_t T, float* out,
+                  sbfe_maxkey_t* utt_max, cudaStream_t stream) {
+  if (B == 0 || T == 0) return 0;
+  const int bins = d->n_fft / 2 + 1;
+  const int64_t tiles = (T + kMelFrames - 1) / kMelFrames;
+  if (tiles * B > 0x7fffffff) return SBFE_E_TOOBIG;
+  const size_t smem = (size_t)kMelFrames * bins * sizeof(float);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(mel_db_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+  }
+  const DbParams db{d->multiplier * 0.30102999566398120f, d->amin, d->db_offset, d->floor_db,
+                    d->log_mel};
+  mel_db_kernel<<<(unsigned)(tiles * B), kMelThreads, smem, stream>>>(
+      spec, T, bins, d->n_mels, d->d_mel_start, d->d_mel_count, d->d_mel_offset, d->d_mel_weight,
+      db, out, utt_max, (unsigned)tiles);
+  return check_last();
+}
+
+}  // namespace sbfe

@@ -1,0 +1,228 @@
+// InputNormalization kernels (speechbrain/processing/features.py:1000-1145).
+//   stats   : per (utterance, feature) mean and unbiased std over the first
+//             n_b = rint(lengths[b] * T) frames                  (:1020-1031, 1120-1145)
+//   reduce  : sum over utterances -> the [2F+1] all-reduce payload (:1083-1085)
+//   update  : running global statistics                          (:1090-1114)
+//   apply   : (x - mean) / std over ALL T frames, padding too     (:1035, 1088, 1116)
+// The reference does this with a Python loop over sentences (a host sync per
+// sentence); here nothing leaves the device.
+#include "common.cuh"
+
+namespace sbfe {
+
+constexpr int kNormThreads = 256;
+constexpr int kStatChunk = 256;  // frames per CTA in the statistics pass
+
+__device__ __forceinline__ int valid_frames(const float* lengths, int64_t b, int64_t T) {
+  // torch.round(lengths[b] * T).int(): float32 product, round-half-to-even (:1023)
+  int n = __float2int_rn(lengths[b] * (float)T);
+  return n < 0 ? 0 : (n > T ? (int)T : n);
+}
+
+// partial sums about the pivot K = x[b, 0, f]:  ws[b][chunk][f] = (sum, sumsq)
+__global__ void __launch_bounds__(kNormThreads)
+norm_stats_partial_kernel(const float* __restrict__ x, const float* __restrict__ lengths,
+                          int64_t T, int F, const sbfe_maxkey_t* __restrict__ utt_max,
+                          float top_db, double2* __restrict__ ws, unsigned chunks, int bx) {
+  __shared__ double2 s_red[kNormThreads];
+  const int64_t b = blockIdx.x / chunks;
+  const int c = blockIdx.x - b * chunks;
+  const int n = valid_frames(lengths, b, T);
+  const int t_lo = c * kStatChunk;
+  const int t_hi = min(n, t_lo + kStatChunk);
+  const int by = kNormThreads / bx;
+  const int tx = threadIdx.x % bx, ty = threadIdx.x / bx;
+  const float floor_b = clamp_floor(utt_max, b, top_db);
+  const float* xb = x + b * T * F;
+  for (int f0 = 0; f0 < F; f0 += bx) {
+    const int f = f0 + tx;
+    float s1 = 0.f, s2 = 0.f;
+    if (f < F && t_lo < t_hi) {
+      const float pivot = fmaxf(__ldg(xb + f), floor_b);
+      for (int t = t_lo + ty; t < t_hi; t += by) {
+        const float d = fmaxf(__ldg(xb + (int64_t)t * F + f), floor_b) - pivot;
+        s1 += d;
+        s2 = fmaf(d, d, s2);
+      }
+    }
+    s_red[threadIdx.x] = make_double2((double)s1, (double)s2);
+    __syncthreads();
+    if (ty == 0 && f < F) {
+      double a1 = 0.0, a2 = 0.0;
+      for (int r = 0; r < by; ++r) {
+        a1 += s_red[r * bx + tx].x;
+        a2 += s_red[r * bx + tx].y;
+      }
+      ws[((int64_t)b * chunks + c) * F + f] = make_double2(a1, a2);
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void norm_stats_final_kernel(const float* __restrict__ x,
+                                        const float* __restrict__ lengths, int64_t B, int64_t T,
+                                        int F, int mean_norm, int std_norm, float eps,
+                                        const sbfe_maxkey_t* __restrict__ utt_max, float top_db,
+                                        const double2* __restrict__ ws, unsigned chunks,
+                                        float* __restrict__ mean, float* __restrict__ stdv) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= B * F) return;
+  const int64_t b = i / F;
+  const int f = (int)(i - b * F);
+  const int n = valid_frames(lengths, b, T);
+  double s1 = 0.0, s2 = 0.0;
+  for (unsigned c = 0; c < chunks; ++c) {
+    const double2 v = ws[((int64_t)b * chunks + c) * F + f];
+    s1 += v.x;
+    s2 += v.y;
+  }
+  const float floor_b = clamp_floor(utt_max, b, top_db);
+  const double pivot = (T > 0) ? (double)fmaxf(x[b * T * F + f], floor_b) : 0.0;
+  // n == 0: mean of an empty slice is NaN, n == 1: unbiased std is NaN (torch)
+  const double m = (n > 0) ? pivot + s1 / n : (double)NAN;
+  double var = (n > 1) ? (s2 - s1 * s1 / n) / (n - 1) : (double)NAN;
+  if (var < 0.0) var = 0.0;
+  float sd = (float)sqrt(var);
+  if (sd == sd) sd = fmaxf(sd, eps);  // torch.max propagates NaN
+  mean[i] = mean_norm ? (float)m : 0.f;
+  stdv[i] = std_norm ? sd : 1.f;
+}
+
+__global__ void norm_reduce_kernel(const float* __restrict__ mean, const float* __restrict__ stdv,
+                                   int64_t B, int F, float* __restrict__ cur) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f < F) {
+    float a = 0.f, s = 0.f;
+    for (int64_t b = 0; b < B; ++b) {
+      a += mean[b * F + f];
+      s += stdv[b * F + f];
+    }
+    cur[f] = a;
+    cur[F + f] = s;
+  }
+  if (f == 0) cur[2 * F] = (float)B;
+}
+
+__global__ void norm_update_kernel(const float* __restrict__ cur, int F, int first, float weight,
+                                   float* __restrict__ gmean, float* __restrict__ gstd) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= F) return;
+  const float n = cur[2 * F];
+  const float cm = cur[f] / n, cs = cur[F + f] / n;
+  if (first) {
+    gmean[f] = cm;
+    gstd[f] = cs;
+  } else {
+    gmean[f] = (1.f - weight) * gmean[f] + weight * cm;
+    gstd[f] = (1.f - weight) * gstd[f] + weight * cs;
+  }
+}
+
+// out = (max(x, floor_b) - mean) / std.  VEC = 4 when F % 4 == 0 and 16 B aligned.
+template <int VEC>
+__global__ void __launch_bounds__(kNormThreads)
+norm_apply_kernel(const float* __restrict__ x, int64_t T, int F, const float* __restrict__ mean,
+                  const float* __restrict__ stdv, int per_utt,
+                  const sbfe_maxkey_t* __restrict__ utt_max, float top_db,
+                  float* __restrict__ out, unsigned chunks, int rows_per_cta, int bx) {
+  const int64_t b = blockIdx.x / chunks;
+  const int c = blockIdx.x - b * chunks;
+  const int by = kNormThreads / bx;
+  const int tx = threadIdx.x % bx, ty = threadIdx.x / bx;
+  const float floor_b = clamp_floor(utt_max, b, top_db);
+  const int64_t t_lo = (int64_t)c * rows_per_cta;
+  const int64_t t_hi = min(T, t_lo + rows_per_cta);
+  const float* m = mean + (per_utt ? b * F : 0);
+  const float* s = stdv + (per_utt ? b * F : 0);
+  const float* xb = x + b * T * F;
+  float* ob = out + b * T * F;
+  const int FV = F / VEC;
+  for (int fv = tx; fv < FV; fv += bx) {
+    float mm[VEC], ss[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) {
+      mm[k] = __ldg(m + fv * VEC + k);
+      ss[k] = __ldg(s + fv * VEC + k);
+    }
+    for (int64_t t = t_lo + ty; t < t_hi; t += by) {
+      const int64_t o = t * F + fv * VEC;
+      if (VEC == 4) {
+        float4 v = *reinterpret_cast<const float4*>(xb + o);
+        v.x = (fmaxf(v.x, floor_b) - mm[0]) / ss[0];
+        v.y = (fmaxf(v.y, floor_b) - mm[1]) / ss[1];
+        v.z = (fmaxf(v.z, floor_b) - mm[2]) / ss[2];
+        v.w = (fmaxf(v.w, floor_b) - mm[3]) / ss[3];
+        *reinterpret_cast<float4*>(ob + o) = v;
+      } else {
+        ob[o] = (fmaxf(xb[o], floor_b) - mm[0]) / ss[0];
+      }
+    }
+  }
+}
+
+static int pick_bx(int cols) {  // power of two <= 256 covering `cols`
+  int bx = 1;
+  while (bx < cols && bx < kNormThreads) bx <<= 1;
+  return bx;
+}
+
+int64_t norm_workspace_bytes(int64_t B, int64_t T, int F) {
+  const int64_t chunks = (T + kStatChunk - 1) / kStatChunk;
+  return B * (chunks > 0 ? chunks : 1) * F * (int64_t)sizeof(double2);
+}
+
+int launch_norm_stats(const float* x, const float* lengths, int64_t B, int64_t T, int F,
+                      int mean_norm, int std_norm, float eps, const sbfe_maxkey_t* utt_max,
+                      float top_db, float* mean, float* stdv, void* ws, int64_t ws_bytes,
+                      cudaStream_t stream) {
+  if (B == 0 || F == 0) return 0;
+  const int64_t chunks = (T + kStatChunk - 1) / kStatChunk;
+  if (ws_bytes < norm_workspace_bytes(B, T, F)) return SBFE_E_NOSPACE;
+  if (chunks * B > 0x7fffffff || B * F > 0x7fffffff) return SBFE_E_TOOBIG;
+  if (chunks > 0) {
+    norm_stats_partial_kernel<<<(unsigned)(chunks * B), kNormThreads, 0, stream>>>(
+        x, lengths, T, F, utt_max, top_db, (double2*)ws, (unsigned)chunks, pick_bx(F));
+    int rc = check_last();
+    if (rc) return rc;
+  }
+  norm_stats_final_kernel<<<(unsigned)((B * F + 255) / 256), 256, 0, stream>>>(
+      x, lengths, B, T, F, mean_norm, std_norm, eps, utt_max, top_db, (const double2*)ws,
+      (unsigned)chunks, mean, stdv);
+  return check_last();
+}
+
+int launch_norm_reduce(const float* mean, const float* stdv, int64_t B, int F, float* cur,
+                       cudaStream_t stream) {
+  norm_reduce_kernel<<<(F + 127) / 128 > 0 ? (F + 127) / 128 : 1, 128, 0, stream>>>(mean, stdv, B, F, cur);
+  return check_last();
+}
+
+int launch_norm_update(const float* cur, int F, int first, float weight, float* gmean,
+                       float* gstd, cudaStream_t stream) {
+  if (F == 0) return 0;
+  norm_update_kernel<<<(F + 127) / 128, 128, 0, stream>>>(cur, F, first, weight, gmean, gstd);
+  return check_last();
+}
+
+int launch_norm_apply(const float* x, int64_t B, int64_t T, int F, const float* mean,
+                      const float* stdv, int per_utt, const sbfe_maxkey_t* utt_max, float top_db,
+                      float* out, cudaStream_t stream) {
+  if (B == 0 || T == 0 || F == 0) return 0;
+  const bool vec = (F % 4 == 0) &&
+                   ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+  const int cols = vec ? F / 4 : F;
+  const int bx = pick_bx(cols);
+  const int by = kNormThreads / bx;
+  int rows = by * 8;  // 8 rows per thread
+  const int64_t chunks = (T + rows - 1) / rows;
+  if (chunks * B > 0x7fffffff) return SBFE_E_TOOBIG;
+  if (vec)
+    norm_apply_kernel<4><<<(unsigned)(chunks * B), kNormThreads, 0, stream>>>(
+        x, T, F, mean, stdv, per_utt, utt_max, top_db, out, (unsigned)chunks, rows, bx);
+  else
+    norm_apply_kernel<1><<<(unsigned)(chunks * B), kNormThreads, 0, stream>>>(
+        x, T, F, mean, stdv, per_utt, utt_max, top_db, out, (unsigned)chunks, rows, bx);
+  return check_last();
+}
+
+}  // namespace sbfe

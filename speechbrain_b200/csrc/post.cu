@@ -1,0 +1,193 @@
+// Post stage: top_db clamp -> DCT -> deltas (x2, concatenated) -> context window,
+// fused in one pass so that only the final [B, T, F_out] tensor is written.
+//   _amplitude_to_DB clamp  speechbrain/processing/features.py:706-710
+//   DCT.forward             speechbrain/processing/features.py:764-786
+//   Deltas.forward          speechbrain/processing/features.py:820-852
+//   ContextWindow.forward   speechbrain/processing/features.py:897-937
+//   composition             speechbrain/lobes/features.py:141-146, 274-280
+#include "common.cuh"
+
+namespace sbfe {
+
+// ---- pure clamp (Fbank without deltas/context), float4-vectorised -----------
+__global__ void clamp_kernel(const float* __restrict__ x, int64_t per_utt,
+                             const sbfe_maxkey_t* __restrict__ utt_max, float top_db,
+                             float* __restrict__ out, unsigned chunks) {
+  const int64_t b = blockIdx.x / chunks;
+  const int64_t c = blockIdx.x - b * chunks;
+  const float floor_b = clamp_floor(utt_max, b, top_db);
+  const float* src = x + b * per_utt;
+  float* dst = out + b * per_utt;
+  const int64_t chunk = (per_utt + chunks - 1) / chunks;
+  const int64_t lo = c * chunk, hi = min(per_utt, lo + chunk);
+  const bool vec = ((reinterpret_cast<uintptr_t>(src + lo) | reinterpret_cast<uintptr_t>(dst + lo)) & 15) == 0;
+  if (vec) {
+    const int64_t n4 = (hi - lo) / 4;
+    const float4* s4 = reinterpret_cast<const float4*>(src + lo);
+    float4* d4 = reinterpret_cast<float4*>(dst + lo);
+    for (int64_t i = threadIdx.x; i < n4; i += blockDim.x) {
+      float4 v = s4[i];
+      v.x = fmaxf(v.x, floor_b); v.y = fmaxf(v.y, floor_b);
+      v.z = fmaxf(v.z, floor_b); v.w = fmaxf(v.w, floor_b);
+      d4[i] = v;
+    }
+    for (int64_t i = lo + n4 * 4 + threadIdx.x; i < hi; i += blockDim.x)
+      dst[i] = fmaxf(src[i], floor_b);
+  } else {
+    for (int64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) dst[i] = fmaxf(src[i], floor_b);
+  }
+}
+
+struct PostParams {
+  const float* x;
+  float* out;
+  const sbfe_maxkey_t* utt_max;
+  const float* dct;  // [F_in][F0] or null
+  int64_t T;
+  float top_db, inv_denom;
+  int F_in, F0;      // F0 = features after the optional DCT
+  int deltas, n;     // n = (window-1)/2
+  int context, left, right;
+  int tile;          // frames per CTA
+  unsigned tiles;
+};
+
+constexpr int kPostThreads = 256;
+
+__global__ void __launch_bounds__(kPostThreads) post_kernel(const PostParams p) {
+  extern __shared__ __align__(16) float smem[];
+  const int n2 = p.deltas ? 2 * p.n : 0;       // halo of the base features per side (delta of delta)
+  const int n1 = p.deltas ? p.n : 0;
+  const int ctxl = p.context ? p.left : 0, ctxr = p.context ? p.right : 0;
+  const int C = ctxl + ctxr + 1;
+  const int fr_out = p.tile + ctxl + ctxr;     // frames whose features feed the outputs
+  const int fr_d = fr_out + 2 * n1;            // delta frames staged
+  const int fr_b = fr_out + 2 * n2;            // base frames staged
+  float* s_base = smem;                        // [fr_b][F0]
+  float* s_d = s_base + fr_b * p.F0;           // [fr_d][F0]   (deltas only)
+  float* s_dd = s_d + (p.deltas ? fr_d * p.F0 : 0);   // [fr_out][F0]
+  float* s_in = s_dd + (p.deltas ? fr_out * p.F0 : 0);  // [fr_b][F_in] (DCT only)
+  float* s_dct = s_in + (p.dct ? fr_b * p.F_in : 0);    // [F_in][F0]
+
+  const int64_t b = blockIdx.x / p.tiles;
+  const int64_t t0 = (int64_t)(blockIdx.x - b * p.tiles) * p.tile;
+  const int64_t T = p.T;
+  const float floor_b = clamp_floor(p.utt_max, b, p.top_db);
+  const float* xb = p.x + b * T * p.F_in;
+  const int64_t base_lo = t0 - ctxl - n2;      // unclamped frame index of s_base row 0
+  const int64_t d_lo = t0 - ctxl - n1;
+  const int64_t o_lo = t0 - ctxl;
+
+  // stage clamped input rows (replicate-clamped frame index)
+  float* s_stage = p.dct ? s_in : s_base;
+  for (int i = threadIdx.x; i < fr_b * p.F_in; i += kPostThreads) {
+    const int r = i / p.F_in, f = i - r * p.F_in;
+    int64_t u = base_lo + r;
+    u = u < 0 ? 0 : (u > T - 1 ? T - 1 : u);
+    s_stage[i] = fmaxf(__ldg(xb + u * p.F_in + f), floor_b);
+  }
+  if (p.dct)
+    for (int i = threadIdx.x; i < p.F_in * p.F0; i += kPostThreads) s_dct[i] = __ldg(p.dct + i);
+  __syncthreads();
+  if (p.dct) {
+    for (int i = threadIdx.x; i < fr_b * p.F0; i += kPostThreads) {
+      const int r = i / p.F0, j = i - r * p.F0;
+      const float* row = s_in + r * p.F_in;
+      float acc = 0.f;
+      for (int m = 0; m < p.F_in; ++m) acc = fmaf(row[m], s_dct[m * p.F0 + j], acc);
+      s_base[i] = acc;
+    }
+    __syncthreads();
+  }
+  if (p.deltas) {
+    // delta at frame v = clamp(u): sum_k k * base[clamp(v + k)] / denom
+    for (int i = threadIdx.x; i < fr_d * p.F0; i += kPostThreads) {
+      const int r = i / p.F0, f = i - r * p.F0;
+      int64_t v = d_lo + r;
+      v = v < 0 ? 0 : (v > T - 1 ? T - 1 : v);
+      const float* col = s_base + (v - base_lo) * p.F0 + f;
+      float acc = 0.f;
+      for (int k = 1; k <= p.n; ++k) acc = fmaf((float)k, col[k * p.F0] - col[-k * p.F0], acc);
+      s_d[i] = acc * p.inv_denom;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < fr_out * p.F0; i += kPostThreads) {
+      const int r = i / p.F0, f = i - r * p.F0;
+      int64_t v = o_lo + r;
+      v = v < 0 ? 0 : (v > T - 1 ? T - 1 : v);
+      const float* col = s_d + (v - d_lo) * p.F0 + f;
+      float acc = 0.f;
+      for (int k = 1; k <= p.n; ++k) acc = fmaf((float)k, col[k * p.F0] - col[-k * p.F0], acc);
+      s_dd[i] = acc * p.inv_denom;
+    }
+    __syncthreads();
+  }
+  // gather: out[t, f*C + c] = feat[t + c - left][f], zero outside [0, T)
+  const int nfeat = p.F0 * (p.deltas ? 3 : 1);
+  const int F_out = nfeat * C;
+  const int64_t left_frames = T - t0;
+  const int nvalid = left_frames < p.tile ? (int)left_frames : p.tile;
+  float* ob = p.out + (b * T + t0) * F_out;
+  for (int i = threadIdx.x; i < nvalid * F_out; i += kPostThreads) {
+    const int t = i / F_out, j = i - t * F_out;
+    const int f = j / C, c = j - f * C;
+    const int64_t u = t0 + t + c - ctxl;
+    float v = 0.f;
+    if (u >= 0 && u < T) {
+      const int r = t + c;  // row relative to o_lo
+      if (f < p.F0) v = s_base[(r + n2) * p.F0 + f];
+      else if (f < 2 * p.F0) v = s_d[(r + n1) * p.F0 + (f - p.F0)];
+      else v = s_dd[r * p.F0 + (f - 2 * p.F0)];
+    }
+    ob[i] = v;
+  }
+}
+
+int launch_post(const float* x, int64_t B, int64_t T, int F_in, const sbfe_maxkey_t* utt_max,
+                float top_db, const float* dct, int n_dct, int deltas, int delta_window,
+                int context, int left, int right, float* out, cudaStream_t stream) {
+  if (B == 0 || T == 0) return 0;
+  if (!context) left = right = 0;
+  if (!dct && !deltas && !(left || right)) {
+    const int64_t per_utt = T * F_in;
+    int64_t chunks = (per_utt + 8191) / 8192;
+    if (chunks * B > 0x7fffffff) return SBFE_E_TOOBIG;
+    clamp_kernel<<<(unsigned)(chunks * B), 256, 0, stream>>>(x, per_utt, utt_max, top_db, out,
+                                                             (unsigned)chunks);
+    return check_last();
+  }
+  if (out == x) return SBFE_E_INVAL;
+  PostParams p;
+  p.x = x; p.out = out; p.utt_max = utt_max; p.dct = dct; p.T = T; p.top_db = top_db;
+  p.F_in = F_in; p.F0 = dct ? n_dct : F_in;
+  p.deltas = deltas ? 1 : 0;
+  p.n = (delta_window - 1) / 2;
+  if (p.deltas && p.n < 1) return SBFE_E_INVAL;
+  p.inv_denom = p.deltas ? 1.0f / ((float)(p.n * (p.n + 1) * (2 * p.n + 1)) / 3.0f) : 0.f;
+  p.context = context ? 1 : 0; p.left = left; p.right = right;
+  const int n2 = p.deltas ? 2 * p.n : 0, n1 = p.deltas ? p.n : 0;
+  size_t smem = 0;
+  int tile = 32;
+  for (;; tile /= 2) {
+    const int fr_out = tile + left + right, fr_d = fr_out + 2 * n1, fr_b = fr_out + 2 * n2;
+    size_t fl = (size_t)fr_b * p.F0;
+    if (p.deltas) fl += (size_t)(fr_d + fr_out) * p.F0;
+    if (dct) fl += (size_t)fr_b * F_in + (size_t)F_in * p.F0;
+    smem = fl * sizeof(float);
+    if (smem <= 200 * 1024 || tile == 1) break;
+  }
+  if (smem > 200 * 1024) return SBFE_E_TOOBIG;
+  p.tile = tile;
+  const int64_t tiles = (T + tile - 1) / tile;
+  if (tiles * B > 0x7fffffff) return SBFE_E_TOOBIG;
+  p.tiles = (unsigned)tiles;
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem);
+    if (e != cudaSuccess) return (int)e;
+  }
+  post_kernel<<<(unsigned)(tiles * B), kPostThreads, smem, stream>>>(p);
+  return check_last();
+}
+
+}  // namespace sbfe
