@@ -99,7 +99,7 @@ SBFE_API int sbfe_filterbank_forward(const sbfe_fbank_desc* desc, const float* d
 /* Post stage, any subset of (in this order):
  *   top_db clamp  x = max(x, max_b - top_db)          (features.py:706-710)
  *   DCT           x @ d_dct[F_in, n_dct]              (features.py:764-786)
- *   Deltas x2     [x, d(x), d(d(x))], window 5        (features.py:820-852; lobes:141-144)
+ *   Deltas        deltas=1: [x, d(x), d(d(x))]; deltas=2: d(x) only   (features.py:820-852; lobes:141-144)
  *   ContextWindow out[t, f*C + c] = x[t + c - left, f] (features.py:897-937)
  * x [B, T, F_in] -> out [B, T, F_out], F_out = (n_dct or F_in) * (3 if deltas) * (left+right+1 if context).
  * d_utt_max NULL => no clamp; d_dct NULL => no DCT; out may alias x only when

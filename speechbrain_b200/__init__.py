@@ -1,0 +1,41 @@
+"""speechbrain_b200: B200-native (sm_100a) acoustic feature frontend for SpeechBrain.
+
+Drop-in replacements for ``speechbrain.lobes.features.{Fbank, MFCC}`` and
+``speechbrain.processing.features.{STFT, spectral_magnitude, Filterbank, DCT,
+Deltas, ContextWindow, InputNormalization}`` backed by hand-written CUDA kernels
+behind a C ABI (include/sbfe.h).  See DESIGN.md / INTEGRATION.md.
+"""
+from .lobes.features import MFCC, Fbank  # noqa: F401
+from .processing.features import (  # noqa: F401
+    DCT, STFT, ContextWindow, Deltas, Filterbank, InputNormalization, spectral_magnitude)
+
+__version__ = "0.1.0"
+
+_PROCESSING = ("STFT", "spectral_magnitude", "Filterbank", "DCT", "Deltas", "ContextWindow",
+               "InputNormalization")
+_LOBES = ("Fbank", "MFCC")
+
+
+def install():
+    """Rebind the frontend names inside an importable ``speechbrain`` so unchanged
+    recipes / YAML (``!new:speechbrain.lobes.features.Fbank``) construct the B200
+    classes.  Opt-in; call before ``load_hyperpyyaml``.  Returns the names patched."""
+    import importlib
+
+    from .processing import normalization
+
+    patched = []
+    proc = importlib.import_module("speechbrain.processing.features")
+    lobes = importlib.import_module("speechbrain.lobes.features")
+    here = importlib.import_module(__name__)
+    for name in _PROCESSING:
+        setattr(proc, name, getattr(here, name))
+        patched.append("speechbrain.processing.features." + name)
+    for name in _PROCESSING:
+        if hasattr(lobes, name):  # lobes imported them by name
+            setattr(lobes, name, getattr(here, name))
+    for name in _LOBES:
+        setattr(lobes, name, getattr(here, name))
+        patched.append("speechbrain.lobes.features." + name)
+    normalization.register_checkpoint_hooks_if_available()
+    return patched

@@ -90,7 +90,7 @@ int sbfe_spectral_magnitude(const float* d_stft, int64_t n, float power, int32_t
 
 int sbfe_filterbank_forward(const sbfe_fbank_desc* d, const float* d_spec, int64_t B, int64_t T,
                             float* d_out, sbfe_maxkey_t* d_utt_max, void* stream) {
-  if (!d || d->n_fft < 2 || d->n_mels < 1 || !d->d_mel_start || !d->d_mel_count ||
+  if (!d || d->n_fft < 0 || (d->n_fft & 1) || d->n_mels < 1 || !d->d_mel_start || !d->d_mel_count ||
       !d->d_mel_offset || !d->d_mel_weight || B < 0 || T < 0)
     return SBFE_E_INVAL;
   if (B == 0 || T == 0) return 0;

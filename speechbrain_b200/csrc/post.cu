@@ -46,7 +46,7 @@ struct PostParams {
   int64_t T;
   float top_db, inv_denom;
   int F_in, F0;      // F0 = features after the optional DCT
-  int deltas, n;     // n = (window-1)/2
+  int deltas, n;     // deltas: 0 none, 1 [x, d, dd], 2 d only;  n = (window-1)/2
   int context, left, right;
   int tile;          // frames per CTA
   unsigned tiles;
@@ -56,8 +56,8 @@ constexpr int kPostThreads = 256;
 
 __global__ void __launch_bounds__(kPostThreads) post_kernel(const PostParams p) {
   extern __shared__ __align__(16) float smem[];
-  const int n2 = p.deltas ? 2 * p.n : 0;       // halo of the base features per side (delta of delta)
-  const int n1 = p.deltas ? p.n : 0;
+  const int n2 = p.deltas == 1 ? 2 * p.n : (p.deltas ? p.n : 0);  // base-feature halo per side
+  const int n1 = p.deltas == 1 ? p.n : 0;                         // delta halo per side
   const int ctxl = p.context ? p.left : 0, ctxr = p.context ? p.right : 0;
   const int C = ctxl + ctxr + 1;
   const int fr_out = p.tile + ctxl + ctxr;     // frames whose features feed the outputs
@@ -65,8 +65,8 @@ __global__ void __launch_bounds__(kPostThreads) post_kernel(const PostParams p) 
   const int fr_b = fr_out + 2 * n2;            // base frames staged
   float* s_base = smem;                        // [fr_b][F0]
   float* s_d = s_base + fr_b * p.F0;           // [fr_d][F0]   (deltas only)
-  float* s_dd = s_d + (p.deltas ? fr_d * p.F0 : 0);   // [fr_out][F0]
-  float* s_in = s_dd + (p.deltas ? fr_out * p.F0 : 0);  // [fr_b][F_in] (DCT only)
+  float* s_dd = s_d + (p.deltas ? fr_d * p.F0 : 0);   // [fr_out][F0]  (deltas == 1 only)
+  float* s_in = s_dd + (p.deltas == 1 ? fr_out * p.F0 : 0);  // [fr_b][F_in] (DCT only)
   float* s_dct = s_in + (p.dct ? fr_b * p.F_in : 0);    // [F_in][F0]
 
   const int64_t b = blockIdx.x / p.tiles;
@@ -111,6 +111,7 @@ __global__ void __launch_bounds__(kPostThreads) post_kernel(const PostParams p) 
       s_d[i] = acc * p.inv_denom;
     }
     __syncthreads();
+    if (p.deltas == 1)
     for (int i = threadIdx.x; i < fr_out * p.F0; i += kPostThreads) {
       const int r = i / p.F0, f = i - r * p.F0;
       int64_t v = o_lo + r;
@@ -123,7 +124,7 @@ __global__ void __launch_bounds__(kPostThreads) post_kernel(const PostParams p) 
     __syncthreads();
   }
   // gather: out[t, f*C + c] = feat[t + c - left][f], zero outside [0, T)
-  const int nfeat = p.F0 * (p.deltas ? 3 : 1);
+  const int nfeat = p.F0 * (p.deltas == 1 ? 3 : 1);
   const int F_out = nfeat * C;
   const int64_t left_frames = T - t0;
   const int nvalid = left_frames < p.tile ? (int)left_frames : p.tile;
@@ -135,7 +136,8 @@ __global__ void __launch_bounds__(kPostThreads) post_kernel(const PostParams p) 
     float v = 0.f;
     if (u >= 0 && u < T) {
       const int r = t + c;  // row relative to o_lo
-      if (f < p.F0) v = s_base[(r + n2) * p.F0 + f];
+      if (p.deltas == 2) v = s_d[(r + n1) * p.F0 + f];
+      else if (f < p.F0) v = s_base[(r + n2) * p.F0 + f];
       else if (f < 2 * p.F0) v = s_d[(r + n1) * p.F0 + (f - p.F0)];
       else v = s_dd[r * p.F0 + (f - 2 * p.F0)];
     }
@@ -160,18 +162,19 @@ int launch_post(const float* x, int64_t B, int64_t T, int F_in, const sbfe_maxke
   PostParams p;
   p.x = x; p.out = out; p.utt_max = utt_max; p.dct = dct; p.T = T; p.top_db = top_db;
   p.F_in = F_in; p.F0 = dct ? n_dct : F_in;
-  p.deltas = deltas ? 1 : 0;
+  p.deltas = deltas == 2 ? 2 : (deltas ? 1 : 0);
   p.n = (delta_window - 1) / 2;
   if (p.deltas && p.n < 1) return SBFE_E_INVAL;
   p.inv_denom = p.deltas ? 1.0f / ((float)(p.n * (p.n + 1) * (2 * p.n + 1)) / 3.0f) : 0.f;
   p.context = context ? 1 : 0; p.left = left; p.right = right;
-  const int n2 = p.deltas ? 2 * p.n : 0, n1 = p.deltas ? p.n : 0;
+  const int n2 = p.deltas == 1 ? 2 * p.n : (p.deltas ? p.n : 0), n1 = p.deltas == 1 ? p.n : 0;
   size_t smem = 0;
   int tile = 32;
   for (;; tile /= 2) {
     const int fr_out = tile + left + right, fr_d = fr_out + 2 * n1, fr_b = fr_out + 2 * n2;
     size_t fl = (size_t)fr_b * p.F0;
-    if (p.deltas) fl += (size_t)(fr_d + fr_out) * p.F0;
+    if (p.deltas) fl += (size_t)fr_d * p.F0;
+    if (p.deltas == 1) fl += (size_t)fr_out * p.F0;
     if (dct) fl += (size_t)fr_b * F_in + (size_t)F_in * p.F0;
     smem = fl * sizeof(float);
     if (smem <= 200 * 1024 || tile == 1) break;

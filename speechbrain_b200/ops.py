@@ -1,0 +1,260 @@
+"""Tensor-level wrappers over the C ABI (include/sbfe.h).
+
+Each function takes / returns torch tensors, launches on
+``torch.cuda.current_stream()`` and never synchronises.  torch is plumbing only
+(device memory + streams); all arithmetic is in libsbfe.so.  CPU tensors raise:
+there is no fallback path.
+"""
+import ctypes as C
+
+import torch
+
+from ._lib import FbankDesc, check, lib
+
+__all__ = [
+    "FrontendTables", "fbank_forward", "stft_forward", "spectral_magnitude",
+    "filterbank_forward", "post_forward", "norm_stats", "norm_reduce", "norm_update",
+    "norm_apply", "decode_utt_max",
+]
+
+
+def _require_cuda(t, name):
+    if not isinstance(t, torch.Tensor):
+        raise TypeError("%s must be a torch.Tensor" % name)
+    if not t.is_cuda:
+        raise RuntimeError(
+            "%s is on %s: speechbrain_b200 runs on CUDA only (no CPU fallback; keep the "
+            "reference modules for CPU)" % (name, t.device))
+    if t.requires_grad and torch.is_grad_enabled():
+        raise RuntimeError(
+            "%s requires grad: the B200 frontend is forward-only (SURVEY.md N4)" % name)
+
+
+def _f32c(t, name):
+    """float32 + contiguous; half/bfloat16 are promoted like the reference's
+    window multiply does, float64 is rejected like its matmul does."""
+    _require_cuda(t, name)
+    if t.dtype == torch.float64:
+        raise TypeError("%s is float64; the frontend computes in float32" % name)
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+class FrontendTables:
+    """Host-built constant tables of one STFT(+filterbank) configuration, moved
+    to each device on first use (the reference re-copies them on every call:
+    processing/features.py:166, 534-536)."""
+
+    def __init__(self, n_fft, hop, window, fbank_matrix=None, log_mel=True, multiplier=10.0,
+                 amin=1e-10, db_multiplier=0.0):
+        self.n_fft, self.hop = int(n_fft), int(hop)
+        self.bins = self.n_fft // 2 + 1
+        win = window.detach().to("cpu", torch.float32)
+        if win.numel() > self.n_fft:
+            raise ValueError("win_length (%d samples) > n_fft (%d)" % (win.numel(), n_fft))
+        if win.numel() < self.n_fft:  # torch.stft centres a short window inside n_fft
+            left = (self.n_fft - win.numel()) // 2
+            win = torch.nn.functional.pad(win, (left, self.n_fft - win.numel() - left))
+        self.h_window = win.contiguous()
+        self.log_mel = bool(log_mel)
+        self.multiplier, self.amin = float(multiplier), float(amin)
+        self.db_offset = float(multiplier) * float(db_multiplier)
+        # what the reference's float32 ops give for x == amin (features.py:701-702)
+        a = torch.tensor(self.amin, dtype=torch.float32)
+        fl = self.multiplier * torch.log10(torch.clamp(a, min=self.amin))
+        fl -= self.db_offset
+        self.floor_db = float(fl)
+        self.n_mels = 0
+        self._h_mel = None
+        if fbank_matrix is not None:
+            self._set_matrix(fbank_matrix)
+        self._dev = {}
+
+    def _set_matrix(self, mat):
+        mat = mat.detach().to("cpu", torch.float32)
+        if mat.shape[0] != self.bins:
+            raise ValueError("filterbank matrix has %d rows, expected %d" % (mat.shape[0], self.bins))
+        self.n_mels = int(mat.shape[1])
+        start, count, offset, weights = [], [], [], []
+        for m in range(self.n_mels):
+            col = mat[:, m]
+            nz = torch.nonzero(col).flatten()
+            if nz.numel() == 0:
+                s, c = 0, 0
+            else:
+                s, c = int(nz[0]), int(nz[-1]) - int(nz[0]) + 1
+            start.append(s)
+            count.append(c)
+            offset.append(sum(count[:-1]))
+            weights.append(col[s:s + c])
+        w = torch.cat(weights) if weights and sum(count) else torch.zeros(1)
+        self._h_mel = (torch.tensor(start, dtype=torch.int32), torch.tensor(count, dtype=torch.int32),
+                       torch.tensor(offset, dtype=torch.int32), w.contiguous())
+        self.nnz = int(sum(count))
+
+    def on(self, device):
+        key = (device.type, device.index)
+        hit = self._dev.get(key)
+        if hit is not None:
+            return hit
+        d_window = self.h_window.to(device)
+        keep = [d_window]
+        desc = FbankDesc()
+        desc.n_fft, desc.hop, desc.n_mels = self.n_fft, self.hop, self.n_mels
+        desc.log_mel = int(self.log_mel)
+        desc.multiplier, desc.amin = self.multiplier, self.amin
+        desc.db_offset, desc.floor_db = self.db_offset, self.floor_db
+        desc.h_window, desc.d_window = self.h_window.data_ptr(), d_window.data_ptr()
+        if self._h_mel is not None:
+            dev = [t.to(device) for t in self._h_mel]
+            keep += dev
+            desc.d_mel_start, desc.d_mel_count = dev[0].data_ptr(), dev[1].data_ptr()
+            desc.d_mel_offset, desc.d_mel_weight = dev[2].data_ptr(), dev[3].data_ptr()
+        entry = (desc, keep)
+        self._dev[key] = entry
+        return entry
+
+
+def _wav2d(wav):
+    wav = _f32c(wav, "wav")
+    if wav.dim() != 2:
+        raise ValueError("expected a [batch, time] waveform, got shape %s" % (tuple(wav.shape),))
+    return wav
+
+
+def fbank_forward(tables, wav):
+    """wav [B, L] -> (dB or linear mel [B, T, M] WITHOUT the top_db clamp,
+    utt_max keys [B] int32).  sbfe_fbank_forward."""
+    wav = _wav2d(wav)
+    B, L = wav.shape
+    T = 1 + L // tables.hop
+    desc, _ = tables.on(wav.device)
+    out = torch.empty((B, T, tables.n_mels), dtype=torch.float32, device=wav.device)
+    utt_max = torch.zeros((B,), dtype=torch.int32, device=wav.device)
+    L_ = lib()
+    ws_bytes = L_.sbfe_fbank_workspace_bytes(C.byref(desc), B, L)
+    ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=wav.device) if ws_bytes > 0 else None
+    with torch.cuda.device(wav.device):
+        check(L_.sbfe_fbank_forward(C.byref(desc), _ptr(wav), B, L, wav.stride(0), _ptr(out),
+                                    _ptr(utt_max), _ptr(ws), max(ws_bytes, 0), _stream()))
+    return out, utt_max
+
+
+def stft_forward(tables, wav, power_only=False):
+    """wav [B, L] -> [B, T, bins, 2] (or [B, T, bins] power).  sbfe_stft_forward."""
+    wav = _wav2d(wav)
+    B, L = wav.shape
+    T = 1 + L // tables.hop
+    desc, _ = tables.on(wav.device)
+    shape = (B, T, tables.bins) if power_only else (B, T, tables.bins, 2)
+    out = torch.empty(shape, dtype=torch.float32, device=wav.device)
+    with torch.cuda.device(wav.device):
+        check(lib().sbfe_stft_forward(C.byref(desc), _ptr(wav), B, L, wav.stride(0), _ptr(out),
+                                      int(power_only), _stream()))
+    return out
+
+
+def spectral_magnitude(stft, power=1, log=False, eps=1e-14):
+    stft = _f32c(stft, "stft")
+    if stft.shape[-1] != 2:
+        raise ValueError("last dimension must hold (re, im)")
+    out = torch.empty(stft.shape[:-1], dtype=torch.float32, device=stft.device)
+    with torch.cuda.device(stft.device):
+        check(lib().sbfe_spectral_magnitude(_ptr(stft), out.numel(), float(power), int(bool(log)),
+                                            float(eps), _ptr(out), _stream()))
+    return out
+
+
+def filterbank_forward(tables, spec):
+    """spec [B, T, bins] -> (mel [B, T, M] without the clamp, utt_max keys)."""
+    spec = _f32c(spec, "spectrogram")
+    B, T, F = spec.shape
+    if F != tables.bins:
+        raise ValueError("spectrogram has %d bins, filterbank expects %d" % (F, tables.bins))
+    desc, _ = tables.on(spec.device)
+    out = torch.empty((B, T, tables.n_mels), dtype=torch.float32, device=spec.device)
+    utt_max = torch.zeros((B,), dtype=torch.int32, device=spec.device)
+    with torch.cuda.device(spec.device):
+        check(lib().sbfe_filterbank_forward(C.byref(desc), _ptr(spec), B, T, _ptr(out),
+                                            _ptr(utt_max), _stream()))
+    return out, utt_max
+
+
+def post_forward(x, utt_max=None, top_db=80.0, dct=None, deltas=False, delta_window=5,
+                 context=False, left=0, right=0, inplace=False):
+    """clamp -> DCT -> deltas -> context window (sbfe_post_forward)."""
+    x = _f32c(x, "x")
+    B, T, F = x.shape
+    pure_clamp = dct is None and not deltas and not (context and (left or right))
+    F0 = dct.shape[1] if dct is not None else F
+    F_out = F0 * (3 if deltas == 1 or deltas is True else 1) * ((left + right + 1) if context else 1)
+    out = x if (inplace and pure_clamp) else torch.empty((B, T, F_out), dtype=torch.float32,
+                                                         device=x.device)
+    with torch.cuda.device(x.device):
+        check(lib().sbfe_post_forward(_ptr(x), B, T, F, _ptr(utt_max), float(top_db), _ptr(dct),
+                                      int(F0 if dct is not None else 0), int(deltas),
+                                      int(delta_window), int(bool(context)), int(left), int(right),
+                                      _ptr(out), _stream()))
+    return out
+
+
+def norm_stats(x, lengths, mean_norm=True, std_norm=True, eps=1e-10, utt_max=None, top_db=80.0):
+    """Per-utterance mean / unbiased std over the valid frames -> ([B,F], [B,F])."""
+    B, T, F = x.shape
+    lengths = lengths.to(device=x.device, dtype=torch.float32).contiguous()
+    mean = torch.empty((B, F), dtype=torch.float32, device=x.device)
+    std = torch.empty((B, F), dtype=torch.float32, device=x.device)
+    L_ = lib()
+    ws_bytes = L_.sbfe_norm_workspace_bytes(B, T, F)
+    ws = torch.empty((max(ws_bytes, 16),), dtype=torch.uint8, device=x.device)
+    with torch.cuda.device(x.device):
+        check(L_.sbfe_norm_stats(_ptr(x), _ptr(lengths), B, T, F, int(bool(mean_norm)),
+                                 int(bool(std_norm)), float(eps), _ptr(utt_max), float(top_db),
+                                 _ptr(mean), _ptr(std), _ptr(ws), ws_bytes, _stream()))
+    return mean, std
+
+
+def norm_reduce(mean, std):
+    """[B,F] stats -> [2F+1] payload {sum mean, sum std, B} (all-reduce-able)."""
+    B, F = mean.shape
+    cur = torch.empty((2 * F + 1,), dtype=torch.float32, device=mean.device)
+    with torch.cuda.device(mean.device):
+        check(lib().sbfe_norm_reduce(_ptr(mean), _ptr(std), B, F, _ptr(cur), _stream()))
+    return cur
+
+
+def norm_update(cur, glob_mean, glob_std, first, weight):
+    F = glob_mean.numel()
+    with torch.cuda.device(cur.device):
+        check(lib().sbfe_norm_update(_ptr(cur), F, int(bool(first)), float(weight),
+                                     _ptr(glob_mean), _ptr(glob_std), _stream()))
+
+
+def norm_apply(x, mean, std, per_utt, out=None, utt_max=None, top_db=80.0):
+    B, T, F = x.shape
+    if out is None:
+        out = torch.empty_like(x)
+    with torch.cuda.device(x.device):
+        check(lib().sbfe_norm_apply(_ptr(x), B, T, F, _ptr(mean), _ptr(std), int(bool(per_utt)),
+                                    _ptr(utt_max), float(top_db), _ptr(out), _stream()))
+    return out
+
+
+def decode_utt_max(keys):
+    """int32 keys -> float32 maxima on the host (tests / debugging only)."""
+    import struct
+
+    out = []
+    for k in (keys.to(torch.int64) & 0xFFFFFFFF).tolist():
+        bits = (k & 0x7FFFFFFF) if (k & 0x80000000) else (~k & 0xFFFFFFFF)
+        out.append(struct.unpack("<f", struct.pack("<I", bits))[0])
+    return torch.tensor(out, dtype=torch.float32)

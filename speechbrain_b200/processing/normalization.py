@@ -1,0 +1,202 @@
+"""``InputNormalization`` drop-in (reference: speechbrain/processing/features.py:940-1231).
+
+The reference loops over sentences in Python (one host sync and >= 5 tiny kernels
+per sentence).  Here the statistics of the whole batch come from two kernel
+launches and the normalisation from one; nothing is read back to the host except
+in ``speaker`` mode, whose dictionary is keyed by host integers in the reference
+as well.
+"""
+import torch
+
+from .. import ops
+
+__all__ = ["InputNormalization"]
+
+
+def _dist_ready():
+    return torch.distributed.is_available() and torch.distributed.is_initialized()
+
+
+class InputNormalization(torch.nn.Module):
+    """Mean / variance normalisation: ``sentence``, ``speaker``, ``batch`` or
+    ``global`` statistics, same arguments and state as the reference.
+
+    Extra (not in the reference): ``sync_stats``.  When True and a
+    ``torch.distributed`` group is initialised, ``batch``/``global`` statistics
+    are all-reduced (2F+1 floats) so every rank normalises with the statistics
+    of the concatenated global batch.  Default False = the reference's per-rank
+    behaviour.
+    """
+
+    from typing import Dict
+
+    spk_dict_mean: Dict[int, torch.Tensor]
+    spk_dict_std: Dict[int, torch.Tensor]
+    spk_dict_count: Dict[int, int]
+
+    def __init__(self, mean_norm=True, std_norm=True, norm_type="global", avg_factor=None,
+                 requires_grad=False, update_until_epoch=3, sync_stats=False):
+        super().__init__()
+        self.mean_norm = mean_norm
+        self.std_norm = std_norm
+        self.norm_type = norm_type
+        self.avg_factor = avg_factor
+        self.requires_grad = requires_grad
+        self.glob_mean = torch.tensor([0])
+        self.glob_std = torch.tensor([0])
+        self.spk_dict_mean = {}
+        self.spk_dict_std = {}
+        self.spk_dict_count = {}
+        self.weight = 1.0
+        self.count = 0
+        self.eps = 1e-10
+        self.update_until_epoch = update_until_epoch
+        self.sync_stats = sync_stats
+        self.device_inp = torch.device("cpu")
+        # fused-frontend hand-over: (utt_max keys, top_db) of an un-clamped input
+        self._pending_clamp = None
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, x, lengths, spk_ids=torch.tensor([]), epoch=0):
+        """x ``[B, T, F]``, lengths ``[B]`` relative; see :1000-1118."""
+        if x.dim() != 3:
+            raise NotImplementedError("InputNormalization takes [batch, time, features]")
+        if x.dtype != torch.float32 or not x.is_contiguous():
+            if self.norm_type in ("sentence", "speaker"):
+                raise TypeError("in-place normalisation needs a contiguous float32 tensor")
+            x = x.float().contiguous()
+        ops._require_cuda(x, "x")
+        B, T, F = x.shape
+        mean, std = ops.norm_stats(x, lengths, self.mean_norm, self.std_norm, self.eps)
+
+        if self.norm_type == "sentence":
+            return ops.norm_apply(x, mean, std, per_utt=True, out=x)  # in place (:1035)
+
+        if self.norm_type == "speaker":
+            s_mean, s_std = self._speaker_stats(mean, std, spk_ids)
+            return ops.norm_apply(x, s_mean, s_std, per_utt=True, out=x)  # in place (:1081)
+
+        if self.norm_type not in ("batch", "global"):
+            return x
+
+        cur = ops.norm_reduce(mean, std)  # {sum_b mean_b, sum_b std_b, B}
+        if self.sync_stats and _dist_ready():
+            torch.distributed.all_reduce(cur)  # the one collective of the path
+        if self.norm_type == "batch":
+            g_mean = torch.empty((F,), dtype=torch.float32, device=x.device)
+            g_std = torch.empty((F,), dtype=torch.float32, device=x.device)
+            ops.norm_update(cur, g_mean, g_std, first=True, weight=1.0)
+            return ops.norm_apply(x, g_mean, g_std, per_utt=False)
+
+        # global (:1090-1116)
+        if self.training:
+            if self.count == 0:
+                self.glob_mean = torch.empty((F,), dtype=torch.float32, device=x.device)
+                self.glob_std = torch.empty((F,), dtype=torch.float32, device=x.device)
+                ops.norm_update(cur, self.glob_mean, self.glob_std, first=True, weight=1.0)
+            elif epoch < self.update_until_epoch:
+                self.weight = 1 / (self.count + 1) if self.avg_factor is None else self.avg_factor
+                self._stats_to(x.device, F)
+                ops.norm_update(cur, self.glob_mean, self.glob_std, first=False, weight=self.weight)
+            self.count = self.count + 1
+        self._stats_to(x.device, F)
+        return ops.norm_apply(x, self.glob_mean, self.glob_std, per_utt=False)
+
+    def _stats_to(self, device, F):
+        """Global stats as float32 [F] on ``device`` (the never-initialised
+        ``tensor([0])`` broadcasts to zeros -> inf/nan output like the reference)."""
+        for name in ("glob_mean", "glob_std"):
+            t = getattr(self, name)
+            if not isinstance(t, torch.Tensor):
+                t = torch.tensor([t])
+            if t.device != device or t.dtype != torch.float32 or t.numel() != F:
+                t = t.to(device=device, dtype=torch.float32)
+                if t.numel() == 1 and F != 1:
+                    t = t.expand(F)
+                setattr(self, name, t.contiguous())
+
+    def _speaker_stats(self, mean, std, spk_ids):
+        """Per-speaker running statistics (:1037-1081); returns the [B, F] rows to apply."""
+        ids = [int(spk_ids[i][0]) for i in range(mean.shape[0])]
+        rows_m, rows_s = [], []
+        for i, spk in enumerate(ids):
+            cm, cs = mean[i], std[i]
+            if self.training:
+                if spk not in self.spk_dict_mean:
+                    self.spk_dict_mean[spk], self.spk_dict_std[spk] = cm.clone(), cs.clone()
+                    self.spk_dict_count[spk] = 1
+                else:
+                    self.spk_dict_count[spk] += 1
+                    self.weight = (1 / self.spk_dict_count[spk] if self.avg_factor is None
+                                   else self.avg_factor)
+                    self.spk_dict_mean[spk] = ((1 - self.weight) * self.spk_dict_mean[spk].to(cm.device)
+                                               + self.weight * cm)
+                    self.spk_dict_std[spk] = ((1 - self.weight) * self.spk_dict_std[spk].to(cs.device)
+                                              + self.weight * cs)
+                rows_m.append(self.spk_dict_mean[spk])
+                rows_s.append(self.spk_dict_std[spk])
+            elif spk in self.spk_dict_mean:
+                rows_m.append(self.spk_dict_mean[spk].to(cm.device))
+                rows_s.append(self.spk_dict_std[spk].to(cs.device))
+            else:
+                rows_m.append(cm)
+                rows_s.append(cs)
+        return torch.stack(rows_m).contiguous(), torch.stack(rows_s).contiguous()
+
+    # --------------------------------------------------------- state / checkpoint
+    def _statistics_dict(self):
+        """Same 6-key dict the reference saves (:1147-1158)."""
+        return {
+            "count": self.count,
+            "glob_mean": self.glob_mean,
+            "glob_std": self.glob_std,
+            "spk_dict_mean": self.spk_dict_mean,
+            "spk_dict_std": self.spk_dict_std,
+            "spk_dict_count": self.spk_dict_count,
+        }
+
+    def _load_statistics_dict(self, state):
+        """(:1160-1192); ``glob_mean`` may be a legacy python int."""
+        self.count = state["count"]
+        self.glob_mean = state["glob_mean"]
+        self.glob_std = state["glob_std"]
+        self.spk_dict_mean = {k: v.to(self.device_inp) for k, v in state["spk_dict_mean"].items()}
+        self.spk_dict_std = {k: v.to(self.device_inp) for k, v in state["spk_dict_std"].items()}
+        self.spk_dict_count = state["spk_dict_count"]
+        return state
+
+    def to(self, device):
+        """Moves the statistics too (:1194-1203)."""
+        self = super(InputNormalization, self).to(device)
+        if isinstance(self.glob_mean, torch.Tensor):
+            self.glob_mean = self.glob_mean.to(device)
+            self.glob_std = self.glob_std.to(device)
+        for spk in self.spk_dict_mean:
+            self.spk_dict_mean[spk] = self.spk_dict_mean[spk].to(device)
+            self.spk_dict_std[spk] = self.spk_dict_std[spk].to(device)
+        return self
+
+    def _save(self, path):
+        """Checkpoint saver hook: ``torch.save`` of the statistics dict (:1205-1215)."""
+        torch.save(self._statistics_dict(), path)
+
+    def _load(self, path, end_of_epoch=False, device=None):
+        """Checkpoint loader / transfer hook (:1217-1231)."""
+        del end_of_epoch
+        stats = torch.load(path, map_location=device)
+        self._load_statistics_dict(stats)
+
+
+def register_checkpoint_hooks_if_available():
+    """Registers ``_save`` / ``_load`` with SpeechBrain's checkpointer when the
+    reference package is importable (utils/checkpoints.py:197-328); a no-op
+    otherwise.  Called by ``speechbrain_b200.install()``."""
+    try:
+        from speechbrain.utils import checkpoints as ck
+    except Exception:
+        return False
+    cls = InputNormalization
+    ck.DEFAULT_SAVE_HOOKS[cls] = cls._save
+    ck.DEFAULT_LOAD_HOOKS[cls] = cls._load
+    ck.DEFAULT_TRANSFER_HOOKS[cls] = cls._load
+    return True

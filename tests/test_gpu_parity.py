@@ -1,0 +1,201 @@
+"""GPU parity: the CUDA product (through the drop-in modules -> C ABI) against
+the committed outputs of the unmodified reference and against the numpy oracle.
+
+Tolerance protocol: with ref64 = the reference run in float64,
+the product must be at most as far from ref64 as 2x the reference's own float32
+run is (plus one float32 ulp of the dB range), shapes bit-exact, exact-value
+known answers exact.
+"""
+import numpy as np
+import pytest
+import torch
+
+import golden_cases as gc
+from oracle import frontend_np as onp
+
+pytestmark = pytest.mark.gpu
+
+LOBE_CASES = [n for n, s in gc.CASES.items() if s["kind"] in ("fbank", "mfcc", "fbank+norm")]
+OP_CASES = [n for n, s in gc.CASES.items()
+            if s["kind"] in ("stft", "magnitude", "filterbank", "dct", "deltas", "context")]
+SEQ_CASES = [n for n, s in gc.CASES.items() if s["kind"] == "norm_seq"]
+ULP = 1e-5  # ~ one float32 ulp at |dB| ~ 100
+
+
+@pytest.fixture(scope="module")
+def sb():
+    assert torch.cuda.is_available(), "these tests need the B200"
+    import speechbrain_b200
+
+    return speechbrain_b200
+
+
+def dev(x):
+    return torch.from_numpy(np.ascontiguousarray(x)).cuda()
+
+
+def _build_lobe(sb, spec):
+    cls = sb.MFCC if spec["kind"] == "mfcc" else sb.Fbank
+    return cls(**spec["kwargs"])
+
+
+@pytest.mark.parametrize("name", LOBE_CASES)
+def test_lobe_vs_reference(sb, golden, name):
+    spec = gc.CASES[name]
+    x = spec["make_input"]()
+    mod = _build_lobe(sb, spec)
+    # host constants are built with the same torch calls as the reference
+    assert np.array_equal(mod.compute_fbanks.f_central.numpy(), golden[f"{name}/fc"])
+    assert np.array_equal(mod.compute_fbanks.band.numpy(), golden[f"{name}/band"])
+    assert np.array_equal(mod.compute_STFT.window.numpy(), golden[f"{name}/window"])
+    got_t = mod(dev(x))
+    got = got_t.cpu().numpy()
+    ref32 = golden[f"{name}/ref32"]
+    assert got.shape == ref32.shape and got.dtype == np.float32
+    assert np.isfinite(got).all()
+    mult = 30.0 if (spec["kind"] == "mfcc") else 1.0  # DCT sums ~23 dB values
+    if f"{name}/ref64" in golden.files:
+        ref64 = golden[f"{name}/ref64"]
+        noise = np.abs(ref32 - ref64).max()
+        err = np.abs(got - ref64).max()
+        assert err <= 2 * noise + mult * ULP, (err, noise)
+        assert np.abs(got - ref64).mean() <= 2 * np.abs(ref32 - ref64).mean() + ULP
+    assert np.abs(got - ref32).max() < 2e-3 * mult
+    if name == "cfg1_fbank40_8x1s":  # north_star gate on the CPU-runnable config
+        assert np.abs(got - ref32).max() <= 1e-4
+    if spec["kind"] == "fbank+norm":
+        norm = sb.InputNormalization(**spec["norm"])
+        lens = torch.tensor(spec["lengths"], dtype=torch.float32).cuda()
+        out = norm(got_t, lens)
+        if spec["norm"]["norm_type"] == "sentence":
+            assert out.data_ptr() == got_t.data_ptr()  # in place, like the reference
+        out = out.cpu().numpy()
+        n32, n64 = golden[f"{name}/norm32"], golden[f"{name}/norm64"]
+        assert np.abs(out - n64).max() <= 2 * np.abs(n32 - n64).max() + 2e-5
+        # and against the oracle normalising OUR features (isolates the norm kernels)
+        o = onp.InputNormalizationOracle(**spec["norm"])(got.astype(np.float64), spec["lengths"])
+        assert np.abs(out - o).max() < 2e-5
+
+
+@pytest.mark.parametrize("name", OP_CASES)
+def test_op_vs_reference(sb, golden, name):
+    spec = gc.CASES[name]
+    x = spec["make_input"]()
+    ref = golden[f"{name}/ref32"]
+    kind, kw = spec["kind"], dict(spec["kwargs"])
+    if kind == "stft":
+        got = sb.STFT(**kw)(dev(x))
+        tol = 2e-4 * np.abs(ref).max()
+    elif kind == "magnitude":
+        got = sb.spectral_magnitude(dev(x), **kw)
+        tol = 2e-6 * max(1.0, np.abs(ref).max())
+    elif kind == "filterbank":
+        got = sb.Filterbank(**kw)(dev(x))
+        tol = 1e-4 if kw.get("log_mel", True) else 1e-5 * np.abs(ref).max()
+    elif kind == "dct":
+        got = sb.DCT(**kw)(dev(x))
+        tol = 1e-5 * np.abs(ref).max()
+    elif kind == "deltas":
+        got = sb.Deltas(**kw)(dev(x))
+        tol = 1e-5
+    else:
+        got = sb.ContextWindow(**kw)(dev(x))
+        tol = 0.0
+    got = got.cpu().numpy()
+    assert got.shape == ref.shape
+    assert np.abs(got - ref).max() <= tol, np.abs(got - ref).max()
+
+
+@pytest.mark.parametrize("name", SEQ_CASES)
+def test_norm_sequence_vs_reference(sb, golden, name):
+    spec = gc.CASES[name]
+    norm = sb.InputNormalization(**spec["norm"])
+    for i, st in enumerate(spec["steps"]):
+        x = gc.synth_feats(st["seed"], spec["shape"])
+        norm.train(st["training"])
+        kw = {"epoch": st["epoch"]}
+        if st["spk_ids"] is not None:
+            kw["spk_ids"] = torch.tensor(st["spk_ids"]).unsqueeze(1)
+        xin = dev(x)
+        y = norm(xin, torch.tensor(st["lengths"], dtype=torch.float32).cuda(), **kw)
+        inplace = spec["norm"]["norm_type"] in ("sentence", "speaker")
+        assert (y.data_ptr() == xin.data_ptr()) == inplace
+        if not inplace:
+            assert np.array_equal(xin.cpu().numpy(), x)  # input left intact
+        ref = golden[f"{name}/step{i}"]
+        got = y.cpu().numpy()
+        assert got.shape == ref.shape
+        assert np.abs(got - ref).max() < 2e-5 * max(1.0, np.abs(ref).max()), (i, np.abs(got - ref).max())
+        if spec["norm"]["norm_type"] == "global":
+            assert norm.count == int(golden[f"{name}/step{i}_count"])
+            gm = golden[f"{name}/step{i}_glob_mean"]
+            np.testing.assert_allclose(np.broadcast_to(norm.glob_mean.cpu().numpy(), gm.shape), gm,
+                                       rtol=1e-5, atol=1e-5)
+
+
+# ---- known answers of reference tests/unittests/test_features.py, on the GPU ----
+def test_ka_deltas_context(sb):
+    ones = torch.ones(10, 101, 20, device="cuda")
+    assert torch.equal(sb.Deltas(input_size=20)(ones), torch.zeros_like(ones))
+    x = torch.tensor([1.0, 2.0, 3.0], device="cuda").view(1, 3, 1)
+    want = torch.tensor([[0, 1, 2], [1, 2, 3], [2, 3, 0]], device="cuda").float().unsqueeze(0)
+    assert torch.equal(sb.ContextWindow(left_frames=1, right_frames=1)(x), want)
+    r = torch.rand(2, 10, 5, device="cuda")
+    assert torch.equal(sb.ContextWindow()(r), r)
+
+
+def test_ka_filterbank(sb):
+    fb = sb.Filterbank()
+    out = fb(torch.zeros(10, 101, 201, device="cuda"))
+    assert torch.equal(out, torch.full_like(out, -100.0))
+    assert torch.equal(fb._amplitude_to_DB(torch.zeros(1, 1, 1, device="cuda")),
+                       torch.tensor([[[-100.0]]], device="cuda"))
+    a = torch.rand(1, 101, 201, device="cuda") * 10
+    b = torch.rand(1, 101, 201, device="cuda")
+    both = fb(torch.cat([a, b]))
+    assert torch.sum(torch.abs(fb(a)[0] - both[0])) < 8e-5
+    assert torch.sum(torch.abs(fb(b)[0] - both[1])) < 8e-5
+    x = torch.rand(10, 101, 201, device="cuda")
+    two = fb(torch.stack((x, x), -1))[..., 0]
+    assert torch.sum(fb(x) - two) < 5e-5
+
+
+def test_ka_input_normalization(sb):
+    x = torch.tensor([1.0, 2, 3, 0, 0, 0], device="cuda").view(1, 6, 1)
+    out = sb.InputNormalization()(x, torch.tensor([0.5], device="cuda")).squeeze()
+    assert torch.equal(out, torch.tensor([-1.0, 0, 1, -2, -2, -2], device="cuda"))
+
+
+def test_shapes_and_errors(sb):
+    x = torch.randn(10, 16000, device="cuda")
+    assert sb.STFT(sample_rate=16000)(x).shape == (10, 101, 201, 2)
+    assert sb.Fbank()(x).shape == (10, 101, 40)
+    assert sb.MFCC()(x).shape == (10, 101, 660)
+    assert sb.Fbank()(torch.randn(2, 0, device="cuda")).shape == (2, 1, 40)
+    with pytest.raises(RuntimeError):
+        sb.Fbank()(torch.randn(2, 1600))  # CPU tensor: no fallback
+    with pytest.raises(ValueError):
+        sb.DCT(input_size=10, n_out=20)
+    half = sb.Fbank()(x.half())
+    assert half.dtype == torch.float32
+
+
+@pytest.mark.parametrize("B,L,kw", [(32, 256000, {"n_mels": 80}), (3, 48000 + 77, {"n_mels": 80}),
+                                    (2, 480000, {"n_mels": 80})])
+def test_full_size_properties(sb, B, L, kw):
+    """BASELINE-size checks through size-independent properties: batch
+    independence, time-shift equivariance by whole hops, clamp floor."""
+    g = torch.Generator(device="cuda").manual_seed(5)
+    wav = torch.randn(B, L, device="cuda", generator=g) * 0.1
+    mod = sb.Fbank(**kw)
+    full = mod(wav)
+    assert full.shape == (B, 1 + L // 160, 80) and torch.isfinite(full).all()
+    one = mod(wav[1:2].clone())
+    assert torch.equal(one[0], full[1])  # utterances are independent, bit for bit
+    # frames away from the edges depend only on their own 400 samples
+    shifted = mod(wav[:1, 160 * 7:].clone())
+    a, b_ = full[0, 7 + 3:-3], shifted[0, 3:-3]
+    floor = max(full[0].max(), shifted[0].max()) - 80 + 1e-3
+    keep = (a > floor) & (b_ > floor)
+    assert torch.equal(a[keep], b_[keep])
+    assert (full.amax(dim=(1, 2)) - full.amin(dim=(1, 2)) <= 80.0 + 1e-4).all()

@@ -1,0 +1,112 @@
+"""CPU-side checks: the C-ABI library builds/loads and exports every symbol that
+include/sbfe.h declares, host tables match the reference's constants, and the
+product refuses CPU tensors instead of falling back."""
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    from speechbrain_b200 import _lib
+
+    handle = _lib.lib()
+    header = open(os.path.join(ROOT, "include", "sbfe.h")).read()
+    declared = set(re.findall(r"SBFE_API [\w\*\s]+?(sbfe_\w+)\(", header))
+    assert declared and declared == set(_lib.SIGNATURES)
+    for name in declared:
+        assert getattr(handle, name) is not None
+    assert handle.sbfe_abi_version() == 1
+    assert handle.sbfe_num_frames(16000, 160) == 101
+    assert handle.sbfe_error_string(-1).decode().startswith("sbfe")
+
+
+def test_library_is_sm100a_and_has_no_oracle_dependency():
+    from speechbrain_b200 import _build
+
+    out = subprocess.run(["cuobjdump", "-lelf", _build.LIB], capture_output=True, text=True).stdout
+    assert "sm_100a" in out
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "speechbrain_b200")):
+        for f in files:
+            if f.endswith(".py"):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in src, "product must not touch the oracle: " + f
+
+
+def test_host_codelets_match_naive_dft(tmp_path):
+    for name in ("codelet_check", "frame400_check"):
+        exe = tmp_path / name
+        subprocess.run(["g++", "-O2", "-o", str(exe), os.path.join(ROOT, "tests", "host", name + ".cpp")],
+                       check=True)
+        res = subprocess.run([str(exe)], capture_output=True, text=True)
+        assert res.returncode == 0, res.stdout
+
+
+def test_host_tables_match_reference_constants(golden):
+    import speechbrain_b200 as sb
+
+    fb = sb.Fbank(n_mels=80)
+    name = "cfg2_fbank80_sentnorm_4x2s"
+    assert np.array_equal(fb.compute_fbanks.f_central.numpy(), golden[f"{name}/fc"])
+    assert np.array_equal(fb.compute_fbanks.band.numpy(), golden[f"{name}/band"])
+    assert np.array_equal(fb.compute_STFT.window.numpy(), golden[f"{name}/window"])
+    tab = fb._frontend_tables()
+    assert tab.nnz == 387 and tab.n_mels == 80  # 387 non-zeros for 80 mels
+    dense = fb.compute_fbanks.fbank_matrix()
+    start, count, offset, w = tab._h_mel
+    rebuilt = torch.zeros_like(dense)
+    for m in range(80):
+        s, c, o = int(start[m]), int(count[m]), int(offset[m])
+        rebuilt[s:s + c, m] = w[o:o + c]
+    assert torch.equal(rebuilt, dense)
+    assert tab.floor_db == -100.0
+
+
+def test_drop_in_surface():
+    import speechbrain_b200 as sb
+
+    assert list(sb.Fbank().state_dict()) == ["compute_deltas.kernel"]
+    assert list(sb.MFCC().state_dict()) == ["compute_deltas.kernel"]
+    assert sb.MFCC().state_dict()["compute_deltas.kernel"].shape == (20, 1, 5)
+    n = sb.InputNormalization()
+    assert set(n._statistics_dict()) == {"count", "glob_mean", "glob_std", "spk_dict_mean",
+                                         "spk_dict_std", "spk_dict_count"}
+    import inspect
+    assert list(inspect.signature(n.forward).parameters)[:2] == ["x", "lengths"]
+    with pytest.raises(ValueError):
+        sb.DCT(input_size=10, n_out=20)
+    with pytest.raises(NotImplementedError):
+        sb.Fbank(requires_grad=True)
+
+
+def test_cpu_tensors_are_refused():
+    import speechbrain_b200 as sb
+
+    with pytest.raises(RuntimeError, match="CUDA only"):
+        sb.Fbank()(torch.randn(2, 1600))
+    with pytest.raises(RuntimeError, match="CUDA only"):
+        sb.InputNormalization()(torch.randn(2, 10, 4), torch.ones(2))
+
+
+def test_checkpoint_roundtrip(tmp_path):
+    import speechbrain_b200 as sb
+
+    a = sb.InputNormalization()
+    a.count, a.glob_mean, a.glob_std = 7, torch.arange(4.0), torch.ones(4) * 2
+    a.spk_dict_mean[3], a.spk_dict_std[3], a.spk_dict_count[3] = torch.zeros(4), torch.ones(4), 2
+    p = str(tmp_path / "normalizer.ckpt")
+    a._save(p)
+    raw = torch.load(p)
+    assert set(raw) == {"count", "glob_mean", "glob_std", "spk_dict_mean", "spk_dict_std", "spk_dict_count"}
+    b = sb.InputNormalization()
+    b._load(p, end_of_epoch=False, device="cpu")
+    assert b.count == 7 and torch.equal(b.glob_mean, a.glob_mean) and b.spk_dict_count == {3: 2}
+    # legacy checkpoints hold python ints (reference features.py:1169-1171)
+    torch.save({**raw, "glob_mean": 0, "glob_std": 0}, p)
+    b._load(p)
+    assert b.glob_mean == 0
