@@ -1,0 +1,367 @@
+#!/usr/bin/env python
+"""Benchmark of the B200-native SpeechBrain feature frontend.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Workload (BASELINE.json configs[1], the config the metric is quoted on):
+LibriSpeech ASR frontend = Fbank(n_mels=80) + InputNormalization("sentence") on
+a batch of 32 x 16 s synthetic 16 kHz waveforms PER GPU (weak scaling: utterances
+are independent, no data-path collective).  A step = one pass of that frontend
+over one batch.  Prints ONE JSON line (rank 0).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SR, BATCH, SECONDS, N_MELS, HOP = 16000, 32, 16, 80, 160
+L = SR * SECONDS
+T = 1 + L // HOP
+AUDIO_S_PER_STEP = BATCH * SECONDS                       # per GPU
+ALG_BYTES_PER_STEP = 4 * BATCH * L + 4 * BATCH * T * N_MELS  # read wav once + write feats once
+POOL = 8  # rotating input buffers: 8 x 32.8 MB = 262 MB > 126 MB L2
+METRIC = "audio-seconds/sec of Fbank(80 mel)+sentence InputNormalization"
+CONFIG = {
+    "workload": "cfg2 LibriSpeech ASR frontend: Fbank n_mels=80 + sentence InputNormalization, "
+                "batch 32 x 16 s @16 kHz per GPU",
+    "batch_per_gpu": BATCH, "seconds": SECONDS, "n_mels": N_MELS, "n_fft": 400, "hop": HOP,
+    "l2": "inputs rotate over %d buffers (%.0f MB > 126 MB L2)" % (POOL, POOL * 4 * BATCH * L / 1e6),
+}
+
+
+def synth_batch(seed, device):
+    """randn * 0.1, variable lengths in [0.6, 1.0] with zero-padded tails."""
+    g = torch.Generator(device="cpu").manual_seed(1234 + seed)
+    lengths = torch.linspace(0.6, 1.0, BATCH)[torch.randperm(BATCH, generator=g)]
+    wav = torch.randn(BATCH, L, generator=g) * 0.1
+    for i in range(BATCH):
+        wav[i, int(round(float(lengths[i]) * L)):] = 0.0
+    return wav.to(device), lengths.to(device)
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            self.thread.join(timeout=2)
+
+    def summary(self):
+        sm = [int(r[0]) for r in self.rows if r and r[0].isdigit()]
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6
+                          for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": int(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ------------------------------------------------------------------ CPU arm
+def cpu_port_step(wav, lengths):
+    from oracle import frontend_torch as ot
+
+    with torch.no_grad():
+        return ot.fbank_sentence_norm(wav, lengths, n_mels=N_MELS)
+
+
+def time_cpu_port(n_utts, reps, warm=1):
+    """Times the torch-CPU port of the reference path on `n_utts` x 16 s with all
+    host threads; returns (audio-s/s from the best rep, threads, sample text)."""
+    torch.set_num_threads(os.cpu_count() or 1)
+    wav, lengths = synth_batch(0, "cpu")
+    wav, lengths = wav[:n_utts].contiguous(), lengths[:n_utts].contiguous()
+    for _ in range(warm):
+        cpu_port_step(wav, lengths)
+    best = float("inf")
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        cpu_port_step(wav, lengths)
+        best = min(best, time.perf_counter() - t0)
+    sample = "%d x %d s utterances of the cfg2 batch, best of %d (torch CPU ops, %d threads)" % (
+        n_utts, SECONDS, reps, torch.get_num_threads())
+    return n_utts * SECONDS / best, torch.get_num_threads(), sample, best
+
+
+def run_reference_arm(args, rank):
+    if rank != 0:
+        return
+    steps = max(1, args.steps)
+    torch.set_num_threads(os.cpu_count() or 1)
+    wav, lengths = synth_batch(0, "cpu")
+    for _ in range(max(1, args.warmup)):
+        cpu_port_step(wav, lengths)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        cpu_port_step(wav, lengths)
+    dt = (time.perf_counter() - t0) / steps
+    val = AUDIO_S_PER_STEP / dt
+    cores = torch.get_num_threads()
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "audio-s/s",
+        "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "config": CONFIG,
+        "cpu_baseline": {"value": val, "unit": "audio-s/s", "cores": cores, "kind": "port",
+                         "sample": "full cfg2 batch (32 x 16 s) per step, torch CPU ops restating "
+                                   "the reference chain (oracle/frontend_torch.py)"},
+        "e2e": {"value": val, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------ GPU arm
+def build_frontend():
+    import speechbrain_b200 as sb
+
+    return sb.Fbank(n_mels=N_MELS), sb.InputNormalization(norm_type="sentence")
+
+
+def frontend_step(fb, norm, wav, lengths):
+    """The public API a recipe's compute_forward calls (train.py:66-68)."""
+    return norm(fb(wav), lengths)
+
+
+def time_device_resident(fb, norm, pool, steps, warmup, use_graph):
+    """K steps with inputs already in HBM; returns elapsed ms (CUDA events)."""
+    stream = torch.cuda.current_stream()
+    outs = [None] * len(pool)
+    if use_graph:
+        graphs = []
+        side = torch.cuda.Stream()
+        side.wait_stream(stream)
+        with torch.cuda.stream(side):
+            for wav, lens in pool[:2]:
+                frontend_step(fb, norm, wav, lens)
+        stream.wait_stream(side)
+        torch.cuda.synchronize()
+        for i, (wav, lens) in enumerate(pool):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                outs[i] = frontend_step(fb, norm, wav, lens)
+            graphs.append(g)
+
+        def run(i):
+            graphs[i % len(pool)].replay()
+    else:
+        def run(i):
+            wav, lens = pool[i % len(pool)]
+            outs[i % len(pool)] = frontend_step(fb, norm, wav, lens)
+    for i in range(warmup):
+        run(i)
+    return run, outs
+
+
+def kernel_only_ms(fb, pool, reps):
+    """Average duration of the dominant kernel (fused fbank400) alone: one CUDA
+    graph holding one launch per pool slot, replayed `reps` times, CUDA events on
+    the launching stream."""
+    from speechbrain_b200 import ops
+
+    tables = fb._frontend_tables()
+    for wav, _ in pool[:2]:
+        ops.fbank_forward(tables, wav)
+    torch.cuda.synchronize()
+    keep = []
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for wav, _ in pool:
+            keep.append(ops.fbank_forward(tables, wav))
+    for _ in range(3):
+        g.replay()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(reps):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / (reps * len(pool))
+
+
+def time_e2e(fb, norm, host_pool, lens_dev, steps, warmup, barrier):
+    """Public API with HOST buffers: every step copies its waveform batch from
+    pinned host memory, runs the frontend, and copies the features back to
+    pinned host memory.  Copies are pipelined on their own streams (PCIe is full
+    duplex).  Returns (seconds for `steps` steps, h2d bytes, d2h bytes)."""
+    dev = torch.device("cuda", torch.cuda.current_device())
+    s_in, s_out, s_cmp = torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.current_stream()
+    d_in = [torch.empty((BATCH, L), device=dev) for _ in range(2)]
+    h_out = [torch.empty((BATCH, T, N_MELS), pin_memory=True) for _ in range(2)]
+    ev_in = [torch.cuda.Event() for _ in range(2)]
+    ev_cmp = [torch.cuda.Event() for _ in range(2)]
+    ev_out = [torch.cuda.Event() for _ in range(2)]
+    live = [None, None]
+
+    def step(i):
+        k = i & 1
+        with torch.cuda.stream(s_in):
+            s_in.wait_event(ev_cmp[k])          # compute of step i-2 has consumed d_in[k]
+            d_in[k].copy_(host_pool[i % len(host_pool)], non_blocking=True)
+            ev_in[k].record(s_in)
+        s_cmp.wait_event(ev_in[k])
+        out = frontend_step(fb, norm, d_in[k], lens_dev)
+        ev_cmp[k].record(s_cmp)
+        with torch.cuda.stream(s_out):
+            s_out.wait_event(ev_cmp[k])
+            s_out.wait_event(ev_out[k])          # h_out[k] of step i-2 is complete
+            h_out[k].copy_(out, non_blocking=True)
+            ev_out[k].record(s_out)
+        out.record_stream(s_out)
+        live[k] = out
+
+    for i in range(warmup):
+        step(i)
+    torch.cuda.synchronize()
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(steps):
+        step(warmup + i)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    barrier()
+    return dt, 4 * BATCH * L, 4 * BATCH * T * N_MELS, float(h_out[(warmup + steps - 1) & 1].abs().mean())
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of CUDA graphs")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference_arm(args, rank)
+        return
+    args.warmup = max(3, args.warmup)
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = world > 1
+    if dist:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.distributed.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist:
+            torch.distributed.barrier()
+
+    def max_over_ranks(x):
+        if not dist:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        return float(t)
+
+    fb, norm = build_frontend()
+    host_pool, pool = [], []
+    for i in range(POOL):
+        wav, lens = synth_batch(i + 100 * rank, "cpu")
+        host_pool.append(wav.pin_memory())
+        pool.append((wav.to(dev), lens.to(dev)))
+    lens_dev = pool[0][1]
+
+    # ---- device-resident throughput: exactly K timed steps -------------------
+    run, outs = time_device_resident(fb, norm, pool, args.steps, args.warmup, not args.no_graph)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    with ClockSampler(local) as clocks:
+        e0.record()
+        for i in range(args.steps):
+            run(args.warmup + i)
+        e1.record()
+        torch.cuda.synchronize()
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    value = world * AUDIO_S_PER_STEP * args.steps / (ms / 1e3)
+
+    # ---- dominant kernel alone -> roofline ------------------------------------
+    k_ms = kernel_only_ms(fb, pool, reps=max(4, args.steps // POOL))
+    peak, peak_src = peaks()
+    k_bytes = 4 * BATCH * L + 4 * BATCH * T * N_MELS
+    achieved = k_bytes / (k_ms / 1e3) / 1e9
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):
+        traffic = json.load(open(tp)).get("fbank400_kernel_dram_bytes_per_launch")
+
+    # ---- end to end with host buffers -----------------------------------------
+    e2e_steps = min(args.steps, 100)
+    dt, h2d, d2h, _ = time_e2e(fb, norm, host_pool, lens_dev, e2e_steps, args.warmup, barrier)
+    dt = max_over_ranks(dt)
+    e2e_value = world * AUDIO_S_PER_STEP * e2e_steps / dt
+
+    line = {
+        "metric": METRIC, "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": dict(CONFIG, launch="eager" if args.no_graph else "one CUDA graph per step",
+                       parallelism="utterance-sharded x%d, no collective" % world),
+        "clocks": clocks.summary(),
+        "e2e": {"value": e2e_value, "unit": "audio-s/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+                "note": "pinned host wav -> H2D -> Fbank+norm via public API -> D2H features; "
+                        "copies pipelined on separate streams"},
+        "gpu_launches": 5 * args.steps,
+        "roofline": {"bound": "hbm", "kernel": "fbank400_kernel (fused frame+window+rFFT400+mel+dB)",
+                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "peak_source": peak_src, "us_per_launch": k_ms * 1e3,
+                     "alg_bytes_per_launch": k_bytes, "traffic": traffic,
+                     "step_frac": (ALG_BYTES_PER_STEP / (ms / args.steps / 1e3) / 1e9) / peak},
+    }
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        v, cores, sample, _ = time_cpu_port(8, reps=5)
+        line["cpu_baseline"] = {"value": v, "unit": "audio-s/s", "cores": cores, "kind": "port",
+                                "sample": sample}
+    if rank == 0:
+        print(json.dumps(line))
+    if dist:
+        torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

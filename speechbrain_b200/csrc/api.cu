@@ -65,7 +65,7 @@ int sbfe_fbank_forward(const sbfe_fbank_desc* d, const float* d_wav, int64_t B, 
                        int64_t ws_bytes, void* stream) {
   if (!desc_ok(d, true) || B < 0 || L < 0 || wav_stride < L) return SBFE_E_INVAL;
   if (B == 0) return 0;
-  if (!d_wav || !d_out) return SBFE_E_INVAL;
+  if ((!d_wav && L > 0) || !d_out) return SBFE_E_INVAL;
   cudaStream_t s = (cudaStream_t)stream;
   if (fused_ok(d)) return launch_fbank400(d, d_wav, B, L, wav_stride, d_out, d_utt_max, s);
   if (!d_ws || ws_bytes < sbfe_fbank_workspace_bytes(d, B, L)) return SBFE_E_NOSPACE;
@@ -78,7 +78,7 @@ int sbfe_stft_forward(const sbfe_fbank_desc* d, const float* d_wav, int64_t B, i
                       int64_t wav_stride, float* d_out, int32_t power_only, void* stream) {
   if (!desc_ok(d, false) || B < 0 || L < 0 || wav_stride < L) return SBFE_E_INVAL;
   if (B == 0) return 0;
-  if (!d_wav || !d_out) return SBFE_E_INVAL;
+  if ((!d_wav && L > 0) || !d_out) return SBFE_E_INVAL;
   return launch_stft_generic(d, d_wav, B, L, wav_stride, d_out, power_only, (cudaStream_t)stream);
 }
 

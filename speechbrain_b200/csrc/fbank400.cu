@@ -35,6 +35,7 @@ constexpr int kWarps = 10;
 constexpr int kThreads = kWarps * 32;
 constexpr int kNfft = 400;
 constexpr int kBins = 201;
+constexpr int kMaxSmem = (31 * 400 + 400 + 40 + 400 * 32) * 4;  // hop = 400 worst case
 
 struct Fbank400Params {
   float window[kNfft];   // zero-padded to n_fft
@@ -222,16 +223,22 @@ int launch_fbank400(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64
   prm.tiles = (unsigned)tiles;
   const size_t smem = (size_t)(region_a_floats(d->hop) + 400 * kTile) * sizeof(float);
   dim3 grid((unsigned)(tiles * B));
-  cudaError_t e;
-  if (d->hop == 160) {
-    e = cudaFuncSetAttribute(fbank400_kernel<160>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)smem);
+  // opt in to > 48 KB dynamic smem once per process (hop <= 400 bounds the size)
+  static bool attr_done[64] = {};  // per device; a duplicate set is harmless
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64 || !attr_done[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(fbank400_kernel<160>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(fbank400_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               kMaxSmem);
     if (e != cudaSuccess) return (int)e;
+    if (dev >= 0 && dev < 64) attr_done[dev] = true;
+  }
+  if (d->hop == 160) {
     fbank400_kernel<160><<<grid, kThreads, smem, stream>>>(prm);
   } else {
-    e = cudaFuncSetAttribute(fbank400_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)smem);
-    if (e != cudaSuccess) return (int)e;
     fbank400_kernel<0><<<grid, kThreads, smem, stream>>>(prm);
   }
   return check_last();

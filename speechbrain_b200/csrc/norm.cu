@@ -36,16 +36,18 @@ norm_stats_partial_kernel(const float* __restrict__ x, const float* __restrict__
   const float* xb = x + b * T * F;
   for (int f0 = 0; f0 < F; f0 += bx) {
     const int f = f0 + tx;
-    float s1 = 0.f, s2 = 0.f;
+    // double accumulators: the pass is memory-bound and B200 runs fp64 adds at
+    // half the fp32 rate, so exactness of the statistics is free
+    double s1 = 0.0, s2 = 0.0;
     if (f < F && t_lo < t_hi) {
       const float pivot = fmaxf(__ldg(xb + f), floor_b);
       for (int t = t_lo + ty; t < t_hi; t += by) {
-        const float d = fmaxf(__ldg(xb + (int64_t)t * F + f), floor_b) - pivot;
+        const double d = (double)(fmaxf(__ldg(xb + (int64_t)t * F + f), floor_b) - pivot);
         s1 += d;
-        s2 = fmaf(d, d, s2);
+        s2 = fma(d, d, s2);
       }
     }
-    s_red[threadIdx.x] = make_double2((double)s1, (double)s2);
+    s_red[threadIdx.x] = make_double2(s1, s2);
     __syncthreads();
     if (ty == 0 && f < F) {
       double a1 = 0.0, a2 = 0.0;

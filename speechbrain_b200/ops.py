@@ -144,7 +144,7 @@ def fbank_forward(tables, wav):
     ws_bytes = L_.sbfe_fbank_workspace_bytes(C.byref(desc), B, L)
     ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=wav.device) if ws_bytes > 0 else None
     with torch.cuda.device(wav.device):
-        check(L_.sbfe_fbank_forward(C.byref(desc), _ptr(wav), B, L, wav.stride(0), _ptr(out),
+        check(L_.sbfe_fbank_forward(C.byref(desc), _ptr(wav), B, L, L, _ptr(out),
                                     _ptr(utt_max), _ptr(ws), max(ws_bytes, 0), _stream()))
     return out, utt_max
 
@@ -158,7 +158,7 @@ def stft_forward(tables, wav, power_only=False):
     shape = (B, T, tables.bins) if power_only else (B, T, tables.bins, 2)
     out = torch.empty(shape, dtype=torch.float32, device=wav.device)
     with torch.cuda.device(wav.device):
-        check(lib().sbfe_stft_forward(C.byref(desc), _ptr(wav), B, L, wav.stride(0), _ptr(out),
+        check(lib().sbfe_stft_forward(C.byref(desc), _ptr(wav), B, L, L, _ptr(out),
                                       int(power_only), _stream()))
     return out
 

@@ -70,8 +70,11 @@ def test_lobe_vs_reference(sb, golden, name):
         if spec["norm"]["norm_type"] == "sentence":
             assert out.data_ptr() == got_t.data_ptr()  # in place, like the reference
         out = out.cpu().numpy()
-        n32, n64 = golden[f"{name}/norm32"], golden[f"{name}/norm64"]
-        assert np.abs(out - n64).max() <= 2 * np.abs(n32 - n64).max() + 2e-5
+        # end to end against the reference: feature error (dB) is divided by the
+        # per-channel std, so the bound is the dB bound over the smallest std
+        n32 = golden[f"{name}/norm32"]
+        assert np.abs(out - n32).max() < 2e-3
+        assert np.abs(out - n32).mean() < 2e-5
         # and against the oracle normalising OUR features (isolates the norm kernels)
         o = onp.InputNormalizationOracle(**spec["norm"])(got.astype(np.float64), spec["lengths"])
         assert np.abs(out - o).max() < 2e-5
