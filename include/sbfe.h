@@ -61,6 +61,7 @@ typedef struct sbfe_fbank_desc {
   const int32_t* d_mel_count;   /* [M] */
   const int32_t* d_mel_offset;  /* [M] */
   const float* d_mel_weight;    /* [nnz] */
+  int32_t mel_nnz;              /* total number of stored weights */
 } sbfe_fbank_desc;
 
 SBFE_API int sbfe_abi_version(void);

@@ -34,6 +34,7 @@ class FbankDesc(C.Structure):
         ("d_mel_count", C.c_void_p),
         ("d_mel_offset", C.c_void_p),
         ("d_mel_weight", C.c_void_p),
+        ("mel_nnz", C.c_int32),
     ]
 
 

@@ -29,10 +29,9 @@ static bool desc_ok(const sbfe_fbank_desc* d, bool need_mel) {
     return false;
   return true;
 }
-// the fused kernel covers n_fft == 400 with any hop <= 400 and M that fits its tile
-static bool fused_ok(const sbfe_fbank_desc* d) {
-  return d->n_fft == 400 && d->hop <= 400 && d->n_mels <= 384;
-}
+// the fused kernel covers n_fft == 400, hop <= 400 and filterbanks whose tables fit in smem
+bool fbank400_supported(const sbfe_fbank_desc* d);
+static bool fused_ok(const sbfe_fbank_desc* d) { return fbank400_supported(d); }
 }  // namespace sbfe
 
 using namespace sbfe;

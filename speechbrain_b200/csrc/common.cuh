@@ -38,10 +38,16 @@ struct DbParams {
   float floor_db;  // exact host-rounded value for x <= amin
   int log_mel;
 };
+// x > amin >= ~1e-38 here, so the flush-to-zero form is exact enough and branch-free
+__device__ __forceinline__ float fast_log2(float x) {
+  float y;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ float to_db(float x, const DbParams& p) {
   if (!p.log_mel) return x;
   // !(x > amin) also catches NaN-free zero/negative inputs exactly like clamp()
-  return (x > p.amin) ? fmaf(__log2f(x), p.scale, -p.offset) : p.floor_db;
+  return (x > p.amin) ? fmaf(fast_log2(x), p.scale, -p.offset) : p.floor_db;
 }
 
 inline int check_last(void) {

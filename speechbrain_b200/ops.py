@@ -119,6 +119,7 @@ class FrontendTables:
             keep += dev
             desc.d_mel_start, desc.d_mel_count = dev[0].data_ptr(), dev[1].data_ptr()
             desc.d_mel_offset, desc.d_mel_weight = dev[2].data_ptr(), dev[3].data_ptr()
+            desc.mel_nnz = self.nnz
         entry = (desc, keep)
         self._dev[key] = entry
         return entry
