@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define SBFE_ABI_VERSION 1
+#define SBFE_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define SBFE_API __attribute__((visibility("default")))
@@ -61,7 +61,12 @@ typedef struct sbfe_fbank_desc {
   const int32_t* d_mel_count;   /* [M] */
   const int32_t* d_mel_offset;  /* [M] */
   const float* d_mel_weight;    /* [nnz] */
-  int32_t mel_nnz;              /* total number of stored weights */
+  int32_t mel_nnz;              /* total number of stored weights (padding included) */
+  int32_t mel_pad4;             /* 1: every mel_offset[m] is a multiple of 4 and each filter's
+                                   weights are followed by zeros up to a multiple of 4 entries
+                                   (mel_count stays the unpadded count).  Enables the 128-bit
+                                   weight loads of the fused n_fft = 400 / hop = 160 kernel;
+                                   0 is always valid (slower kernel). */
 } sbfe_fbank_desc;
 
 SBFE_API int sbfe_abi_version(void);

@@ -35,6 +35,7 @@ class FbankDesc(C.Structure):
         ("d_mel_offset", C.c_void_p),
         ("d_mel_weight", C.c_void_p),
         ("mel_nnz", C.c_int32),
+        ("mel_pad4", C.c_int32),
     ]
 
 
@@ -93,7 +94,7 @@ def lib():
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(handle, name)
             fn.restype, fn.argtypes = res, args
-        if handle.sbfe_abi_version() != 1:
+        if handle.sbfe_abi_version() != 2:
             raise SbfeUnavailable("libsbfe.so ABI version mismatch")
         _lib = handle
         return _lib

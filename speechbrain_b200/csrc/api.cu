@@ -6,6 +6,8 @@
 namespace sbfe {
 int launch_fbank400(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
                     sbfe_maxkey_t*, cudaStream_t);
+int launch_fbank400_v3(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
+                       sbfe_maxkey_t*, cudaStream_t);
 int launch_stft_generic(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
                         int, cudaStream_t);
 int launch_spectral_magnitude(const float*, int64_t, float, int, float, float*, cudaStream_t);
@@ -31,7 +33,11 @@ static bool desc_ok(const sbfe_fbank_desc* d, bool need_mel) {
 }
 // the fused kernel covers n_fft == 400, hop <= 400 and filterbanks whose tables fit in smem
 bool fbank400_supported(const sbfe_fbank_desc* d);
-static bool fused_ok(const sbfe_fbank_desc* d) { return fbank400_supported(d); }
+// packed-f32x2 kernel: additionally hop == 160 and the padded filter layout (mel_pad4)
+bool fbank400_v3_supported(const sbfe_fbank_desc* d);
+static bool fused_ok(const sbfe_fbank_desc* d) {
+  return fbank400_v3_supported(d) || fbank400_supported(d);
+}
 }  // namespace sbfe
 
 using namespace sbfe;
@@ -66,6 +72,8 @@ int sbfe_fbank_forward(const sbfe_fbank_desc* d, const float* d_wav, int64_t B, 
   if (B == 0) return 0;
   if ((!d_wav && L > 0) || !d_out) return SBFE_E_INVAL;
   cudaStream_t s = (cudaStream_t)stream;
+  if (fbank400_v3_supported(d))
+    return launch_fbank400_v3(d, d_wav, B, L, wav_stride, d_out, d_utt_max, s);
   if (fused_ok(d)) return launch_fbank400(d, d_wav, B, L, wav_stride, d_out, d_utt_max, s);
   if (!d_ws || ws_bytes < sbfe_fbank_workspace_bytes(d, B, L)) return SBFE_E_NOSPACE;
   int rc = launch_stft_generic(d, d_wav, B, L, wav_stride, (float*)d_ws, 1, s);

@@ -1,0 +1,417 @@
+// v3 of the fused frame + window + real-FFT(400) + power + sparse mel + dB kernel
+// (n_fft = 400, hop = 160: every recipe default).  Same contract as fbank400.cu:
+//   STFT.forward          speechbrain/processing/features.py:133-188
+//   spectral_magnitude    speechbrain/processing/features.py:327-356 (power=1)
+//   Filterbank.forward    speechbrain/processing/features.py:490-551
+//   _amplitude_to_DB      speechbrain/processing/features.py:701-702 (log part)
+//
+// What changed against v2 (profiles/r1_baseline.md: 31.5 M warp-instructions, only
+// 31 % of them FP32; ALU pipe > FMA pipe):
+//  * PACKED f32x2 MATH: a thread owns TWO frames (p, p+16) of the 32-frame tile and
+//    every add/mul/fma is one FADD2/FMUL2/FFMA2 on a 64-bit register pair.
+//  * 20 EQUAL WORK UNITS IN BOTH FFT STAGES: thread = (frame pair p = lane & 15,
+//    unit s = 2*warp + (lane >> 4)); stage 1 unit = residue n2, stage 2 unit =
+//    (k1, even/odd half) after one radix-2 DIF step (fft_packed.cuh).  v2 left 9 of
+//    20 role slots idle in stage 2.
+//  * ROLE CONSTANTS ARE DATA, NOT CODE: window taps / twiddles of a unit come from
+//    shared memory with 128-bit loads (one address per half-warp, broadcast), so the
+//    two half-warps of a warp run identical instructions; all shared-memory offsets
+//    are compile-time immediates (no index arithmetic in the hot loops).
+//  * VECTOR EXCHANGE: stage 1 -> stage 2 goes through float4 {re0, re1, im0, im1}
+//    entries; both halves of a warp read the same entry (broadcast).
+#include <cmath>
+#include <cstring>
+
+#include "common.cuh"
+#include "fft_packed.cuh"
+
+namespace sbfe {
+
+namespace v3 {
+
+#include "fbank400_tables.inc"
+
+constexpr int kTile = 32;            // frames per tile
+constexpr int kPairs = 16;           // frame pairs (p, p + 16)
+constexpr int kUnits = 20;           // work units per stage
+constexpr int kWarps = kUnits / 2;
+constexpr int kThreads = kWarps * 32;
+constexpr int kHop = 160;
+constexpr int kPad = 2;              // (kHop + kPad) % 32 == 2: conflict-free scalar reads
+constexpr int kPitch = kHop + kPad;
+constexpr int kNfft = 400;
+constexpr int kBins = 201;
+constexpr int kSpan = (kTile - 1) * kHop + kNfft;                // 5360 samples per tile
+constexpr int kChunks = kSpan / 2;                                // 8-byte cp.async chunks
+constexpr int kCpIters = (kChunks + kThreads - 1) / kThreads;    // 9
+constexpr int kPRows = 204;          // power rows incl. 3 zero rows for padded mel reads
+constexpr int kRegionA = kPRows * kTile;                          // >= padded span (5428)
+constexpr int kRegionE = 200 * kPairs * 4;                        // exchange, float4 entries
+constexpr int kTabW = 400, kTabTw = 400, kTabT2 = 40;
+
+struct Params {
+  DbParams db;
+  int n_mels, mel_nnz;
+  unsigned tiles_per_utt, n_tiles;
+  int64_t L, wav_stride, T;
+  const float* wav;
+  const float* window;     // device, [400], zero-padded / centred to n_fft
+  float* out;
+  sbfe_maxkey_t* utt_max;
+  const int32_t* mel_start;
+  const int32_t* mel_count;
+  const int32_t* mel_offset;
+  const float* mel_weight;
+};
+
+__host__ __device__ inline size_t smem_floats(int n_mels, int nnz) {
+  return (size_t)2 * kRegionA + kRegionE + kTabW + kTabTw + kTabT2 + ((2 * n_mels + 3) & ~3) +
+         ((nnz + 3) & ~3);
+}
+
+__device__ __forceinline__ void cp_async8(float* smem_dst, const float* gsrc, int src_bytes) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" ::"r"(d), "l"(gsrc), "r"(src_bytes)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc, int src_bytes) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(d), "l"(gsrc), "r"(src_bytes)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory");
+}
+
+// asynchronous copy of one tile's waveform span into `dst` (pitch kPitch per hop); samples
+// outside [0, L) are zero-filled by the copy engine (src-size < cp-size)
+__device__ __forceinline__ void prefetch_tile(const Params& prm, unsigned tile, float* dst, int tid) {
+  const int64_t b = tile / prm.tiles_per_utt;
+  const int64_t t0 = (int64_t)(tile - b * prm.tiles_per_utt) * kTile;
+  const int64_t g0 = t0 * kHop - kNfft / 2;                 // even
+  const int lo = g0 < 0 ? (int)(-g0) : 0;                   // 0 or 200
+  const int64_t rem = prm.L - g0;
+  const int hi = rem <= 0 ? 0 : (rem < kSpan ? (int)rem : kSpan);
+  const float* row = prm.wav + b * prm.wav_stride;
+  const float* wsrc = row + g0;                             // dereferenced inside [lo, hi) only
+  if ((reinterpret_cast<uintptr_t>(row) & 7) == 0) {
+#pragma unroll
+    for (int k = 0; k < kCpIters; ++k) {
+      const int c = k * kThreads + tid;
+      if (c < kChunks) {
+        const int i = 2 * c;
+        int n = hi - i;
+        n = (i < lo || n < 0) ? 0 : (n > 2 ? 2 : n);
+        cp_async8(dst + i + (i / kHop) * kPad, n ? wsrc + i : prm.window, 4 * n);
+      }
+    }
+  } else {
+    for (int i = tid; i < kSpan; i += kThreads) {
+      const bool ok = i >= lo && i < hi;
+      cp_async4(dst + i + (i / kHop) * kPad, ok ? wsrc + i : prm.window, ok ? 4 : 0);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 2) fbank400_v3_kernel(const __grid_constant__ Params prm) {
+  extern __shared__ __align__(16) float smem[];
+  float* s_a = smem;                       // 2 x [staged waveform | P[bin][32]]
+  float* s_e = s_a + 2 * kRegionA;         // exchange, later the output tile
+  float* s_tw = s_e + kRegionE;            // [n2][20]: window taps of residue n2 (n1 order)
+  float* s_tt = s_tw + kTabW;              // [n2][20]: (re, im) of W400^(k1*n2), k1 = 1..9, 2 pad
+  float* s_t2 = s_tt + kTabTw;             // [h][20]
+  int2* s_meta = reinterpret_cast<int2*>(s_t2 + kTabT2);
+  const int M = prm.n_mels;
+  float* s_w = reinterpret_cast<float*>(s_meta) + ((2 * M + 3) & ~3);  // 16-byte aligned
+
+  const int tid = threadIdx.x;
+  const int lane = tid & 31, warp = tid >> 5;
+  const int p = lane & 15, h = lane >> 4;
+  const int unit = 2 * warp + h;
+
+  // ---- once per CTA: first prefetch, then the constant tables -----------------------------
+  unsigned tile = blockIdx.x;
+  if (tile < prm.n_tiles) prefetch_tile(prm, tile, s_a, tid);
+  cp_async_commit();
+  for (int i = tid; i < kTabW; i += kThreads) {
+    const int n1 = i / 20, n2 = i - n1 * 20;   // window[i] is tap n1 of residue n2
+    s_tw[n2 * 20 + n1] = __ldg(prm.window + i);
+    s_tt[i] = kTw400[i];
+  }
+  if (tid < kTabT2) s_t2[tid] = kT2[tid];
+  for (int m = tid; m < M; m += kThreads)
+    s_meta[m] = make_int2(__ldg(prm.mel_start + m) | (__ldg(prm.mel_count + m) << 16),
+                          __ldg(prm.mel_offset + m));
+  for (int i = tid; i < prm.mel_nnz; i += kThreads) s_w[i] = __ldg(prm.mel_weight + i);
+  if (tid < 2 * (kPRows - kBins) * kTile) {
+    const int r = tid / ((kPRows - kBins) * kTile), i = tid - r * (kPRows - kBins) * kTile;
+    s_a[r * kRegionA + kBins * kTile + i] = 0.f;
+  }
+  const float db_scale = prm.db.scale, db_amin = prm.db.amin, db_off = prm.db.offset,
+              db_floor = prm.db.floor_db;
+  const bool log_mel = prm.db.log_mel != 0;
+  float4* s_e4 = reinterpret_cast<float4*>(s_e);
+  const int opitch = M | 1;
+  float* s_o = s_e;
+
+#pragma unroll 1
+  for (int it = 0; tile < prm.n_tiles; ++it, tile += gridDim.x) {
+    float* s_wave = s_a + (it & 1) * kRegionA;
+    {  // next tile's waveform flies while this one is transformed
+      const unsigned nxt = tile + gridDim.x;
+      if (nxt < prm.n_tiles) prefetch_tile(prm, nxt, s_a + ((it & 1) ^ 1) * kRegionA, tid);
+      cp_async_commit();
+    }
+    cp_async_wait<1>();
+    __syncthreads();  // this tile's span (all threads' copies) is in smem; s_e / s_o are free
+    const int64_t b = tile / prm.tiles_per_utt;
+    const int64_t t0 = (int64_t)(tile - b * prm.tiles_per_utt) * kTile;
+
+    // ---- stage 1: unit = residue n2: windowed real DFT20 over n1, twiddle, exchange --------
+    {
+      const int n2 = unit;
+      float wv[20], tw[20];
+      {
+        const float4* w4 = reinterpret_cast<const float4*>(s_tw + n2 * 20);
+        const float4* t4 = reinterpret_cast<const float4*>(s_tt + n2 * 20);
+#pragma unroll
+        for (int q = 0; q < 5; ++q) {
+          const float4 a = w4[q], c = t4[q];
+          wv[4 * q] = a.x; wv[4 * q + 1] = a.y; wv[4 * q + 2] = a.z; wv[4 * q + 3] = a.w;
+          tw[4 * q] = c.x; tw[4 * q + 1] = c.y; tw[4 * q + 2] = c.z; tw[4 * q + 3] = c.w;
+        }
+      }
+      const float* xa = s_wave + p * kPitch + n2;
+      f2 x[20];
+#pragma unroll
+      for (int n1 = 0; n1 < 20; ++n1) {
+        const int off = 20 * n1 + ((20 * n1) / kHop) * kPad;  // n2 < 20 never crosses a hop boundary
+        x[n1] = mk2(xa[off], xa[off + kPairs * kPitch]);
+      }
+      cx<f2> Y[11];
+      rdft20<true>(x, wv, Y);
+      float4* dst = s_e4 + (n2 * 10) * kPairs + p;
+      dst[0] = make_float4(Y[0].re.v.x, Y[0].re.v.y, Y[10].re.v.x, Y[10].re.v.y);
+#pragma unroll
+      for (int k1 = 1; k1 <= 9; ++k1) {
+        const cx<f2> t = cmuls(Y[k1], tw[2 * (k1 - 1)], tw[2 * (k1 - 1) + 1]);
+        dst[k1 * kPairs] = make_float4(t.re.v.x, t.re.v.y, t.im.v.x, t.im.v.y);
+      }
+    }
+    __syncthreads();
+
+    // ---- stage 2: unit = (k1, half): DFT over n2, power -> P[bin][2p .. 2p+1] ---------------
+    float* s_p = s_wave;
+    {
+      float2* prow = reinterpret_cast<float2*>(s_p) + p;  // row stride = 16 float2
+      if (warp != 0) {
+        const int k1 = warp;
+        float tr[10], ti[10];
+        {
+          const float4* c4 = reinterpret_cast<const float4*>(s_t2 + h * 20);
+          float tmp[20];
+#pragma unroll
+          for (int q = 0; q < 5; ++q) {
+            const float4 a = c4[q];
+            tmp[4 * q] = a.x; tmp[4 * q + 1] = a.y; tmp[4 * q + 2] = a.z; tmp[4 * q + 3] = a.w;
+          }
+#pragma unroll
+          for (int n = 0; n < 10; ++n) { tr[n] = tmp[n]; ti[n] = tmp[10 + n]; }
+        }
+        const float sigma = h ? -1.f : 1.f;
+        const float4* src = s_e4 + k1 * kPairs + p;
+        cx<f2> a[20];
+#pragma unroll
+        for (int n2 = 0; n2 < 20; ++n2) {
+          const float4 q = src[n2 * 10 * kPairs];
+          a[n2] = cx<f2>{mk2(q.x, q.y), mk2(q.z, q.w)};
+        }
+        cx<f2> C[10];
+        stage2_half(a, sigma, tr, ti, C);
+        // bin of output j: k = k1 + 20h + 40j, mirrored above 200
+        float2* pr = prow + (k1 + 20 * h) * kPairs;
+#pragma unroll
+        for (int j = 0; j < 10; ++j) {
+          const f2 pw = fmat(C[j].im, C[j].im, f2{__fmul2_rn(C[j].re.v, C[j].re.v)});
+          if (j < 5) pr[40 * j * kPairs] = pw.v;
+        }
+        float2* pm = prow + (kNfft - k1 - 20 * h) * kPairs;
+#pragma unroll
+        for (int j = 5; j < 10; ++j) {
+          const f2 pw = fmat(C[j].im, C[j].im, f2{__fmul2_rn(C[j].re.v, C[j].re.v)});
+          pm[-40 * j * kPairs] = pw.v;
+        }
+      } else {
+        const float4* src = s_e4 + p;
+        f2 y[20];
+#pragma unroll
+        for (int n2 = 0; n2 < 20; ++n2) {
+          const float4 q = src[n2 * 10 * kPairs];
+          y[n2] = h ? mk2(q.z, q.w) : mk2(q.x, q.y);
+        }
+        if (h == 0) {  // k1 = 0: bins 20*k2
+          const float none[20] = {};
+          cx<f2> X[11];
+          rdft20<false>(y, none, X);
+          prow[0] = __fmul2_rn(X[0].re.v, X[0].re.v);
+          prow[200 * kPairs] = __fmul2_rn(X[10].re.v, X[10].re.v);
+#pragma unroll
+          for (int k2 = 1; k2 <= 9; ++k2)
+            prow[20 * k2 * kPairs] =
+                fmat(X[k2].im, X[k2].im, f2{__fmul2_rn(X[k2].re.v, X[k2].re.v)}).v;
+        } else {  // k1 = 10: bins 10 + 20*k2
+          cx<f2> C[10];
+          stage2_k10(y, C);
+#pragma unroll
+          for (int j = 0; j < 10; ++j) {
+            const int bin = j < 5 ? 10 + 40 * j : 390 - 40 * j;
+            prow[bin * kPairs] = fmat(C[j].im, C[j].im, f2{__fmul2_rn(C[j].re.v, C[j].re.v)}).v;
+          }
+        }
+      }
+    }
+    __syncthreads();
+
+    // ---- stage 3: sparse mel projection + dB -> output tile [32][M] in smem -----------------
+    {
+      float vmax0 = -INFINITY, vmax1 = -INFINITY;
+      const float2* pp0 = reinterpret_cast<const float2*>(s_p) + p;
+#pragma unroll 1
+      for (int m = unit; m < M; m += kUnits) {
+        const int2 meta = s_meta[m];
+        const int cnt = meta.x >> 16;
+        const float4* wt = reinterpret_cast<const float4*>(s_w + meta.y);
+        const float2* pp = pp0 + (meta.x & 0xffff) * kPairs;
+        f2 acc = mk2(0.f, 0.f);
+#define SBFE_MEL_GROUP(g)                                                 \
+  {                                                                       \
+    const float4 w4 = wt[g];                                              \
+    acc = fmas(f2{pp[(4 * (g) + 0) * kPairs]}, w4.x, acc);                \
+    acc = fmas(f2{pp[(4 * (g) + 1) * kPairs]}, w4.y, acc);                \
+    acc = fmas(f2{pp[(4 * (g) + 2) * kPairs]}, w4.z, acc);                \
+    acc = fmas(f2{pp[(4 * (g) + 3) * kPairs]}, w4.w, acc);                \
+  }
+        if (cnt > 0) {
+          SBFE_MEL_GROUP(0)
+          if (cnt > 4) {
+            SBFE_MEL_GROUP(1)
+            if (cnt > 8) {
+              SBFE_MEL_GROUP(2)
+              if (cnt > 12) {
+                SBFE_MEL_GROUP(3)
+#pragma unroll 1
+                for (int g = 4; 4 * g < cnt; ++g) SBFE_MEL_GROUP(g)
+              }
+            }
+          }
+        }
+#undef SBFE_MEL_GROUP
+        float v0 = acc.v.x, v1 = acc.v.y;
+        if (log_mel) {
+          v0 = (v0 > db_amin) ? fmaf(fast_log2(v0), db_scale, -db_off) : db_floor;
+          v1 = (v1 > db_amin) ? fmaf(fast_log2(v1), db_scale, -db_off) : db_floor;
+        }
+        s_o[p * opitch + m] = v0;
+        s_o[(p + kPairs) * opitch + m] = v1;
+        vmax0 = fmaxf(vmax0, v0);
+        vmax1 = fmaxf(vmax1, v1);
+      }
+      if (prm.utt_max != nullptr) {
+        float vmax = fmaxf((t0 + p) < prm.T ? vmax0 : -INFINITY,
+                           (t0 + p + kPairs) < prm.T ? vmax1 : -INFINITY);
+        vmax = warp_max(vmax);
+        if (lane == 0 && vmax > -INFINITY) atomicMax(prm.utt_max + b, max_key_encode(vmax));
+      }
+    }
+    __syncthreads();
+
+    // ---- stage 4: coalesced store of the valid part of the tile ---------------------------------
+    {
+      const int64_t left = prm.T - t0;
+      const int nvalid = left < kTile ? (int)left : kTile;
+      float* o = prm.out + (b * prm.T + t0) * M;
+      const int total = nvalid * M;
+      if ((M & 3) == 0 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+        int e = tid * 4;
+        int t = e / M, m = e - t * M;
+        const int dt = (kThreads * 4) / M, dm = (kThreads * 4) - dt * M;
+        for (; e < total; e += kThreads * 4) {
+          const float* s = s_o + t * opitch + m;
+          *reinterpret_cast<float4*>(o + e) = make_float4(s[0], s[1], s[2], s[3]);
+          t += dt;
+          m += dm;
+          if (m >= M) { m -= M; ++t; }
+        }
+      } else {
+        int e = tid;
+        int t = e / M, m = e - t * M;
+        const int dt = kThreads / M, dm = kThreads - dt * M;
+        for (; e < total; e += kThreads) {
+          o[e] = s_o[t * opitch + m];
+          t += dt;
+          m += dm;
+          if (m >= M) { m -= M; ++t; }
+        }
+      }
+    }
+    // the barrier at the top of the next iteration orders these s_o reads before its stage 1
+  }
+  cp_async_wait<0>();
+}
+
+constexpr int kMaxSmem = 110 * 1024;  // two CTAs per SM
+
+}  // namespace v3
+
+// hop 160, filter tables in the padded layout (every filter's weights start at a multiple
+// of 4 and are zero-padded to a multiple of 4), everything fits in half an SM's smem
+bool fbank400_v3_supported(const sbfe_fbank_desc* d) {
+  return d->n_fft == 400 && d->hop == v3::kHop && d->mel_pad4 == 1 && d->n_mels >= 1 &&
+         d->n_mels <= 1024 && d->mel_nnz >= 0 &&
+         v3::smem_floats(d->n_mels, d->mel_nnz) * sizeof(float) <= (size_t)v3::kMaxSmem;
+}
+
+int launch_fbank400_v3(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64_t L,
+                       int64_t wav_stride, float* out, sbfe_maxkey_t* utt_max, cudaStream_t stream) {
+  using namespace v3;
+  Params prm;
+  prm.db = DbParams{d->multiplier * 0.30102999566398120f, d->amin, d->db_offset, d->floor_db,
+                    d->log_mel};
+  prm.n_mels = d->n_mels;
+  prm.mel_nnz = d->mel_nnz;
+  prm.L = L;
+  prm.wav_stride = wav_stride;
+  prm.T = 1 + L / kHop;
+  prm.wav = wav;
+  prm.window = d->d_window;
+  prm.out = out;
+  prm.utt_max = utt_max;
+  prm.mel_start = d->d_mel_start;
+  prm.mel_count = d->d_mel_count;
+  prm.mel_offset = d->d_mel_offset;
+  prm.mel_weight = d->d_mel_weight;
+  const int64_t tiles = (prm.T + kTile - 1) / kTile;
+  if (tiles * B > 0x7fffffff) return SBFE_E_TOOBIG;
+  prm.tiles_per_utt = (unsigned)tiles;
+  prm.n_tiles = (unsigned)(tiles * B);
+  const size_t smem = smem_floats(d->n_mels, d->mel_nnz) * sizeof(float);
+  static int n_sm[64] = {};  // per device; also marks "attribute set" (a duplicate set is harmless)
+  int dev = 0;
+  cudaGetDevice(&dev);
+  int sms = (dev >= 0 && dev < 64) ? n_sm[dev] : 0;
+  if (sms == 0) {
+    cudaError_t e = cudaFuncSetAttribute(fbank400_v3_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev >= 0 && dev < 64) n_sm[dev] = sms;
+  }
+  // persistent: two CTAs per SM, each strides over the tiles
+  const unsigned grid = prm.n_tiles < (unsigned)(2 * sms) ? prm.n_tiles : (unsigned)(2 * sms);
+  fbank400_v3_kernel<<<grid, kThreads, smem, stream>>>(prm);
+  return check_last();
+}
+
+}  // namespace sbfe

@@ -84,7 +84,7 @@ class FrontendTables:
         if mat.shape[0] != self.bins:
             raise ValueError("filterbank matrix has %d rows, expected %d" % (mat.shape[0], self.bins))
         self.n_mels = int(mat.shape[1])
-        start, count, offset, weights = [], [], [], []
+        start, count, offset, weights, fill = [], [], [], [], 0
         for m in range(self.n_mels):
             col = mat[:, m]
             nz = torch.nonzero(col).flatten()
@@ -94,12 +94,15 @@ class FrontendTables:
                 s, c = int(nz[0]), int(nz[-1]) - int(nz[0]) + 1
             start.append(s)
             count.append(c)
-            offset.append(sum(count[:-1]))
-            weights.append(col[s:s + c])
-        w = torch.cat(weights) if weights and sum(count) else torch.zeros(1)
+            offset.append(fill)
+            # padded layout (sbfe_fbank_desc.mel_pad4): zeros up to a multiple of 4 entries
+            pad = (-c) % 4
+            weights.append(torch.cat([col[s:s + c], torch.zeros(pad)]))
+            fill += c + pad
+        w = torch.cat(weights) if weights and fill else torch.zeros(4)
         self._h_mel = (torch.tensor(start, dtype=torch.int32), torch.tensor(count, dtype=torch.int32),
                        torch.tensor(offset, dtype=torch.int32), w.contiguous())
-        self.nnz = int(sum(count))
+        self.nnz = int(fill)
 
     def on(self, device):
         key = (device.type, device.index)
@@ -120,6 +123,7 @@ class FrontendTables:
             desc.d_mel_start, desc.d_mel_count = dev[0].data_ptr(), dev[1].data_ptr()
             desc.d_mel_offset, desc.d_mel_weight = dev[2].data_ptr(), dev[3].data_ptr()
             desc.mel_nnz = self.nnz
+            desc.mel_pad4 = 1
         entry = (desc, keep)
         self._dev[key] = entry
         return entry

@@ -21,7 +21,7 @@ def test_library_exports_every_declared_symbol():
     assert declared and declared == set(_lib.SIGNATURES)
     for name in declared:
         assert getattr(handle, name) is not None
-    assert handle.sbfe_abi_version() == 1
+    assert handle.sbfe_abi_version() == 2
     assert handle.sbfe_num_frames(16000, 160) == 101
     assert handle.sbfe_error_string(-1).decode().startswith("sbfe")
 
@@ -39,7 +39,7 @@ def test_library_is_sm100a_and_has_no_oracle_dependency():
 
 
 def test_host_codelets_match_naive_dft(tmp_path):
-    for name in ("codelet_check", "frame400_check"):
+    for name in ("codelet_check", "frame400_check", "frame400_v3_check"):
         exe = tmp_path / name
         subprocess.run(["g++", "-O2", "-o", str(exe), os.path.join(ROOT, "tests", "host", name + ".cpp")],
                        check=True)
@@ -56,9 +56,12 @@ def test_host_tables_match_reference_constants(golden):
     assert np.array_equal(fb.compute_fbanks.band.numpy(), golden[f"{name}/band"])
     assert np.array_equal(fb.compute_STFT.window.numpy(), golden[f"{name}/window"])
     tab = fb._frontend_tables()
-    assert tab.nnz == 387 and tab.n_mels == 80  # 387 non-zeros for 80 mels
     dense = fb.compute_fbanks.fbank_matrix()
     start, count, offset, w = tab._h_mel
+    assert int(count.sum()) == 387 and tab.n_mels == 80  # 387 non-zeros for 80 mels
+    # padded layout of sbfe_fbank_desc.mel_pad4: offsets multiples of 4, zero fill
+    assert all(int(o) % 4 == 0 for o in offset) and tab.nnz == w.numel() and tab.nnz % 4 == 0
+    assert int(torch.count_nonzero(w)) == 387
     rebuilt = torch.zeros_like(dense)
     for m in range(80):
         s, c, o = int(start[m]), int(count[m]), int(offset[m])
