@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define SBFE_ABI_VERSION 2
+#define SBFE_ABI_VERSION 3
 
 #if defined(__GNUC__)
 #define SBFE_API __attribute__((visibility("default")))
@@ -86,7 +86,28 @@ SBFE_API int64_t sbfe_fbank_workspace_bytes(const sbfe_fbank_desc* desc, int64_t
  * receives the key of max_{t,m} out[b] (must be zeroed by the caller first). */
 SBFE_API int sbfe_fbank_forward(const sbfe_fbank_desc* desc, const float* d_wav, int64_t B, int64_t L,
                        int64_t wav_stride, float* d_out, sbfe_maxkey_t* d_utt_max,
-                       void* d_workspace, int64_t workspace_bytes, void* stream);
+                       float* d_tile_stats, void* d_workspace, int64_t workspace_bytes,
+                       void* stream);
+
+/* Per-tile column statistics.  When sbfe_fbank_tile_frames(desc) = R > 0 (fused n_fft 400 /
+ * hop 160 kernel), sbfe_fbank_forward can also write d_tile_stats
+ * [B][ceil(T/R)][3][M] = {mean, M2 = sum of squared deviations, min} of every feature column
+ * over the frames of each R-frame tile (un-clamped values; pass NULL to skip).  They let
+ *   sbfe_clamp_tiles       apply the top_db clamp (features.py:706-710) in place, touching
+ *                          only tiles that hold a value below the floor, and
+ *   sbfe_norm_stats_tiles  produce the InputNormalization statistics (features.py:1020-1031,
+ *                          1120-1145; same contract as sbfe_norm_stats) without a pass over x:
+ *                          only tiles cut by the valid length or holding clamped values are
+ *                          re-read. */
+SBFE_API int32_t sbfe_fbank_tile_frames(const sbfe_fbank_desc* desc);
+SBFE_API int sbfe_clamp_tiles(float* d_x, int64_t B, int64_t T, int32_t F,
+                     const sbfe_maxkey_t* d_utt_max, float top_db, const float* d_tile_stats,
+                     int32_t tile_frames, void* stream);
+SBFE_API int sbfe_norm_stats_tiles(const float* d_x, const float* d_lengths, int64_t B, int64_t T,
+                          int32_t F, int32_t mean_norm, int32_t std_norm, float eps,
+                          const sbfe_maxkey_t* d_utt_max, float top_db,
+                          const float* d_tile_stats, int32_t tile_frames, float* d_mean,
+                          float* d_std, void* stream);
 
 /* STFT.forward for [B, L] input (processing/features.py:133-188):
  * out [B, T, bins, 2] (re, im), or, with power_only != 0, [B, T, bins] = re^2+im^2. */

@@ -48,7 +48,11 @@ SIGNATURES = {
     "sbfe_error_string": (C.c_char_p, [C.c_int]),
     "sbfe_num_frames": (_I64, [_I64, _I32]),
     "sbfe_fbank_workspace_bytes": (_I64, [_DESC, _I64, _I64]),
-    "sbfe_fbank_forward": (C.c_int, [_DESC, _P, _I64, _I64, _I64, _P, _P, _P, _I64, _P]),
+    "sbfe_fbank_forward": (C.c_int, [_DESC, _P, _I64, _I64, _I64, _P, _P, _P, _P, _I64, _P]),
+    "sbfe_fbank_tile_frames": (_I32, [_DESC]),
+    "sbfe_clamp_tiles": (C.c_int, [_P, _I64, _I64, _I32, _P, _F, _P, _I32, _P]),
+    "sbfe_norm_stats_tiles": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, _I32, _F, _P, _F, _P, _I32,
+                                        _P, _P, _P]),
     "sbfe_stft_forward": (C.c_int, [_DESC, _P, _I64, _I64, _I64, _P, _I32, _P]),
     "sbfe_spectral_magnitude": (C.c_int, [_P, _I64, _F, _I32, _F, _P, _P]),
     "sbfe_filterbank_forward": (C.c_int, [_DESC, _P, _I64, _I64, _P, _P, _P]),
@@ -94,7 +98,7 @@ def lib():
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(handle, name)
             fn.restype, fn.argtypes = res, args
-        if handle.sbfe_abi_version() != 2:
+        if handle.sbfe_abi_version() != 3:
             raise SbfeUnavailable("libsbfe.so ABI version mismatch")
         _lib = handle
         return _lib

@@ -7,7 +7,12 @@ namespace sbfe {
 int launch_fbank400(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
                     sbfe_maxkey_t*, cudaStream_t);
 int launch_fbank400_v3(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
-                       sbfe_maxkey_t*, cudaStream_t);
+                       sbfe_maxkey_t*, float*, cudaStream_t);
+int launch_clamp_tiles(float*, int64_t, int64_t, int, const sbfe_maxkey_t*, float, const float*, int,
+                       cudaStream_t);
+int launch_norm_stats_tiles(const float*, const float*, int64_t, int64_t, int, int, int, float,
+                            const sbfe_maxkey_t*, float, const float*, int, float*, float*,
+                            cudaStream_t);
 int launch_stft_generic(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
                         int, cudaStream_t);
 int launch_spectral_magnitude(const float*, int64_t, float, int, float, float*, cudaStream_t);
@@ -65,15 +70,20 @@ int64_t sbfe_fbank_workspace_bytes(const sbfe_fbank_desc* d, int64_t B, int64_t 
   return B * (1 + L / d->hop) * (int64_t)(d->n_fft / 2 + 1) * (int64_t)sizeof(float);
 }
 
+int32_t sbfe_fbank_tile_frames(const sbfe_fbank_desc* d) {
+  return (d && desc_ok(d, true) && fbank400_v3_supported(d)) ? 32 : 0;
+}
+
 int sbfe_fbank_forward(const sbfe_fbank_desc* d, const float* d_wav, int64_t B, int64_t L,
-                       int64_t wav_stride, float* d_out, sbfe_maxkey_t* d_utt_max, void* d_ws,
-                       int64_t ws_bytes, void* stream) {
+                       int64_t wav_stride, float* d_out, sbfe_maxkey_t* d_utt_max,
+                       float* d_tile_stats, void* d_ws, int64_t ws_bytes, void* stream) {
   if (!desc_ok(d, true) || B < 0 || L < 0 || wav_stride < L) return SBFE_E_INVAL;
   if (B == 0) return 0;
   if ((!d_wav && L > 0) || !d_out) return SBFE_E_INVAL;
   cudaStream_t s = (cudaStream_t)stream;
   if (fbank400_v3_supported(d))
-    return launch_fbank400_v3(d, d_wav, B, L, wav_stride, d_out, d_utt_max, s);
+    return launch_fbank400_v3(d, d_wav, B, L, wav_stride, d_out, d_utt_max, d_tile_stats, s);
+  if (d_tile_stats) return SBFE_E_INVAL;  // only where sbfe_fbank_tile_frames() != 0
   if (fused_ok(d)) return launch_fbank400(d, d_wav, B, L, wav_stride, d_out, d_utt_max, s);
   if (!d_ws || ws_bytes < sbfe_fbank_workspace_bytes(d, B, L)) return SBFE_E_NOSPACE;
   int rc = launch_stft_generic(d, d_wav, B, L, wav_stride, (float*)d_ws, 1, s);
@@ -115,6 +125,27 @@ int sbfe_post_forward(const float* d_x, int64_t B, int64_t T, int32_t F_in,
   if (!d_x || !d_out) return SBFE_E_INVAL;
   return launch_post(d_x, B, T, F_in, d_utt_max, top_db, d_dct, n_dct, deltas, delta_window,
                      context, left, right, d_out, (cudaStream_t)stream);
+}
+
+int sbfe_clamp_tiles(float* d_x, int64_t B, int64_t T, int32_t F, const sbfe_maxkey_t* d_utt_max,
+                     float top_db, const float* d_tile_stats, int32_t tile_frames, void* stream) {
+  if (B < 0 || T < 0 || F < 0 || tile_frames < 1) return SBFE_E_INVAL;
+  if (B == 0 || T == 0 || F == 0) return 0;
+  if (!d_x || !d_utt_max || !d_tile_stats) return SBFE_E_INVAL;
+  return launch_clamp_tiles(d_x, B, T, F, d_utt_max, top_db, d_tile_stats, tile_frames,
+                            (cudaStream_t)stream);
+}
+
+int sbfe_norm_stats_tiles(const float* d_x, const float* d_lengths, int64_t B, int64_t T, int32_t F,
+                          int32_t mean_norm, int32_t std_norm, float eps,
+                          const sbfe_maxkey_t* d_utt_max, float top_db, const float* d_tile_stats,
+                          int32_t tile_frames, float* d_mean, float* d_std, void* stream) {
+  if (B < 0 || T < 0 || F < 0 || tile_frames < 1) return SBFE_E_INVAL;
+  if (B == 0 || F == 0) return 0;
+  if (!d_x || !d_lengths || !d_mean || !d_std || !d_tile_stats) return SBFE_E_INVAL;
+  return launch_norm_stats_tiles(d_x, d_lengths, B, T, F, mean_norm, std_norm, eps, d_utt_max,
+                                 top_db, d_tile_stats, tile_frames, d_mean, d_std,
+                                 (cudaStream_t)stream);
 }
 
 int64_t sbfe_norm_workspace_bytes(int64_t B, int64_t T, int32_t F) {

@@ -58,6 +58,7 @@ struct Params {
   const float* window;     // device, [400], zero-padded / centred to n_fft
   float* out;
   sbfe_maxkey_t* utt_max;
+  float* tile_stats;       // optional [n_tiles][3][M]: mean, M2, min of every column of the tile
   const int32_t* mel_start;
   const int32_t* mel_count;
   const int32_t* mel_offset;
@@ -356,6 +357,35 @@ __global__ void __launch_bounds__(kThreads, 2) fbank400_v3_kernel(const __grid_c
         }
       }
     }
+    // ---- per-tile column statistics (un-clamped values) for InputNormalization --------------------
+    // mean / M2 (sum of squared deviations) / min over the tile's existing frames, so that the
+    // normalisation needs no second pass over the features (norm.cu: norm_stats_tiles_kernel)
+    if (prm.tile_stats != nullptr) {
+      const int64_t left = prm.T - t0;
+      const int nvalid = left < kTile ? (int)left : kTile;
+      float* ts = prm.tile_stats + (size_t)tile * 3 * M;
+      for (int m = tid; m < M; m += kThreads) {
+        const float* col = s_o + m;
+        const float x0 = col[0];
+        float s1a = 0.f, s1b = 0.f, s2a = 0.f, s2b = 0.f, mna = x0, mnb = x0;
+        int r = 1;
+        for (; r + 1 < nvalid; r += 2) {
+          const float va = col[r * opitch], vb = col[(r + 1) * opitch];
+          const float da = va - x0, db = vb - x0;
+          s1a += da; s1b += db;
+          s2a = fmaf(da, da, s2a); s2b = fmaf(db, db, s2b);
+          mna = fminf(mna, va); mnb = fminf(mnb, vb);
+        }
+        if (r < nvalid) {
+          const float va = col[r * opitch], da = va - x0;
+          s1a += da; s2a = fmaf(da, da, s2a); mna = fminf(mna, va);
+        }
+        const float s1 = s1a + s1b, s2 = s2a + s2b, inv = 1.f / (float)nvalid;
+        ts[m] = fmaf(s1, inv, x0);
+        ts[M + m] = fmaxf(fmaf(-s1 * inv, s1, s2), 0.f);
+        ts[2 * M + m] = fminf(mna, mnb);
+      }
+    }
     // the barrier at the top of the next iteration orders these s_o reads before its stage 1
   }
   cp_async_wait<0>();
@@ -374,7 +404,8 @@ bool fbank400_v3_supported(const sbfe_fbank_desc* d) {
 }
 
 int launch_fbank400_v3(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64_t L,
-                       int64_t wav_stride, float* out, sbfe_maxkey_t* utt_max, cudaStream_t stream) {
+                       int64_t wav_stride, float* out, sbfe_maxkey_t* utt_max, float* tile_stats,
+                       cudaStream_t stream) {
   using namespace v3;
   Params prm;
   prm.db = DbParams{d->multiplier * 0.30102999566398120f, d->amin, d->db_offset, d->floor_db,
@@ -388,6 +419,7 @@ int launch_fbank400_v3(const sbfe_fbank_desc* d, const float* wav, int64_t B, in
   prm.window = d->d_window;
   prm.out = out;
   prm.utt_max = utt_max;
+  prm.tile_stats = tile_stats;
   prm.mel_start = d->d_mel_start;
   prm.mel_count = d->d_mel_count;
   prm.mel_offset = d->d_mel_offset;

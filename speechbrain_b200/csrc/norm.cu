@@ -90,6 +90,84 @@ __global__ void norm_stats_final_kernel(const float* __restrict__ x,
   stdv[i] = std_norm ? sd : 1.f;
 }
 
+// ---- statistics from the per-tile column partials of the fused Fbank kernel ---------------
+// tile_stats [B][tiles][3][F] = mean, M2, min of every column over the tile's existing
+// frames (UN-clamped values).  A tile's partial is used as is when all of its frames are
+// inside the utterance's valid length and nothing in that column is below the top_db
+// floor; otherwise (at most the one tile straddling n_b, plus tiles with clamped values)
+// the column is recomputed from x.  Partials are merged with Chan's update in double.
+struct Moments {
+  double n, mean, m2;
+};
+__device__ __forceinline__ void merge(Moments& a, double nb, double mb, double m2b) {
+  if (nb <= 0.0) return;
+  const double n = a.n + nb, d = mb - a.mean;
+  a.mean += d * (nb / n);
+  a.m2 += m2b + d * d * (a.n * nb / n);
+  a.n = n;
+}
+
+constexpr int kTileStatCols = 32;    // feature columns per CTA (one 128-byte row segment)
+constexpr int kTileStatGroups = 8;   // tile groups per CTA
+constexpr int kTileStatThreads = kTileStatCols * kTileStatGroups;
+
+// grid = (ceil(F / 32), B); thread = (column, tile group)
+__global__ void __launch_bounds__(kTileStatThreads)
+norm_stats_tiles_kernel(const float* __restrict__ x, const float* __restrict__ lengths, int64_t T,
+                        int F, int tile, int tiles, const float* __restrict__ tile_stats,
+                        const sbfe_maxkey_t* __restrict__ utt_max, float top_db, int mean_norm,
+                        int std_norm, float eps, float* __restrict__ mean, float* __restrict__ stdv) {
+  __shared__ double s_red[3 * kTileStatThreads];
+  const int64_t b = blockIdx.y;
+  const int n = valid_frames(lengths, b, T);
+  const float floor_b = clamp_floor(utt_max, b, top_db);
+  const int tx = threadIdx.x % kTileStatCols, ty = threadIdx.x / kTileStatCols;
+  const int f = blockIdx.x * kTileStatCols + tx;
+  const float* xb = x + b * T * F;
+  const float* tsb = tile_stats + (size_t)b * tiles * 3 * F;
+  Moments acc{0.0, 0.0, 0.0};
+  if (f < F) {
+    const int used = (n + tile - 1) / tile;  // tiles holding at least one valid frame
+    for (int j = ty; j < used; j += kTileStatGroups) {
+      const int r_lo = j * tile;
+      const int64_t exist = T - r_lo < tile ? T - r_lo : tile;
+      const int cnt = n - r_lo < exist ? n - r_lo : (int)exist;
+      const float* ts = tsb + (size_t)j * 3 * F + f;
+      const float t_mean = __ldg(ts), t_m2 = __ldg(ts + F), t_min = __ldg(ts + 2 * F);
+      if (cnt == exist && t_min >= floor_b) {
+        merge(acc, (double)cnt, (double)t_mean, (double)t_m2);
+      } else {
+        const float* col = xb + (int64_t)r_lo * F + f;
+        float s = 0.f;  // <= 32 values of similar magnitude: float sums are exact enough
+        for (int r = 0; r < cnt; ++r) s += fmaxf(__ldg(col + (int64_t)r * F), floor_b);
+        const float m = s / (float)cnt;
+        float q = 0.f;
+        for (int r = 0; r < cnt; ++r) {
+          const float d = fmaxf(__ldg(col + (int64_t)r * F), floor_b) - m;
+          q = fmaf(d, d, q);
+        }
+        merge(acc, (double)cnt, (double)m, (double)q);
+      }
+    }
+  }
+  s_red[threadIdx.x] = acc.n;
+  s_red[kTileStatThreads + threadIdx.x] = acc.mean;
+  s_red[2 * kTileStatThreads + threadIdx.x] = acc.m2;
+  __syncthreads();
+  if (ty == 0 && f < F) {
+    for (int r = 1; r < kTileStatGroups; ++r)
+      merge(acc, s_red[r * kTileStatCols + tx], s_red[kTileStatThreads + r * kTileStatCols + tx],
+            s_red[2 * kTileStatThreads + r * kTileStatCols + tx]);
+    // n == 0: mean of an empty slice is NaN, n == 1: unbiased std is NaN (torch)
+    const double m = (acc.n > 0.0) ? acc.mean : (double)NAN;
+    const double var = (acc.n > 1.0) ? acc.m2 / (acc.n - 1.0) : (double)NAN;
+    float sd = (float)sqrt(var < 0.0 ? 0.0 : var);
+    if (sd == sd) sd = fmaxf(sd, eps);  // torch.max propagates NaN
+    mean[b * F + f] = mean_norm ? (float)m : 0.f;
+    stdv[b * F + f] = std_norm ? sd : 1.f;
+  }
+}
+
 __global__ void norm_reduce_kernel(const float* __restrict__ mean, const float* __restrict__ stdv,
                                    int64_t B, int F, float* __restrict__ cur) {
   const int f = blockIdx.x * blockDim.x + threadIdx.x;
@@ -190,6 +268,21 @@ int launch_norm_stats(const float* x, const float* lengths, int64_t B, int64_t T
   norm_stats_final_kernel<<<(unsigned)((B * F + 255) / 256), 256, 0, stream>>>(
       x, lengths, B, T, F, mean_norm, std_norm, eps, utt_max, top_db, (const double2*)ws,
       (unsigned)chunks, mean, stdv);
+  return check_last();
+}
+
+int launch_norm_stats_tiles(const float* x, const float* lengths, int64_t B, int64_t T, int F,
+                            int mean_norm, int std_norm, float eps, const sbfe_maxkey_t* utt_max,
+                            float top_db, const float* tile_stats, int tile, float* mean,
+                            float* stdv, cudaStream_t stream) {
+  if (B == 0 || F == 0) return 0;
+  if (B > 0x7fffffff || T > 0x7fffffff) return SBFE_E_TOOBIG;
+  const int tiles = (int)((T + tile - 1) / tile);
+  if (B > 65535) return SBFE_E_TOOBIG;
+  const dim3 grid((unsigned)((F + kTileStatCols - 1) / kTileStatCols), (unsigned)B);
+  norm_stats_tiles_kernel<<<grid, kTileStatThreads, 0, stream>>>(
+      x, lengths, T, F, tile, tiles, tile_stats, utt_max, top_db, mean_norm, std_norm, eps, mean,
+      stdv);
   return check_last();
 }
 

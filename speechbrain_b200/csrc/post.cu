@@ -38,6 +38,37 @@ __global__ void clamp_kernel(const float* __restrict__ x, int64_t per_utt,
   }
 }
 
+// ---- tile-aware clamp: only tiles that hold a value below the floor are touched -----------
+// (tile_stats from the fused Fbank kernel: [B][tiles][3][F], plane 2 = column minima)
+constexpr int kClampTileThreads = 128;
+__global__ void __launch_bounds__(kClampTileThreads)
+clamp_tiles_kernel(float* __restrict__ x, int64_t T, int F, int tile, unsigned tiles,
+                   const sbfe_maxkey_t* __restrict__ utt_max, float top_db,
+                   const float* __restrict__ tile_stats) {
+  const int64_t b = blockIdx.x / tiles;
+  const int j = blockIdx.x - b * tiles;
+  const float floor_b = clamp_floor(utt_max, b, top_db);
+  const float* mn = tile_stats + ((size_t)blockIdx.x * 3 + 2) * F;
+  int below = 0;
+  for (int f = threadIdx.x; f < F; f += kClampTileThreads) below |= (__ldg(mn + f) < floor_b);
+  if (!__syncthreads_or(below)) return;
+  const int64_t r_lo = (int64_t)j * tile;
+  const int64_t rows = T - r_lo < tile ? T - r_lo : tile;
+  float* p = x + (b * T + r_lo) * F;
+  const int64_t n = rows * F;
+  for (int64_t i = threadIdx.x; i < n; i += kClampTileThreads) p[i] = fmaxf(p[i], floor_b);
+}
+
+int launch_clamp_tiles(float* x, int64_t B, int64_t T, int F, const sbfe_maxkey_t* utt_max,
+                       float top_db, const float* tile_stats, int tile, cudaStream_t stream) {
+  if (B == 0 || T == 0 || F == 0) return 0;
+  const int64_t tiles = (T + tile - 1) / tile;
+  if (tiles * B > 0x7fffffff) return SBFE_E_TOOBIG;
+  clamp_tiles_kernel<<<(unsigned)(tiles * B), kClampTileThreads, 0, stream>>>(
+      x, T, F, tile, (unsigned)tiles, utt_max, top_db, tile_stats);
+  return check_last();
+}
+
 struct PostParams {
   const float* x;
   float* out;

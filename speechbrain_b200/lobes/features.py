@@ -59,8 +59,19 @@ class _Lobe(torch.nn.Module):
                 "speechbrain_b200 Fbank/MFCC take [batch, time] waveforms (for multi-channel "
                 "input the reference sums over the channel axis, lobes/features.py:138-139)")
         fb = self.compute_fbanks
-        feats, utt_max = ops.fbank_forward(self._frontend_tables(), wav)
         ctx = self.context and self.context_window.context_len > 1
+        if dct is None and not self.deltas and not ctx and fb.log_mel:
+            # plain log-mel: the fused kernel also emits per-tile column statistics; the clamp
+            # then only touches tiles that need it and a following InputNormalization gets its
+            # statistics without another pass (handed over on the returned tensor)
+            feats, utt_max, ts = ops.fbank_forward(self._frontend_tables(), wav, tile_stats=True)
+            if ts is not None:
+                ops.clamp_tiles(feats, ts, fb.top_db)
+                ts.version = feats._version
+                feats._sbfe_tile_stats = ts
+                return feats
+        else:
+            feats, utt_max = ops.fbank_forward(self._frontend_tables(), wav)
         return ops.post_forward(
             feats, utt_max if fb.log_mel else None, fb.top_db,
             dct=dct, deltas=1 if self.deltas else 0,

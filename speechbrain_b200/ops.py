@@ -13,7 +13,7 @@ from ._lib import FbankDesc, check, lib
 
 __all__ = [
     "FrontendTables", "fbank_forward", "stft_forward", "spectral_magnitude",
-    "filterbank_forward", "post_forward", "norm_stats", "norm_reduce", "norm_update",
+    "filterbank_forward", "post_forward", "norm_stats", "norm_stats_tiles", "clamp_tiles", "TileStats", "norm_reduce", "norm_update",
     "norm_apply", "decode_utt_max",
 ]
 
@@ -136,9 +136,20 @@ def _wav2d(wav):
     return wav
 
 
-def fbank_forward(tables, wav):
+class TileStats:
+    """Per-tile column statistics emitted by the fused Fbank kernel (include/sbfe.h:
+    sbfe_fbank_tile_frames) plus what is needed to use them later."""
+
+    __slots__ = ("stats", "frames", "utt_max", "top_db", "version")
+
+    def __init__(self, stats, frames, utt_max, top_db):
+        self.stats, self.frames, self.utt_max, self.top_db = stats, frames, utt_max, top_db
+        self.version = None
+
+
+def fbank_forward(tables, wav, tile_stats=False):
     """wav [B, L] -> (dB or linear mel [B, T, M] WITHOUT the top_db clamp,
-    utt_max keys [B] int32).  sbfe_fbank_forward."""
+    utt_max keys [B] int32[, TileStats or None]).  sbfe_fbank_forward."""
     wav = _wav2d(wav)
     B, L = wav.shape
     T = 1 + L // tables.hop
@@ -148,10 +159,42 @@ def fbank_forward(tables, wav):
     L_ = lib()
     ws_bytes = L_.sbfe_fbank_workspace_bytes(C.byref(desc), B, L)
     ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=wav.device) if ws_bytes > 0 else None
+    ts, frames = None, 0
+    if tile_stats and B > 0:
+        frames = int(L_.sbfe_fbank_tile_frames(C.byref(desc)))
+        if frames > 0:
+            ts = torch.empty((B, (T + frames - 1) // frames, 3, tables.n_mels),
+                             dtype=torch.float32, device=wav.device)
     with torch.cuda.device(wav.device):
         check(L_.sbfe_fbank_forward(C.byref(desc), _ptr(wav), B, L, L, _ptr(out),
-                                    _ptr(utt_max), _ptr(ws), max(ws_bytes, 0), _stream()))
+                                    _ptr(utt_max), _ptr(ts), _ptr(ws), max(ws_bytes, 0), _stream()))
+    if tile_stats:
+        return out, utt_max, (TileStats(ts, frames, utt_max, 0.0) if ts is not None else None)
     return out, utt_max
+
+
+def clamp_tiles(x, ts, top_db):
+    """In-place top_db clamp that only touches tiles holding a value below the floor."""
+    B, T, F = x.shape
+    with torch.cuda.device(x.device):
+        check(lib().sbfe_clamp_tiles(_ptr(x), B, T, F, _ptr(ts.utt_max), float(top_db),
+                                     _ptr(ts.stats), ts.frames, _stream()))
+    ts.top_db = float(top_db)
+    return x
+
+
+def norm_stats_tiles(x, lengths, ts, mean_norm=True, std_norm=True, eps=1e-10):
+    """norm_stats from the fused kernel's tile partials (no pass over x)."""
+    B, T, F = x.shape
+    lengths = lengths.to(device=x.device, dtype=torch.float32).contiguous()
+    mean = torch.empty((B, F), dtype=torch.float32, device=x.device)
+    std = torch.empty((B, F), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        check(lib().sbfe_norm_stats_tiles(_ptr(x), _ptr(lengths), B, T, F, int(bool(mean_norm)),
+                                          int(bool(std_norm)), float(eps), _ptr(ts.utt_max),
+                                          float(ts.top_db), _ptr(ts.stats), ts.frames, _ptr(mean),
+                                          _ptr(std), _stream()))
+    return mean, std
 
 
 def stft_forward(tables, wav, power_only=False):

@@ -67,7 +67,15 @@ class InputNormalization(torch.nn.Module):
             x = x.float().contiguous()
         ops._require_cuda(x, "x")
         B, T, F = x.shape
-        mean, std = ops.norm_stats(x, lengths, self.mean_norm, self.std_norm, self.eps)
+        ts = getattr(x, "_sbfe_tile_stats", None)
+        if ts is not None:  # one-shot hand-over from the fused Fbank kernel (lobes/features.py)
+            x._sbfe_tile_stats = None
+            if ts.version != x._version or tuple(ts.stats.shape[::3]) != (B, F):
+                ts = None
+        if ts is not None:
+            mean, std = ops.norm_stats_tiles(x, lengths, ts, self.mean_norm, self.std_norm, self.eps)
+        else:
+            mean, std = ops.norm_stats(x, lengths, self.mean_norm, self.std_norm, self.eps)
 
         if self.norm_type == "sentence":
             return ops.norm_apply(x, mean, std, per_utt=True, out=x)  # in place (:1035)

@@ -202,3 +202,36 @@ def test_full_size_properties(sb, B, L, kw):
     keep = (a > floor) & (b_ > floor)
     assert torch.equal(a[keep], b_[keep])
     assert (full.amax(dim=(1, 2)) - full.amin(dim=(1, 2)) <= 80.0 + 1e-4).all()
+
+
+def test_tile_stats_path_matches_generic_kernels(sb):
+    """Fused-kernel tile statistics + tile-aware clamp == the generic clamp / stats kernels,
+    with silence tails (values at the top_db floor), an all-zero utterance and valid lengths
+    that cut tiles."""
+    from speechbrain_b200 import ops
+
+    rng = np.random.default_rng(5)
+    wav = (rng.standard_normal((6, 3 * 16000 + 77)) * 0.1).astype(np.float32)
+    wav[1, 30000:] = 0
+    wav[2, 100:] = 0
+    wav[3, :] = 0
+    wav[4, 20000:20800] *= 1e-5
+    x = dev(wav)
+    fb = sb.Fbank(n_mels=80)
+    feats = fb(x)
+    ts = getattr(feats, "_sbfe_tile_stats", None)
+    assert ts is not None and ts.frames == 32
+    raw, utt_max = ops.fbank_forward(fb._frontend_tables(), x)
+    ref = ops.post_forward(raw, utt_max, 80.0)
+    assert torch.equal(feats, ref)
+    lens = torch.tensor([1.0, 0.73, 0.5, 0.051, 1.0, 0.9]).cuda()
+    m1, s1 = ops.norm_stats_tiles(feats, lens, ts)
+    m2, s2 = ops.norm_stats(feats, lens)
+    assert torch.allclose(m1, m2, rtol=1e-5, atol=2e-5), float((m1 - m2).abs().max())
+    assert torch.allclose(s1, s2, rtol=2e-5, atol=2e-5), float((s1 - s2).abs().max())
+    # the hand-over is one-shot and version-checked
+    norm = sb.InputNormalization(norm_type="sentence")
+    want = (feats - m2[:, None, :]) / s2[:, None, :]
+    got = norm(feats, lens)
+    assert getattr(got, "_sbfe_tile_stats", None) is None
+    assert torch.allclose(got, want, rtol=1e-4, atol=1e-4)
