@@ -87,25 +87,37 @@ __device__ __forceinline__ void cp_async_wait() {
 }
 
 // asynchronous copy of one tile's waveform span into `dst` (pitch kPitch per hop); samples
-// outside [0, L) are zero-filled by the copy engine (src-size < cp-size)
-__device__ __forceinline__ void prefetch_tile(const Params& prm, unsigned tile, float* dst, int tid) {
+// outside [0, L) are zero-filled by the copy engine (src-size < cp-size).
+// Chunk c = k*kThreads + tid covers samples i = 2c, 2c+1: with 80 chunks per hop and
+// kThreads = 4*80 the thread's sample / smem offsets are base + k*{640, 648}: immediates.
+__device__ __forceinline__ void prefetch_tile(const Params& prm, unsigned tile, float* dst, int tid,
+                                              int ibase, int dbase) {
+  static_assert(kThreads == 4 * (kHop / 2), "chunk mapping assumes 4 hops per pass");
   const int64_t b = tile / prm.tiles_per_utt;
   const int64_t t0 = (int64_t)(tile - b * prm.tiles_per_utt) * kTile;
   const int64_t g0 = t0 * kHop - kNfft / 2;                 // even
+  const float* row = prm.wav + b * prm.wav_stride;
+  const float* wsrc = row + g0;                             // dereferenced inside [lo, hi) only
+  const bool al8 = (reinterpret_cast<uintptr_t>(row) & 7) == 0;
+  if (al8 && g0 >= 0 && g0 + kSpan <= prm.L) {              // interior tile: no guards at all
+    const float* src = wsrc + ibase;
+    float* d = dst + dbase;
+#pragma unroll
+    for (int k = 0; k < kCpIters; ++k)
+      if (k * kThreads + tid < kChunks) cp_async8(d + k * (4 * kPitch), src + k * (4 * kHop), 8);
+    return;
+  }
   const int lo = g0 < 0 ? (int)(-g0) : 0;                   // 0 or 200
   const int64_t rem = prm.L - g0;
   const int hi = rem <= 0 ? 0 : (rem < kSpan ? (int)rem : kSpan);
-  const float* row = prm.wav + b * prm.wav_stride;
-  const float* wsrc = row + g0;                             // dereferenced inside [lo, hi) only
-  if ((reinterpret_cast<uintptr_t>(row) & 7) == 0) {
-#pragma unroll
+  if (al8) {
+#pragma unroll 1
     for (int k = 0; k < kCpIters; ++k) {
-      const int c = k * kThreads + tid;
-      if (c < kChunks) {
-        const int i = 2 * c;
+      if (k * kThreads + tid < kChunks) {
+        const int i = ibase + k * (4 * kHop);
         int n = hi - i;
         n = (i < lo || n < 0) ? 0 : (n > 2 ? 2 : n);
-        cp_async8(dst + i + (i / kHop) * kPad, n ? wsrc + i : prm.window, 4 * n);
+        cp_async8(dst + dbase + k * (4 * kPitch), n ? wsrc + i : prm.window, 4 * n);
       }
     }
   } else {
@@ -133,8 +145,10 @@ __global__ void __launch_bounds__(kThreads, 2) fbank400_v3_kernel(const __grid_c
   const int unit = 2 * warp + h;
 
   // ---- once per CTA: first prefetch, then the constant tables -----------------------------
+  const int ibase = kHop * (tid / (kHop / 2)) + 2 * (tid % (kHop / 2));
+  const int dbase = ibase + kPad * (tid / (kHop / 2));
   unsigned tile = blockIdx.x;
-  if (tile < prm.n_tiles) prefetch_tile(prm, tile, s_a, tid);
+  if (tile < prm.n_tiles) prefetch_tile(prm, tile, s_a, tid, ibase, dbase);
   cp_async_commit();
   for (int i = tid; i < kTabW; i += kThreads) {
     const int n1 = i / 20, n2 = i - n1 * 20;   // window[i] is tap n1 of residue n2
@@ -162,7 +176,7 @@ __global__ void __launch_bounds__(kThreads, 2) fbank400_v3_kernel(const __grid_c
     float* s_wave = s_a + (it & 1) * kRegionA;
     {  // next tile's waveform flies while this one is transformed
       const unsigned nxt = tile + gridDim.x;
-      if (nxt < prm.n_tiles) prefetch_tile(prm, nxt, s_a + ((it & 1) ^ 1) * kRegionA, tid);
+      if (nxt < prm.n_tiles) prefetch_tile(prm, nxt, s_a + ((it & 1) ^ 1) * kRegionA, tid, ibase, dbase);
       cp_async_commit();
     }
     cp_async_wait<1>();
@@ -322,8 +336,9 @@ __global__ void __launch_bounds__(kThreads, 2) fbank400_v3_kernel(const __grid_c
       if (prm.utt_max != nullptr) {
         float vmax = fmaxf((t0 + p) < prm.T ? vmax0 : -INFINITY,
                            (t0 + p + kPairs) < prm.T ? vmax1 : -INFINITY);
-        vmax = warp_max(vmax);
-        if (lane == 0 && vmax > -INFINITY) atomicMax(prm.utt_max + b, max_key_encode(vmax));
+        // same address from every lane: the compiler aggregates this into one warp reduction
+        // (CREDUX.MAX) + one REDG
+        if (vmax > -INFINITY) atomicMax(prm.utt_max + b, max_key_encode(vmax));
       }
     }
     __syncthreads();

@@ -199,43 +199,71 @@ __global__ void norm_update_kernel(const float* __restrict__ cur, int F, int fir
 }
 
 // out = (max(x, floor_b) - mean) / std.  VEC = 4 when F % 4 == 0 and 16 B aligned.
+// An utterance is treated as a flat array of T*F/VEC vectors; a CTA takes kApplyIters
+// consecutive blocks of kNormThreads vectors, all loads issued before the first store.
+constexpr int kApplyIters = 8;
+
 template <int VEC>
 __global__ void __launch_bounds__(kNormThreads)
-norm_apply_kernel(const float* __restrict__ x, int64_t T, int F, const float* __restrict__ mean,
+norm_apply_kernel(const float* x, int64_t T, int F, const float* __restrict__ mean,
                   const float* __restrict__ stdv, int per_utt,
-                  const sbfe_maxkey_t* __restrict__ utt_max, float top_db,
-                  float* __restrict__ out, unsigned chunks, int rows_per_cta, int bx) {
+                  const sbfe_maxkey_t* __restrict__ utt_max, float top_db, float* out,
+                  unsigned chunks) {
+  extern __shared__ __align__(16) float s_ms[];  // mean[F] | std[F]
   const int64_t b = blockIdx.x / chunks;
   const int c = blockIdx.x - b * chunks;
-  const int by = kNormThreads / bx;
-  const int tx = threadIdx.x % bx, ty = threadIdx.x / bx;
-  const float floor_b = clamp_floor(utt_max, b, top_db);
-  const int64_t t_lo = (int64_t)c * rows_per_cta;
-  const int64_t t_hi = min(T, t_lo + rows_per_cta);
   const float* m = mean + (per_utt ? b * F : 0);
   const float* s = stdv + (per_utt ? b * F : 0);
+  for (int f = threadIdx.x; f < F; f += kNormThreads) {
+    s_ms[f] = __ldg(m + f);
+    s_ms[F + f] = __ldg(s + f);
+  }
+  const float floor_b = clamp_floor(utt_max, b, top_db);
+  const int FV = F / VEC;
+  const int64_t nvec = T * FV;
+  const int64_t i0 = (int64_t)c * (kNormThreads * kApplyIters) + threadIdx.x;
   const float* xb = x + b * T * F;
   float* ob = out + b * T * F;
-  const int FV = F / VEC;
-  for (int fv = tx; fv < FV; fv += bx) {
-    float mm[VEC], ss[VEC];
+  int col = (int)(i0 % FV);
+  const int dcol = kNormThreads % FV;
+  if (VEC == 4) {
+    float4 v[kApplyIters];
 #pragma unroll
-    for (int k = 0; k < VEC; ++k) {
-      mm[k] = __ldg(m + fv * VEC + k);
-      ss[k] = __ldg(s + fv * VEC + k);
+    for (int k = 0; k < kApplyIters; ++k) {
+      const int64_t i = i0 + (int64_t)k * kNormThreads;
+      if (i < nvec) v[k] = *reinterpret_cast<const float4*>(xb + 4 * i);
     }
-    for (int64_t t = t_lo + ty; t < t_hi; t += by) {
-      const int64_t o = t * F + fv * VEC;
-      if (VEC == 4) {
-        float4 v = *reinterpret_cast<const float4*>(xb + o);
-        v.x = (fmaxf(v.x, floor_b) - mm[0]) / ss[0];
-        v.y = (fmaxf(v.y, floor_b) - mm[1]) / ss[1];
-        v.z = (fmaxf(v.z, floor_b) - mm[2]) / ss[2];
-        v.w = (fmaxf(v.w, floor_b) - mm[3]) / ss[3];
-        *reinterpret_cast<float4*>(ob + o) = v;
-      } else {
-        ob[o] = (fmaxf(xb[o], floor_b) - mm[0]) / ss[0];
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < kApplyIters; ++k) {
+      const int64_t i = i0 + (int64_t)k * kNormThreads;
+      if (i < nvec) {
+        const float4 mm = *reinterpret_cast<const float4*>(s_ms + 4 * col);
+        const float4 ss = *reinterpret_cast<const float4*>(s_ms + F + 4 * col);
+        float4 r;
+        r.x = (fmaxf(v[k].x, floor_b) - mm.x) / ss.x;
+        r.y = (fmaxf(v[k].y, floor_b) - mm.y) / ss.y;
+        r.z = (fmaxf(v[k].z, floor_b) - mm.z) / ss.z;
+        r.w = (fmaxf(v[k].w, floor_b) - mm.w) / ss.w;
+        *reinterpret_cast<float4*>(ob + 4 * i) = r;
       }
+      col += dcol;
+      if (col >= FV) col -= FV;
+    }
+  } else {
+    float v[kApplyIters];
+#pragma unroll
+    for (int k = 0; k < kApplyIters; ++k) {
+      const int64_t i = i0 + (int64_t)k * kNormThreads;
+      if (i < nvec) v[k] = xb[i];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < kApplyIters; ++k) {
+      const int64_t i = i0 + (int64_t)k * kNormThreads;
+      if (i < nvec) ob[i] = (fmaxf(v[k], floor_b) - s_ms[col]) / s_ms[F + col];
+      col += dcol;
+      if (col >= FV) col -= FV;
     }
   }
 }
@@ -305,18 +333,18 @@ int launch_norm_apply(const float* x, int64_t B, int64_t T, int F, const float* 
   if (B == 0 || T == 0 || F == 0) return 0;
   const bool vec = (F % 4 == 0) &&
                    ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
-  const int cols = vec ? F / 4 : F;
-  const int bx = pick_bx(cols);
-  const int by = kNormThreads / bx;
-  int rows = by * 8;  // 8 rows per thread
-  const int64_t chunks = (T + rows - 1) / rows;
+  const int64_t nvec = T * (vec ? F / 4 : F);
+  const int64_t per_cta = (int64_t)kNormThreads * kApplyIters;
+  const int64_t chunks = (nvec + per_cta - 1) / per_cta;
   if (chunks * B > 0x7fffffff) return SBFE_E_TOOBIG;
+  const size_t smem = (size_t)2 * F * sizeof(float);
+  if (smem > 48 * 1024) return SBFE_E_TOOBIG;
   if (vec)
-    norm_apply_kernel<4><<<(unsigned)(chunks * B), kNormThreads, 0, stream>>>(
-        x, T, F, mean, stdv, per_utt, utt_max, top_db, out, (unsigned)chunks, rows, bx);
+    norm_apply_kernel<4><<<(unsigned)(chunks * B), kNormThreads, smem, stream>>>(
+        x, T, F, mean, stdv, per_utt, utt_max, top_db, out, (unsigned)chunks);
   else
-    norm_apply_kernel<1><<<(unsigned)(chunks * B), kNormThreads, 0, stream>>>(
-        x, T, F, mean, stdv, per_utt, utt_max, top_db, out, (unsigned)chunks, rows, bx);
+    norm_apply_kernel<1><<<(unsigned)(chunks * B), kNormThreads, smem, stream>>>(
+        x, T, F, mean, stdv, per_utt, utt_max, top_db, out, (unsigned)chunks);
   return check_last();
 }
 
