@@ -176,7 +176,9 @@ __global__ void __launch_bounds__(kThreads, 2) fbank400_v3_kernel(const __grid_c
     float* s_wave = s_a + (it & 1) * kRegionA;
     {  // next tile's waveform flies while this one is transformed
       const unsigned nxt = tile + gridDim.x;
+#ifndef SBFE_EXP_NOPREFETCH
       if (nxt < prm.n_tiles) prefetch_tile(prm, nxt, s_a + ((it & 1) ^ 1) * kRegionA, tid, ibase, dbase);
+#endif
       cp_async_commit();
     }
     cp_async_wait<1>();
@@ -217,6 +219,10 @@ __global__ void __launch_bounds__(kThreads, 2) fbank400_v3_kernel(const __grid_c
     }
     __syncthreads();
 
+#ifdef SBFE_EXP_SKIP234
+    if (s_e[tid] == 1.2345e-30f) prm.out[0] = 1.f;
+    continue;
+#endif
     // ---- stage 2: unit = (k1, half): DFT over n2, power -> P[bin][2p .. 2p+1] ---------------
     float* s_p = s_wave;
     {
@@ -289,6 +295,10 @@ __global__ void __launch_bounds__(kThreads, 2) fbank400_v3_kernel(const __grid_c
     }
     __syncthreads();
 
+#ifdef SBFE_EXP_SKIP34
+    if (s_p[tid] == 1.2345e-30f) prm.out[0] = 1.f;
+    continue;
+#endif
     // ---- stage 3: sparse mel projection + dB -> output tile [32][M] in smem -----------------
     {
       float vmax0 = -INFINITY, vmax1 = -INFINITY;
@@ -343,6 +353,10 @@ __global__ void __launch_bounds__(kThreads, 2) fbank400_v3_kernel(const __grid_c
     }
     __syncthreads();
 
+#ifdef SBFE_EXP_SKIP4
+    if (s_o[tid] == 1.2345e-30f) prm.out[0] = 1.f;
+    continue;
+#endif
     // ---- stage 4: coalesced store of the valid part of the tile ---------------------------------
     {
       const int64_t left = prm.T - t0;
@@ -414,7 +428,8 @@ constexpr int kMaxSmem = 110 * 1024;  // two CTAs per SM
 // of 4 and are zero-padded to a multiple of 4), everything fits in half an SM's smem
 bool fbank400_v3_supported(const sbfe_fbank_desc* d) {
   return d->n_fft == 400 && d->hop == v3::kHop && d->mel_pad4 == 1 && d->n_mels >= 1 &&
-         d->n_mels <= 1024 && d->mel_nnz >= 0 &&
+         d->n_mels <= 384 && d->mel_nnz >= 0 &&  // output tile [32][M|1] must fit in region E
+        
          v3::smem_floats(d->n_mels, d->mel_nnz) * sizeof(float) <= (size_t)v3::kMaxSmem;
 }
 
