@@ -346,7 +346,7 @@ def main():
                 "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                 "note": "pinned host wav -> H2D -> Fbank+norm via public API -> D2H features; "
                         "copies pipelined on separate streams"},
-        "gpu_launches": 5 * args.steps,  # fill(utt_max) + fbank400_v3 + clamp_tiles + norm_stats_tiles + norm_apply
+        "gpu_launches": 4 * args.steps,  # fbank400_v3 + clamp_tiles + norm_stats_tiles + norm_apply
         "roofline": {"bound": "hbm", "kernel": "fbank400_kernel (fused frame+window+rFFT400+mel+dB)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "peak_source": peak_src, "us_per_launch": k_ms * 1e3,

@@ -90,9 +90,13 @@ SBFE_API int sbfe_fbank_forward(const sbfe_fbank_desc* desc, const float* d_wav,
                        void* stream);
 
 /* Per-tile column statistics.  When sbfe_fbank_tile_frames(desc) = R > 0 (fused n_fft 400 /
- * hop 160 kernel), sbfe_fbank_forward can also write d_tile_stats
- * [B][ceil(T/R)][3][M] = {mean, M2 = sum of squared deviations, min} of every feature column
- * over the frames of each R-frame tile (un-clamped values; pass NULL to skip).  They let
+ * hop 160 kernel), sbfe_fbank_forward can also write d_tile_stats: [B][ceil(T/R)] records of
+ * W = sbfe_fbank_tile_stats_floats(desc) = 3*M + 16 words: [3][M] floats = {mean, M2 = sum of
+ * squared deviations, min} of every feature column over the frames of the R-frame tile
+ * (un-clamped values), then 16 max keys (sbfe_maxkey_t, 0 = unused) whose maximum over an
+ * utterance's records is the utterance maximum.  Pass NULL to skip.  With tile records
+ * d_utt_max may be NULL in sbfe_fbank_forward (no atomics, no memset) and in the two consumers
+ * below (the floor is rebuilt from the keys).  They let
  *   sbfe_clamp_tiles       apply the top_db clamp (features.py:706-710) in place, touching
  *                          only tiles that hold a value below the floor, and
  *   sbfe_norm_stats_tiles  produce the InputNormalization statistics (features.py:1020-1031,
@@ -100,6 +104,7 @@ SBFE_API int sbfe_fbank_forward(const sbfe_fbank_desc* desc, const float* d_wav,
  *                          only tiles cut by the valid length or holding clamped values are
  *                          re-read. */
 SBFE_API int32_t sbfe_fbank_tile_frames(const sbfe_fbank_desc* desc);
+SBFE_API int32_t sbfe_fbank_tile_stats_floats(const sbfe_fbank_desc* desc);
 SBFE_API int sbfe_clamp_tiles(float* d_x, int64_t B, int64_t T, int32_t F,
                      const sbfe_maxkey_t* d_utt_max, float top_db, const float* d_tile_stats,
                      int32_t tile_frames, void* stream);

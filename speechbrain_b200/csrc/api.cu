@@ -74,6 +74,10 @@ int32_t sbfe_fbank_tile_frames(const sbfe_fbank_desc* d) {
   return (d && desc_ok(d, true) && fbank400_v3_supported(d)) ? 32 : 0;
 }
 
+int32_t sbfe_fbank_tile_stats_floats(const sbfe_fbank_desc* d) {
+  return sbfe_fbank_tile_frames(d) ? (int32_t)tile_rec_words(d->n_mels) : 0;
+}
+
 int sbfe_fbank_forward(const sbfe_fbank_desc* d, const float* d_wav, int64_t B, int64_t L,
                        int64_t wav_stride, float* d_out, sbfe_maxkey_t* d_utt_max,
                        float* d_tile_stats, void* d_ws, int64_t ws_bytes, void* stream) {
@@ -131,7 +135,7 @@ int sbfe_clamp_tiles(float* d_x, int64_t B, int64_t T, int32_t F, const sbfe_max
                      float top_db, const float* d_tile_stats, int32_t tile_frames, void* stream) {
   if (B < 0 || T < 0 || F < 0 || tile_frames < 1) return SBFE_E_INVAL;
   if (B == 0 || T == 0 || F == 0) return 0;
-  if (!d_x || !d_utt_max || !d_tile_stats) return SBFE_E_INVAL;
+  if (!d_x || !d_tile_stats) return SBFE_E_INVAL;
   return launch_clamp_tiles(d_x, B, T, F, d_utt_max, top_db, d_tile_stats, tile_frames,
                             (cudaStream_t)stream);
 }

@@ -23,6 +23,32 @@ __device__ __forceinline__ float clamp_floor(const sbfe_maxkey_t* utt_max, int64
   return max_key_decode(utt_max[b]) - top_db;
 }
 
+// Per-tile record of the fused Fbank kernel (include/sbfe.h, sbfe_fbank_tile_stats_floats):
+// [3][F] floats = column mean / M2 / min, then kTileKeys max keys (one per producing warp, 0 =
+// unused) from which consumers rebuild the utterance maximum without atomics or a memset.
+constexpr int kTileKeys = 16;
+__host__ __device__ inline size_t tile_rec_words(int F) { return (size_t)3 * F + kTileKeys; }
+
+// top_db floor of utterance b from the tile records (whole CTA must call; uses one barrier pair)
+__device__ __forceinline__ float block_floor_from_tiles(const float* tile_stats, int64_t b, int tiles,
+                                                        int F, float top_db) {
+  __shared__ unsigned s_floor_key;
+  if (threadIdx.x == 0) s_floor_key = 0u;
+  __syncthreads();
+  const size_t rec = tile_rec_words(F);
+  const unsigned* base = reinterpret_cast<const unsigned*>(tile_stats) + (size_t)b * tiles * rec + 3 * F;
+  unsigned k = 0u;
+  for (int i = threadIdx.x; i < tiles * kTileKeys; i += blockDim.x) {
+    const unsigned v = __ldg(base + (size_t)(i / kTileKeys) * rec + (i % kTileKeys));
+    k = v > k ? v : k;
+  }
+  k = __reduce_max_sync(0xffffffffu, k);
+  if ((threadIdx.x & 31) == 0 && k) atomicMax(&s_floor_key, k);
+  __syncthreads();
+  const unsigned key = s_floor_key;
+  return key ? max_key_decode(key) - top_db : -INFINITY;
+}
+
 __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));

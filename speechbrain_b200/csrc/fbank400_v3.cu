@@ -58,7 +58,7 @@ struct Params {
   const float* window;     // device, [400], zero-padded / centred to n_fft
   float* out;
   sbfe_maxkey_t* utt_max;
-  float* tile_stats;       // optional [n_tiles][3][M]: mean, M2, min of every column of the tile
+  float* tile_stats;       // optional [n_tiles] records of tile_rec_words(M) (common.cuh)
   const int32_t* mel_start;
   const int32_t* mel_count;
   const int32_t* mel_offset;
@@ -128,7 +128,10 @@ __device__ __forceinline__ void prefetch_tile(const Params& prm, unsigned tile, 
   }
 }
 
-__global__ void __launch_bounds__(kThreads, 2) fbank400_v3_kernel(const __grid_constant__ Params prm) {
+#ifndef SBFE_EXP_MINB
+#define SBFE_EXP_MINB 2
+#endif
+__global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(const __grid_constant__ Params prm) {
   extern __shared__ __align__(16) float smem[];
   float* s_a = smem;                       // 2 x [staged waveform | P[bin][32]]
   float* s_e = s_a + 2 * kRegionA;         // exchange, later the output tile
@@ -343,12 +346,19 @@ __global__ void __launch_bounds__(kThreads, 2) fbank400_v3_kernel(const __grid_c
         vmax0 = fmaxf(vmax0, v0);
         vmax1 = fmaxf(vmax1, v1);
       }
-      if (prm.utt_max != nullptr) {
-        float vmax = fmaxf((t0 + p) < prm.T ? vmax0 : -INFINITY,
-                           (t0 + p + kPairs) < prm.T ? vmax1 : -INFINITY);
+      {
+        const float vmax = fmaxf((t0 + p) < prm.T ? vmax0 : -INFINITY,
+                                 (t0 + p + kPairs) < prm.T ? vmax1 : -INFINITY);
+        const unsigned key = vmax > -INFINITY ? max_key_encode(vmax) : 0u;
+        if (prm.tile_stats != nullptr) {  // one key per warp in the tile record: no atomics
+          const unsigned wk = __reduce_max_sync(0xffffffffu, key);
+          unsigned* keys = reinterpret_cast<unsigned*>(prm.tile_stats) + (size_t)tile * tile_rec_words(M) + 3 * M;
+          if (lane == 0) keys[warp] = wk;
+          if (warp == 0 && lane >= kWarps && lane < kTileKeys) keys[lane] = 0u;
+        }
         // same address from every lane: the compiler aggregates this into one warp reduction
         // (CREDUX.MAX) + one REDG
-        if (vmax > -INFINITY) atomicMax(prm.utt_max + b, max_key_encode(vmax));
+        if (prm.utt_max != nullptr && key) atomicMax(prm.utt_max + b, key);
       }
     }
     __syncthreads();
@@ -392,7 +402,7 @@ __global__ void __launch_bounds__(kThreads, 2) fbank400_v3_kernel(const __grid_c
     if (prm.tile_stats != nullptr) {
       const int64_t left = prm.T - t0;
       const int nvalid = left < kTile ? (int)left : kTile;
-      float* ts = prm.tile_stats + (size_t)tile * 3 * M;
+      float* ts = prm.tile_stats + (size_t)tile * tile_rec_words(M);
       for (int m = tid; m < M; m += kThreads) {
         const float* col = s_o + m;
         const float x0 = col[0];

@@ -95,20 +95,21 @@ __global__ void norm_stats_final_kernel(const float* __restrict__ x,
 // frames (UN-clamped values).  A tile's partial is used as is when all of its frames are
 // inside the utterance's valid length and nothing in that column is below the top_db
 // floor; otherwise (at most the one tile straddling n_b, plus tiles with clamped values)
-// the column is recomputed from x.  Partials are merged with Chan's update in double.
+// the column is recomputed from x.  Partials are merged with Chan's update (float: <= a few
+// hundred well-conditioned merges, error ~1e-6 relative).
 struct Moments {
-  double n, mean, m2;
+  float n, mean, m2;
 };
-__device__ __forceinline__ void merge(Moments& a, double nb, double mb, double m2b) {
-  if (nb <= 0.0) return;
-  const double n = a.n + nb, d = mb - a.mean;
-  a.mean += d * (nb / n);
-  a.m2 += m2b + d * d * (a.n * nb / n);
+__device__ __forceinline__ void merge(Moments& a, float nb, float mb, float m2b) {
+  if (nb <= 0.f) return;
+  const float n = a.n + nb, d = mb - a.mean, r = __fdividef(nb, n);
+  a.mean = fmaf(d, r, a.mean);
+  a.m2 += fmaf(d * d, a.n * r, m2b);
   a.n = n;
 }
 
-constexpr int kTileStatCols = 32;    // feature columns per CTA (one 128-byte row segment)
-constexpr int kTileStatGroups = 8;   // tile groups per CTA
+constexpr int kTileStatCols = 32;     // feature columns per CTA (one 128-byte row segment)
+constexpr int kTileStatGroups = 16;   // tile groups per CTA
 constexpr int kTileStatThreads = kTileStatCols * kTileStatGroups;
 
 // grid = (ceil(F / 32), B); thread = (column, tile group)
@@ -117,28 +118,32 @@ norm_stats_tiles_kernel(const float* __restrict__ x, const float* __restrict__ l
                         int F, int tile, int tiles, const float* __restrict__ tile_stats,
                         const sbfe_maxkey_t* __restrict__ utt_max, float top_db, int mean_norm,
                         int std_norm, float eps, float* __restrict__ mean, float* __restrict__ stdv) {
-  __shared__ double s_red[3 * kTileStatThreads];
+  __shared__ float s_red[3 * kTileStatThreads];
   const int64_t b = blockIdx.y;
   const int n = valid_frames(lengths, b, T);
-  const float floor_b = clamp_floor(utt_max, b, top_db);
+  const float floor_b = utt_max ? clamp_floor(utt_max, b, top_db)
+                                : block_floor_from_tiles(tile_stats, b, tiles, F, top_db);
   const int tx = threadIdx.x % kTileStatCols, ty = threadIdx.x / kTileStatCols;
   const int f = blockIdx.x * kTileStatCols + tx;
   const float* xb = x + b * T * F;
-  const float* tsb = tile_stats + (size_t)b * tiles * 3 * F;
-  Moments acc{0.0, 0.0, 0.0};
+  const size_t rec = tile_rec_words(F);
+  const float* tsb = tile_stats + (size_t)b * tiles * rec;
+  Moments acc{0.f, 0.f, 0.f};
   if (f < F) {
-    const int used = (n + tile - 1) / tile;  // tiles holding at least one valid frame
-    for (int j = ty; j < used; j += kTileStatGroups) {
+    // tiles whose existing frames are all valid: [0, n / tile), plus the short last tile when
+    // the whole utterance is valid
+    const int whole = (n >= T) ? tiles : n / tile;
+#pragma unroll 4
+    for (int j = ty; j < whole; j += kTileStatGroups) {
       const int r_lo = j * tile;
-      const int64_t exist = T - r_lo < tile ? T - r_lo : tile;
-      const int cnt = n - r_lo < exist ? n - r_lo : (int)exist;
-      const float* ts = tsb + (size_t)j * 3 * F + f;
+      const int cnt = T - r_lo < tile ? (int)(T - r_lo) : tile;
+      const float* ts = tsb + (size_t)j * rec + f;
       const float t_mean = __ldg(ts), t_m2 = __ldg(ts + F), t_min = __ldg(ts + 2 * F);
-      if (cnt == exist && t_min >= floor_b) {
-        merge(acc, (double)cnt, (double)t_mean, (double)t_m2);
-      } else {
+      if (t_min >= floor_b) {
+        merge(acc, (float)cnt, t_mean, t_m2);
+      } else {  // clamped values inside the valid part: rare, recompute the column
         const float* col = xb + (int64_t)r_lo * F + f;
-        float s = 0.f;  // <= 32 values of similar magnitude: float sums are exact enough
+        float s = 0.f;
         for (int r = 0; r < cnt; ++r) s += fmaxf(__ldg(col + (int64_t)r * F), floor_b);
         const float m = s / (float)cnt;
         float q = 0.f;
@@ -146,7 +151,25 @@ norm_stats_tiles_kernel(const float* __restrict__ x, const float* __restrict__ l
           const float d = fmaxf(__ldg(col + (int64_t)r * F), floor_b) - m;
           q = fmaf(d, d, q);
         }
-        merge(acc, (double)cnt, (double)m, (double)q);
+        merge(acc, (float)cnt, m, q);
+      }
+    }
+    // rows of the tile cut by the valid length, spread over the tile groups (sums about the
+    // tile's first row)
+    const int r_cut = whole * tile;
+    if (whole < tiles && r_cut < n) {
+      const float* col = xb + (int64_t)r_cut * F + f;
+      const float pivot = fmaxf(__ldg(col), floor_b);
+      float s1 = 0.f, s2 = 0.f;
+      int c = 0;
+      for (int r = ty; r < n - r_cut; r += kTileStatGroups, ++c) {
+        const float d = fmaxf(__ldg(col + (int64_t)r * F), floor_b) - pivot;
+        s1 += d;
+        s2 = fmaf(d, d, s2);
+      }
+      if (c > 0) {
+        const float mloc = s1 / (float)c;
+        merge(acc, (float)c, pivot + mloc, fmaxf(fmaf(-mloc, s1, s2), 0.f));
       }
     }
   }
@@ -159,11 +182,10 @@ norm_stats_tiles_kernel(const float* __restrict__ x, const float* __restrict__ l
       merge(acc, s_red[r * kTileStatCols + tx], s_red[kTileStatThreads + r * kTileStatCols + tx],
             s_red[2 * kTileStatThreads + r * kTileStatCols + tx]);
     // n == 0: mean of an empty slice is NaN, n == 1: unbiased std is NaN (torch)
-    const double m = (acc.n > 0.0) ? acc.mean : (double)NAN;
-    const double var = (acc.n > 1.0) ? acc.m2 / (acc.n - 1.0) : (double)NAN;
-    float sd = (float)sqrt(var < 0.0 ? 0.0 : var);
+    const float m = (acc.n > 0.f) ? acc.mean : NAN;
+    float sd = (acc.n > 1.f) ? sqrtf(fmaxf(acc.m2, 0.f) / (acc.n - 1.f)) : NAN;
     if (sd == sd) sd = fmaxf(sd, eps);  // torch.max propagates NaN
-    mean[b * F + f] = mean_norm ? (float)m : 0.f;
+    mean[b * F + f] = mean_norm ? m : 0.f;
     stdv[b * F + f] = std_norm ? sd : 1.f;
   }
 }

@@ -39,16 +39,21 @@ __global__ void clamp_kernel(const float* __restrict__ x, int64_t per_utt,
 }
 
 // ---- tile-aware clamp: only tiles that hold a value below the floor are touched -----------
-// (tile_stats from the fused Fbank kernel: [B][tiles][3][F], plane 2 = column minima)
+// (tile records of the fused Fbank kernel, common.cuh: plane 2 = column minima; utt_max NULL:
+// the utterance maximum is rebuilt from the records' keys)
 constexpr int kClampTileThreads = 128;
+// one CTA per tile (a warp-per-tile variant with one floor per 8-tile CTA measured 2x slower:
+// the tiles that need clamping cluster at the utterance tails)
 __global__ void __launch_bounds__(kClampTileThreads)
 clamp_tiles_kernel(float* __restrict__ x, int64_t T, int F, int tile, unsigned tiles,
                    const sbfe_maxkey_t* __restrict__ utt_max, float top_db,
                    const float* __restrict__ tile_stats) {
   const int64_t b = blockIdx.x / tiles;
   const int j = blockIdx.x - b * tiles;
-  const float floor_b = clamp_floor(utt_max, b, top_db);
-  const float* mn = tile_stats + ((size_t)blockIdx.x * 3 + 2) * F;
+  const float* mn = tile_stats + (size_t)blockIdx.x * tile_rec_words(F) + 2 * F;
+  // quick reject against the tile's own maximum first? no: the floor needs the utterance max
+  const float floor_b = utt_max ? clamp_floor(utt_max, b, top_db)
+                                : block_floor_from_tiles(tile_stats, b, (int)tiles, F, top_db);
   int below = 0;
   for (int f = threadIdx.x; f < F; f += kClampTileThreads) below |= (__ldg(mn + f) < floor_b);
   if (!__syncthreads_or(below)) return;
@@ -56,14 +61,24 @@ clamp_tiles_kernel(float* __restrict__ x, int64_t T, int F, int tile, unsigned t
   const int64_t rows = T - r_lo < tile ? T - r_lo : tile;
   float* p = x + (b * T + r_lo) * F;
   const int64_t n = rows * F;
-  for (int64_t i = threadIdx.x; i < n; i += kClampTileThreads) p[i] = fmaxf(p[i], floor_b);
+  if ((F & 3) == 0 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+    float4* p4 = reinterpret_cast<float4*>(p);
+    for (int64_t i = threadIdx.x; i < n / 4; i += kClampTileThreads) {
+      float4 v = p4[i];
+      v.x = fmaxf(v.x, floor_b); v.y = fmaxf(v.y, floor_b);
+      v.z = fmaxf(v.z, floor_b); v.w = fmaxf(v.w, floor_b);
+      p4[i] = v;
+    }
+  } else {
+    for (int64_t i = threadIdx.x; i < n; i += kClampTileThreads) p[i] = fmaxf(p[i], floor_b);
+  }
 }
 
 int launch_clamp_tiles(float* x, int64_t B, int64_t T, int F, const sbfe_maxkey_t* utt_max,
                        float top_db, const float* tile_stats, int tile, cudaStream_t stream) {
   if (B == 0 || T == 0 || F == 0) return 0;
   const int64_t tiles = (T + tile - 1) / tile;
-  if (tiles * B > 0x7fffffff) return SBFE_E_TOOBIG;
+  if (tiles * B > 0x7fffffff || tiles > 0x7fffffff / kTileKeys) return SBFE_E_TOOBIG;
   clamp_tiles_kernel<<<(unsigned)(tiles * B), kClampTileThreads, 0, stream>>>(
       x, T, F, tile, (unsigned)tiles, utt_max, top_db, tile_stats);
   return check_last();

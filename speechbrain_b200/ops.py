@@ -155,7 +155,6 @@ def fbank_forward(tables, wav, tile_stats=False):
     T = 1 + L // tables.hop
     desc, _ = tables.on(wav.device)
     out = torch.empty((B, T, tables.n_mels), dtype=torch.float32, device=wav.device)
-    utt_max = torch.zeros((B,), dtype=torch.int32, device=wav.device)
     L_ = lib()
     ws_bytes = L_.sbfe_fbank_workspace_bytes(C.byref(desc), B, L)
     ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=wav.device) if ws_bytes > 0 else None
@@ -163,13 +162,16 @@ def fbank_forward(tables, wav, tile_stats=False):
     if tile_stats and B > 0:
         frames = int(L_.sbfe_fbank_tile_frames(C.byref(desc)))
         if frames > 0:
-            ts = torch.empty((B, (T + frames - 1) // frames, 3, tables.n_mels),
-                             dtype=torch.float32, device=wav.device)
+            words = int(L_.sbfe_fbank_tile_stats_floats(C.byref(desc)))
+            ts = torch.empty((B, (T + frames - 1) // frames, words), dtype=torch.float32,
+                             device=wav.device)
+    # with tile records the utterance maximum travels in them: no atomics, no memset
+    utt_max = None if ts is not None else torch.zeros((B,), dtype=torch.int32, device=wav.device)
     with torch.cuda.device(wav.device):
         check(L_.sbfe_fbank_forward(C.byref(desc), _ptr(wav), B, L, L, _ptr(out),
                                     _ptr(utt_max), _ptr(ts), _ptr(ws), max(ws_bytes, 0), _stream()))
     if tile_stats:
-        return out, utt_max, (TileStats(ts, frames, utt_max, 0.0) if ts is not None else None)
+        return out, utt_max, (TileStats(ts, frames, None, 0.0) if ts is not None else None)
     return out, utt_max
 
 
