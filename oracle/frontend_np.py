@@ -38,6 +38,7 @@ __all__ = [
     "filterbank",
     "dct_matrix",
     "dct",
+    "sentence_stats",
     "deltas",
     "context_window",
     "InputNormalizationOracle",
@@ -302,6 +303,20 @@ def _round_half_even_frames(rel_len, t_len):
     """``torch.round(lengths[i] * T).int()`` (processing/features.py:1023):
     float32 product, round-half-to-even."""
     return int(np.rint(_F32(rel_len) * _F32(t_len)))
+
+
+def sentence_stats(x, lengths, mean_norm=True, std_norm=True, eps=1e-10):
+    """Per-sentence mean / unbiased std over the valid frames, ``[B, F]`` each
+    (``_compute_current_stats``, processing/features.py:1120-1145, called per sentence at
+    :1020-1031)."""
+    means, stds = [], []
+    for i in range(x.shape[0]):
+        seg = x[i, 0:_round_half_even_frames(lengths[i], x.shape[1])]
+        means.append(seg.mean(axis=0) if mean_norm else np.zeros(x.shape[2], x.dtype))
+        with np.errstate(invalid="ignore", divide="ignore"):
+            std = seg.std(axis=0, ddof=1) if std_norm else np.ones(x.shape[2], x.dtype)
+        stds.append(np.maximum(std, x.dtype.type(eps)))
+    return np.stack(means), np.stack(stds)
 
 
 class InputNormalizationOracle:

@@ -17,6 +17,17 @@ def _dist_ready():
     return torch.distributed.is_available() and torch.distributed.is_initialized()
 
 
+def sync_payload(cur, group=None):
+    """All-reduce (sum) of the ``[2F+1]`` statistics payload ``{sum_b mean_b, sum_b std_b, B}``:
+    the one collective of the path.  Statistics are means of per-sentence
+    vectors, so summing payloads over ranks and dividing by the summed count equals the
+    reference run single-process on the concatenated global batch, uneven shards included.
+    NCCL on the GPUs of a job; device-agnostic so the host logic is testable over gloo."""
+    if _dist_ready() and torch.distributed.get_world_size(group) > 1:
+        torch.distributed.all_reduce(cur, op=torch.distributed.ReduceOp.SUM, group=group)
+    return cur
+
+
 class InputNormalization(torch.nn.Module):
     """Mean / variance normalisation: ``sentence``, ``speaker``, ``batch`` or
     ``global`` statistics, same arguments and state as the reference.
@@ -88,8 +99,8 @@ class InputNormalization(torch.nn.Module):
             return x
 
         cur = ops.norm_reduce(mean, std)  # {sum_b mean_b, sum_b std_b, B}
-        if self.sync_stats and _dist_ready():
-            torch.distributed.all_reduce(cur)  # the one collective of the path
+        if self.sync_stats:
+            sync_payload(cur)  # the one collective of the path
         if self.norm_type == "batch":
             g_mean = torch.empty((F,), dtype=torch.float32, device=x.device)
             g_std = torch.empty((F,), dtype=torch.float32, device=x.device)
