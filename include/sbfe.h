@@ -91,10 +91,10 @@ SBFE_API int sbfe_fbank_forward(const sbfe_fbank_desc* desc, const float* d_wav,
 
 /* Per-tile column statistics.  When sbfe_fbank_tile_frames(desc) = R > 0 (fused n_fft 400 /
  * hop 160 kernel), sbfe_fbank_forward can also write d_tile_stats: [B][ceil(T/R)] records of
- * W = sbfe_fbank_tile_stats_floats(desc) = 3*M + 16 words: [3][M] floats = {mean, M2 = sum of
+ * W = sbfe_fbank_tile_stats_floats(desc) = 3*M + 4 words: [3][M] floats = {mean, M2 = sum of
  * squared deviations, min} of every feature column over the frames of the R-frame tile
- * (un-clamped values), then 16 max keys (sbfe_maxkey_t, 0 = unused) whose maximum over an
- * utterance's records is the utterance maximum.  Pass NULL to skip.  With tile records
+ * (un-clamped values), then the tile's max key (sbfe_maxkey_t) and 3 zero words; the maximum
+ * of the keys over an utterance's records is the utterance maximum.  Pass NULL to skip.  With tile records
  * d_utt_max may be NULL in sbfe_fbank_forward (no atomics, no memset) and in the two consumers
  * below (the floor is rebuilt from the keys).  They let
  *   sbfe_clamp_tiles       apply the top_db clamp (features.py:706-710) in place, touching

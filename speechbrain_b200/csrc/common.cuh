@@ -24,9 +24,10 @@ __device__ __forceinline__ float clamp_floor(const sbfe_maxkey_t* utt_max, int64
 }
 
 // Per-tile record of the fused Fbank kernel (include/sbfe.h, sbfe_fbank_tile_stats_floats):
-// [3][F] floats = column mean / M2 / min, then kTileKeys max keys (one per producing warp, 0 =
-// unused) from which consumers rebuild the utterance maximum without atomics or a memset.
-constexpr int kTileKeys = 16;
+// [3][F] floats = column mean / M2 / min, then kTileKeys words of which the first is the max key
+// of the tile (the rest pads the record to 16 bytes); consumers rebuild the utterance maximum
+// from the keys: no global atomics, no memset.
+constexpr int kTileKeys = 4;
 __host__ __device__ inline size_t tile_rec_words(int F) { return (size_t)3 * F + kTileKeys; }
 
 // top_db floor of utterance b from the tile records (whole CTA must call; uses one barrier pair)

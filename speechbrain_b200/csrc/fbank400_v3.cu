@@ -142,6 +142,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
   const int M = prm.n_mels;
   float* s_w = reinterpret_cast<float*>(s_meta) + ((2 * M + 3) & ~3);  // 16-byte aligned
 
+  __shared__ unsigned s_tile_key;  // max key of the current tile (tile records)
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
   const int p = lane & 15, h = lane >> 4;
@@ -188,6 +189,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
     __syncthreads();  // this tile's span (all threads' copies) is in smem; s_e / s_o are free
     const int64_t b = tile / prm.tiles_per_utt;
     const int64_t t0 = (int64_t)(tile - b * prm.tiles_per_utt) * kTile;
+    if (tid == 0) s_tile_key = 0u;  // two barriers before stage 3 raises it, read after the third
 
     // ---- stage 1: unit = residue n2: windowed real DFT20 over n1, twiddle, exchange --------
     {
@@ -350,11 +352,9 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
         const float vmax = fmaxf((t0 + p) < prm.T ? vmax0 : -INFINITY,
                                  (t0 + p + kPairs) < prm.T ? vmax1 : -INFINITY);
         const unsigned key = vmax > -INFINITY ? max_key_encode(vmax) : 0u;
-        if (prm.tile_stats != nullptr) {  // one key per warp in the tile record: no atomics
+        if (prm.tile_stats != nullptr) {  // tile maximum via one shared word, stored after the barrier
           const unsigned wk = __reduce_max_sync(0xffffffffu, key);
-          unsigned* keys = reinterpret_cast<unsigned*>(prm.tile_stats) + (size_t)tile * tile_rec_words(M) + 3 * M;
-          if (lane == 0) keys[warp] = wk;
-          if (warp == 0 && lane >= kWarps && lane < kTileKeys) keys[lane] = 0u;
+          if (lane == 0 && wk) atomicMax(&s_tile_key, wk);
         }
         // same address from every lane: the compiler aggregates this into one warp reduction
         // (CREDUX.MAX) + one REDG
@@ -400,6 +400,9 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
     // mean / M2 (sum of squared deviations) / min over the tile's existing frames, so that the
     // normalisation needs no second pass over the features (norm.cu: norm_stats_tiles_kernel)
     if (prm.tile_stats != nullptr) {
+      if (tid < kTileKeys)
+        reinterpret_cast<unsigned*>(prm.tile_stats)[(size_t)tile * tile_rec_words(M) + 3 * M + tid] =
+            tid == 0 ? s_tile_key : 0u;
       const int64_t left = prm.T - t0;
       const int nvalid = left < kTile ? (int)left : kTile;
       float* ts = prm.tile_stats + (size_t)tile * tile_rec_words(M);

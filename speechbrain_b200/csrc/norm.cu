@@ -190,19 +190,31 @@ norm_stats_tiles_kernel(const float* __restrict__ x, const float* __restrict__ l
   }
 }
 
-__global__ void norm_reduce_kernel(const float* __restrict__ mean, const float* __restrict__ stdv,
-                                   int64_t B, int F, float* __restrict__ cur) {
-  const int f = blockIdx.x * blockDim.x + threadIdx.x;
-  if (f < F) {
-    float a = 0.f, s = 0.f;
-    for (int64_t b = 0; b < B; ++b) {
-      a += mean[b * F + f];
-      s += stdv[b * F + f];
+// grid = ceil(F / 32) CTAs of 32 columns x 8 utterance groups
+__global__ void __launch_bounds__(256)
+norm_reduce_kernel(const float* __restrict__ mean, const float* __restrict__ stdv, int64_t B, int F,
+                   float* __restrict__ cur) {
+  __shared__ float s_a[256], s_s[256];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int f = blockIdx.x * 32 + tx;
+  float a = 0.f, s = 0.f;
+  if (f < F)
+    for (int64_t b = ty; b < B; b += 8) {
+      a += __ldg(mean + b * F + f);
+      s += __ldg(stdv + b * F + f);
+    }
+  s_a[threadIdx.x] = a;
+  s_s[threadIdx.x] = s;
+  __syncthreads();
+  if (ty == 0 && f < F) {
+    for (int r = 1; r < 8; ++r) {
+      a += s_a[r * 32 + tx];
+      s += s_s[r * 32 + tx];
     }
     cur[f] = a;
     cur[F + f] = s;
   }
-  if (f == 0) cur[2 * F] = (float)B;
+  if (blockIdx.x == 0 && threadIdx.x == 0) cur[2 * F] = (float)B;
 }
 
 __global__ void norm_update_kernel(const float* __restrict__ cur, int F, int first, float weight,
@@ -338,7 +350,7 @@ int launch_norm_stats_tiles(const float* x, const float* lengths, int64_t B, int
 
 int launch_norm_reduce(const float* mean, const float* stdv, int64_t B, int F, float* cur,
                        cudaStream_t stream) {
-  norm_reduce_kernel<<<(F + 127) / 128 > 0 ? (F + 127) / 128 : 1, 128, 0, stream>>>(mean, stdv, B, F, cur);
+  norm_reduce_kernel<<<(F + 31) / 32, 256, 0, stream>>>(mean, stdv, B, F, cur);
   return check_last();
 }
 

@@ -42,8 +42,9 @@ __global__ void clamp_kernel(const float* __restrict__ x, int64_t per_utt,
 // (tile records of the fused Fbank kernel, common.cuh: plane 2 = column minima; utt_max NULL:
 // the utterance maximum is rebuilt from the records' keys)
 constexpr int kClampTileThreads = 128;
-// one CTA per tile (a warp-per-tile variant with one floor per 8-tile CTA measured 2x slower:
-// the tiles that need clamping cluster at the utterance tails)
+// one CTA per tile: the tiles that need clamping cluster at the utterance tails, so anything
+// coarser serialises them (8 tiles per CTA measured 3x slower on padded batches).  The floor
+// costs one key per tile of the utterance (a single load per thread).
 __global__ void __launch_bounds__(kClampTileThreads)
 clamp_tiles_kernel(float* __restrict__ x, int64_t T, int F, int tile, unsigned tiles,
                    const sbfe_maxkey_t* __restrict__ utt_max, float top_db,
@@ -51,7 +52,6 @@ clamp_tiles_kernel(float* __restrict__ x, int64_t T, int F, int tile, unsigned t
   const int64_t b = blockIdx.x / tiles;
   const int j = blockIdx.x - b * tiles;
   const float* mn = tile_stats + (size_t)blockIdx.x * tile_rec_words(F) + 2 * F;
-  // quick reject against the tile's own maximum first? no: the floor needs the utterance max
   const float floor_b = utt_max ? clamp_floor(utt_max, b, top_db)
                                 : block_floor_from_tiles(tile_stats, b, (int)tiles, F, top_db);
   int below = 0;
@@ -334,7 +334,8 @@ int launch_post(const float* x, int64_t B, int64_t T, int F_in, const sbfe_maxke
     const int nfeat = p.F0 * (p.deltas == 1 ? 3 : 1), C = left + right + 1;
     const int F_out = nfeat * C;
     if ((F_out & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
-      for (int tile = 64; tile >= 8; tile /= 2) {
+      // 64-frame tiles halve the halo work; 32-frame tiles when that leaves too few CTAs
+      for (int tile = ((T + 63) / 64) * B >= 1184 ? 64 : 32; tile >= 8; tile /= 2) {
         const int fr_out = tile + left + right, fr_d = fr_out + 2 * n1, fr_b = fr_out + 2 * n2;
         size_t fl = (size_t)fr_out * (nfeat | 1) + (size_t)fr_b * p.F0;
         if (p.deltas) fl += (size_t)fr_d * p.F0;
@@ -351,8 +352,9 @@ int launch_post(const float* x, int64_t B, int64_t T, int F_in, const sbfe_maxke
           if (e != cudaSuccess) return (int)e;
         }
         const int nvec = F_out / 4;
-        int threads = 256;
-        if (nvec > 128) threads = nvec >= 1024 ? 1024 : ((nvec + 31) / 32) * 32;
+        // whole row groups of nvec threads (rounded to warps), up to 512 threads
+        const int rowthr = ((nvec + 31) / 32) * 32;
+        const int threads = rowthr >= 512 ? (rowthr > 1024 ? 1024 : rowthr) : rowthr * (512 / rowthr);
         post_fast_kernel<<<(unsigned)(tiles * B), threads, smem, stream>>>(p);
         return check_last();
       }

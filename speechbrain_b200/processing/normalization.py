@@ -81,7 +81,7 @@ class InputNormalization(torch.nn.Module):
         ts = getattr(x, "_sbfe_tile_stats", None)
         if ts is not None:  # one-shot hand-over from the fused Fbank kernel (lobes/features.py)
             x._sbfe_tile_stats = None
-            if ts.version != x._version or tuple(ts.stats.shape[::2]) != (B, 3 * F + 16):
+            if ts.version != x._version or tuple(ts.stats.shape[::2]) != (B, 3 * F + 4):
                 ts = None
         if ts is not None:
             mean, std = ops.norm_stats_tiles(x, lengths, ts, self.mean_norm, self.std_norm, self.eps)
