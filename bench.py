@@ -347,7 +347,7 @@ def main():
                 "note": "pinned host wav -> H2D -> Fbank+norm via public API -> D2H features; "
                         "copies pipelined on separate streams"},
         "gpu_launches": 4 * args.steps,  # fbank400_v3 + clamp_tiles + norm_stats_tiles + norm_apply
-        "roofline": {"bound": "hbm", "kernel": "fbank400_kernel (fused frame+window+rFFT400+mel+dB)",
+        "roofline": {"bound": "hbm", "kernel": "v3::fbank400_v3_kernel (fused frame+window+rFFT400+power+mel+dB+tile records)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "peak_source": peak_src, "us_per_launch": k_ms * 1e3,
                      "alg_bytes_per_launch": k_bytes, "traffic": traffic,
