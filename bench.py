@@ -218,14 +218,21 @@ def kernel_only_ms(fb, pool, reps):
     return e0.elapsed_time(e1) / (reps * len(pool))
 
 
-def time_e2e(fb, norm, host_pool, lens_dev, steps, warmup, barrier):
-    """Public API with HOST buffers: every step copies its waveform batch from
-    pinned host memory, runs the frontend, and copies the features back to
-    pinned host memory.  Copies are pipelined on their own streams (PCIe is full
-    duplex).  Returns (seconds for `steps` steps, h2d bytes, d2h bytes)."""
+def time_e2e(fb, norm, host_pool, steps, warmup, barrier, padded=False):
+    """Public API with HOST buffers: every step uploads its batch from pinned host memory
+    (a RaggedBatch: only the valid samples cross PCIe, the fused kernel zero-fills the
+    padding), runs the frontend, and copies the features back to pinned host memory.  Copies
+    are pipelined on their own streams (PCIe is full duplex).  Returns (seconds for `steps`
+    steps, mean h2d bytes, d2h bytes, checksum)."""
+    import speechbrain_b200 as sb
+
     dev = torch.device("cuda", torch.cuda.current_device())
     s_in, s_out, s_cmp = torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.current_stream()
-    d_in = [torch.empty((BATCH, L), device=dev) for _ in range(2)]
+    cap = max(h.packed.numel() for h in host_pool)
+    d_packed = [torch.empty((cap,), device=dev) for _ in range(2)]
+    d_off = [torch.empty((BATCH,), dtype=torch.int64, device=dev) for _ in range(2)]
+    d_ns = [torch.empty((BATCH,), dtype=torch.int32, device=dev) for _ in range(2)]
+    d_len = [torch.empty((BATCH,), dtype=torch.float32, device=dev) for _ in range(2)]
     h_out = [torch.empty((BATCH, T, N_MELS), pin_memory=True) for _ in range(2)]
     ev_in = [torch.cuda.Event() for _ in range(2)]
     ev_cmp = [torch.cuda.Event() for _ in range(2)]
@@ -234,12 +241,21 @@ def time_e2e(fb, norm, host_pool, lens_dev, steps, warmup, barrier):
 
     def step(i):
         k = i & 1
+        h = host_pool[i % len(host_pool)]
+        n = h.packed.numel()
         with torch.cuda.stream(s_in):
-            s_in.wait_event(ev_cmp[k])          # compute of step i-2 has consumed d_in[k]
-            d_in[k].copy_(host_pool[i % len(host_pool)], non_blocking=True)
+            s_in.wait_event(ev_cmp[k])          # compute of step i-2 has consumed slot k
+            d_packed[k][:n].copy_(h.packed, non_blocking=True)
+            d_off[k].copy_(h.offsets, non_blocking=True)
+            d_ns[k].copy_(h.nsamples, non_blocking=True)
+            d_len[k].copy_(h.lengths, non_blocking=True)
             ev_in[k].record(s_in)
         s_cmp.wait_event(ev_in[k])
-        out = frontend_step(fb, norm, d_in[k], lens_dev)
+        if padded:  # diagnostic (--e2e-padded): the packed buffer IS the padded [B, L] batch
+            out = frontend_step(fb, norm, d_packed[k][:n].view(BATCH, L), d_len[k])
+        else:
+            rb = sb.RaggedBatch(d_packed[k][:n], d_off[k], d_ns[k], h.max_len, d_len[k])
+            out = frontend_step(fb, norm, rb, rb.lengths)
         ev_cmp[k].record(s_cmp)
         with torch.cuda.stream(s_out):
             s_out.wait_event(ev_cmp[k])
@@ -259,7 +275,8 @@ def time_e2e(fb, norm, host_pool, lens_dev, steps, warmup, barrier):
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
     barrier()
-    return dt, 4 * BATCH * L, 4 * BATCH * T * N_MELS, float(h_out[(warmup + steps - 1) & 1].abs().mean())
+    h2d = sum(host_pool[(warmup + i) % len(host_pool)].nbytes for i in range(steps)) / steps
+    return dt, int(h2d), 4 * BATCH * T * N_MELS, float(h_out[(warmup + steps - 1) & 1].abs().mean())
 
 
 def main():
@@ -270,6 +287,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of CUDA graphs")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-padded", action="store_true",
+                    help="diagnostic: upload the zero-padded float32 batch instead of the ragged one")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -298,10 +317,16 @@ def main():
         return float(t)
 
     fb, norm = build_frontend()
+    from speechbrain_b200 import RaggedBatch
+
     host_pool, pool = [], []
     for i in range(POOL):
         wav, lens = synth_batch(i + 100 * rank, "cpu")
-        host_pool.append(wav.pin_memory())
+        if args.e2e_padded:
+            host_pool.append(RaggedBatch(wav.reshape(-1).pin_memory(), torch.zeros(BATCH, dtype=torch.int64).pin_memory(),
+                                         torch.zeros(BATCH, dtype=torch.int32).pin_memory(), L, lens.pin_memory()))
+        else:
+            host_pool.append(RaggedBatch.from_padded(wav, lens))  # what a ragged collate yields
         pool.append((wav.to(dev), lens.to(dev)))
     lens_dev = pool[0][1]
 
@@ -331,7 +356,8 @@ def main():
 
     # ---- end to end with host buffers -----------------------------------------
     e2e_steps = min(args.steps, 100)
-    dt, h2d, d2h, _ = time_e2e(fb, norm, host_pool, lens_dev, e2e_steps, args.warmup, barrier)
+    dt, h2d, d2h, _ = time_e2e(fb, norm, host_pool, e2e_steps, args.warmup, barrier,
+                               padded=args.e2e_padded)
     dt = max_over_ranks(dt)
     e2e_value = world * AUDIO_S_PER_STEP * e2e_steps / dt
 
@@ -344,8 +370,10 @@ def main():
         "clocks": clocks.summary(),
         "e2e": {"value": e2e_value, "unit": "audio-s/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "steps": e2e_steps,
-                "note": "pinned host wav -> H2D -> Fbank+norm via public API -> D2H features; "
-                        "copies pipelined on separate streams"},
+                "note": "pinned host RaggedBatch (valid samples only; zero padding re-created "
+                        "on the fly by the fused kernel, bit-identical to the padded batch) -> H2D "
+                        "-> Fbank+norm via public API -> D2H features; copies pipelined on "
+                        "separate streams; padded float32 batch would be %d B" % (4 * BATCH * L)},
         "gpu_launches": 4 * args.steps,  # fbank400_v3 + clamp_tiles + norm_stats_tiles + norm_apply
         "roofline": {"bound": "hbm", "kernel": "v3::fbank400_v3_kernel (fused frame+window+rFFT400+power+mel+dB+tile records)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,

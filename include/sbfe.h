@@ -89,6 +89,18 @@ SBFE_API int sbfe_fbank_forward(const sbfe_fbank_desc* desc, const float* d_wav,
                        float* d_tile_stats, void* d_workspace, int64_t workspace_bytes,
                        void* stream);
 
+/* Ragged ingest (the step before the path: speechbrain/dataio/batch.py:20-190 pads on the CPU
+ * and copies the padding over PCIe).  The batch arrives as ONE packed buffer holding only the
+ * valid samples: utterance b = d_packed[d_offsets[b] .. + d_nsamples[b]) (offsets multiples of
+ * 4 samples for 16-byte aligned rows), d_nsamples[b] <= L.  Result = sbfe_fbank_forward on the
+ * zero-padded [B, L] batch, bit for bit; the padding is never materialised (the copy engine of
+ * the fused kernel zero-fills).  Only where sbfe_fbank_tile_frames(desc) != 0, else
+ * SBFE_E_INVAL. */
+SBFE_API int sbfe_fbank_forward_ragged(const sbfe_fbank_desc* desc, const float* d_packed,
+                              const int64_t* d_offsets, const int32_t* d_nsamples, int64_t B,
+                              int64_t L, float* d_out, sbfe_maxkey_t* d_utt_max,
+                              float* d_tile_stats, void* stream);
+
 /* Per-tile column statistics.  When sbfe_fbank_tile_frames(desc) = R > 0 (fused n_fft 400 /
  * hop 160 kernel), sbfe_fbank_forward can also write d_tile_stats: [B][ceil(T/R)] records of
  * W = sbfe_fbank_tile_stats_floats(desc) = 3*M + 4 words: [3][M] floats = {mean, M2 = sum of

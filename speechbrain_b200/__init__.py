@@ -5,6 +5,7 @@ Drop-in replacements for ``speechbrain.lobes.features.{Fbank, MFCC}`` and
 Deltas, ContextWindow, InputNormalization}`` backed by hand-written CUDA kernels
 behind a C ABI (include/sbfe.h).  See DESIGN.md / INTEGRATION.md.
 """
+from .dataio import RaggedBatch  # noqa: F401
 from .lobes.features import MFCC, Fbank  # noqa: F401
 from .processing.features import (  # noqa: F401
     DCT, STFT, ContextWindow, Deltas, Filterbank, InputNormalization, spectral_magnitude)

@@ -55,6 +55,8 @@ struct Params {
   unsigned tiles_per_utt, n_tiles;
   int64_t L, wav_stride, T;
   const float* wav;
+  const int64_t* offsets;  // ragged input: utterance b starts at wav + offsets[b] ...
+  const int32_t* nsamples; // ... and holds nsamples[b] <= L samples (the rest of [0, L) is zero)
   const float* window;     // device, [400], zero-padded / centred to n_fft
   float* out;
   sbfe_maxkey_t* utt_max;
@@ -96,10 +98,11 @@ __device__ __forceinline__ void prefetch_tile(const Params& prm, unsigned tile, 
   const int64_t b = tile / prm.tiles_per_utt;
   const int64_t t0 = (int64_t)(tile - b * prm.tiles_per_utt) * kTile;
   const int64_t g0 = t0 * kHop - kNfft / 2;                 // even
-  const float* row = prm.wav + b * prm.wav_stride;
+  const float* row = prm.wav + (prm.offsets ? __ldg(prm.offsets + b) : b * prm.wav_stride);
+  const int64_t Lb = prm.nsamples ? (int64_t)__ldg(prm.nsamples + b) : prm.L;
   const float* wsrc = row + g0;                             // dereferenced inside [lo, hi) only
   const bool al8 = (reinterpret_cast<uintptr_t>(row) & 7) == 0;
-  if (al8 && g0 >= 0 && g0 + kSpan <= prm.L) {              // interior tile: no guards at all
+  if (al8 && g0 >= 0 && g0 + kSpan <= Lb) {                 // interior tile: no guards at all
     const float* src = wsrc + ibase;
     float* d = dst + dbase;
 #pragma unroll
@@ -108,7 +111,7 @@ __device__ __forceinline__ void prefetch_tile(const Params& prm, unsigned tile, 
     return;
   }
   const int lo = g0 < 0 ? (int)(-g0) : 0;                   // 0 or 200
-  const int64_t rem = prm.L - g0;
+  const int64_t rem = Lb - g0;
   const int hi = rem <= 0 ? 0 : (rem < kSpan ? (int)rem : kSpan);
   if (al8) {
 #pragma unroll 1
@@ -446,9 +449,9 @@ bool fbank400_v3_supported(const sbfe_fbank_desc* d) {
          v3::smem_floats(d->n_mels, d->mel_nnz) * sizeof(float) <= (size_t)v3::kMaxSmem;
 }
 
-int launch_fbank400_v3(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64_t L,
-                       int64_t wav_stride, float* out, sbfe_maxkey_t* utt_max, float* tile_stats,
-                       cudaStream_t stream) {
+int launch_fbank400_v3(const sbfe_fbank_desc* d, const float* wav, const int64_t* offsets,
+                       const int32_t* nsamples, int64_t B, int64_t L, int64_t wav_stride, float* out,
+                       sbfe_maxkey_t* utt_max, float* tile_stats, cudaStream_t stream) {
   using namespace v3;
   Params prm;
   prm.db = DbParams{d->multiplier * 0.30102999566398120f, d->amin, d->db_offset, d->floor_db,
@@ -459,6 +462,8 @@ int launch_fbank400_v3(const sbfe_fbank_desc* d, const float* wav, int64_t B, in
   prm.wav_stride = wav_stride;
   prm.T = 1 + L / kHop;
   prm.wav = wav;
+  prm.offsets = offsets;
+  prm.nsamples = nsamples;
   prm.window = d->d_window;
   prm.out = out;
   prm.utt_max = utt_max;

@@ -54,7 +54,7 @@ class _Lobe(torch.nn.Module):
         return self._tables
 
     def _features(self, wav, dct):
-        if wav.dim() != 2:
+        if not hasattr(wav, "packed") and wav.dim() != 2:
             raise NotImplementedError(
                 "speechbrain_b200 Fbank/MFCC take [batch, time] waveforms (for multi-channel "
                 "input the reference sums over the channel axis, lobes/features.py:138-139)")

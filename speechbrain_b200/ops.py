@@ -147,11 +147,27 @@ class TileStats:
         self.version = None
 
 
+def ragged_supported(tables, device):
+    """True when sbfe_fbank_forward_ragged can take this configuration."""
+    desc, _ = tables.on(device)
+    return int(lib().sbfe_fbank_tile_frames(C.byref(desc))) > 0
+
+
 def fbank_forward(tables, wav, tile_stats=False):
-    """wav [B, L] -> (dB or linear mel [B, T, M] WITHOUT the top_db clamp,
-    utt_max keys [B] int32[, TileStats or None]).  sbfe_fbank_forward."""
-    wav = _wav2d(wav)
-    B, L = wav.shape
+    """wav [B, L] (or a dataio.RaggedBatch) -> (dB or linear mel [B, T, M] WITHOUT the top_db
+    clamp, utt_max keys [B] int32[, TileStats or None]).  sbfe_fbank_forward[_ragged]."""
+    ragged = None
+    if hasattr(wav, "packed"):
+        ragged = wav
+        _require_cuda(ragged.packed, "wav")
+        if ragged.packed.dtype != torch.float32 or not ragged_supported(tables, ragged.device):
+            wav, ragged = ragged.to_padded(), None
+    if ragged is not None:
+        B, L, dev_ = ragged.batch_size, ragged.max_len, ragged.device
+        wav = ragged.packed
+    else:
+        wav = _wav2d(wav)
+        B, L = wav.shape
     T = 1 + L // tables.hop
     desc, _ = tables.on(wav.device)
     out = torch.empty((B, T, tables.n_mels), dtype=torch.float32, device=wav.device)
@@ -168,8 +184,14 @@ def fbank_forward(tables, wav, tile_stats=False):
     # with tile records the utterance maximum travels in them: no atomics, no memset
     utt_max = None if ts is not None else torch.zeros((B,), dtype=torch.int32, device=wav.device)
     with torch.cuda.device(wav.device):
-        check(L_.sbfe_fbank_forward(C.byref(desc), _ptr(wav), B, L, L, _ptr(out),
-                                    _ptr(utt_max), _ptr(ts), _ptr(ws), max(ws_bytes, 0), _stream()))
+        if ragged is not None:
+            check(L_.sbfe_fbank_forward_ragged(C.byref(desc), _ptr(wav), _ptr(ragged.offsets),
+                                               _ptr(ragged.nsamples), B, L, _ptr(out),
+                                               _ptr(utt_max), _ptr(ts), _stream()))
+        else:
+            check(L_.sbfe_fbank_forward(C.byref(desc), _ptr(wav), B, L, L, _ptr(out),
+                                        _ptr(utt_max), _ptr(ts), _ptr(ws), max(ws_bytes, 0),
+                                        _stream()))
     if tile_stats:
         return out, utt_max, (TileStats(ts, frames, None, 0.0) if ts is not None else None)
     return out, utt_max

@@ -235,3 +235,26 @@ def test_tile_stats_path_matches_generic_kernels(sb):
     got = norm(feats, lens)
     assert getattr(got, "_sbfe_tile_stats", None) is None
     assert torch.allclose(got, want, rtol=1e-4, atol=1e-4)
+
+
+def test_ragged_ingest_is_bit_identical(sb):
+    """RaggedBatch (packed valid samples, zero-fill in the kernel) == the padded batch."""
+    rng = np.random.default_rng(9)
+    sizes = [48000, 31999, 160, 47777, 1, 20480]
+    wavs = [torch.from_numpy((rng.standard_normal(n) * 0.1).astype(np.float32)) for n in sizes]
+    rb = sb.RaggedBatch.from_list(wavs, pin_memory=False).to("cuda")
+    padded = rb.to_padded()
+    assert padded.shape == (6, 48000)
+    fb = sb.Fbank(n_mels=80)
+    a, b = fb(rb), fb(padded)
+    assert a.shape == b.shape == (6, 301, 80) and torch.equal(a, b)
+    mf = sb.MFCC()
+    assert torch.equal(mf(rb), mf(padded))
+    norm = sb.InputNormalization(norm_type="sentence")
+    # (the 1-sample utterance has 0 valid frames: NaN statistics, like the reference)
+    assert torch.allclose(norm(fb(rb), rb.lengths), norm(fb(padded), rb.lengths), rtol=0, atol=0,
+                          equal_nan=True)
+    # from_padded round trip
+    host = padded.cpu()
+    rb2 = sb.RaggedBatch.from_padded(host, rb.lengths.cpu(), pin_memory=False).to("cuda")
+    assert torch.equal(fb(rb2), b)
