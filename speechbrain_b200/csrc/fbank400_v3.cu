@@ -311,45 +311,58 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
     {
       float vmax0 = -INFINITY, vmax1 = -INFINITY;
       const float2* pp0 = reinterpret_cast<const float2*>(s_p) + p;
+      // four filters (m, m+20, m+40, m+60) in flight per thread: their loads and FMA chains
+      // are independent, which hides the shared-memory latency a one-filter loop exposes
 #pragma unroll 1
-      for (int m = unit; m < M; m += kUnits) {
-        const int2 meta = s_meta[m];
-        const int cnt = meta.x >> 16;
-        const float4* wt = reinterpret_cast<const float4*>(s_w + meta.y);
-        const float2* pp = pp0 + (meta.x & 0xffff) * kPairs;
-        f2 acc = mk2(0.f, 0.f);
-#define SBFE_MEL_GROUP(g)                                                 \
-  {                                                                       \
-    const float4 w4 = wt[g];                                              \
-    acc = fmas(f2{pp[(4 * (g) + 0) * kPairs]}, w4.x, acc);                \
-    acc = fmas(f2{pp[(4 * (g) + 1) * kPairs]}, w4.y, acc);                \
-    acc = fmas(f2{pp[(4 * (g) + 2) * kPairs]}, w4.z, acc);                \
-    acc = fmas(f2{pp[(4 * (g) + 3) * kPairs]}, w4.w, acc);                \
+      for (int m0 = unit; m0 < M; m0 += 4 * kUnits) {
+        int cnt[4];
+        const float4* wt[4];
+        const float2* pp[4];
+        f2 acc[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int m = m0 + i * kUnits;
+          const int2 meta = m < M ? s_meta[m] : make_int2(0, 0);
+          cnt[i] = meta.x >> 16;
+          wt[i] = reinterpret_cast<const float4*>(s_w + meta.y);
+          pp[i] = pp0 + (meta.x & 0xffff) * kPairs;
+          acc[i] = mk2(0.f, 0.f);
+        }
+#define SBFE_MEL_GROUP(i, g)                                                    \
+  {                                                                             \
+    const float4 w4 = wt[i][g];                                                 \
+    acc[i] = fmas(f2{pp[i][(4 * (g) + 0) * kPairs]}, w4.x, acc[i]);             \
+    acc[i] = fmas(f2{pp[i][(4 * (g) + 1) * kPairs]}, w4.y, acc[i]);             \
+    acc[i] = fmas(f2{pp[i][(4 * (g) + 2) * kPairs]}, w4.z, acc[i]);             \
+    acc[i] = fmas(f2{pp[i][(4 * (g) + 3) * kPairs]}, w4.w, acc[i]);             \
   }
-        if (cnt > 0) {
-          SBFE_MEL_GROUP(0)
-          if (cnt > 4) {
-            SBFE_MEL_GROUP(1)
-            if (cnt > 8) {
-              SBFE_MEL_GROUP(2)
-              if (cnt > 12) {
-                SBFE_MEL_GROUP(3)
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            if (cnt[i] > 4 * g) SBFE_MEL_GROUP(i, g)
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
 #pragma unroll 1
-                for (int g = 4; 4 * g < cnt; ++g) SBFE_MEL_GROUP(g)
-              }
-            }
-          }
+          for (int g = 4; 4 * g < cnt[i]; ++g) SBFE_MEL_GROUP(i, g)
         }
 #undef SBFE_MEL_GROUP
-        float v0 = acc.v.x, v1 = acc.v.y;
-        if (log_mel) {
-          v0 = (v0 > db_amin) ? fmaf(fast_log2(v0), db_scale, -db_off) : db_floor;
-          v1 = (v1 > db_amin) ? fmaf(fast_log2(v1), db_scale, -db_off) : db_floor;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int m = m0 + i * kUnits;
+          if (m < M) {
+            float v0 = acc[i].v.x, v1 = acc[i].v.y;
+            if (log_mel) {
+              v0 = (v0 > db_amin) ? fmaf(fast_log2(v0), db_scale, -db_off) : db_floor;
+              v1 = (v1 > db_amin) ? fmaf(fast_log2(v1), db_scale, -db_off) : db_floor;
+            }
+            s_o[p * opitch + m] = v0;
+            s_o[(p + kPairs) * opitch + m] = v1;
+            vmax0 = fmaxf(vmax0, v0);
+            vmax1 = fmaxf(vmax1, v1);
+          }
         }
-        s_o[p * opitch + m] = v0;
-        s_o[(p + kPairs) * opitch + m] = v1;
-        vmax0 = fmaxf(vmax0, v0);
-        vmax1 = fmaxf(vmax1, v1);
       }
       {
         const float vmax = fmaxf((t0 + p) < prm.T ? vmax0 : -INFINITY,
