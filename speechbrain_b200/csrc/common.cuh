@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../../include/sbfe.h"
 
@@ -80,6 +81,49 @@ __device__ __forceinline__ float to_db(float x, const DbParams& p) {
 inline int check_last(void) {
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : (int)e;
+}
+
+// ---- programmatic dependent launch (stream order kept, launch latency overlapped) ----------
+// A step is four short kernels back to back; each one's launch + prologue would otherwise sit
+// on the critical path.  Every kernel of this library (1) executes pdl_wait() before it reads
+// or writes anything another kernel may touch - it returns once the preceding kernel in the
+// stream has completed and its writes are visible - and (2) calls pdl_launch_dependents() so
+// that the NEXT kernel may be scheduled early and park in its own pdl_wait().  Because every
+// kernel waits unconditionally, completion is transitive along the stream.  Kernels of other
+// libraries never trigger early, so mixing with them degrades to ordinary stream order.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
+// SBFE_PDL=0 in the environment turns the launch attribute off (plain stream order).
+inline bool pdl_enabled() {
+  static const int on = [] {
+    const char* v = getenv("SBFE_PDL");
+    return (v != nullptr && v[0] == '0') ? 0 : 1;
+  }();
+  return on != 0;
+}
+
+template <typename... KArgs, typename... Args>
+inline int launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                      cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    return (int)e;
+  }
+  return check_last();
 }
 
 }  // namespace sbfe

@@ -151,12 +151,11 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
   const int p = lane & 15, h = lane >> 4;
   const int unit = 2 * warp + h;
 
-  // ---- once per CTA: first prefetch, then the constant tables -----------------------------
+  // ---- once per CTA: the constant tables (they are not produced by the preceding kernel, so
+  // this part may overlap its tail: see pdl_wait in common.cuh), then the first prefetch ------
   const int ibase = kHop * (tid / (kHop / 2)) + 2 * (tid % (kHop / 2));
   const int dbase = ibase + kPad * (tid / (kHop / 2));
   unsigned tile = blockIdx.x;
-  if (tile < prm.n_tiles) prefetch_tile(prm, tile, s_a, tid, ibase, dbase);
-  cp_async_commit();
   for (int i = tid; i < kTabW; i += kThreads) {
     const int n1 = i / 20, n2 = i - n1 * 20;   // window[i] is tap n1 of residue n2
     s_tw[n2 * 20 + n1] = __ldg(prm.window + i);
@@ -171,6 +170,9 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
     const int r = tid / ((kPRows - kBins) * kTile), i = tid - r * (kPRows - kBins) * kTile;
     s_a[r * kRegionA + kBins * kTile + i] = 0.f;
   }
+  pdl_wait();  // from here on the waveform is read and out / tile records are written
+  if (tile < prm.n_tiles) prefetch_tile(prm, tile, s_a, tid, ibase, dbase);
+  cp_async_commit();
   const float db_scale = prm.db.scale, db_amin = prm.db.amin, db_off = prm.db.offset,
               db_floor = prm.db.floor_db;
   const bool log_mel = prm.db.log_mel != 0;
@@ -183,6 +185,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
     float* s_wave = s_a + (it & 1) * kRegionA;
     {  // next tile's waveform flies while this one is transformed
       const unsigned nxt = tile + gridDim.x;
+      if (nxt >= prm.n_tiles) pdl_launch_dependents();  // last tile of this CTA: let the next kernel in
 #ifndef SBFE_EXP_NOPREFETCH
       if (nxt < prm.n_tiles) prefetch_tile(prm, nxt, s_a + ((it & 1) ^ 1) * kRegionA, tid, ibase, dbase);
 #endif
@@ -422,26 +425,37 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
       const int64_t left = prm.T - t0;
       const int nvalid = left < kTile ? (int)left : kTile;
       float* ts = prm.tile_stats + (size_t)tile * tile_rec_words(M);
-      for (int m = tid; m < M; m += kThreads) {
-        const float* col = s_o + m;
+      // thread = (column, quarter of the rows): 4 partial sums about the column's first value,
+      // merged with two shuffles; lanes (8 columns x 4 quarters) hit 32 distinct banks
+      const int q = tid & 3;
+      for (int m0 = 0; m0 < M; m0 += kThreads / 4) {
+        const int m = m0 + (tid >> 2);
+        const bool live = m < M;
+        const float* col = s_o + (live ? m : 0);
         const float x0 = col[0];
-        float s1a = 0.f, s1b = 0.f, s2a = 0.f, s2b = 0.f, mna = x0, mnb = x0;
-        int r = 1;
-        for (; r + 1 < nvalid; r += 2) {
-          const float va = col[r * opitch], vb = col[(r + 1) * opitch];
-          const float da = va - x0, db = vb - x0;
-          s1a += da; s1b += db;
-          s2a = fmaf(da, da, s2a); s2b = fmaf(db, db, s2b);
-          mna = fminf(mna, va); mnb = fminf(mnb, vb);
+        float s1 = 0.f, s2 = 0.f, mn = x0;
+#pragma unroll
+        for (int r = 0; r < kTile / 4; ++r) {
+          const int row = q * (kTile / 4) + r;
+          if (row < nvalid) {
+            const float v = col[row * opitch], d = v - x0;
+            s1 += d;
+            s2 = fmaf(d, d, s2);
+            mn = fminf(mn, v);
+          }
         }
-        if (r < nvalid) {
-          const float va = col[r * opitch], da = va - x0;
-          s1a += da; s2a = fmaf(da, da, s2a); mna = fminf(mna, va);
+#pragma unroll
+        for (int o = 1; o <= 2; o <<= 1) {
+          s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+          s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+          mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
         }
-        const float s1 = s1a + s1b, s2 = s2a + s2b, inv = 1.f / (float)nvalid;
-        ts[m] = fmaf(s1, inv, x0);
-        ts[M + m] = fmaxf(fmaf(-s1 * inv, s1, s2), 0.f);
-        ts[2 * M + m] = fminf(mna, mnb);
+        if (live) {
+          const float inv = 1.f / (float)nvalid;
+          if (q == 0) ts[m] = fmaf(s1, inv, x0);
+          if (q == 1) ts[M + m] = fmaxf(fmaf(-s1 * inv, s1, s2), 0.f);
+          if (q == 2) ts[2 * M + m] = mn;
+        }
       }
     }
     // the barrier at the top of the next iteration orders these s_o reads before its stage 1
@@ -503,8 +517,7 @@ int launch_fbank400_v3(const sbfe_fbank_desc* d, const float* wav, const int64_t
   }
   // persistent: two CTAs per SM, each strides over the tiles
   const unsigned grid = prm.n_tiles < (unsigned)(2 * sms) ? prm.n_tiles : (unsigned)(2 * sms);
-  fbank400_v3_kernel<<<grid, kThreads, smem, stream>>>(prm);
-  return check_last();
+  return launch_pdl(fbank400_v3_kernel, dim3(grid), dim3(kThreads), (size_t)smem, stream, prm);
 }
 
 }  // namespace sbfe

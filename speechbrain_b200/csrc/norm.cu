@@ -24,6 +24,8 @@ __global__ void __launch_bounds__(kNormThreads)
 norm_stats_partial_kernel(const float* __restrict__ x, const float* __restrict__ lengths,
                           int64_t T, int F, const sbfe_maxkey_t* __restrict__ utt_max,
                           float top_db, double2* __restrict__ ws, unsigned chunks, int bx) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ double2 s_red[kNormThreads];
   const int64_t b = blockIdx.x / chunks;
   const int c = blockIdx.x - b * chunks;
@@ -67,6 +69,8 @@ __global__ void norm_stats_final_kernel(const float* __restrict__ x,
                                         const sbfe_maxkey_t* __restrict__ utt_max, float top_db,
                                         const double2* __restrict__ ws, unsigned chunks,
                                         float* __restrict__ mean, float* __restrict__ stdv) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= B * F) return;
   const int64_t b = i / F;
@@ -118,6 +122,8 @@ norm_stats_tiles_kernel(const float* __restrict__ x, const float* __restrict__ l
                         int F, int tile, int tiles, const float* __restrict__ tile_stats,
                         const sbfe_maxkey_t* __restrict__ utt_max, float top_db, int mean_norm,
                         int std_norm, float eps, float* __restrict__ mean, float* __restrict__ stdv) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float s_red[3 * kTileStatThreads];
   const int64_t b = blockIdx.y;
   const int n = valid_frames(lengths, b, T);
@@ -133,6 +139,22 @@ norm_stats_tiles_kernel(const float* __restrict__ x, const float* __restrict__ l
     // tiles whose existing frames are all valid: [0, n / tile), plus the short last tile when
     // the whole utterance is valid
     const int whole = (n >= T) ? tiles : n / tile;
+    // rows of the tile cut by the valid length, spread over the tile groups (at most
+    // ceil((tile - 1) / 16) per thread): requested first so that they fly with the records
+    const int r_cut = whole * tile;
+    const bool cut = whole < tiles && r_cut < n;
+    constexpr int kCutRows = 2;
+    float cv[kCutRows], pivot = 0.f;
+    int c = 0;
+    if (cut) {
+      const float* col = xb + (int64_t)r_cut * F + f;
+      pivot = __ldg(col);
+#pragma unroll
+      for (int i = 0; i < kCutRows; ++i) {
+        const int r = ty + i * kTileStatGroups;
+        cv[i] = (r < n - r_cut) ? __ldg(col + (int64_t)r * F) : NAN;
+      }
+    }
 #pragma unroll 4
     for (int j = ty; j < whole; j += kTileStatGroups) {
       const int r_lo = j * tile;
@@ -154,16 +176,21 @@ norm_stats_tiles_kernel(const float* __restrict__ x, const float* __restrict__ l
         merge(acc, (float)cnt, m, q);
       }
     }
-    // rows of the tile cut by the valid length, spread over the tile groups (sums about the
-    // tile's first row)
-    const int r_cut = whole * tile;
-    if (whole < tiles && r_cut < n) {
+    if (cut) {  // sums about the cut tile's first row
       const float* col = xb + (int64_t)r_cut * F + f;
-      const float pivot = fmaxf(__ldg(col), floor_b);
+      pivot = fmaxf(pivot, floor_b);
       float s1 = 0.f, s2 = 0.f;
-      int c = 0;
-      for (int r = ty; r < n - r_cut; r += kTileStatGroups, ++c) {
-        const float d = fmaxf(__ldg(col + (int64_t)r * F), floor_b) - pivot;
+#pragma unroll
+      for (int i = 0; i < kCutRows; ++i) {
+        if (ty + i * kTileStatGroups < n - r_cut) {
+          const float d = fmaxf(cv[i], floor_b) - pivot;
+          s1 += d;
+          s2 = fmaf(d, d, s2);
+          ++c;
+        }
+      }
+      for (int r = ty + kCutRows * kTileStatGroups; r < n - r_cut; r += kTileStatGroups, ++c) {
+        const float d = fmaxf(__ldg(col + (int64_t)r * F), floor_b) - pivot;  // tile > 32 rows only
         s1 += d;
         s2 = fmaf(d, d, s2);
       }
@@ -173,14 +200,24 @@ norm_stats_tiles_kernel(const float* __restrict__ x, const float* __restrict__ l
       }
     }
   }
-  s_red[threadIdx.x] = acc.n;
-  s_red[kTileStatThreads + threadIdx.x] = acc.mean;
-  s_red[2 * kTileStatThreads + threadIdx.x] = acc.m2;
-  __syncthreads();
+  // tree merge over the 16 tile groups (4 levels instead of a 15-long dependent chain)
+  float* s_n = s_red;
+  float* s_m = s_red + kTileStatThreads;
+  float* s_q = s_red + 2 * kTileStatThreads;
+#pragma unroll
+  for (int half = kTileStatGroups / 2; half >= 1; half >>= 1) {
+    if (ty >= half && ty < 2 * half) {
+      s_n[threadIdx.x] = acc.n;
+      s_m[threadIdx.x] = acc.mean;
+      s_q[threadIdx.x] = acc.m2;
+    }
+    __syncthreads();
+    if (ty < half) {
+      const int o = threadIdx.x + half * kTileStatCols;
+      merge(acc, s_n[o], s_m[o], s_q[o]);
+    }
+  }
   if (ty == 0 && f < F) {
-    for (int r = 1; r < kTileStatGroups; ++r)
-      merge(acc, s_red[r * kTileStatCols + tx], s_red[kTileStatThreads + r * kTileStatCols + tx],
-            s_red[2 * kTileStatThreads + r * kTileStatCols + tx]);
     // n == 0: mean of an empty slice is NaN, n == 1: unbiased std is NaN (torch)
     const float m = (acc.n > 0.f) ? acc.mean : NAN;
     float sd = (acc.n > 1.f) ? sqrtf(fmaxf(acc.m2, 0.f) / (acc.n - 1.f)) : NAN;
@@ -194,6 +231,8 @@ norm_stats_tiles_kernel(const float* __restrict__ x, const float* __restrict__ l
 __global__ void __launch_bounds__(256)
 norm_reduce_kernel(const float* __restrict__ mean, const float* __restrict__ stdv, int64_t B, int F,
                    float* __restrict__ cur) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float s_a[256], s_s[256];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int f = blockIdx.x * 32 + tx;
@@ -219,6 +258,8 @@ norm_reduce_kernel(const float* __restrict__ mean, const float* __restrict__ std
 
 __global__ void norm_update_kernel(const float* __restrict__ cur, int F, int first, float weight,
                                    float* __restrict__ gmean, float* __restrict__ gstd) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int f = blockIdx.x * blockDim.x + threadIdx.x;
   if (f >= F) return;
   const float n = cur[2 * F];
@@ -243,6 +284,8 @@ norm_apply_kernel(const float* x, int64_t T, int F, const float* __restrict__ me
                   const float* __restrict__ stdv, int per_utt,
                   const sbfe_maxkey_t* __restrict__ utt_max, float top_db, float* out,
                   unsigned chunks) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ __align__(16) float s_ms[];  // mean[F] | std[F]
   const int64_t b = blockIdx.x / chunks;
   const int c = blockIdx.x - b * chunks;
@@ -322,15 +365,14 @@ int launch_norm_stats(const float* x, const float* lengths, int64_t B, int64_t T
   if (ws_bytes < norm_workspace_bytes(B, T, F)) return SBFE_E_NOSPACE;
   if (chunks * B > 0x7fffffff || B * F > 0x7fffffff) return SBFE_E_TOOBIG;
   if (chunks > 0) {
-    norm_stats_partial_kernel<<<(unsigned)(chunks * B), kNormThreads, 0, stream>>>(
-        x, lengths, T, F, utt_max, top_db, (double2*)ws, (unsigned)chunks, pick_bx(F));
-    int rc = check_last();
+    int rc = launch_pdl(norm_stats_partial_kernel, dim3((unsigned)(chunks * B)), dim3(kNormThreads),
+                        0, stream, x, lengths, T, F, utt_max, top_db, (double2*)ws,
+                        (unsigned)chunks, pick_bx(F));
     if (rc) return rc;
   }
-  norm_stats_final_kernel<<<(unsigned)((B * F + 255) / 256), 256, 0, stream>>>(
-      x, lengths, B, T, F, mean_norm, std_norm, eps, utt_max, top_db, (const double2*)ws,
-      (unsigned)chunks, mean, stdv);
-  return check_last();
+  return launch_pdl(norm_stats_final_kernel, dim3((unsigned)((B * F + 255) / 256)), dim3(256), 0,
+                    stream, x, lengths, B, T, F, mean_norm, std_norm, eps, utt_max, top_db,
+                    (const double2*)ws, (unsigned)chunks, mean, stdv);
 }
 
 int launch_norm_stats_tiles(const float* x, const float* lengths, int64_t B, int64_t T, int F,
@@ -342,23 +384,21 @@ int launch_norm_stats_tiles(const float* x, const float* lengths, int64_t B, int
   const int tiles = (int)((T + tile - 1) / tile);
   if (B > 65535) return SBFE_E_TOOBIG;
   const dim3 grid((unsigned)((F + kTileStatCols - 1) / kTileStatCols), (unsigned)B);
-  norm_stats_tiles_kernel<<<grid, kTileStatThreads, 0, stream>>>(
+  return launch_pdl(norm_stats_tiles_kernel, grid, dim3(kTileStatThreads), 0, stream,
       x, lengths, T, F, tile, tiles, tile_stats, utt_max, top_db, mean_norm, std_norm, eps, mean,
       stdv);
-  return check_last();
 }
 
 int launch_norm_reduce(const float* mean, const float* stdv, int64_t B, int F, float* cur,
                        cudaStream_t stream) {
-  norm_reduce_kernel<<<(F + 31) / 32, 256, 0, stream>>>(mean, stdv, B, F, cur);
-  return check_last();
+  return launch_pdl(norm_reduce_kernel, dim3((F + 31) / 32), dim3(256), 0, stream, mean, stdv, B, F, cur);
 }
 
 int launch_norm_update(const float* cur, int F, int first, float weight, float* gmean,
                        float* gstd, cudaStream_t stream) {
   if (F == 0) return 0;
-  norm_update_kernel<<<(F + 127) / 128, 128, 0, stream>>>(cur, F, first, weight, gmean, gstd);
-  return check_last();
+  return launch_pdl(norm_update_kernel, dim3((F + 127) / 128), dim3(128), 0, stream, cur, F, first,
+                    weight, gmean, gstd);
 }
 
 int launch_norm_apply(const float* x, int64_t B, int64_t T, int F, const float* mean,
@@ -373,13 +413,9 @@ int launch_norm_apply(const float* x, int64_t B, int64_t T, int F, const float* 
   if (chunks * B > 0x7fffffff) return SBFE_E_TOOBIG;
   const size_t smem = (size_t)2 * F * sizeof(float);
   if (smem > 48 * 1024) return SBFE_E_TOOBIG;
-  if (vec)
-    norm_apply_kernel<4><<<(unsigned)(chunks * B), kNormThreads, smem, stream>>>(
-        x, T, F, mean, stdv, per_utt, utt_max, top_db, out, (unsigned)chunks);
-  else
-    norm_apply_kernel<1><<<(unsigned)(chunks * B), kNormThreads, smem, stream>>>(
-        x, T, F, mean, stdv, per_utt, utt_max, top_db, out, (unsigned)chunks);
-  return check_last();
+  return launch_pdl(vec ? norm_apply_kernel<4> : norm_apply_kernel<1>, dim3((unsigned)(chunks * B)),
+                    dim3(kNormThreads), smem, stream, x, T, F, mean, stdv, per_utt, utt_max, top_db,
+                    out, (unsigned)chunks);
 }
 
 }  // namespace sbfe

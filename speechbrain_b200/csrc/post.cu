@@ -13,6 +13,8 @@ namespace sbfe {
 __global__ void clamp_kernel(const float* __restrict__ x, int64_t per_utt,
                              const sbfe_maxkey_t* __restrict__ utt_max, float top_db,
                              float* __restrict__ out, unsigned chunks) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int64_t b = blockIdx.x / chunks;
   const int64_t c = blockIdx.x - b * chunks;
   const float floor_b = clamp_floor(utt_max, b, top_db);
@@ -49,14 +51,18 @@ __global__ void __launch_bounds__(kClampTileThreads)
 clamp_tiles_kernel(float* __restrict__ x, int64_t T, int F, int tile, unsigned tiles,
                    const sbfe_maxkey_t* __restrict__ utt_max, float top_db,
                    const float* __restrict__ tile_stats) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int64_t b = blockIdx.x / tiles;
   const int j = blockIdx.x - b * tiles;
   const float* mn = tile_stats + (size_t)blockIdx.x * tile_rec_words(F) + 2 * F;
+  // the tile's column minima are requested before the floor is rebuilt (one memory round trip,
+  // not two): min over this thread's columns first, compared once the floor is known
+  float lo = INFINITY;
+  for (int f = threadIdx.x; f < F; f += kClampTileThreads) lo = fminf(lo, __ldg(mn + f));
   const float floor_b = utt_max ? clamp_floor(utt_max, b, top_db)
                                 : block_floor_from_tiles(tile_stats, b, (int)tiles, F, top_db);
-  int below = 0;
-  for (int f = threadIdx.x; f < F; f += kClampTileThreads) below |= (__ldg(mn + f) < floor_b);
-  if (!__syncthreads_or(below)) return;
+  if (!__syncthreads_or(lo < floor_b)) return;
   const int64_t r_lo = (int64_t)j * tile;
   const int64_t rows = T - r_lo < tile ? T - r_lo : tile;
   float* p = x + (b * T + r_lo) * F;
@@ -79,9 +85,8 @@ int launch_clamp_tiles(float* x, int64_t B, int64_t T, int F, const sbfe_maxkey_
   if (B == 0 || T == 0 || F == 0) return 0;
   const int64_t tiles = (T + tile - 1) / tile;
   if (tiles * B > 0x7fffffff || tiles > 0x7fffffff / kTileKeys) return SBFE_E_TOOBIG;
-  clamp_tiles_kernel<<<(unsigned)(tiles * B), kClampTileThreads, 0, stream>>>(
-      x, T, F, tile, (unsigned)tiles, utt_max, top_db, tile_stats);
-  return check_last();
+  return launch_pdl(clamp_tiles_kernel, dim3((unsigned)(tiles * B)), dim3(kClampTileThreads), 0,
+                    stream, x, T, F, tile, (unsigned)tiles, utt_max, top_db, tile_stats);
 }
 
 struct PostParams {
@@ -101,6 +106,8 @@ struct PostParams {
 constexpr int kPostThreads = 256;
 
 __global__ void __launch_bounds__(kPostThreads) post_kernel(const PostParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ __align__(16) float smem[];
   const int n2 = p.deltas == 1 ? 2 * p.n : (p.deltas ? p.n : 0);  // base-feature halo per side
   const int n1 = p.deltas == 1 ? p.n : 0;                         // delta halo per side
@@ -197,6 +204,8 @@ __global__ void __launch_bounds__(kPostThreads) post_kernel(const PostParams p) 
 // output element (the generic kernel above is instruction-bound on exactly that: 660 outputs
 // per frame for the MFCC default).  Requires F_out % 4 == 0.
 __global__ void post_fast_kernel(const PostParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ __align__(16) float smem[];
   const int nthr = blockDim.x;
   const int n2 = p.deltas == 1 ? 2 * p.n : (p.deltas ? p.n : 0);
@@ -316,9 +325,8 @@ int launch_post(const float* x, int64_t B, int64_t T, int F_in, const sbfe_maxke
     const int64_t per_utt = T * F_in;
     int64_t chunks = (per_utt + 8191) / 8192;
     if (chunks * B > 0x7fffffff) return SBFE_E_TOOBIG;
-    clamp_kernel<<<(unsigned)(chunks * B), 256, 0, stream>>>(x, per_utt, utt_max, top_db, out,
-                                                             (unsigned)chunks);
-    return check_last();
+    return launch_pdl(clamp_kernel, dim3((unsigned)(chunks * B)), dim3(256), 0, stream, x, per_utt,
+                      utt_max, top_db, out, (unsigned)chunks);
   }
   if (out == x) return SBFE_E_INVAL;
   PostParams p;
@@ -355,8 +363,8 @@ int launch_post(const float* x, int64_t B, int64_t T, int F_in, const sbfe_maxke
         // whole row groups of nvec threads (rounded to warps), up to 512 threads
         const int rowthr = ((nvec + 31) / 32) * 32;
         const int threads = rowthr >= 512 ? (rowthr > 1024 ? 1024 : rowthr) : rowthr * (512 / rowthr);
-        post_fast_kernel<<<(unsigned)(tiles * B), threads, smem, stream>>>(p);
-        return check_last();
+        return launch_pdl(post_fast_kernel, dim3((unsigned)(tiles * B)), dim3(threads), smem, stream,
+                          p);
       }
     }
   }
@@ -381,8 +389,7 @@ int launch_post(const float* x, int64_t B, int64_t T, int F_in, const sbfe_maxke
                                          (int)smem);
     if (e != cudaSuccess) return (int)e;
   }
-  post_kernel<<<(unsigned)(tiles * B), kPostThreads, smem, stream>>>(p);
-  return check_last();
+  return launch_pdl(post_kernel, dim3((unsigned)(tiles * B)), dim3(kPostThreads), smem, stream, p);
 }
 
 }  // namespace sbfe

@@ -11,6 +11,7 @@ ops:
 import torch
 
 from .. import ops
+from .._jit import traceable
 from ..processing.features import DCT, STFT, ContextWindow, Deltas, Filterbank
 
 __all__ = ["Fbank", "MFCC"]
@@ -96,6 +97,7 @@ class Fbank(_Lobe):
                           win_length, hop_length)
         self.compute_deltas = Deltas(input_size=n_mels)
 
+    @traceable()
     def forward(self, wav):
         """wav ``[B, L]`` -> ``[B, 1 + L//hop, n_mels * (3 if deltas) * (C if context)]``."""
         return self._features(wav, None)
@@ -118,5 +120,6 @@ class MFCC(_Lobe):
         self.compute_dct = DCT(input_size=n_mels, n_out=n_mfcc)
         self.compute_deltas = Deltas(input_size=n_mfcc)
 
+    @traceable()
     def forward(self, wav):
         return self._features(wav, self.compute_dct.matrix_on(wav.device))

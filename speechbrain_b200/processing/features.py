@@ -12,6 +12,7 @@ import math
 import torch
 
 from .. import ops
+from .._jit import traceable
 
 logger = logging.getLogger(__name__)
 
@@ -58,6 +59,7 @@ class STFT(torch.nn.Module):
             self._tables = ops.FrontendTables(self.n_fft, self.hop_length, win)
         return self._tables
 
+    @traceable()
     def forward(self, x):
         self._check_supported()
         if x.dim() == 3:  # [B, L, C] -> [B*C, L]   (processing/features.py:143-146)
@@ -161,6 +163,7 @@ class Filterbank(torch.nn.Module):
         bw = self.band.float().cpu().unsqueeze(1).expand(-1, self.n_stft)
         return self._create_fbank_matrix(fc, bw)
 
+    @traceable()
     def forward(self, spectrogram):
         sp_shape = spectrogram.shape
         if len(sp_shape) == 4:  # [B, T, F, C] -> [B*C, T, F]     (:541-545)
@@ -214,6 +217,7 @@ class DCT(torch.nn.Module):
             self._dev[key] = self.dct_mat.float().contiguous().to(device)
         return self._dev[key]
 
+    @traceable()
     def forward(self, x):
         input_shape = x.shape
         if len(input_shape) == 4:  # same flat reshape as the reference (:774-775)
@@ -239,6 +243,7 @@ class Deltas(torch.nn.Module):
             torch.arange(-self.n, self.n + 1, dtype=torch.float32).repeat(input_size, 1, 1),
         )
 
+    @traceable()
     def forward(self, x):
         if x.dim() != 3:
             raise NotImplementedError("speechbrain_b200.Deltas takes [batch, time, features]")
@@ -260,6 +265,7 @@ class ContextWindow(torch.nn.Module):
             self.kernel = torch.roll(self.kernel, self.right_frames - self.left_frames, 1)
         self.first_call = True
 
+    @traceable()
     def forward(self, x):
         if x.dim() != 3:
             raise NotImplementedError("speechbrain_b200.ContextWindow takes [batch, time, features]")

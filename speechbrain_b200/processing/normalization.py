@@ -9,6 +9,7 @@ as well.
 import torch
 
 from .. import ops
+from .._jit import traceable
 
 __all__ = ["InputNormalization"]
 
@@ -68,6 +69,7 @@ class InputNormalization(torch.nn.Module):
         self._pending_clamp = None
 
     # ------------------------------------------------------------------ forward
+    @traceable(lambda self: 0 if self.norm_type in ("sentence", "speaker") else None)
     def forward(self, x, lengths, spk_ids=torch.tensor([]), epoch=0):
         """x ``[B, T, F]``, lengths ``[B]`` relative; see :1000-1118."""
         if x.dim() != 3:

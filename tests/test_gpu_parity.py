@@ -258,3 +258,42 @@ def test_ragged_ingest_is_bit_identical(sb):
     host = padded.cpu()
     rb2 = sb.RaggedBatch.from_padded(host, rb.lengths.cpu(), pin_memory=False).to("cuda")
     assert torch.equal(fb(rb2), b)
+
+
+# ---- torch.jit.trace, as the reference's unit tests do (tests/unittests/test_features.py:
+# 14, 39, 56, 66, 97, 107): the traced module must replay the CUDA kernels, not a constant ----
+def test_modules_survive_jit_trace(sb):
+    g = torch.Generator().manual_seed(11)
+    wav = torch.randn(4, 16000, generator=g).cuda()
+    wav2 = torch.randn(4, 16000, generator=g).cuda()
+    spec = torch.rand(4, 101, 201, generator=g).cuda()
+    spec2 = torch.rand(4, 101, 201, generator=g).cuda()
+    feat = torch.rand(4, 101, 40, generator=g).cuda()
+    feat2 = torch.rand(4, 101, 40, generator=g).cuda()
+    cases = [
+        (sb.STFT(sample_rate=16000), wav, wav2),
+        (sb.Filterbank(), spec, spec2),
+        (sb.DCT(input_size=40), feat, feat2),
+        (sb.Deltas(input_size=40), feat, feat2),
+        (sb.ContextWindow(left_frames=2, right_frames=3), feat, feat2),
+        (sb.Fbank(), wav, wav2),
+        (sb.MFCC(), wav, wav2),
+    ]
+    for mod, a, b in cases:
+        traced = torch.jit.trace(mod, (a,))
+        assert "sbfe::module_call" in str(traced.graph), type(mod).__name__
+        # a different input through the traced graph == the eager module on that input
+        assert torch.equal(traced(b), mod(b)), type(mod).__name__
+
+    lens = torch.tensor([1.0, 0.8, 0.5, 0.3]).cuda()
+    for kind in ("sentence", "batch"):
+        norm = sb.InputNormalization(norm_type=kind)
+        traced = torch.jit.trace(norm, (feat.clone(), lens))
+        x = feat2.clone()
+        y = traced(x, lens)
+        want = sb.InputNormalization(norm_type=kind)(feat2.clone(), lens)
+        assert torch.equal(y, want), kind
+        if kind == "sentence":  # the in-place contract survives tracing
+            assert torch.equal(x, want)
+        else:
+            assert torch.equal(x, feat2)

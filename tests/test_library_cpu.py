@@ -113,3 +113,34 @@ def test_checkpoint_roundtrip(tmp_path):
     torch.save({**raw, "glob_mean": 0, "glob_std": 0}, p)
     b._load(p)
     assert b.glob_mean == 0
+
+
+def test_jit_trace_bridge_records_one_operator():
+    """speechbrain_b200/_jit.py: under torch.jit.trace a module forward becomes one
+    sbfe::module_call node that re-enters the Python forward on replay (no kernels needed
+    to check the mechanism: the body below is invisible to the tracer, like a ctypes call)."""
+    import torch
+
+    from speechbrain_b200 import _jit
+
+    class Twice(torch.nn.Module):
+        @_jit.traceable()
+        def forward(self, x):
+            return torch.from_numpy(x.numpy() * 2)
+
+    class MinusInPlace(torch.nn.Module):
+        @_jit.traceable(0)
+        def forward(self, x, lengths, epoch=0):
+            x.copy_(torch.from_numpy(x.numpy() - 1 - epoch))
+            return x
+
+    t = torch.jit.trace(Twice(), (torch.ones(3),))
+    assert "sbfe::module_call" in str(t.graph)
+    assert torch.equal(t(torch.full((3,), 5.0)), torch.full((3,), 10.0))
+    m = MinusInPlace()
+    t = torch.jit.trace(m, (torch.ones(3), torch.ones(1)))
+    y = torch.full((3,), 5.0)
+    r = t(y, torch.ones(1))
+    assert torch.equal(r, torch.full((3,), 4.0)) and torch.equal(y, r)
+    # eager calls are untouched by the decorator
+    assert torch.equal(m(torch.full((3,), 5.0), torch.ones(1), epoch=2), torch.full((3,), 2.0))
