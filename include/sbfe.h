@@ -62,11 +62,15 @@ typedef struct sbfe_fbank_desc {
   const int32_t* d_mel_offset;  /* [M] */
   const float* d_mel_weight;    /* [nnz] */
   int32_t mel_nnz;              /* total number of stored weights (padding included) */
-  int32_t mel_pad4;             /* 1: every mel_offset[m] is a multiple of 4 and each filter's
+  int32_t mel_pad4;             /* 0: plain CSR (always valid, slower kernel).
+                                   1: every mel_offset[m] is a multiple of 4 and each filter's
                                    weights are followed by zeros up to a multiple of 4 entries
-                                   (mel_count stays the unpadded count).  Enables the 128-bit
-                                   weight loads of the fused n_fft = 400 / hop = 160 kernel;
-                                   0 is always valid (slower kernel). */
+                                   (mel_count stays the unpadded count).
+                                   2: as 1, and filters (2k, 2k+1) both store 4*G weights with
+                                   G = max over the pair of ceil(mel_count / 4), zero filled, with
+                                   mel_start[m] + 4*G <= 4*ceil(bins / 4) for both.  Needed by the
+                                   fused n_fft = 400 / hop = 160 kernel (128-bit weight loads,
+                                   warp-uniform trip counts). */
 } sbfe_fbank_desc;
 
 SBFE_API int sbfe_abi_version(void);

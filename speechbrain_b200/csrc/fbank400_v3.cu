@@ -92,11 +92,9 @@ __device__ __forceinline__ void cp_async_wait() {
 // outside [0, L) are zero-filled by the copy engine (src-size < cp-size).
 // Chunk c = k*kThreads + tid covers samples i = 2c, 2c+1: with 80 chunks per hop and
 // kThreads = 4*80 the thread's sample / smem offsets are base + k*{640, 648}: immediates.
-__device__ __forceinline__ void prefetch_tile(const Params& prm, unsigned tile, float* dst, int tid,
-                                              int ibase, int dbase) {
+__device__ __forceinline__ void prefetch_tile(const Params& prm, int64_t b, int64_t t0, float* dst,
+                                              int tid, int ibase, int dbase) {
   static_assert(kThreads == 4 * (kHop / 2), "chunk mapping assumes 4 hops per pass");
-  const int64_t b = tile / prm.tiles_per_utt;
-  const int64_t t0 = (int64_t)(tile - b * prm.tiles_per_utt) * kTile;
   const int64_t g0 = t0 * kHop - kNfft / 2;                 // even
   const float* row = prm.wav + (prm.offsets ? __ldg(prm.offsets + b) : b * prm.wav_stride);
   const int64_t Lb = prm.nsamples ? (int64_t)__ldg(prm.nsamples + b) : prm.L;
@@ -171,30 +169,42 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
     s_a[r * kRegionA + kBins * kTile + i] = 0.f;
   }
   pdl_wait();  // from here on the waveform is read and out / tile records are written
-  if (tile < prm.n_tiles) prefetch_tile(prm, tile, s_a, tid, ibase, dbase);
+  // (utterance, first frame) of the tile in flight: one division per tile, carried over
+  unsigned nb = tile / prm.tiles_per_utt;
+  int nt0 = (int)(tile - nb * prm.tiles_per_utt) * kTile;
+  if (tile < prm.n_tiles) prefetch_tile(prm, nb, nt0, s_a, tid, ibase, dbase);
   cp_async_commit();
-  const float db_scale = prm.db.scale, db_amin = prm.db.amin, db_off = prm.db.offset,
-              db_floor = prm.db.floor_db;
+  float db_scale = prm.db.scale, db_amin = prm.db.amin, db_off = prm.db.offset,
+        db_floor = prm.db.floor_db;
+  // keep them in registers (the compiler otherwise re-reads the constant bank under predicates)
+  asm volatile("" : "+f"(db_scale), "+f"(db_amin), "+f"(db_off), "+f"(db_floor));
   const bool log_mel = prm.db.log_mel != 0;
   float4* s_e4 = reinterpret_cast<float4*>(s_e);
   const int opitch = M | 1;
   float* s_o = s_e;
+  // stage-4 walk of this thread over the [frames][M] tile (vector / scalar), tile-invariant
+  const int st_t4 = (tid * 4) / M, st_m4 = tid * 4 - st_t4 * M;
+  const int st_dt4 = (kThreads * 4) / M, st_dm4 = kThreads * 4 - st_dt4 * M;
+  const int st_t1 = tid / M, st_m1 = tid - st_t1 * M;
+  const int st_dt1 = kThreads / M, st_dm1 = kThreads - st_dt1 * M;
 
 #pragma unroll 1
   for (int it = 0; tile < prm.n_tiles; ++it, tile += gridDim.x) {
     float* s_wave = s_a + (it & 1) * kRegionA;
+    const int64_t b = nb;
+    const int64_t t0 = nt0;
     {  // next tile's waveform flies while this one is transformed
       const unsigned nxt = tile + gridDim.x;
       if (nxt >= prm.n_tiles) pdl_launch_dependents();  // last tile of this CTA: let the next kernel in
+      nb = nxt / prm.tiles_per_utt;
+      nt0 = (int)(nxt - nb * prm.tiles_per_utt) * kTile;
 #ifndef SBFE_EXP_NOPREFETCH
-      if (nxt < prm.n_tiles) prefetch_tile(prm, nxt, s_a + ((it & 1) ^ 1) * kRegionA, tid, ibase, dbase);
+      if (nxt < prm.n_tiles) prefetch_tile(prm, nb, nt0, s_a + ((it & 1) ^ 1) * kRegionA, tid, ibase, dbase);
 #endif
       cp_async_commit();
     }
     cp_async_wait<1>();
     __syncthreads();  // this tile's span (all threads' copies) is in smem; s_e / s_o are free
-    const int64_t b = tile / prm.tiles_per_utt;
-    const int64_t t0 = (int64_t)(tile - b * prm.tiles_per_utt) * kTile;
     if (tid == 0) s_tile_key = 0u;  // two barriers before stage 3 raises it, read after the third
 
     // ---- stage 1: unit = residue n2: windowed real DFT20 over n1, twiddle, exchange --------
@@ -317,8 +327,8 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
       // four filters (m, m+20, m+40, m+60) in flight per thread: their loads and FMA chains
       // are independent, which hides the shared-memory latency a one-filter loop exposes
 #pragma unroll 1
-      for (int m0 = unit; m0 < M; m0 += 4 * kUnits) {
-        int cnt[4];
+      for (int m0 = unit; m0 - h < M; m0 += 4 * kUnits) {   // m0 - h = 2 * warp: warp-uniform
+        int G[4];
         const float4* wt[4];
         const float2* pp[4];
         f2 acc[4];
@@ -326,7 +336,9 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
         for (int i = 0; i < 4; ++i) {
           const int m = m0 + i * kUnits;
           const int2 meta = m < M ? s_meta[m] : make_int2(0, 0);
-          cnt[i] = meta.x >> 16;
+          // the warp's two filters (2k, 2k+1) store the same number of 4-weight groups
+          // (mel_pad4 == 2), so the trip count is warp-uniform: no divergence bookkeeping
+          G[i] = __reduce_max_sync(0xffffffffu, ((meta.x >> 16) + 3) >> 2);
           wt[i] = reinterpret_cast<const float4*>(s_w + meta.y);
           pp[i] = pp0 + (meta.x & 0xffff) * kPairs;
           acc[i] = mk2(0.f, 0.f);
@@ -343,23 +355,25 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
         for (int g = 0; g < 4; ++g) {
 #pragma unroll
           for (int i = 0; i < 4; ++i)
-            if (cnt[i] > 4 * g) SBFE_MEL_GROUP(i, g)
+            if (g < G[i]) SBFE_MEL_GROUP(i, g)
         }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
 #pragma unroll 1
-          for (int g = 4; 4 * g < cnt[i]; ++g) SBFE_MEL_GROUP(i, g)
+          for (int g = 4; g < G[i]; ++g) SBFE_MEL_GROUP(i, g)
         }
 #undef SBFE_MEL_GROUP
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const int m = m0 + i * kUnits;
+          float v0 = acc[i].v.x, v1 = acc[i].v.y;
+          if (log_mel) {  // branch-free: log2 of everything, select afterwards
+            const float l0 = fmaf(fast_log2(v0), db_scale, -db_off);
+            const float l1 = fmaf(fast_log2(v1), db_scale, -db_off);
+            v0 = (v0 > db_amin) ? l0 : db_floor;
+            v1 = (v1 > db_amin) ? l1 : db_floor;
+          }
           if (m < M) {
-            float v0 = acc[i].v.x, v1 = acc[i].v.y;
-            if (log_mel) {
-              v0 = (v0 > db_amin) ? fmaf(fast_log2(v0), db_scale, -db_off) : db_floor;
-              v1 = (v1 > db_amin) ? fmaf(fast_log2(v1), db_scale, -db_off) : db_floor;
-            }
             s_o[p * opitch + m] = v0;
             s_o[(p + kPairs) * opitch + m] = v1;
             vmax0 = fmaxf(vmax0, v0);
@@ -394,8 +408,8 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
       const int total = nvalid * M;
       if ((M & 3) == 0 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
         int e = tid * 4;
-        int t = e / M, m = e - t * M;
-        const int dt = (kThreads * 4) / M, dm = (kThreads * 4) - dt * M;
+        int t = st_t4, m = st_m4;
+        const int dt = st_dt4, dm = st_dm4;
         for (; e < total; e += kThreads * 4) {
           const float* s = s_o + t * opitch + m;
           *reinterpret_cast<float4*>(o + e) = make_float4(s[0], s[1], s[2], s[3]);
@@ -405,8 +419,8 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
         }
       } else {
         int e = tid;
-        int t = e / M, m = e - t * M;
-        const int dt = kThreads / M, dm = kThreads - dt * M;
+        int t = st_t1, m = st_m1;
+        const int dt = st_dt1, dm = st_dm1;
         for (; e < total; e += kThreads) {
           o[e] = s_o[t * opitch + m];
           t += dt;
@@ -470,7 +484,7 @@ constexpr int kMaxSmem = 110 * 1024;  // two CTAs per SM
 // hop 160, filter tables in the padded layout (every filter's weights start at a multiple
 // of 4 and are zero-padded to a multiple of 4), everything fits in half an SM's smem
 bool fbank400_v3_supported(const sbfe_fbank_desc* d) {
-  return d->n_fft == 400 && d->hop == v3::kHop && d->mel_pad4 == 1 && d->n_mels >= 1 &&
+  return d->n_fft == 400 && d->hop == v3::kHop && d->mel_pad4 == 2 && d->n_mels >= 1 &&
          d->n_mels <= 384 && d->mel_nnz >= 0 &&  // output tile [32][M|1] must fit in region E
         
          v3::smem_floats(d->n_mels, d->mel_nnz) * sizeof(float) <= (size_t)v3::kMaxSmem;

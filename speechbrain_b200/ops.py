@@ -84,21 +84,28 @@ class FrontendTables:
         if mat.shape[0] != self.bins:
             raise ValueError("filterbank matrix has %d rows, expected %d" % (mat.shape[0], self.bins))
         self.n_mels = int(mat.shape[1])
+        # pair-uniform padded layout (sbfe_fbank_desc.mel_pad4 == 2): filters (2k, 2k+1) store
+        # the same number G of 4-weight groups, zero filled, every offset a multiple of 4, and
+        # start + 4 G never leaves the zero-extended spectrum (rows = 4 * ceil(bins / 4)) - a
+        # filter that would is moved down and gets leading zeros instead
+        rows = 4 * ((self.bins + 3) // 4)
+        spans = []
+        for m in range(self.n_mels):
+            nz = torch.nonzero(mat[:, m]).flatten()
+            spans.append((0, 0) if nz.numel() == 0 else (int(nz[0]), int(nz[-1]) - int(nz[0]) + 1))
         start, count, offset, weights, fill = [], [], [], [], 0
         for m in range(self.n_mels):
-            col = mat[:, m]
-            nz = torch.nonzero(col).flatten()
-            if nz.numel() == 0:
-                s, c = 0, 0
-            else:
-                s, c = int(nz[0]), int(nz[-1]) - int(nz[0]) + 1
+            mate = m ^ 1
+            groups = max((spans[m][1] + 3) // 4,
+                         (spans[mate][1] + 3) // 4 if mate < self.n_mels else 0)
+            s, c = spans[m]
+            shift = max(0, s + 4 * groups - rows)
+            s, c = s - shift, c + shift
             start.append(s)
             count.append(c)
             offset.append(fill)
-            # padded layout (sbfe_fbank_desc.mel_pad4): zeros up to a multiple of 4 entries
-            pad = (-c) % 4
-            weights.append(torch.cat([col[s:s + c], torch.zeros(pad)]))
-            fill += c + pad
+            weights.append(torch.cat([mat[s:s + c, m], torch.zeros(4 * groups - c)]))
+            fill += 4 * groups
         w = torch.cat(weights) if weights and fill else torch.zeros(4)
         self._h_mel = (torch.tensor(start, dtype=torch.int32), torch.tensor(count, dtype=torch.int32),
                        torch.tensor(offset, dtype=torch.int32), w.contiguous())
@@ -123,7 +130,7 @@ class FrontendTables:
             desc.d_mel_start, desc.d_mel_count = dev[0].data_ptr(), dev[1].data_ptr()
             desc.d_mel_offset, desc.d_mel_weight = dev[2].data_ptr(), dev[3].data_ptr()
             desc.mel_nnz = self.nnz
-            desc.mel_pad4 = 1
+            desc.mel_pad4 = 2
         entry = (desc, keep)
         self._dev[key] = entry
         return entry

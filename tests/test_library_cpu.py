@@ -59,8 +59,12 @@ def test_host_tables_match_reference_constants(golden):
     dense = fb.compute_fbanks.fbank_matrix()
     start, count, offset, w = tab._h_mel
     assert int(count.sum()) == 387 and tab.n_mels == 80  # 387 non-zeros for 80 mels
-    # padded layout of sbfe_fbank_desc.mel_pad4: offsets multiples of 4, zero fill
+    # padded layout of sbfe_fbank_desc.mel_pad4 == 2: offsets multiples of 4, zero fill, filters
+    # (2k, 2k+1) store the same number of 4-weight groups, start + 4 G stays inside 204 rows
     assert all(int(o) % 4 == 0 for o in offset) and tab.nnz == w.numel() and tab.nnz % 4 == 0
+    stored = torch.diff(torch.cat([offset, torch.tensor([tab.nnz], dtype=torch.int32)]))
+    assert torch.equal(stored[0::2], stored[1::2])
+    assert bool((stored >= 4 * ((count + 3) // 4)).all()) and int((start + stored).max()) <= 204
     assert int(torch.count_nonzero(w)) == 387
     rebuilt = torch.zeros_like(dense)
     for m in range(80):
@@ -144,3 +148,28 @@ def test_jit_trace_bridge_records_one_operator():
     assert torch.equal(r, torch.full((3,), 4.0)) and torch.equal(y, r)
     # eager calls are untouched by the decorator
     assert torch.equal(m(torch.full((3,), 5.0), torch.ones(1), epoch=2), torch.full((3,), 2.0))
+
+
+def test_mel_layout_moves_a_filter_that_would_leave_the_spectrum():
+    """mel_pad4 == 2 (include/sbfe.h): a narrow filter at the top of the spectrum paired with a
+    wide one stores the pair's group count; it is moved down with leading zeros so that
+    start + 4 G <= 204, and the table still describes the same matrix."""
+    import torch
+
+    from speechbrain_b200 import ops
+
+    mat = torch.zeros(201, 3)
+    mat[180:201, 0] = torch.arange(1, 22).float()
+    mat[199:201, 1] = torch.tensor([0.5, 0.25])
+    mat[5:7, 2] = 1.0
+    tab = ops.FrontendTables(400, 160, torch.hamming_window(400), mat)
+    start, count, offset, w = tab._h_mel
+    stored = torch.diff(torch.cat([offset, torch.tensor([tab.nnz], dtype=torch.int32)]))
+    assert stored.tolist() == [24, 24, 4]
+    assert int(start[1]) == 180 and int(count[1]) == 21 and int((start + stored).max()) <= 204
+    rebuilt = torch.zeros_like(mat)
+    for m in range(3):
+        s, c, o = int(start[m]), int(count[m]), int(offset[m])
+        rebuilt[s:s + c, m] = w[o:o + c]
+        assert torch.count_nonzero(w[o + c:o + int(stored[m])]) == 0
+    assert torch.equal(rebuilt, mat)
