@@ -327,14 +327,16 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
       // four filters (m, m+20, m+40, m+60) in flight per thread: their loads and FMA chains
       // are independent, which hides the shared-memory latency a one-filter loop exposes
 #pragma unroll 1
-      for (int m0 = unit; m0 - h < M; m0 += 4 * kUnits) {   // m0 - h = 2 * warp: warp-uniform
+      for (int mb = 0; mb < M; mb += 4 * kUnits) {   // block-uniform trip count
         int G[4];
         const float4* wt[4];
         const float2* pp[4];
         f2 acc[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          const int m = m0 + i * kUnits;
+          // odd slots run backwards over the units: filters widen with m, so unit u gets
+          // (narrow, wide, narrow, wide)-ish work and the warps reach the barrier together
+          const int m = mb + i * kUnits + ((i & 1) ? kUnits - 1 - unit : unit);
           const int2 meta = m < M ? s_meta[m] : make_int2(0, 0);
           // the warp's two filters (2k, 2k+1) store the same number of 4-weight groups
           // (mel_pad4 == 2), so the trip count is warp-uniform: no divergence bookkeeping
@@ -365,7 +367,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
 #undef SBFE_MEL_GROUP
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          const int m = m0 + i * kUnits;
+          const int m = mb + i * kUnits + ((i & 1) ? kUnits - 1 - unit : unit);
           float v0 = acc[i].v.x, v1 = acc[i].v.y;
           if (log_mel) {  // branch-free: log2 of everything, select afterwards
             const float l0 = fmaf(fast_log2(v0), db_scale, -db_off);
