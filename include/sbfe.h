@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define SBFE_ABI_VERSION 3
+#define SBFE_ABI_VERSION 4
 
 #if defined(__GNUC__)
 #define SBFE_API __attribute__((visibility("default")))
@@ -182,6 +182,31 @@ SBFE_API int sbfe_norm_update(const float* d_cur, int32_t F, int32_t first, floa
 SBFE_API int sbfe_norm_apply(const float* d_x, int64_t B, int64_t T, int32_t F, const float* d_mean,
                     const float* d_std, int32_t per_utt, const sbfe_maxkey_t* d_utt_max,
                     float top_db, float* d_out, void* stream);
+
+/* ---- next row: SpecAugment on features ----------------------------------
+ * speechbrain/lobes/augment.py:32-201.  x [B, T, F] -> out [B, T, F]:
+ *   time warp (:116-150)  rows [0, c) resampled onto [0, w) and rows [c, T) onto [w, T) along
+ *                         time with torch.nn.functional.interpolate(align_corners=True)
+ *                         semantics; warp_mode 0 = bicubic (A = -0.75, clamped taps),
+ *                         1 = bilinear; warp_c < 0: no warp;
+ *   masks (:152-201)      element (t, f) of utterance b becomes the fill value when
+ *                         fpos[b,i] <= f < fpos[b,i] + flen[b,i] for some i < n_fmask or
+ *                         tpos[b,i] <= t < tpos[b,i] + tlen[b,i] for some i < n_tmask.
+ * The draws c, w, *pos, *len are the caller's (the reference's torch.randint calls, int64).
+ * Fill = *d_fill when d_fill != NULL (device scalar, e.g. from sbfe_mean), else `fill`.
+ * With a warp d_out must differ from d_x; without one d_out must equal d_x and only the
+ * masked elements are written (nothing is read).  n_*mask <= 16. */
+SBFE_API int sbfe_specaugment_forward(const float* d_x, int64_t B, int64_t T, int32_t F,
+                             int32_t warp_c, int32_t warp_w, int32_t warp_mode,
+                             const int64_t* d_fpos, const int64_t* d_flen, int32_t n_fmask,
+                             const int64_t* d_tpos, const int64_t* d_tlen, int32_t n_tmask,
+                             const float* d_fill, float fill, float* d_out, void* stream);
+
+/* mean over n floats as a device scalar (x.mean() of augment.py:196); two small launches,
+ * double accumulation, workspace of sbfe_mean_workspace_bytes() bytes. */
+SBFE_API int64_t sbfe_mean_workspace_bytes(void);
+SBFE_API int sbfe_mean(const float* d_x, int64_t n, float* d_mean, void* d_workspace,
+              int64_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus
 }

@@ -2,10 +2,12 @@
 
 Drop-in replacements for ``speechbrain.lobes.features.{Fbank, MFCC}`` and
 ``speechbrain.processing.features.{STFT, spectral_magnitude, Filterbank, DCT,
-Deltas, ContextWindow, InputNormalization}`` backed by hand-written CUDA kernels
+Deltas, ContextWindow, InputNormalization}`` (and, next to the path,
+``speechbrain.lobes.augment.SpecAugment``) backed by hand-written CUDA kernels
 behind a C ABI (include/sbfe.h).  See DESIGN.md / INTEGRATION.md.
 """
 from .dataio import RaggedBatch  # noqa: F401
+from .lobes.augment import SpecAugment  # noqa: F401
 from .lobes.features import MFCC, Fbank  # noqa: F401
 from .processing.features import (  # noqa: F401
     DCT, STFT, ContextWindow, Deltas, Filterbank, InputNormalization, spectral_magnitude)
@@ -38,5 +40,11 @@ def install():
     for name in _LOBES:
         setattr(lobes, name, getattr(here, name))
         patched.append("speechbrain.lobes.features." + name)
+    try:  # the step after the path (lobes/augment.py pulls in torchaudio; optional)
+        aug = importlib.import_module("speechbrain.lobes.augment")
+        aug.SpecAugment = here.SpecAugment
+        patched.append("speechbrain.lobes.augment.SpecAugment")
+    except Exception:
+        pass
     normalization.register_checkpoint_hooks_if_available()
     return patched

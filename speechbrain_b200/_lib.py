@@ -66,6 +66,10 @@ SIGNATURES = {
     "sbfe_norm_reduce": (C.c_int, [_P, _P, _I64, _I32, _P, _P]),
     "sbfe_norm_update": (C.c_int, [_P, _I32, _I32, _F, _P, _P, _P]),
     "sbfe_norm_apply": (C.c_int, [_P, _I64, _I64, _I32, _P, _P, _I32, _P, _F, _P, _P]),
+    "sbfe_specaugment_forward": (C.c_int, [_P, _I64, _I64, _I32, _I32, _I32, _I32, _P, _P, _I32, _P,
+                                           _P, _I32, _P, _F, _P, _P]),
+    "sbfe_mean_workspace_bytes": (_I64, []),
+    "sbfe_mean": (C.c_int, [_P, _I64, _P, _P, _I64, _P]),
 }
 
 _lock = threading.Lock()
@@ -100,7 +104,7 @@ def lib():
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(handle, name)
             fn.restype, fn.argtypes = res, args
-        if handle.sbfe_abi_version() != 3:
+        if handle.sbfe_abi_version() != 4:
             raise SbfeUnavailable("libsbfe.so ABI version mismatch")
         _lib = handle
         return _lib

@@ -37,6 +37,11 @@ static bool desc_ok(const sbfe_fbank_desc* d, bool need_mel) {
   return true;
 }
 // the fused kernel covers n_fft == 400, hop <= 400 and filterbanks whose tables fit in smem
+int launch_specaugment(const float*, int64_t, int64_t, int, int, int, int, const int64_t*,
+                       const int64_t*, int, const int64_t*, const int64_t*, int, const float*, float,
+                       float*, cudaStream_t);
+int64_t mean_workspace_bytes();
+int launch_mean(const float*, int64_t, float*, void*, int64_t, cudaStream_t);
 bool fbank400_supported(const sbfe_fbank_desc* d);
 // packed-f32x2 kernel: additionally hop == 160 and the padded filter layout (mel_pad4)
 bool fbank400_v3_supported(const sbfe_fbank_desc* d);
@@ -202,6 +207,26 @@ int sbfe_norm_apply(const float* d_x, int64_t B, int64_t T, int32_t F, const flo
   if (!d_x || !d_out || !d_mean || !d_std) return SBFE_E_INVAL;
   return launch_norm_apply(d_x, B, T, F, d_mean, d_std, per_utt, d_utt_max, top_db, d_out,
                            (cudaStream_t)stream);
+}
+
+int sbfe_specaugment_forward(const float* d_x, int64_t B, int64_t T, int32_t F, int32_t warp_c,
+                             int32_t warp_w, int32_t warp_mode, const int64_t* d_fpos,
+                             const int64_t* d_flen, int32_t n_fmask, const int64_t* d_tpos,
+                             const int64_t* d_tlen, int32_t n_tmask, const float* d_fill,
+                             float fill, float* d_out, void* stream) {
+  if (B < 0 || T < 0 || F < 0) return SBFE_E_INVAL;
+  if (B == 0 || T == 0 || F == 0) return 0;
+  if (!d_x || !d_out) return SBFE_E_INVAL;
+  return launch_specaugment(d_x, B, T, F, warp_c, warp_w, warp_mode, d_fpos, d_flen, n_fmask,
+                            d_tpos, d_tlen, n_tmask, d_fill, fill, d_out, (cudaStream_t)stream);
+}
+
+int64_t sbfe_mean_workspace_bytes(void) { return mean_workspace_bytes(); }
+
+int sbfe_mean(const float* d_x, int64_t n, float* d_mean, void* d_workspace,
+              int64_t workspace_bytes, void* stream) {
+  if (!d_x || !d_mean || !d_workspace) return SBFE_E_INVAL;
+  return launch_mean(d_x, n, d_mean, d_workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -337,3 +337,49 @@ def decode_utt_max(keys):
         bits = (k & 0x7FFFFFFF) if (k & 0x80000000) else (~k & 0xFFFFFFFF)
         out.append(struct.unpack("<f", struct.pack("<I", bits))[0])
     return torch.tensor(out, dtype=torch.float32)
+
+
+def tensor_mean(x):
+    """x.mean() as a device scalar [1] (sbfe_mean; no host round trip)."""
+    x = _f32c(x, "x")
+    L_ = lib()
+    ws = torch.empty((int(L_.sbfe_mean_workspace_bytes()),), dtype=torch.uint8, device=x.device)
+    out = torch.empty((1,), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        check(L_.sbfe_mean(_ptr(x), x.numel(), _ptr(out), _ptr(ws), ws.numel(), _stream()))
+    return out
+
+
+def specaugment_forward(x, warp=None, warp_mode="bicubic", freq_masks=None, time_masks=None,
+                        fill=0.0):
+    """SpecAugment data movement (sbfe_specaugment_forward).  x [B, T, F] float32 contiguous.
+
+    warp = (c, w) python ints or None; freq_masks / time_masks = (pos, len) int64 [B, n] device
+    tensors or None; fill = python float or a device scalar tensor.  With a warp a new tensor is
+    returned; without one the masked elements of ``x`` are overwritten and ``x`` is returned."""
+    _require_cuda(x, "x")
+    if x.dtype != torch.float32 or not x.is_contiguous() or x.dim() != 3:
+        raise TypeError("specaugment_forward needs a contiguous float32 [B, T, F] tensor")
+    B, T, F = x.shape
+    modes = {"bicubic": 0, "bilinear": 1}
+    if warp is not None and warp_mode not in modes:
+        raise NotImplementedError("time_warp_mode=%r (bicubic and bilinear are built)" % (warp_mode,))
+
+    def pair(m):
+        if m is None:
+            return None, None, 0
+        pos, ln = m
+        pos = pos.reshape(B, -1).to(device=x.device, dtype=torch.int64).contiguous()
+        ln = ln.reshape(B, -1).to(device=x.device, dtype=torch.int64).contiguous()
+        return pos, ln, pos.shape[1]
+
+    fpos, flen, nf = pair(freq_masks)
+    tpos, tlen, nt = pair(time_masks)
+    d_fill, f_fill = (fill, 0.0) if isinstance(fill, torch.Tensor) else (None, float(fill))
+    out = torch.empty_like(x) if warp is not None else x
+    c, w = (int(warp[0]), int(warp[1])) if warp is not None else (-1, -1)
+    with torch.cuda.device(x.device):
+        check(lib().sbfe_specaugment_forward(_ptr(x), B, T, F, c, w, modes.get(warp_mode, 0),
+                                             _ptr(fpos), _ptr(flen), nf, _ptr(tpos), _ptr(tlen),
+                                             nt, _ptr(d_fill), f_fill, _ptr(out), _stream()))
+    return out
