@@ -105,6 +105,17 @@ SBFE_API int sbfe_fbank_forward_ragged(const sbfe_fbank_desc* desc, const float*
                               int64_t L, float* d_out, sbfe_maxkey_t* d_utt_max,
                               float* d_tile_stats, void* stream);
 
+/* The same with 16-bit PCM samples (what a .wav / .flac file holds; the reference converts them
+ * to float32 on the CPU, dataio/dataio.py read_audio via torchaudio.load, and ships 4 bytes per
+ * sample over PCIe): sample value = scale * d_packed[i], scale > 0 (1/32768 for torchaudio's
+ * normalisation).  int16 -> float32 is exact and the scale is folded into the window taps, so
+ * for a power-of-two scale the result equals sbfe_fbank_forward_ragged on the converted
+ * float32 samples bit for bit.  Offsets are multiples of 4 samples. */
+SBFE_API int sbfe_fbank_forward_ragged_pcm16(const sbfe_fbank_desc* desc, const int16_t* d_packed,
+                                    const int64_t* d_offsets, const int32_t* d_nsamples,
+                                    int64_t B, int64_t L, float scale, float* d_out,
+                                    sbfe_maxkey_t* d_utt_max, float* d_tile_stats, void* stream);
+
 /* Per-tile column statistics.  When sbfe_fbank_tile_frames(desc) = R > 0 (fused n_fft 400 /
  * hop 160 kernel), sbfe_fbank_forward can also write d_tile_stats: [B][ceil(T/R)] records of
  * W = sbfe_fbank_tile_stats_floats(desc) = 3*M + 4 words: [3][M] floats = {mean, M2 = sum of

@@ -50,6 +50,7 @@ SIGNATURES = {
     "sbfe_fbank_workspace_bytes": (_I64, [_DESC, _I64, _I64]),
     "sbfe_fbank_forward": (C.c_int, [_DESC, _P, _I64, _I64, _I64, _P, _P, _P, _P, _I64, _P]),
     "sbfe_fbank_forward_ragged": (C.c_int, [_DESC, _P, _P, _P, _I64, _I64, _P, _P, _P, _P]),
+    "sbfe_fbank_forward_ragged_pcm16": (C.c_int, [_DESC, _P, _P, _P, _I64, _I64, _F, _P, _P, _P, _P]),
     "sbfe_fbank_tile_frames": (_I32, [_DESC]),
     "sbfe_fbank_tile_stats_floats": (_I32, [_DESC]),
     "sbfe_clamp_tiles": (C.c_int, [_P, _I64, _I64, _I32, _P, _F, _P, _I32, _P]),

@@ -6,8 +6,9 @@
 namespace sbfe {
 int launch_fbank400(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
                     sbfe_maxkey_t*, cudaStream_t);
-int launch_fbank400_v3(const sbfe_fbank_desc*, const float*, const int64_t*, const int32_t*, int64_t,
-                       int64_t, int64_t, float*, sbfe_maxkey_t*, float*, cudaStream_t);
+int launch_fbank400_v3(const sbfe_fbank_desc*, const void*, int, float, const int64_t*,
+                       const int32_t*, int64_t, int64_t, int64_t, float*, sbfe_maxkey_t*, float*,
+                       cudaStream_t);
 int launch_clamp_tiles(float*, int64_t, int64_t, int, const sbfe_maxkey_t*, float, const float*, int,
                        cudaStream_t);
 int launch_norm_stats_tiles(const float*, const float*, int64_t, int64_t, int, int, int, float,
@@ -91,7 +92,7 @@ int sbfe_fbank_forward(const sbfe_fbank_desc* d, const float* d_wav, int64_t B, 
   if ((!d_wav && L > 0) || !d_out) return SBFE_E_INVAL;
   cudaStream_t s = (cudaStream_t)stream;
   if (fbank400_v3_supported(d))
-    return launch_fbank400_v3(d, d_wav, nullptr, nullptr, B, L, wav_stride, d_out, d_utt_max,
+    return launch_fbank400_v3(d, d_wav, 0, 1.f, nullptr, nullptr, B, L, wav_stride, d_out, d_utt_max,
                               d_tile_stats, s);
   if (d_tile_stats) return SBFE_E_INVAL;  // only where sbfe_fbank_tile_frames() != 0
   if (fused_ok(d)) return launch_fbank400(d, d_wav, B, L, wav_stride, d_out, d_utt_max, s);
@@ -109,7 +110,19 @@ int sbfe_fbank_forward_ragged(const sbfe_fbank_desc* d, const float* d_packed,
   if (B == 0) return 0;
   if (!d_packed || !d_offsets || !d_nsamples || !d_out) return SBFE_E_INVAL;
   if (!fbank400_v3_supported(d)) return SBFE_E_INVAL;  // pad on the device and use sbfe_fbank_forward
-  return launch_fbank400_v3(d, d_packed, d_offsets, d_nsamples, B, L, 0, d_out, d_utt_max,
+  return launch_fbank400_v3(d, d_packed, 0, 1.f, d_offsets, d_nsamples, B, L, 0, d_out, d_utt_max,
+                            d_tile_stats, (cudaStream_t)stream);
+}
+
+int sbfe_fbank_forward_ragged_pcm16(const sbfe_fbank_desc* d, const int16_t* d_packed,
+                                    const int64_t* d_offsets, const int32_t* d_nsamples, int64_t B,
+                                    int64_t L, float scale, float* d_out, sbfe_maxkey_t* d_utt_max,
+                                    float* d_tile_stats, void* stream) {
+  if (!desc_ok(d, true) || B < 0 || L < 0 || !(scale > 0.f)) return SBFE_E_INVAL;
+  if (B == 0) return 0;
+  if (!d_packed || !d_offsets || !d_nsamples || !d_out) return SBFE_E_INVAL;
+  if (!fbank400_v3_supported(d)) return SBFE_E_INVAL;  // convert on the device and use sbfe_fbank_forward
+  return launch_fbank400_v3(d, d_packed, 1, scale, d_offsets, d_nsamples, B, L, 0, d_out, d_utt_max,
                             d_tile_stats, (cudaStream_t)stream);
 }
 

@@ -54,7 +54,8 @@ struct Params {
   int n_mels, mel_nnz;
   unsigned tiles_per_utt, n_tiles;
   int64_t L, wav_stride, T;
-  const float* wav;
+  const float* wav;        // float32 samples, or int16 PCM (PCM16 instantiation)
+  float scale;             // PCM16: sample value = scale * int16 (folded into the window table)
   const int64_t* offsets;  // ragged input: utterance b starts at wav + offsets[b] ...
   const int32_t* nsamples; // ... and holds nsamples[b] <= L samples (the rest of [0, L) is zero)
   const float* window;     // device, [400], zero-padded / centred to n_fft
@@ -77,7 +78,7 @@ __device__ __forceinline__ void cp_async8(float* smem_dst, const float* gsrc, in
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" ::"r"(d), "l"(gsrc), "r"(src_bytes)
                : "memory");
 }
-__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc, int src_bytes) {
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc, int src_bytes) {
   const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(d), "l"(gsrc), "r"(src_bytes)
                : "memory");
@@ -92,12 +93,48 @@ __device__ __forceinline__ void cp_async_wait() {
 // outside [0, L) are zero-filled by the copy engine (src-size < cp-size).
 // Chunk c = k*kThreads + tid covers samples i = 2c, 2c+1: with 80 chunks per hop and
 // kThreads = 4*80 the thread's sample / smem offsets are base + k*{640, 648}: immediates.
+template <bool PCM16>
 __device__ __forceinline__ void prefetch_tile(const Params& prm, int64_t b, int64_t t0, float* dst,
                                               int tid, int ibase, int dbase) {
   static_assert(kThreads == 4 * (kHop / 2), "chunk mapping assumes 4 hops per pass");
   const int64_t g0 = t0 * kHop - kNfft / 2;                 // even
-  const float* row = prm.wav + (prm.offsets ? __ldg(prm.offsets + b) : b * prm.wav_stride);
+  const int64_t row0 = prm.offsets ? __ldg(prm.offsets + b) : b * prm.wav_stride;
   const int64_t Lb = prm.nsamples ? (int64_t)__ldg(prm.nsamples + b) : prm.L;
+  const int lo = g0 < 0 ? (int)(-g0) : 0;                   // 0 or 200
+  const int64_t rem = Lb - g0;
+  const int hi = rem <= 0 ? 0 : (rem < kSpan ? (int)rem : kSpan);
+  if constexpr (PCM16) {
+    // same chunk mapping, 2 samples = 4 bytes per chunk; the staged span keeps the float
+    // layout's indices (pitch kPitch per hop) in 16-bit units
+    const int16_t* row = reinterpret_cast<const int16_t*>(prm.wav) + row0;
+    const int16_t* wsrc = row + g0;
+    int16_t* d16 = reinterpret_cast<int16_t*>(dst);
+    const bool al4 = (reinterpret_cast<uintptr_t>(row) & 3) == 0;
+    if (al4 && g0 >= 0 && g0 + kSpan <= Lb) {
+#pragma unroll
+      for (int k = 0; k < kCpIters; ++k)
+        if (k * kThreads + tid < kChunks)
+          cp_async4(d16 + dbase + k * (4 * kPitch), wsrc + ibase + k * (4 * kHop), 4);
+      return;
+    }
+    if (al4) {
+#pragma unroll 1
+      for (int k = 0; k < kCpIters; ++k) {
+        if (k * kThreads + tid < kChunks) {
+          const int i = ibase + k * (4 * kHop);
+          int n = hi - i;
+          n = (i < lo || n < 0) ? 0 : (n > 2 ? 2 : n);
+          cp_async4(d16 + dbase + k * (4 * kPitch), n ? (const void*)(wsrc + i) : (const void*)prm.window,
+                    2 * n);
+        }
+      }
+    } else {  // odd sample offset: plain 16-bit copies (ordered by the barrier that opens the tile)
+      for (int i = tid; i < kSpan; i += kThreads)
+        d16[i + (i / kHop) * kPad] = (i >= lo && i < hi) ? wsrc[i] : (int16_t)0;
+    }
+    return;
+  } else {
+  const float* row = prm.wav + row0;
   const float* wsrc = row + g0;                             // dereferenced inside [lo, hi) only
   const bool al8 = (reinterpret_cast<uintptr_t>(row) & 7) == 0;
   if (al8 && g0 >= 0 && g0 + kSpan <= Lb) {                 // interior tile: no guards at all
@@ -108,9 +145,6 @@ __device__ __forceinline__ void prefetch_tile(const Params& prm, int64_t b, int6
       if (k * kThreads + tid < kChunks) cp_async8(d + k * (4 * kPitch), src + k * (4 * kHop), 8);
     return;
   }
-  const int lo = g0 < 0 ? (int)(-g0) : 0;                   // 0 or 200
-  const int64_t rem = Lb - g0;
-  const int hi = rem <= 0 ? 0 : (rem < kSpan ? (int)rem : kSpan);
   if (al8) {
 #pragma unroll 1
     for (int k = 0; k < kCpIters; ++k) {
@@ -127,11 +161,13 @@ __device__ __forceinline__ void prefetch_tile(const Params& prm, int64_t b, int6
       cp_async4(dst + i + (i / kHop) * kPad, ok ? wsrc + i : prm.window, ok ? 4 : 0);
     }
   }
+  }
 }
 
 #ifndef SBFE_EXP_MINB
 #define SBFE_EXP_MINB 2
 #endif
+template <bool PCM16>
 __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(const __grid_constant__ Params prm) {
   extern __shared__ __align__(16) float smem[];
   float* s_a = smem;                       // 2 x [staged waveform | P[bin][32]]
@@ -156,7 +192,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
   unsigned tile = blockIdx.x;
   for (int i = tid; i < kTabW; i += kThreads) {
     const int n1 = i / 20, n2 = i - n1 * 20;   // window[i] is tap n1 of residue n2
-    s_tw[n2 * 20 + n1] = __ldg(prm.window + i);
+    s_tw[n2 * 20 + n1] = PCM16 ? __ldg(prm.window + i) * prm.scale : __ldg(prm.window + i);
     s_tt[i] = kTw400[i];
   }
   if (tid < kTabT2) s_t2[tid] = kT2[tid];
@@ -172,7 +208,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
   // (utterance, first frame) of the tile in flight: one division per tile, carried over
   unsigned nb = tile / prm.tiles_per_utt;
   int nt0 = (int)(tile - nb * prm.tiles_per_utt) * kTile;
-  if (tile < prm.n_tiles) prefetch_tile(prm, nb, nt0, s_a, tid, ibase, dbase);
+  if (tile < prm.n_tiles) prefetch_tile<PCM16>(prm, nb, nt0, s_a, tid, ibase, dbase);
   cp_async_commit();
   float db_scale = prm.db.scale, db_amin = prm.db.amin, db_off = prm.db.offset,
         db_floor = prm.db.floor_db;
@@ -199,7 +235,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
       nb = nxt / prm.tiles_per_utt;
       nt0 = (int)(nxt - nb * prm.tiles_per_utt) * kTile;
 #ifndef SBFE_EXP_NOPREFETCH
-      if (nxt < prm.n_tiles) prefetch_tile(prm, nb, nt0, s_a + ((it & 1) ^ 1) * kRegionA, tid, ibase, dbase);
+      if (nxt < prm.n_tiles) prefetch_tile<PCM16>(prm, nb, nt0, s_a + ((it & 1) ^ 1) * kRegionA, tid, ibase, dbase);
 #endif
       cp_async_commit();
     }
@@ -221,12 +257,21 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
           tw[4 * q] = c.x; tw[4 * q + 1] = c.y; tw[4 * q + 2] = c.z; tw[4 * q + 3] = c.w;
         }
       }
-      const float* xa = s_wave + p * kPitch + n2;
       f2 x[20];
+      if constexpr (PCM16) {   // int16 -> float is exact; the 2^-15 scale sits in the window taps
+        const int16_t* xa = reinterpret_cast<const int16_t*>(s_wave) + p * kPitch + n2;
 #pragma unroll
-      for (int n1 = 0; n1 < 20; ++n1) {
-        const int off = 20 * n1 + ((20 * n1) / kHop) * kPad;  // n2 < 20 never crosses a hop boundary
-        x[n1] = mk2(xa[off], xa[off + kPairs * kPitch]);
+        for (int n1 = 0; n1 < 20; ++n1) {
+          const int off = 20 * n1 + ((20 * n1) / kHop) * kPad;
+          x[n1] = mk2((float)xa[off], (float)xa[off + kPairs * kPitch]);
+        }
+      } else {
+        const float* xa = s_wave + p * kPitch + n2;
+#pragma unroll
+        for (int n1 = 0; n1 < 20; ++n1) {
+          const int off = 20 * n1 + ((20 * n1) / kHop) * kPad;  // n2 < 20 never crosses a hop boundary
+          x[n1] = mk2(xa[off], xa[off + kPairs * kPitch]);
+        }
       }
       cx<f2> Y[11];
       rdft20<true>(x, wv, Y);
@@ -492,9 +537,10 @@ bool fbank400_v3_supported(const sbfe_fbank_desc* d) {
          v3::smem_floats(d->n_mels, d->mel_nnz) * sizeof(float) <= (size_t)v3::kMaxSmem;
 }
 
-int launch_fbank400_v3(const sbfe_fbank_desc* d, const float* wav, const int64_t* offsets,
-                       const int32_t* nsamples, int64_t B, int64_t L, int64_t wav_stride, float* out,
-                       sbfe_maxkey_t* utt_max, float* tile_stats, cudaStream_t stream) {
+int launch_fbank400_v3(const sbfe_fbank_desc* d, const void* wav, int pcm16, float scale,
+                       const int64_t* offsets, const int32_t* nsamples, int64_t B, int64_t L,
+                       int64_t wav_stride, float* out, sbfe_maxkey_t* utt_max, float* tile_stats,
+                       cudaStream_t stream) {
   using namespace v3;
   Params prm;
   prm.db = DbParams{d->multiplier * 0.30102999566398120f, d->amin, d->db_offset, d->floor_db,
@@ -504,7 +550,8 @@ int launch_fbank400_v3(const sbfe_fbank_desc* d, const float* wav, const int64_t
   prm.L = L;
   prm.wav_stride = wav_stride;
   prm.T = 1 + L / kHop;
-  prm.wav = wav;
+  prm.wav = reinterpret_cast<const float*>(wav);
+  prm.scale = scale;
   prm.offsets = offsets;
   prm.nsamples = nsamples;
   prm.window = d->d_window;
@@ -525,15 +572,19 @@ int launch_fbank400_v3(const sbfe_fbank_desc* d, const float* wav, const int64_t
   cudaGetDevice(&dev);
   int sms = (dev >= 0 && dev < 64) ? n_sm[dev] : 0;
   if (sms == 0) {
-    cudaError_t e = cudaFuncSetAttribute(fbank400_v3_kernel,
+    cudaError_t e = cudaFuncSetAttribute(fbank400_v3_kernel<false>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(fbank400_v3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               kMaxSmem);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (e != cudaSuccess) return (int)e;
     if (dev >= 0 && dev < 64) n_sm[dev] = sms;
   }
   // persistent: two CTAs per SM, each strides over the tiles
   const unsigned grid = prm.n_tiles < (unsigned)(2 * sms) ? prm.n_tiles : (unsigned)(2 * sms);
-  return launch_pdl(fbank400_v3_kernel, dim3(grid), dim3(kThreads), (size_t)smem, stream, prm);
+  return launch_pdl(pcm16 ? fbank400_v3_kernel<true> : fbank400_v3_kernel<false>, dim3(grid),
+                    dim3(kThreads), (size_t)smem, stream, prm);
 }
 
 }  // namespace sbfe

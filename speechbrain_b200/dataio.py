@@ -6,6 +6,12 @@ the padding over PCIe with ``batch.to(device)``.  ``RaggedBatch`` keeps only the
 in ONE pinned host buffer, uploads that, and hands the fused Fbank kernel per-utterance
 offsets; the kernel's copy engine zero-fills the padding on the fly, so the padded ``[B, L]``
 tensor is never materialised and the features are bit-identical to the padded path.
+
+16-bit PCM (what the audio files hold; the reference's ``read_audio`` converts to float32 on
+the CPU, speechbrain/dataio/dataio.py, and then ships 4 bytes per sample) can stay int16 until
+it is on the device: ``RaggedBatch.from_list`` of int16 tensors keeps them packed as int16 and
+the fused kernel converts while it stages the samples (``scale`` = 1/32768, exact), halving
+the PCIe bytes again; results are bit-identical to the float32 route.
 """
 import torch
 
@@ -17,15 +23,17 @@ _ALIGN = 4  # samples: 16-byte aligned utterance starts
 class RaggedBatch:
     """Packed variable-length waveforms.
 
-    Attributes: ``packed`` float32 ``[n]``, ``offsets`` int64 ``[B]``, ``nsamples`` int32
+    Attributes: ``packed`` float32 (or int16 PCM, value = ``scale`` * sample) ``[n]``,
+    ``offsets`` int64 ``[B]``, ``nsamples`` int32
     ``[B]`` (all on one device), ``max_len`` = L of the equivalent padded batch, ``lengths``
     float32 ``[B]`` relative lengths (what ``InputNormalization`` / the recipes call
     ``wav_lens``).
     """
 
-    def __init__(self, packed, offsets, nsamples, max_len, lengths):
+    def __init__(self, packed, offsets, nsamples, max_len, lengths, scale=1.0 / 32768):
         self.packed, self.offsets, self.nsamples = packed, offsets, nsamples
         self.max_len, self.lengths = int(max_len), lengths
+        self.scale = float(scale)  # only meaningful for int16 samples
 
     @property
     def device(self):
@@ -38,7 +46,7 @@ class RaggedBatch:
     @property
     def nbytes(self):
         """Bytes that cross PCIe when this batch is uploaded."""
-        return (self.packed.numel() * 4 + self.offsets.numel() * 8 + self.nsamples.numel() * 4
+        return (self.packed.numel() * self.packed.element_size() + self.offsets.numel() * 8 + self.nsamples.numel() * 4
                 + self.lengths.numel() * 4)
 
     @staticmethod
@@ -52,10 +60,12 @@ class RaggedBatch:
 
     @classmethod
     def from_list(cls, wavs, pin_memory=True):
-        """Host-side collate: list of 1-D float tensors -> packed batch in (pinned) host memory."""
+        """Host-side collate: list of 1-D float (or all-int16 PCM) tensors -> packed batch in
+        (pinned) host memory."""
         sizes = [int(w.numel()) for w in wavs]
         offsets, total = cls.layout(sizes)
-        packed = torch.zeros(total, dtype=torch.float32, pin_memory=pin_memory)
+        pcm = len(wavs) > 0 and all(w.dtype == torch.int16 for w in wavs)
+        packed = torch.zeros(total, dtype=torch.int16 if pcm else torch.float32, pin_memory=pin_memory)
         for w, o, n in zip(wavs, offsets, sizes):
             packed[o:o + n] = w.reshape(-1)
         max_len = max(sizes) if sizes else 0
@@ -79,11 +89,11 @@ class RaggedBatch:
         """Upload (one large + three tiny copies)."""
         mv = lambda t: t.to(device, non_blocking=non_blocking)  # noqa: E731
         return RaggedBatch(mv(self.packed), mv(self.offsets), mv(self.nsamples), self.max_len,
-                           mv(self.lengths))
+                           mv(self.lengths), self.scale)
 
     def to_padded(self):
         """Materialise the zero-padded ``[B, L]`` tensor (fallback / tests)."""
         out = torch.zeros((self.batch_size, self.max_len), dtype=torch.float32, device=self.device)
         for i, (o, n) in enumerate(zip(self.offsets.tolist(), self.nsamples.tolist())):
-            out[i, :n] = self.packed[o:o + n]
-        return out
+            out[i, :n] = self.packed[o:o + n]      # int16 -> float32 is exact
+        return out * self.scale if self.packed.dtype == torch.int16 else out

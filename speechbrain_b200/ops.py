@@ -167,7 +167,8 @@ def fbank_forward(tables, wav, tile_stats=False):
     if hasattr(wav, "packed"):
         ragged = wav
         _require_cuda(ragged.packed, "wav")
-        if ragged.packed.dtype != torch.float32 or not ragged_supported(tables, ragged.device):
+        if ragged.packed.dtype not in (torch.float32, torch.int16) or not ragged_supported(
+                tables, ragged.device):
             wav, ragged = ragged.to_padded(), None
     if ragged is not None:
         B, L, dev_ = ragged.batch_size, ragged.max_len, ragged.device
@@ -191,7 +192,11 @@ def fbank_forward(tables, wav, tile_stats=False):
     # with tile records the utterance maximum travels in them: no atomics, no memset
     utt_max = None if ts is not None else torch.zeros((B,), dtype=torch.int32, device=wav.device)
     with torch.cuda.device(wav.device):
-        if ragged is not None:
+        if ragged is not None and wav.dtype == torch.int16:
+            check(L_.sbfe_fbank_forward_ragged_pcm16(C.byref(desc), _ptr(wav), _ptr(ragged.offsets),
+                                                     _ptr(ragged.nsamples), B, L, ragged.scale,
+                                                     _ptr(out), _ptr(utt_max), _ptr(ts), _stream()))
+        elif ragged is not None:
             check(L_.sbfe_fbank_forward_ragged(C.byref(desc), _ptr(wav), _ptr(ragged.offsets),
                                                _ptr(ragged.nsamples), B, L, _ptr(out),
                                                _ptr(utt_max), _ptr(ts), _stream()))

@@ -260,6 +260,46 @@ def test_ragged_ingest_is_bit_identical(sb):
     assert torch.equal(fb(rb2), b)
 
 
+def test_pcm16_ingest_is_bit_identical(sb, golden):
+    """16-bit PCM kept as int16 until the fused kernel stages it (scale 2^-15 folded into the
+    window) == the same samples converted to float32 on the host, bit for bit."""
+    from speechbrain_b200 import ops
+
+    rng = np.random.default_rng(10)
+    sizes = [48000, 31999, 160, 47777, 1, 0, 20481]
+    pcm = [torch.from_numpy(np.clip(np.rint(rng.standard_normal(n) * 3000), -32768, 32767).astype(np.int16))
+           for n in sizes]
+    pcm[0][:5] = torch.tensor([32767, -32768, 0, 1, -1], dtype=torch.int16)
+    rb16 = sb.RaggedBatch.from_list(pcm, pin_memory=False)
+    assert rb16.packed.dtype == torch.int16 and rb16.nbytes < 2 * sum(sizes) + 200
+    rb32 = sb.RaggedBatch.from_list([w.float() / 32768 for w in pcm], pin_memory=False)
+    rb16, rb32 = rb16.to("cuda"), rb32.to("cuda")
+    assert torch.equal(rb16.to_padded(), rb32.to_padded())
+    for mod in (sb.Fbank(n_mels=80), sb.Fbank(n_mels=40, deltas=True), sb.MFCC()):
+        assert torch.equal(mod(rb16), mod(rb32)), type(mod).__name__
+    fb, norm = sb.Fbank(n_mels=80), sb.InputNormalization(norm_type="sentence")
+    assert torch.allclose(norm(fb(rb16), rb16.lengths), norm(fb(rb32), rb32.lengths), rtol=0, atol=0,
+                          equal_nan=True)
+    # a buffer that starts at an odd sample (2-byte aligned only): the un-vectorised staging path
+    shifted = torch.zeros(rb16.packed.numel() + 1, dtype=torch.int16, device="cuda")
+    shifted[1:] = rb16.packed
+    odd = sb.RaggedBatch(shifted[1:], rb16.offsets, rb16.nsamples, rb16.max_len, rb16.lengths)
+    assert odd.packed.data_ptr() % 4 == 2
+    assert torch.equal(fb(odd), fb(rb32))
+    # real speech from the reference's test sample, as the int16 PCM the file holds
+    import golden_cases as gcases
+
+    speech = torch.from_numpy(np.load(gcases.SPEECH_NPZ)["pcm"].astype(np.int16))
+    a = fb(sb.RaggedBatch.from_list([speech, speech[:9000]], pin_memory=False).to("cuda"))
+    b = fb(sb.RaggedBatch.from_list([speech.float() / 32768, speech[:9000].float() / 32768],
+                                    pin_memory=False).to("cuda"))
+    assert torch.equal(a, b)
+    # a scale that is not a power of two still works (no longer bit-identical, 1-ulp level)
+    rb16.scale = 1.0 / 30000
+    want = fb(rb16.to_padded())
+    torch.testing.assert_close(fb(rb16), want, rtol=0, atol=2e-4)
+
+
 # ---- torch.jit.trace, as the reference's unit tests do (tests/unittests/test_features.py:
 # 14, 39, 56, 66, 97, 107): the traced module must replay the CUDA kernels, not a constant ----
 def test_modules_survive_jit_trace(sb):
