@@ -232,55 +232,91 @@ __global__ void post_fast_kernel(const PostParams p) {
   const int64_t d_lo = t0 - ctxl - n1;
   const int64_t o_lo = t0 - ctxl;
 
+  // staging loops walk (row, feature) incrementally from the thread's first element: one integer
+  // division per thread and phase instead of one per element, 32-bit row arithmetic
+  const int Ti = (int)T, base_lo_i = (int)base_lo, d_lo_i = (int)d_lo, o_lo_i = (int)o_lo;
   float* s_stage = p.dct ? s_in : s_base;
-  for (int i = threadIdx.x; i < fr_b * p.F_in; i += nthr) {
-    const int r = i / p.F_in, f = i - r * p.F_in;
-    int64_t u = base_lo + r;
-    u = u < 0 ? 0 : (u > T - 1 ? T - 1 : u);
-    s_stage[i] = fmaxf(__ldg(xb + u * p.F_in + f), floor_b);
+  {
+    int r = threadIdx.x / p.F_in, f = threadIdx.x - r * p.F_in;
+    const int dr = nthr / p.F_in, df = nthr - dr * p.F_in;
+    while (r < fr_b) {
+      int u = base_lo_i + r;
+      u = u < 0 ? 0 : (u > Ti - 1 ? Ti - 1 : u);
+      s_stage[r * p.F_in + f] = fmaxf(__ldg(xb + (int64_t)u * p.F_in + f), floor_b);
+      r += dr; f += df;
+      if (f >= p.F_in) { f -= p.F_in; ++r; }
+    }
   }
   if (p.dct)
     for (int i = threadIdx.x; i < p.F_in * p.F0; i += nthr) s_dct[i] = __ldg(p.dct + i);
   __syncthreads();
   if (p.dct) {
-    for (int i = threadIdx.x; i < fr_b * p.F0; i += nthr) {
-      const int r = i / p.F0, j = i - r * p.F0;
-      const float* row = s_in + r * p.F_in;
-      float acc = 0.f;
-      for (int m = 0; m < p.F_in; ++m) acc = fmaf(row[m], s_dct[m * p.F0 + j], acc);
-      s_base[i] = acc;
+    if ((p.F0 & 3) == 0) {
+      // thread = (row, 4 coefficients): one row value + one 128-bit matrix load per 4 FMAs
+      const int jg = p.F0 >> 2;
+      for (int i = threadIdx.x; i < fr_b * jg; i += nthr) {
+        const int r = i / jg, j4 = (i - r * jg) * 4;
+        const float* row = s_in + r * p.F_in;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int m = 0; m < p.F_in; ++m) {
+          const float xv = row[m];
+          const float4 w = *reinterpret_cast<const float4*>(s_dct + m * p.F0 + j4);
+          acc.x = fmaf(xv, w.x, acc.x); acc.y = fmaf(xv, w.y, acc.y);
+          acc.z = fmaf(xv, w.z, acc.z); acc.w = fmaf(xv, w.w, acc.w);
+        }
+        float* dst = s_base + r * p.F0 + j4;
+        dst[0] = acc.x; dst[1] = acc.y; dst[2] = acc.z; dst[3] = acc.w;
+      }
+    } else {
+      const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nwarps = nthr >> 5;
+      for (int r = wid; r < fr_b; r += nwarps) {
+        const float* row = s_in + r * p.F_in;
+        for (int j = lane; j < p.F0; j += 32) {
+          float acc = 0.f;
+          for (int m = 0; m < p.F_in; ++m) acc = fmaf(row[m], s_dct[m * p.F0 + j], acc);
+          s_base[r * p.F0 + j] = acc;
+        }
+      }
     }
     __syncthreads();
   }
+  const int r_first = threadIdx.x / p.F0, f_first = threadIdx.x - r_first * p.F0;
+  const int dr0 = nthr / p.F0, df0 = nthr - dr0 * p.F0;
   if (p.deltas) {
-    for (int i = threadIdx.x; i < fr_d * p.F0; i += nthr) {
-      const int r = i / p.F0, f = i - r * p.F0;
-      int64_t v = d_lo + r;
-      v = v < 0 ? 0 : (v > T - 1 ? T - 1 : v);
-      const float* col = s_base + (v - base_lo) * p.F0 + f;
+    int r = r_first, f = f_first;
+    while (r < fr_d) {
+      int v = d_lo_i + r;
+      v = v < 0 ? 0 : (v > Ti - 1 ? Ti - 1 : v);
+      const float* col = s_base + (v - base_lo_i) * p.F0 + f;
       float acc = 0.f;
       for (int k = 1; k <= p.n; ++k) acc = fmaf((float)k, col[k * p.F0] - col[-k * p.F0], acc);
-      s_d[i] = acc * p.inv_denom;
+      s_d[r * p.F0 + f] = acc * p.inv_denom;
+      r += dr0; f += df0;
+      if (f >= p.F0) { f -= p.F0; ++r; }
     }
     __syncthreads();
   }
   // feature rows [base | d | dd] (deltas == 1), [d] (deltas == 2) or [base]
-  for (int i = threadIdx.x; i < fr_out * p.F0; i += nthr) {
-    const int r = i / p.F0, f = i - r * p.F0;
-    float* dst = s_feat + r * P + f;
-    if (p.deltas == 2) {
-      dst[0] = s_d[(r + n1) * p.F0 + f];
-    } else {
-      dst[0] = s_base[(r + n2) * p.F0 + f];
-      if (p.deltas == 1) {
-        dst[p.F0] = s_d[(r + n1) * p.F0 + f];
-        int64_t v = o_lo + r;
-        v = v < 0 ? 0 : (v > T - 1 ? T - 1 : v);
-        const float* col = s_d + (v - d_lo) * p.F0 + f;
-        float acc = 0.f;
-        for (int k = 1; k <= p.n; ++k) acc = fmaf((float)k, col[k * p.F0] - col[-k * p.F0], acc);
-        dst[2 * p.F0] = acc * p.inv_denom;
+  {
+    int r = r_first, f = f_first;
+    while (r < fr_out) {
+      float* dst = s_feat + r * P + f;
+      if (p.deltas == 2) {
+        dst[0] = s_d[(r + n1) * p.F0 + f];
+      } else {
+        dst[0] = s_base[(r + n2) * p.F0 + f];
+        if (p.deltas == 1) {
+          dst[p.F0] = s_d[(r + n1) * p.F0 + f];
+          int v = o_lo_i + r;
+          v = v < 0 ? 0 : (v > Ti - 1 ? Ti - 1 : v);
+          const float* col = s_d + (v - d_lo_i) * p.F0 + f;
+          float acc = 0.f;
+          for (int k = 1; k <= p.n; ++k) acc = fmaf((float)k, col[k * p.F0] - col[-k * p.F0], acc);
+          dst[2 * p.F0] = acc * p.inv_denom;
+        }
       }
+      r += dr0; f += df0;
+      if (f >= p.F0) { f -= p.F0; ++r; }
     }
   }
   __syncthreads();
@@ -300,18 +336,33 @@ __global__ void post_fast_kernel(const PostParams p) {
       off[q] = c * P + f;
       cc[q] = c;
     }
-    for (int t = g; t < nvalid; t += groups) {
-      const float* row = s_feat + t * P;
-      float4 r;
-      r.x = row[off[0]]; r.y = row[off[1]]; r.z = row[off[2]]; r.w = row[off[3]];
-      if (!interior) {
-        const int64_t u0 = o_lo + t;
-        if (u0 + cc[0] < 0 || u0 + cc[0] >= T) r.x = 0.f;
-        if (u0 + cc[1] < 0 || u0 + cc[1] >= T) r.y = 0.f;
-        if (u0 + cc[2] < 0 || u0 + cc[2] >= T) r.z = 0.f;
-        if (u0 + cc[3] < 0 || u0 + cc[3] >= T) r.w = 0.f;
+    // four source pointers and the destination advance by constants: no multiplies in the loop
+    const float* s0 = s_feat + g * P + off[0];
+    const float* s1 = s_feat + g * P + off[1];
+    const float* s2 = s_feat + g * P + off[2];
+    const float* s3 = s_feat + g * P + off[3];
+    float* o = ob + (int64_t)g * F_out + 4 * v;
+    const int sstep = groups * P;
+    const int64_t ostep = (int64_t)groups * F_out;
+    if (interior) {
+#pragma unroll 4
+      for (int t = g; t < nvalid; t += groups) {
+        *reinterpret_cast<float4*>(o) = make_float4(*s0, *s1, *s2, *s3);
+        s0 += sstep; s1 += sstep; s2 += sstep; s3 += sstep;
+        o += ostep;
       }
-      *reinterpret_cast<float4*>(ob + (int64_t)t * F_out + 4 * v) = r;
+    } else {
+      for (int t = g; t < nvalid; t += groups) {
+        float4 r = make_float4(*s0, *s1, *s2, *s3);
+        const int u0 = o_lo_i + t;
+        if (u0 + cc[0] < 0 || u0 + cc[0] >= Ti) r.x = 0.f;
+        if (u0 + cc[1] < 0 || u0 + cc[1] >= Ti) r.y = 0.f;
+        if (u0 + cc[2] < 0 || u0 + cc[2] >= Ti) r.z = 0.f;
+        if (u0 + cc[3] < 0 || u0 + cc[3] >= Ti) r.w = 0.f;
+        *reinterpret_cast<float4*>(o) = r;
+        s0 += sstep; s1 += sstep; s2 += sstep; s3 += sstep;
+        o += ostep;
+      }
     }
   }
 }
