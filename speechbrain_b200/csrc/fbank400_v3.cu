@@ -224,6 +224,25 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
   const int st_t1 = tid / M, st_m1 = tid - st_t1 * M;
   const int st_dt1 = kThreads / M, st_dm1 = kThreads - st_dt1 * M;
 
+  // stage-3 plan of this thread (tile-invariant): its four filters' group counts, weight and
+  // power-row offsets.  Odd slots run backwards over the units: filters widen with m, so unit u
+  // gets (narrow, wide, narrow, wide)-ish work and the warps reach the barrier together.  The
+  // warp's two filters (2k, 2k+1) store the same number of 4-weight groups (mel_pad4 == 2), so
+  // the trip count is warp-uniform (a uniform register): no divergence bookkeeping.
+  auto mel_plan = [&](int mb, int (&G)[4], int (&W)[4], int (&P)[4]) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int m = mb + i * kUnits + ((i & 1) ? kUnits - 1 - unit : unit);
+      const int2 meta = m < M ? s_meta[m] : make_int2(0, 0);
+      G[i] = __reduce_max_sync(0xffffffffu, ((meta.x >> 16) + 3) >> 2);
+      W[i] = meta.y;
+      P[i] = (meta.x & 0xffff) * kPairs;
+    }
+  };
+  int planG[4], planW[4], planP[4];
+  __syncthreads();   // s_meta is complete
+  mel_plan(0, planG, planW, planP);
+
 #pragma unroll 1
   for (int it = 0; tile < prm.n_tiles; ++it, tile += gridDim.x) {
     float* s_wave = s_a + (it & 1) * kRegionA;
@@ -377,17 +396,17 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
         const float4* wt[4];
         const float2* pp[4];
         f2 acc[4];
+        int W[4], P[4];
+        if (mb == 0) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) { G[i] = planG[i]; W[i] = planW[i]; P[i] = planP[i]; }
+        } else {
+          mel_plan(mb, G, W, P);   // M > 80: the later passes plan on the fly
+        }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          // odd slots run backwards over the units: filters widen with m, so unit u gets
-          // (narrow, wide, narrow, wide)-ish work and the warps reach the barrier together
-          const int m = mb + i * kUnits + ((i & 1) ? kUnits - 1 - unit : unit);
-          const int2 meta = m < M ? s_meta[m] : make_int2(0, 0);
-          // the warp's two filters (2k, 2k+1) store the same number of 4-weight groups
-          // (mel_pad4 == 2), so the trip count is warp-uniform: no divergence bookkeeping
-          G[i] = __reduce_max_sync(0xffffffffu, ((meta.x >> 16) + 3) >> 2);
-          wt[i] = reinterpret_cast<const float4*>(s_w + meta.y);
-          pp[i] = pp0 + (meta.x & 0xffff) * kPairs;
+          wt[i] = reinterpret_cast<const float4*>(s_w + W[i]);
+          pp[i] = pp0 + P[i];
           acc[i] = mk2(0.f, 0.f);
         }
 #define SBFE_MEL_GROUP(i, g)                                                    \

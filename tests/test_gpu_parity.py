@@ -260,6 +260,31 @@ def test_ragged_ingest_is_bit_identical(sb):
     assert torch.equal(fb(rb2), b)
 
 
+@pytest.mark.parametrize("n_mels", [96, 128, 161])
+def test_more_than_eighty_filters(sb, n_mels):
+    """n_mels > 80: the fused kernel's mel stage takes several passes of 80 filters (the
+    tile-invariant plan only covers the first); checked against the float64 oracle."""
+    rng = np.random.default_rng(n_mels)
+    wav = (rng.standard_normal((3, 16000 + 53)) * 0.1).astype(np.float32)
+    wav[1, 9000:] = 0
+    fb = sb.Fbank(n_mels=n_mels)
+    got = fb(dev(wav)).cpu().numpy()
+    consts = (fb.compute_fbanks.f_central.numpy(), fb.compute_fbanks.band.numpy())
+    want = onp.fbank(wav, n_mels=n_mels, dtype=np.float64, mel_params=consts,
+                     window=fb.compute_STFT.window.numpy())
+    assert got.shape == want.shape == (3, 101, n_mels)
+    assert np.abs(got - want).max() < 1e-3   # dB; fp32 FFT + lg2.approx vs float64
+    norm = sb.InputNormalization(norm_type="sentence")
+    lens = torch.tensor([1.0, 0.6, 1.0]).cuda()
+    a = norm(fb(dev(wav)), lens).cpu().numpy()
+    b = onp.InputNormalizationOracle(norm_type="sentence")(want.copy(), [1.0, 0.6, 1.0])
+    # a column the top_db clamp made constant has zero variance: (rounding noise) / eps is
+    # arbitrary in every implementation, the reference's float32 included - not compared
+    live = want[:, :60].std(axis=1) > 1e-3                    # [B, M]
+    assert live.mean() > 0.9
+    assert np.abs(a - b)[np.broadcast_to(live[:, None, :], a.shape)].max() < 1e-3
+
+
 def test_pcm16_ingest_is_bit_identical(sb, golden):
     """16-bit PCM kept as int16 until the fused kernel stages it (scale 2^-15 folded into the
     window) == the same samples converted to float32 on the host, bit for bit."""
