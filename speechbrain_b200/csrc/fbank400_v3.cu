@@ -207,7 +207,10 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
   pdl_wait();  // from here on the waveform is read and out / tile records are written
   // (utterance, first frame) of the tile in flight: one division per tile, carried over
   unsigned nb = tile / prm.tiles_per_utt;
-  int nt0 = (int)(tile - nb * prm.tiles_per_utt) * kTile;
+  unsigned nj = tile - nb * prm.tiles_per_utt;               // tile index inside the utterance
+  const unsigned step_b = gridDim.x / prm.tiles_per_utt;     // a grid stride in (utterance, tile)
+  const unsigned step_j = gridDim.x - step_b * prm.tiles_per_utt;
+  int nt0 = (int)nj * kTile;
   if (tile < prm.n_tiles) prefetch_tile<PCM16>(prm, nb, nt0, s_a, tid, ibase, dbase);
   cp_async_commit();
   float db_scale = prm.db.scale, db_amin = prm.db.amin, db_off = prm.db.offset,
@@ -221,6 +224,14 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
   // stage-4 walk of this thread over the [frames][M] tile (vector / scalar), tile-invariant
   const int st_t4 = (tid * 4) / M, st_m4 = tid * 4 - st_t4 * M;
   const int st_dt4 = (kThreads * 4) / M, st_dm4 = kThreads * 4 - st_dt4 * M;
+  // M <= 80 (at most two vectors per thread): their shared-memory offsets, resolved once
+  const bool st_two = (M & 3) == 0 && kTile * M <= 8 * kThreads;
+  int st_so0 = st_t4 * opitch + st_m4, st_so1;
+  {
+    int t = st_t4 + st_dt4, m = st_m4 + st_dm4;
+    if (m >= M) { m -= M; ++t; }
+    st_so1 = t * opitch + m;
+  }
   const int st_t1 = tid / M, st_m1 = tid - st_t1 * M;
   const int st_dt1 = kThreads / M, st_dm1 = kThreads - st_dt1 * M;
 
@@ -251,8 +262,10 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
     {  // next tile's waveform flies while this one is transformed
       const unsigned nxt = tile + gridDim.x;
       if (nxt >= prm.n_tiles) pdl_launch_dependents();  // last tile of this CTA: let the next kernel in
-      nb = nxt / prm.tiles_per_utt;
-      nt0 = (int)(nxt - nb * prm.tiles_per_utt) * kTile;
+      nb += step_b;
+      nj += step_j;
+      if (nj >= prm.tiles_per_utt) { nj -= prm.tiles_per_utt; ++nb; }
+      nt0 = (int)nj * kTile;
 #ifndef SBFE_EXP_NOPREFETCH
       if (nxt < prm.n_tiles) prefetch_tile<PCM16>(prm, nb, nt0, s_a + ((it & 1) ^ 1) * kRegionA, tid, ibase, dbase);
 #endif
@@ -472,7 +485,17 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
       const int nvalid = left < kTile ? (int)left : kTile;
       float* o = prm.out + (b * prm.T + t0) * M;
       const int total = nvalid * M;
-      if ((M & 3) == 0 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+      if (st_two && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+        const int e0 = tid * 4, e1 = e0 + kThreads * 4;
+        if (e0 < total) {
+          const float* s = s_o + st_so0;
+          *reinterpret_cast<float4*>(o + e0) = make_float4(s[0], s[1], s[2], s[3]);
+        }
+        if (e1 < total) {
+          const float* s = s_o + st_so1;
+          *reinterpret_cast<float4*>(o + e1) = make_float4(s[0], s[1], s[2], s[3]);
+        }
+      } else if ((M & 3) == 0 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
         int e = tid * 4;
         int t = st_t4, m = st_m4;
         const int dt = st_dt4, dm = st_dm4;
@@ -531,7 +554,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
           mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
         }
         if (live) {
-          const float inv = 1.f / (float)nvalid;
+          const float inv = nvalid == kTile ? 1.f / kTile : 1.f / (float)nvalid;
           if (q == 0) ts[m] = fmaf(s1, inv, x0);
           if (q == 1) ts[M + m] = fmaxf(fmaf(-s1 * inv, s1, s2), 0.f);
           if (q == 2) ts[2 * M + m] = mn;
