@@ -93,8 +93,10 @@ __device__ __forceinline__ void cp_async_wait() {
 // outside [0, L) are zero-filled by the copy engine (src-size < cp-size).
 // Chunk c = k*kThreads + tid covers samples i = 2c, 2c+1: with 80 chunks per hop and
 // kThreads = 4*80 the thread's sample / smem offsets are base + k*{640, 648}: immediates.
+// Returns true when the staging used the aligned chunk mapping (thread -> chunks k*kThreads + tid),
+// which lets a thread look at its own copies before the barrier (all-zero tile detection).
 template <bool PCM16>
-__device__ __forceinline__ void prefetch_tile(const Params& prm, int64_t b, int64_t t0, float* dst,
+__device__ __forceinline__ bool prefetch_tile(const Params& prm, int64_t b, int64_t t0, float* dst,
                                               int tid, int ibase, int dbase) {
   static_assert(kThreads == 4 * (kHop / 2), "chunk mapping assumes 4 hops per pass");
   const int64_t g0 = t0 * kHop - kNfft / 2;                 // even
@@ -115,7 +117,7 @@ __device__ __forceinline__ void prefetch_tile(const Params& prm, int64_t b, int6
       for (int k = 0; k < kCpIters; ++k)
         if (k * kThreads + tid < kChunks)
           cp_async4(d16 + dbase + k * (4 * kPitch), wsrc + ibase + k * (4 * kHop), 4);
-      return;
+      return true;
     }
     if (al4) {
 #pragma unroll 1
@@ -132,7 +134,7 @@ __device__ __forceinline__ void prefetch_tile(const Params& prm, int64_t b, int6
       for (int i = tid; i < kSpan; i += kThreads)
         d16[i + (i / kHop) * kPad] = (i >= lo && i < hi) ? wsrc[i] : (int16_t)0;
     }
-    return;
+    return al4;
   } else {
   const float* row = prm.wav + row0;
   const float* wsrc = row + g0;                             // dereferenced inside [lo, hi) only
@@ -143,7 +145,7 @@ __device__ __forceinline__ void prefetch_tile(const Params& prm, int64_t b, int6
 #pragma unroll
     for (int k = 0; k < kCpIters; ++k)
       if (k * kThreads + tid < kChunks) cp_async8(d + k * (4 * kPitch), src + k * (4 * kHop), 8);
-    return;
+    return true;
   }
   if (al8) {
 #pragma unroll 1
@@ -161,6 +163,7 @@ __device__ __forceinline__ void prefetch_tile(const Params& prm, int64_t b, int6
       cp_async4(dst + i + (i / kHop) * kPad, ok ? wsrc + i : prm.window, ok ? 4 : 0);
     }
   }
+  return al8;
   }
 }
 
@@ -211,7 +214,8 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
   const unsigned step_b = gridDim.x / prm.tiles_per_utt;     // a grid stride in (utterance, tile)
   const unsigned step_j = gridDim.x - step_b * prm.tiles_per_utt;
   int nt0 = (int)nj * kTile;
-  if (tile < prm.n_tiles) prefetch_tile<PCM16>(prm, nb, nt0, s_a, tid, ibase, dbase);
+  bool chunked = false, nxt_chunked = false;   // staging mode of the current / next tile (uniform)
+  if (tile < prm.n_tiles) nxt_chunked = prefetch_tile<PCM16>(prm, nb, nt0, s_a, tid, ibase, dbase);
   cp_async_commit();
   float db_scale = prm.db.scale, db_amin = prm.db.amin, db_off = prm.db.offset,
         db_floor = prm.db.floor_db;
@@ -259,6 +263,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
     float* s_wave = s_a + (it & 1) * kRegionA;
     const int64_t b = nb;
     const int64_t t0 = nt0;
+    chunked = nxt_chunked;
     {  // next tile's waveform flies while this one is transformed
       const unsigned nxt = tile + gridDim.x;
       if (nxt >= prm.n_tiles) pdl_launch_dependents();  // last tile of this CTA: let the next kernel in
@@ -267,12 +272,61 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
       if (nj >= prm.tiles_per_utt) { nj -= prm.tiles_per_utt; ++nb; }
       nt0 = (int)nj * kTile;
 #ifndef SBFE_EXP_NOPREFETCH
-      if (nxt < prm.n_tiles) prefetch_tile<PCM16>(prm, nb, nt0, s_a + ((it & 1) ^ 1) * kRegionA, tid, ibase, dbase);
+      if (nxt < prm.n_tiles)
+        nxt_chunked = prefetch_tile<PCM16>(prm, nb, nt0, s_a + ((it & 1) ^ 1) * kRegionA, tid, ibase, dbase);
 #endif
       cp_async_commit();
     }
     cp_async_wait<1>();
-    __syncthreads();  // this tile's span (all threads' copies) is in smem; s_e / s_o are free
+    // ---- all-zero span (padding behind the utterance, digital silence): the transform of zeros
+    // is zero, every output is exactly the floor (or 0 for linear mel) - write that and move on.
+    // Each thread probes the first chunk it staged itself (visible to it after wait_group); the
+    // vote rides on the barrier that opens the tile; only a tile whose probes are all zero pays
+    // for the full check.  Bit-identical to the full path: 0 * w accumulates to +0, +0 <= amin.
+    {
+      auto chunk_nonzero = [&](int k) -> int {
+        if constexpr (PCM16) {
+          return *reinterpret_cast<const int*>(reinterpret_cast<const int16_t*>(s_wave) + dbase +
+                                               k * (4 * kPitch)) != 0;
+        } else {
+          const float2 v = *reinterpret_cast<const float2*>(s_wave + dbase + k * (4 * kPitch));
+          return (v.x != 0.f) | (v.y != 0.f);
+        }
+      };
+      int nz = chunked ? chunk_nonzero(0) : 1;
+      // the barrier: this tile's span (all threads' copies) is in smem; s_e / s_o are free
+      if (__syncthreads_or(nz) == 0) {
+        nz = 0;
+#pragma unroll 1
+        for (int k = 1; k < kCpIters; ++k)
+          if (k * kThreads + tid < kChunks) nz |= chunk_nonzero(k);
+        if (__syncthreads_or(nz) == 0) {
+          const int64_t left = prm.T - t0;
+          const int nvalid = left < kTile ? (int)left : kTile;
+          const float v = log_mel ? db_floor : 0.f;
+          float* o = prm.out + (b * prm.T + t0) * M;
+          const int total = nvalid * M;
+          if ((M & 3) == 0 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+            for (int e = tid * 4; e < total; e += kThreads * 4)
+              *reinterpret_cast<float4*>(o + e) = make_float4(v, v, v, v);
+          } else {
+            for (int e = tid; e < total; e += kThreads) o[e] = v;
+          }
+          const unsigned key = max_key_encode(v);
+          if (prm.tile_stats != nullptr) {
+            float* ts = prm.tile_stats + (size_t)tile * tile_rec_words(M);
+            for (int m = tid; m < M; m += kThreads) {
+              ts[m] = v;
+              ts[M + m] = 0.f;
+              ts[2 * M + m] = v;
+            }
+            if (tid < kTileKeys) reinterpret_cast<unsigned*>(ts)[3 * M + tid] = tid == 0 ? key : 0u;
+          }
+          if (prm.utt_max != nullptr && tid == 0) atomicMax(prm.utt_max + b, key);
+          continue;
+        }
+      }
+    }
     if (tid == 0) s_tile_key = 0u;  // two barriers before stage 3 raises it, read after the third
 
     // ---- stage 1: unit = residue n2: windowed real DFT20 over n1, twiddle, exchange --------
@@ -464,13 +518,13 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
         const float vmax = fmaxf((t0 + p) < prm.T ? vmax0 : -INFINITY,
                                  (t0 + p + kPairs) < prm.T ? vmax1 : -INFINITY);
         const unsigned key = vmax > -INFINITY ? max_key_encode(vmax) : 0u;
-        if (prm.tile_stats != nullptr) {  // tile maximum via one shared word, stored after the barrier
-          const unsigned wk = __reduce_max_sync(0xffffffffu, key);
-          if (lane == 0 && wk) atomicMax(&s_tile_key, wk);
+        // one warp reduction, then one atomic per warp: the tile maximum via a shared word
+        // (stored with the tile record after the barrier) and / or the utterance maximum
+        const unsigned wk = __reduce_max_sync(0xffffffffu, key);
+        if (lane == 0 && wk) {
+          if (prm.tile_stats != nullptr) atomicMax(&s_tile_key, wk);
+          if (prm.utt_max != nullptr) atomicMax(prm.utt_max + b, wk);
         }
-        // same address from every lane: the compiler aggregates this into one warp reduction
-        // (CREDUX.MAX) + one REDG
-        if (prm.utt_max != nullptr && key) atomicMax(prm.utt_max + b, key);
       }
     }
     __syncthreads();

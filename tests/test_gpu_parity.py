@@ -260,6 +260,49 @@ def test_ragged_ingest_is_bit_identical(sb):
     assert torch.equal(fb(rb2), b)
 
 
+def test_all_zero_tiles_take_the_constant_path(sb):
+    """Padding behind an utterance / digital silence: the fused kernel writes the floor without
+    transforming (fbank400_v3.cu); results must equal what the transform of zeros gives."""
+    from speechbrain_b200 import ops
+
+    rng = np.random.default_rng(21)
+    wav = (rng.standard_normal((5, 48000)) * 0.1).astype(np.float32)
+    wav[1, 10000:] = 0                       # padded tail
+    wav[2] = 0                               # silent utterance
+    wav[3] = 0
+    wav[3, 30007] = 1e-3                     # one sample deep inside an otherwise silent tile
+    wav[4, 12000:30000] = -0.0               # silence in the middle, negative zeros
+    fb = sb.Fbank(n_mels=80)
+    feats, keys = ops.fbank_forward(fb._frontend_tables(), dev(wav))    # un-clamped
+    got = feats.cpu().numpy()
+    consts = (fb.compute_fbanks.f_central.numpy(), fb.compute_fbanks.band.numpy())
+    want = onp.fbank(wav, n_mels=80, dtype=np.float64, mel_params=consts,
+                     window=fb.compute_STFT.window.numpy())          # with the top_db clamp
+    assert np.abs(fb(dev(wav)).cpu().numpy() - want).max() < 1e-3
+    t = np.arange(301)
+    silent = lambda lo, hi: (t * 160 - 200 >= lo) & (t * 160 + 200 <= hi)   # frames inside [lo, hi)
+    assert (got[1][silent(10000, 48000)] == -100.0).all()
+    assert (got[2] == -100.0).all()
+    touched = (t * 160 - 200 <= 30007) & (30007 < t * 160 + 200)    # frames whose window holds it
+    assert touched.sum() in (2, 3) and (got[3][~touched] == -100.0).all()
+    assert (got[3][touched].max(axis=1) > -100.0).all()
+    assert (got[4][silent(12000, 30000)] == -100.0).all()
+    assert ops.decode_utt_max(keys)[2].item() == -100.0
+    # the statistics hand-over sees constant tiles as (mean = floor, M2 = 0)
+    lens = torch.tensor([1.0, 0.5, 1.0, 1.0, 1.0]).cuda()
+    a = sb.InputNormalization(norm_type="sentence", std_norm=False)(fb(dev(wav)), lens)
+    f2 = fb(dev(wav))
+    f2._sbfe_tile_stats = None
+    b = sb.InputNormalization(norm_type="sentence", std_norm=False)(f2, lens)
+    torch.testing.assert_close(a, b, rtol=0, atol=2e-4)
+    # linear mel: zeros stay zeros
+    lin = sb.Fbank(n_mels=40)
+    lin.compute_fbanks.log_mel = False
+    lin._tables = None
+    out = lin(dev(wav))
+    assert bool((out[2] == 0).all())
+
+
 @pytest.mark.parametrize("n_mels", [96, 128, 161])
 def test_more_than_eighty_filters(sb, n_mels):
     """n_mels > 80: the fused kernel's mel stage takes several passes of 80 filters (the
