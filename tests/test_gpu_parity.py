@@ -405,3 +405,83 @@ def test_modules_survive_jit_trace(sb):
             assert torch.equal(x, want)
         else:
             assert torch.equal(x, feat2)
+
+
+# ---- guard bands: the kernels write exactly their outputs (compute-sanitizer is not available
+# on the GPU pool, so out-of-bounds stores are caught with canaries around every output) ----
+@pytest.mark.parametrize("B,L,M", [(3, 16000 + 53, 80), (2, 5119, 23), (1, 160 * 33, 40), (5, 0, 80),
+                                   (2, 48000, 128)])
+def test_outputs_stay_inside_their_buffers(sb, B, L, M):
+    import ctypes as C
+
+    from speechbrain_b200 import _lib, ops
+
+    G, CAN = 4096, 1234567.0
+    L_ = _lib.lib()
+    fb = sb.Fbank(n_mels=M)
+    tab = fb._frontend_tables()
+    desc, _ = tab.on(torch.device("cuda", 0))
+    T = 1 + L // 160
+    wav = torch.randn(B, max(L, 1), device="cuda")[:, :L].contiguous() * 0.1
+    frames = int(L_.sbfe_fbank_tile_frames(C.byref(desc)))
+    words = int(L_.sbfe_fbank_tile_stats_floats(C.byref(desc)))
+    tiles = (T + frames - 1) // frames
+    n_out, n_ts = B * T * M, B * tiles * words
+    buf_o = torch.full((n_out + 2 * G,), CAN, device="cuda")
+    buf_t = torch.full((n_ts + 2 * G,), CAN, device="cuda")
+    s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    rc = L_.sbfe_fbank_forward(C.byref(desc), C.c_void_p(wav.data_ptr()), B, L, max(L, 1),
+                               C.c_void_p(buf_o[G:].data_ptr()), None, C.c_void_p(buf_t[G:].data_ptr()),
+                               None, 0, s)
+    assert rc == 0
+    torch.cuda.synchronize()
+    for buf, n in ((buf_o, n_out), (buf_t, n_ts)):
+        assert bool((buf[:G] == CAN).all()) and bool((buf[G + n:] == CAN).all())
+    out = buf_o[G:G + n_out].view(B, T, M)
+    assert not bool((out == CAN).any())
+    want, _ = ops.fbank_forward(tab, wav)
+    assert torch.equal(out, want)
+    # clamp (tile-selective) and normalisation in place, MFCC post-processing, SpecAugment out of place
+    ts = ops.TileStats(buf_t[G:G + n_ts].view(B, tiles, words), frames, None, 0.0)
+    ops.clamp_tiles(out, ts, 80.0)
+    lens = torch.linspace(0.5, 1.0, B, device="cuda")
+    mean, std = ops.norm_stats_tiles(out, lens, ts)
+    ops.norm_apply(out, mean, std, per_utt=True, out=out)
+    torch.cuda.synchronize()
+    assert bool((buf_o[:G] == CAN).all()) and bool((buf_o[G + n_out:] == CAN).all())
+    if T > 12:
+        n_aug = B * T * M
+        buf_a = torch.full((n_aug + 2 * G,), CAN, device="cuda")
+        z = torch.zeros(B, 1, dtype=torch.int64, device="cuda")
+        rc = L_.sbfe_specaugment_forward(C.c_void_p(out.data_ptr()), B, T, M, T // 2, T // 2 + 1, 0,
+                                         C.c_void_p(z.data_ptr()), C.c_void_p((z + 3).data_ptr()), 1,
+                                         C.c_void_p(z.data_ptr()), C.c_void_p((z + 2).data_ptr()), 1,
+                                         None, 0.0, C.c_void_p(buf_a[G:].data_ptr()), s)
+        assert rc == 0
+        torch.cuda.synchronize()
+        assert bool((buf_a[:G] == CAN).all()) and bool((buf_a[G + n_aug:] == CAN).all())
+        assert not bool((buf_a[G:G + n_aug] == CAN).any())
+
+
+def test_post_output_stays_inside_its_buffer(sb):
+    import ctypes as C
+
+    from speechbrain_b200 import _lib
+
+    G, CAN = 4096, 1234567.0
+    L_ = _lib.lib()
+    for B, T, F, n_dct, deltas, left, right in [(3, 101, 23, 20, 1, 5, 5), (2, 37, 40, 0, 1, 0, 0),
+                                                (1, 7, 23, 20, 0, 2, 3), (4, 64, 40, 0, 0, 1, 1)]:
+        x = torch.randn(B, T, F, device="cuda")
+        F0 = n_dct if n_dct else F
+        F_out = F0 * (3 if deltas else 1) * (left + right + 1)
+        dct = sb.DCT(input_size=F, n_out=n_dct).matrix_on(x.device) if n_dct else None
+        buf = torch.full((B * T * F_out + 2 * G,), CAN, device="cuda")
+        rc = L_.sbfe_post_forward(C.c_void_p(x.data_ptr()), B, T, F, None, 80.0,
+                                  C.c_void_p(dct.data_ptr()) if n_dct else None, n_dct, deltas, 5,
+                                  int(bool(left or right)), left, right, C.c_void_p(buf[G:].data_ptr()),
+                                  C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        assert rc == 0
+        torch.cuda.synchronize()
+        assert bool((buf[:G] == CAN).all()) and bool((buf[G + B * T * F_out:] == CAN).all())
+        assert not bool((buf[G:G + B * T * F_out] == CAN).any())
