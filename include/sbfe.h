@@ -194,6 +194,22 @@ SBFE_API int sbfe_norm_apply(const float* d_x, int64_t B, int64_t T, int32_t F, 
                     const float* d_std, int32_t per_utt, const sbfe_maxkey_t* d_utt_max,
                     float top_db, float* d_out, void* stream);
 
+/* ---- next row: speaker-mode statistics (processing/features.py:1037-1081) --
+ * The speaker dictionary stays on the host (ids -> rows of d_table_mean / d_table_std [rows, F]);
+ * this call replays the batch in order: for sentence i with current statistics
+ * d_mean[i], d_std[i] ([B, F], from sbfe_norm_stats*):
+ *   d_row[i] < 0              no table entry is used: out[i] = the sentence's own statistics;
+ *   d_mode[i] = 2             first sight of the speaker: table[row] = current;
+ *   d_mode[i] = 1             table[row] = (1 - w) * table[row] + w * current, with
+ *                             w = d_weight[i] and (1 - w) = d_weight[B + i] (both rounded by the
+ *                             caller; evaluated as two products and a sum, like the reference);
+ *   d_mode[i] = 0             read only;
+ * and out[i] = table[row] after the update - what sbfe_norm_apply(per_utt = 1) then uses. */
+SBFE_API int sbfe_norm_speaker_update(const float* d_mean, const float* d_std, int64_t B, int32_t F,
+                             const int32_t* d_row, const int32_t* d_mode, const float* d_weight,
+                             float* d_table_mean, float* d_table_std, float* d_out_mean,
+                             float* d_out_std, void* stream);
+
 /* ---- next row: SpecAugment on features ----------------------------------
  * speechbrain/lobes/augment.py:32-201.  x [B, T, F] -> out [B, T, F]:
  *   time warp (:116-150)  rows [0, c) resampled onto [0, w) and rows [c, T) onto [w, T) along

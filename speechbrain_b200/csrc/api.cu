@@ -43,6 +43,9 @@ int launch_specaugment(const float*, int64_t, int64_t, int, int, int, int, const
                        float*, cudaStream_t);
 int64_t mean_workspace_bytes();
 int launch_mean(const float*, int64_t, float*, void*, int64_t, cudaStream_t);
+int launch_norm_speaker_update(const float*, const float*, int64_t, int, const int32_t*,
+                               const int32_t*, const float*, float*, float*, float*, float*,
+                               cudaStream_t);
 bool fbank400_supported(const sbfe_fbank_desc* d);
 // packed-f32x2 kernel: additionally hop == 160 and the padded filter layout (mel_pad4)
 bool fbank400_v3_supported(const sbfe_fbank_desc* d);
@@ -220,6 +223,18 @@ int sbfe_norm_apply(const float* d_x, int64_t B, int64_t T, int32_t F, const flo
   if (!d_x || !d_out || !d_mean || !d_std) return SBFE_E_INVAL;
   return launch_norm_apply(d_x, B, T, F, d_mean, d_std, per_utt, d_utt_max, top_db, d_out,
                            (cudaStream_t)stream);
+}
+
+int sbfe_norm_speaker_update(const float* d_mean, const float* d_std, int64_t B, int32_t F,
+                             const int32_t* d_row, const int32_t* d_mode, const float* d_weight,
+                             float* d_table_mean, float* d_table_std, float* d_out_mean,
+                             float* d_out_std, void* stream) {
+  if (B < 0 || F < 0) return SBFE_E_INVAL;
+  if (B == 0 || F == 0) return 0;
+  if (!d_mean || !d_std || !d_row || !d_mode || !d_weight || !d_out_mean || !d_out_std)
+    return SBFE_E_INVAL;
+  return launch_norm_speaker_update(d_mean, d_std, B, F, d_row, d_mode, d_weight, d_table_mean,
+                                    d_table_std, d_out_mean, d_out_std, (cudaStream_t)stream);
 }
 
 int sbfe_specaugment_forward(const float* d_x, int64_t B, int64_t T, int32_t F, int32_t warp_c,

@@ -418,4 +418,57 @@ int launch_norm_apply(const float* x, int64_t B, int64_t T, int F, const float* 
                     out, (unsigned)chunks);
 }
 
+// ---- speaker mode (processing/features.py:1037-1081): running per-speaker statistics ---------
+// The dictionary lives on the host (python ints -> table rows); this kernel replays the batch in
+// order for every feature column: row[i] < 0: unseen speaker outside training -> the sentence's
+// own statistics; mode[i] = 2: first sight -> the row becomes the sentence's statistics;
+// mode[i] = 1: row = (1 - w) * row + w * current (two roundings and an add, like the reference's
+// eager ops: no FMA contraction); mode[i] = 0: read only.  out[i] = the row AFTER its update,
+// which is what the reference normalises sentence i with.
+__global__ void norm_speaker_update_kernel(const float* __restrict__ mean,
+                                           const float* __restrict__ stdv, int B, int F,
+                                           const int32_t* __restrict__ row,
+                                           const int32_t* __restrict__ mode,
+                                           const float* __restrict__ weight, float* tab_mean,
+                                           float* tab_std, float* __restrict__ out_mean,
+                                           float* __restrict__ out_std) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= F) return;
+  for (int i = 0; i < B; ++i) {   // in batch order: a speaker may appear more than once
+    const int r = row[i];
+    float m = mean[(int64_t)i * F + f], s = stdv[(int64_t)i * F + f];
+    if (r >= 0) {
+      float* tm = tab_mean + (int64_t)r * F + f;
+      float* tsd = tab_std + (int64_t)r * F + f;
+      const int md = mode[i];
+      if (md == 1) {
+        const float w = weight[i], k = weight[B + i];   // w and (1 - w), rounded on the host
+        m = __fadd_rn(__fmul_rn(k, *tm), __fmul_rn(w, m));
+        s = __fadd_rn(__fmul_rn(k, *tsd), __fmul_rn(w, s));
+      } else if (md == 0) {
+        m = *tm;
+        s = *tsd;
+      }
+      if (md != 0) {
+        *tm = m;
+        *tsd = s;
+      }
+    }
+    out_mean[(int64_t)i * F + f] = m;
+    out_std[(int64_t)i * F + f] = s;
+  }
+}
+
+int launch_norm_speaker_update(const float* mean, const float* stdv, int64_t B, int F,
+                               const int32_t* row, const int32_t* mode, const float* weight,
+                               float* tab_mean, float* tab_std, float* out_mean, float* out_std,
+                               cudaStream_t stream) {
+  if (B == 0 || F == 0) return 0;
+  if (B > 0x7fffffff) return SBFE_E_TOOBIG;
+  return launch_pdl(norm_speaker_update_kernel, dim3((F + 127) / 128), dim3(128), 0, stream, mean,
+                    stdv, (int)B, F, row, mode, weight, tab_mean, tab_std, out_mean, out_std);
+}
+
 }  // namespace sbfe

@@ -323,6 +323,18 @@ def norm_update(cur, glob_mean, glob_std, first, weight):
                                      _ptr(glob_mean), _ptr(glob_std), _stream()))
 
 
+def norm_speaker_update(mean, std, row, mode, weight, table_mean, table_std):
+    """Speaker-mode running statistics (sbfe_norm_speaker_update): returns the [B, F] rows to
+    normalise with; updates the table rows in place."""
+    B, F = mean.shape
+    out_m, out_s = torch.empty_like(mean), torch.empty_like(std)
+    with torch.cuda.device(mean.device):
+        check(lib().sbfe_norm_speaker_update(_ptr(mean), _ptr(std), B, F, _ptr(row), _ptr(mode),
+                                             _ptr(weight), _ptr(table_mean), _ptr(table_std),
+                                             _ptr(out_m), _ptr(out_s), _stream()))
+    return out_m, out_s
+
+
 def norm_apply(x, mean, std, per_utt, out=None, utt_max=None, top_db=80.0):
     B, T, F = x.shape
     if out is None:

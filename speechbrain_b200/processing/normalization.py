@@ -65,8 +65,8 @@ class InputNormalization(torch.nn.Module):
         self.update_until_epoch = update_until_epoch
         self.sync_stats = sync_stats
         self.device_inp = torch.device("cpu")
-        # fused-frontend hand-over: (utt_max keys, top_db) of an un-clamped input
-        self._pending_clamp = None
+        # speaker mode: device tables behind spk_dict_mean / spk_dict_std (see _speaker_table)
+        self._spk_tab, self._spk_row, self._spk_dirty = None, {}, False
 
     # ------------------------------------------------------------------ forward
     @traceable(lambda self: 0 if self.norm_type in ("sentence", "speaker") else None)
@@ -136,33 +136,67 @@ class InputNormalization(torch.nn.Module):
                     t = t.expand(F)
                 setattr(self, name, t.contiguous())
 
+    # ------------------------------------------------------------ speaker mode
+    def _speaker_table(self, device, F, extra):
+        """The per-speaker statistics as rows of two device tables; ``spk_dict_mean`` /
+        ``spk_dict_std`` (the reference's attributes, also what ``_save`` writes) hold views of
+        the rows, so they follow the kernel's in-place updates."""
+        tab = self._spk_tab
+        stale = (tab is None or tab[0].device != device or tab[0].shape[1] != F
+                 or self._spk_dirty or len(self._spk_row) != len(self.spk_dict_mean))
+        need = len(self.spk_dict_mean) + extra
+        if stale or need > tab[0].shape[0]:
+            cap = max(16, 2 * need)
+            tm = torch.zeros((cap, F), dtype=torch.float32, device=device)
+            ts = torch.ones((cap, F), dtype=torch.float32, device=device)
+            self._spk_row = {}
+            for r, spk in enumerate(self.spk_dict_mean):
+                tm[r] = self.spk_dict_mean[spk].to(device=device, dtype=torch.float32)
+                ts[r] = self.spk_dict_std[spk].to(device=device, dtype=torch.float32)
+                self._spk_row[spk] = r
+            for spk, r in self._spk_row.items():
+                self.spk_dict_mean[spk], self.spk_dict_std[spk] = tm[r], ts[r]
+            self._spk_tab, self._spk_dirty = (tm, ts), False
+        return self._spk_tab
+
     def _speaker_stats(self, mean, std, spk_ids):
-        """Per-speaker running statistics (:1037-1081); returns the [B, F] rows to apply."""
-        ids = [int(spk_ids[i][0]) for i in range(mean.shape[0])]
-        rows_m, rows_s = [], []
-        for i, spk in enumerate(ids):
-            cm, cs = mean[i], std[i]
+        """Per-speaker running statistics (:1037-1081); returns the [B, F] rows to apply.  The
+        dictionary logic (ids, counts, weights) runs on the host like the reference's, the
+        arithmetic in one kernel that replays the batch in order (sbfe_norm_speaker_update)."""
+        B, F = mean.shape
+        ids = [int(v) for v in spk_ids.reshape(B, -1)[:, 0].tolist()]
+        new = len({s for s in ids if s not in self.spk_dict_mean}) if self.training else 0
+        tm, ts = self._speaker_table(mean.device, F, new)
+        row, mode, w, k = [], [], [], []
+        fresh = {}
+        for spk in ids:
+            r, md, wt = -1, 0, 0.0
             if self.training:
-                if spk not in self.spk_dict_mean:
-                    self.spk_dict_mean[spk], self.spk_dict_std[spk] = cm.clone(), cs.clone()
+                if spk not in self._spk_row:
+                    r = self._spk_row[spk] = len(self._spk_row)
+                    fresh[spk] = r
                     self.spk_dict_count[spk] = 1
+                    md = 2
                 else:
-                    self.spk_dict_count[spk] += 1
+                    r = self._spk_row[spk]
+                    self.spk_dict_count[spk] = self.spk_dict_count[spk] + 1
                     self.weight = (1 / self.spk_dict_count[spk] if self.avg_factor is None
                                    else self.avg_factor)
-                    self.spk_dict_mean[spk] = ((1 - self.weight) * self.spk_dict_mean[spk].to(cm.device)
-                                               + self.weight * cm)
-                    self.spk_dict_std[spk] = ((1 - self.weight) * self.spk_dict_std[spk].to(cs.device)
-                                              + self.weight * cs)
-                rows_m.append(self.spk_dict_mean[spk])
-                rows_s.append(self.spk_dict_std[spk])
-            elif spk in self.spk_dict_mean:
-                rows_m.append(self.spk_dict_mean[spk].to(cm.device))
-                rows_s.append(self.spk_dict_std[spk].to(cs.device))
-            else:
-                rows_m.append(cm)
-                rows_s.append(cs)
-        return torch.stack(rows_m).contiguous(), torch.stack(rows_s).contiguous()
+                    md, wt = 1, self.weight
+            elif spk in self._spk_row:
+                r = self._spk_row[spk]
+            row.append(r)
+            mode.append(md)
+            w.append(wt)
+            k.append(1 - wt)
+        dev = mean.device
+        out = ops.norm_speaker_update(
+            mean, std, torch.tensor(row, dtype=torch.int32).to(dev, non_blocking=True),
+            torch.tensor(mode, dtype=torch.int32).to(dev, non_blocking=True),
+            torch.tensor(w + k, dtype=torch.float32).to(dev, non_blocking=True), tm, ts)
+        for spk, r in fresh.items():
+            self.spk_dict_mean[spk], self.spk_dict_std[spk] = tm[r], ts[r]
+        return out
 
     # --------------------------------------------------------- state / checkpoint
     def _statistics_dict(self):
@@ -184,6 +218,7 @@ class InputNormalization(torch.nn.Module):
         self.spk_dict_mean = {k: v.to(self.device_inp) for k, v in state["spk_dict_mean"].items()}
         self.spk_dict_std = {k: v.to(self.device_inp) for k, v in state["spk_dict_std"].items()}
         self.spk_dict_count = state["spk_dict_count"]
+        self._spk_dirty = True
         return state
 
     def to(self, device):
@@ -195,6 +230,7 @@ class InputNormalization(torch.nn.Module):
         for spk in self.spk_dict_mean:
             self.spk_dict_mean[spk] = self.spk_dict_mean[spk].to(device)
             self.spk_dict_std[spk] = self.spk_dict_std[spk].to(device)
+        self._spk_dirty = True
         return self
 
     def _save(self, path):

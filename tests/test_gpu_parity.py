@@ -136,6 +136,45 @@ def test_norm_sequence_vs_reference(sb, golden, name):
                                        rtol=1e-5, atol=1e-5)
 
 
+def test_speaker_mode_state_round_trip(sb, tmp_path):
+    """Speaker statistics live in device tables behind spk_dict_mean / spk_dict_std: the
+    reference's attributes, checkpoint file and .to() keep working, table growth included."""
+    g = torch.Generator().manual_seed(3)
+    a = sb.InputNormalization(norm_type="speaker")
+    lens = torch.tensor([1.0, 0.7, 0.9, 0.5]).cuda()
+    for step in range(12):   # 4 new speakers per step: the 16-row table has to grow
+        x = torch.randn(4, 50, 24, generator=g).cuda()
+        spk = torch.arange(4 * step, 4 * step + 4).unsqueeze(1)
+        a(x, lens, spk_ids=spk)
+    assert len(a.spk_dict_mean) == 48 and a.spk_dict_count[5] == 1
+    x = torch.randn(4, 50, 24, generator=g).cuda()
+    spk = torch.tensor([[5], [5], [40], [0]])
+    ya = a(x.clone(), lens, spk_ids=spk)
+    assert a.spk_dict_count[5] == 3 and a.weight == 0.5     # the last update was speaker 0's second
+    # the dictionary values are the live table rows
+    assert a.spk_dict_mean[5].data_ptr() == a._spk_tab[0][a._spk_row[5]].data_ptr()
+    path = str(tmp_path / "normalizer.ckpt")
+    a._save(path)
+    state = torch.load(path)
+    assert set(state) == {"count", "glob_mean", "glob_std", "spk_dict_mean", "spk_dict_std",
+                          "spk_dict_count"} and len(state["spk_dict_mean"]) == 48
+    b = sb.InputNormalization(norm_type="speaker")
+    b._load(path, device="cuda")
+    assert b.spk_dict_count == a.spk_dict_count
+    for k in a.spk_dict_mean:
+        assert torch.equal(a.spk_dict_mean[k], b.spk_dict_mean[k].cuda())
+    x2 = torch.randn(4, 50, 24, generator=g).cuda()
+    spk2 = torch.tensor([[7], [100], [7], [5]])
+    a.to("cpu").to("cuda")          # statistics follow the module (:1194-1203)
+    assert torch.equal(a(x2.clone(), lens, spk_ids=spk2), b(x2.clone(), lens, spk_ids=spk2))
+    a.eval(), b.eval()
+    spk3 = torch.tensor([[7], [999], [100], [5]])            # 999 was never seen: own statistics
+    ya, yb = a(x2.clone(), lens, spk_ids=spk3), b(x2.clone(), lens, spk_ids=spk3)
+    assert torch.equal(ya, yb) and 999 not in a.spk_dict_mean
+    own = sb.InputNormalization(norm_type="sentence")(x2.clone(), lens)
+    assert torch.equal(ya[1], own[1])
+
+
 # ---- known answers of reference tests/unittests/test_features.py, on the GPU ----
 def test_ka_deltas_context(sb):
     ones = torch.ones(10, 101, 20, device="cuda")
