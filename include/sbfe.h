@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define SBFE_ABI_VERSION 4
+#define SBFE_ABI_VERSION 5
 
 #if defined(__GNUC__)
 #define SBFE_API __attribute__((visibility("default")))
@@ -129,7 +129,13 @@ SBFE_API int sbfe_fbank_forward_ragged_pcm16(const sbfe_fbank_desc* desc, const 
  *   sbfe_norm_stats_tiles  produce the InputNormalization statistics (features.py:1020-1031,
  *                          1120-1145; same contract as sbfe_norm_stats) without a pass over x:
  *                          only tiles cut by the valid length or holding clamped values are
- *                          re-read. */
+ *                          re-read.
+ * flags = SBFE_STATS_BESIDE_CLAMP: the caller states that the launch made on `stream` just
+ * before this one is sbfe_clamp_tiles on the same d_x with the same records and top_db.  The
+ * statistics do not depend on whether that clamp has landed yet (every value is read through
+ * max(., floor)), so the kernel then runs beside it instead of after it; stream order for
+ * everything that FOLLOWS is unchanged.  0 is always correct. */
+#define SBFE_STATS_BESIDE_CLAMP 1
 SBFE_API int32_t sbfe_fbank_tile_frames(const sbfe_fbank_desc* desc);
 SBFE_API int32_t sbfe_fbank_tile_stats_floats(const sbfe_fbank_desc* desc);
 SBFE_API int sbfe_clamp_tiles(float* d_x, int64_t B, int64_t T, int32_t F,
@@ -139,7 +145,7 @@ SBFE_API int sbfe_norm_stats_tiles(const float* d_x, const float* d_lengths, int
                           int32_t F, int32_t mean_norm, int32_t std_norm, float eps,
                           const sbfe_maxkey_t* d_utt_max, float top_db,
                           const float* d_tile_stats, int32_t tile_frames, float* d_mean,
-                          float* d_std, void* stream);
+                          float* d_std, int32_t flags, void* stream);
 
 /* STFT.forward for [B, L] input (processing/features.py:133-188):
  * out [B, T, bins, 2] (re, im), or, with power_only != 0, [B, T, bins] = re^2+im^2. */

@@ -55,7 +55,7 @@ SIGNATURES = {
     "sbfe_fbank_tile_stats_floats": (_I32, [_DESC]),
     "sbfe_clamp_tiles": (C.c_int, [_P, _I64, _I64, _I32, _P, _F, _P, _I32, _P]),
     "sbfe_norm_stats_tiles": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, _I32, _F, _P, _F, _P, _I32,
-                                        _P, _P, _P]),
+                                        _P, _P, _I32, _P]),
     "sbfe_stft_forward": (C.c_int, [_DESC, _P, _I64, _I64, _I64, _P, _I32, _P]),
     "sbfe_spectral_magnitude": (C.c_int, [_P, _I64, _F, _I32, _F, _P, _P]),
     "sbfe_filterbank_forward": (C.c_int, [_DESC, _P, _I64, _I64, _P, _P, _P]),
@@ -106,12 +106,17 @@ def lib():
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(handle, name)
             fn.restype, fn.argtypes = res, args
-        if handle.sbfe_abi_version() != 4:
+        if handle.sbfe_abi_version() != 5:
             raise SbfeUnavailable("libsbfe.so ABI version mismatch")
         _lib = handle
         return _lib
 
 
+launches = 0  # library launches made by this process (ops.py: what was launched last)
+
+
 def check(rc):
+    global launches
+    launches += 1
     if rc != 0:
         raise RuntimeError("sbfe call failed (%d): %s" % (rc, lib().sbfe_error_string(rc).decode()))

@@ -12,7 +12,7 @@ int launch_fbank400_v3(const sbfe_fbank_desc*, const void*, int, float, const in
 int launch_clamp_tiles(float*, int64_t, int64_t, int, const sbfe_maxkey_t*, float, const float*, int,
                        cudaStream_t);
 int launch_norm_stats_tiles(const float*, const float*, int64_t, int64_t, int, int, int, float,
-                            const sbfe_maxkey_t*, float, const float*, int, float*, float*,
+                            const sbfe_maxkey_t*, float, const float*, int, float*, float*, int,
                             cudaStream_t);
 int launch_stft_generic(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
                         int, cudaStream_t);
@@ -177,13 +177,15 @@ int sbfe_clamp_tiles(float* d_x, int64_t B, int64_t T, int32_t F, const sbfe_max
 int sbfe_norm_stats_tiles(const float* d_x, const float* d_lengths, int64_t B, int64_t T, int32_t F,
                           int32_t mean_norm, int32_t std_norm, float eps,
                           const sbfe_maxkey_t* d_utt_max, float top_db, const float* d_tile_stats,
-                          int32_t tile_frames, float* d_mean, float* d_std, void* stream) {
+                          int32_t tile_frames, float* d_mean, float* d_std, int32_t flags,
+                          void* stream) {
   if (B < 0 || T < 0 || F < 0 || tile_frames < 1) return SBFE_E_INVAL;
+  if (flags & ~SBFE_STATS_BESIDE_CLAMP) return SBFE_E_INVAL;
   if (B == 0 || F == 0) return 0;
   if (!d_x || !d_lengths || !d_mean || !d_std || !d_tile_stats) return SBFE_E_INVAL;
   return launch_norm_stats_tiles(d_x, d_lengths, B, T, F, mean_norm, std_norm, eps, d_utt_max,
                                  top_db, d_tile_stats, tile_frames, d_mean, d_std,
-                                 (cudaStream_t)stream);
+                                 (flags & SBFE_STATS_BESIDE_CLAMP) != 0, (cudaStream_t)stream);
 }
 
 int64_t sbfe_norm_workspace_bytes(int64_t B, int64_t T, int32_t F) {

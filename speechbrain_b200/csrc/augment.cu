@@ -86,8 +86,8 @@ constexpr int kAugMaxCols = 1024;  // column groups whose mask bits are cached i
 
 template <int VEC>
 __global__ void __launch_bounds__(kAugThreads) specaug_kernel(const AugParams p) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   __shared__ RowPlan s_row[kAugRows];
   __shared__ int s_m[4 * kAugMaxMasks];        // fpos | fend | tpos | tend of this utterance
   __shared__ unsigned char s_cm[kAugMaxCols];  // per column group: VEC mask bits
@@ -233,8 +233,8 @@ constexpr int kMeanCtas = 296;
 
 __global__ void __launch_bounds__(kMeanThreads) mean_partial_kernel(const float* __restrict__ x,
                                                                    int64_t n, double* part) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   __shared__ double s_red[kMeanThreads];
   double s = 0.0;
   const int64_t stride = (int64_t)gridDim.x * kMeanThreads;
@@ -250,8 +250,8 @@ __global__ void __launch_bounds__(kMeanThreads) mean_partial_kernel(const float*
 }
 
 __global__ void mean_final_kernel(const double* part, int parts, int64_t n, float* out) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   if (threadIdx.x == 0 && blockIdx.x == 0) {
     double s = 0.0;
     for (int i = 0; i < parts; ++i) s += part[i];

@@ -87,9 +87,13 @@ inline int check_last(void) {
 // A step is four short kernels back to back; each one's launch + prologue would otherwise sit
 // on the critical path.  Every kernel of this library (1) executes pdl_wait() before it reads
 // or writes anything another kernel may touch - it returns once the preceding kernel in the
-// stream has completed and its writes are visible - and (2) calls pdl_launch_dependents() so
-// that the NEXT kernel may be scheduled early and park in its own pdl_wait().  Because every
-// kernel waits unconditionally, completion is transitive along the stream.  Kernels of other
+// stream has completed and its writes are visible - and (2) calls pdl_launch_dependents()
+// AFTER that wait, so that the NEXT kernel may be scheduled early and park in its own
+// pdl_wait().  Two invariants follow: completion is transitive along the stream (every kernel
+// waits before it exits), and when a kernel starts, everything before its DIRECT predecessor
+// has completed (the predecessor triggered only after its own wait).  The second one lets a
+// kernel that reads nothing its direct predecessor writes run beside it and wait at its END
+// instead (norm_stats_tiles_kernel next to clamp_tiles_kernel, norm.cu).  Kernels of other
 // libraries never trigger early, so mixing with them degrades to ordinary stream order.
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() {

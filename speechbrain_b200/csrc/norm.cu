@@ -24,8 +24,8 @@ __global__ void __launch_bounds__(kNormThreads)
 norm_stats_partial_kernel(const float* __restrict__ x, const float* __restrict__ lengths,
                           int64_t T, int F, const sbfe_maxkey_t* __restrict__ utt_max,
                           float top_db, double2* __restrict__ ws, unsigned chunks, int bx) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   __shared__ double2 s_red[kNormThreads];
   const int64_t b = blockIdx.x / chunks;
   const int c = blockIdx.x - b * chunks;
@@ -69,8 +69,8 @@ __global__ void norm_stats_final_kernel(const float* __restrict__ x,
                                         const sbfe_maxkey_t* __restrict__ utt_max, float top_db,
                                         const double2* __restrict__ ws, unsigned chunks,
                                         float* __restrict__ mean, float* __restrict__ stdv) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= B * F) return;
   const int64_t b = i / F;
@@ -117,64 +117,95 @@ constexpr int kTileStatGroups = 16;   // tile groups per CTA
 constexpr int kTileStatThreads = kTileStatCols * kTileStatGroups;
 
 // grid = (ceil(F / 32), B); thread = (column, tile group)
+// beside_clamp: the kernel launched just before this one is clamp_tiles_kernel on the same x
+// (or anything else that leaves lengths and the records alone and writes x only as
+// x = max(x, floor) with the same floor).  Every read of x below goes through fmaxf(., floor),
+// which gives the same value before and after that write, so this kernel does not wait for
+// it: it runs beside the clamp and waits at its end, which keeps completion transitive for
+// whatever follows (common.cuh).
 __global__ void __launch_bounds__(kTileStatThreads)
-norm_stats_tiles_kernel(const float* __restrict__ x, const float* __restrict__ lengths, int64_t T,
+norm_stats_tiles_kernel(const float* x, const float* __restrict__ lengths, int64_t T,
                         int F, int tile, int tiles, const float* __restrict__ tile_stats,
                         const sbfe_maxkey_t* __restrict__ utt_max, float top_db, int mean_norm,
-                        int std_norm, float eps, float* __restrict__ mean, float* __restrict__ stdv) {
-  pdl_launch_dependents();
-  pdl_wait();
+                        int std_norm, float eps, float* __restrict__ mean, float* __restrict__ stdv,
+                        int beside_clamp) {
+  if (!beside_clamp) {
+    pdl_wait();
+    pdl_launch_dependents();
+  }
   __shared__ float s_red[3 * kTileStatThreads];
   const int64_t b = blockIdx.y;
-  const int n = valid_frames(lengths, b, T);
-  const float floor_b = utt_max ? clamp_floor(utt_max, b, top_db)
-                                : block_floor_from_tiles(tile_stats, b, tiles, F, top_db);
   const int tx = threadIdx.x % kTileStatCols, ty = threadIdx.x / kTileStatCols;
   const int f = blockIdx.x * kTileStatCols + tx;
   const float* xb = x + b * T * F;
   const size_t rec = tile_rec_words(F);
   const float* tsb = tile_stats + (size_t)b * tiles * rec;
+  // the first kSpec records of this thread are requested before the valid length and the
+  // floor are known (which of them count is decided afterwards): one memory round trip for
+  // length, keys and records instead of two
+  constexpr int kSpec = 4;
+  float pm[kSpec], pq[kSpec], pn[kSpec];
+#pragma unroll
+  for (int k = 0; k < kSpec; ++k) {
+    const int j = ty + k * kTileStatGroups;
+    if (f < F && j < tiles) {
+      const float* ts = tsb + (size_t)j * rec + f;
+      pm[k] = __ldg(ts);
+      pq[k] = __ldg(ts + F);
+      pn[k] = __ldg(ts + 2 * F);
+    }
+  }
+  const int n = valid_frames(lengths, b, T);
+  // tiles whose existing frames are all valid: [0, n / tile), plus the short last tile when
+  // the whole utterance is valid
+  const int whole = (n >= T) ? tiles : n / tile;
+  // rows of the tile cut by the valid length, spread over the tile groups (at most
+  // ceil((tile - 1) / 16) per thread): requested as soon as the length is here, so that they
+  // fly while the floor is being rebuilt
+  const int r_cut = whole * tile;
+  const bool cut = f < F && whole < tiles && r_cut < n;
+  constexpr int kCutRows = 2;
+  float cv[kCutRows], pivot = 0.f;
+  if (cut) {
+    const float* col = xb + (int64_t)r_cut * F + f;
+    pivot = col[0];
+#pragma unroll
+    for (int i = 0; i < kCutRows; ++i) {
+      const int r = ty + i * kTileStatGroups;
+      cv[i] = (r < n - r_cut) ? col[(int64_t)r * F] : NAN;
+    }
+  }
+  const float floor_b = utt_max ? clamp_floor(utt_max, b, top_db)
+                                : block_floor_from_tiles(tile_stats, b, tiles, F, top_db);
   Moments acc{0.f, 0.f, 0.f};
   if (f < F) {
-    // tiles whose existing frames are all valid: [0, n / tile), plus the short last tile when
-    // the whole utterance is valid
-    const int whole = (n >= T) ? tiles : n / tile;
-    // rows of the tile cut by the valid length, spread over the tile groups (at most
-    // ceil((tile - 1) / 16) per thread): requested first so that they fly with the records
-    const int r_cut = whole * tile;
-    const bool cut = whole < tiles && r_cut < n;
-    constexpr int kCutRows = 2;
-    float cv[kCutRows], pivot = 0.f;
     int c = 0;
-    if (cut) {
-      const float* col = xb + (int64_t)r_cut * F + f;
-      pivot = __ldg(col);
-#pragma unroll
-      for (int i = 0; i < kCutRows; ++i) {
-        const int r = ty + i * kTileStatGroups;
-        cv[i] = (r < n - r_cut) ? __ldg(col + (int64_t)r * F) : NAN;
-      }
-    }
-#pragma unroll 4
-    for (int j = ty; j < whole; j += kTileStatGroups) {
+    auto take = [&](int j, float t_mean, float t_m2, float t_min) {
       const int r_lo = j * tile;
       const int cnt = T - r_lo < tile ? (int)(T - r_lo) : tile;
-      const float* ts = tsb + (size_t)j * rec + f;
-      const float t_mean = __ldg(ts), t_m2 = __ldg(ts + F), t_min = __ldg(ts + 2 * F);
       if (t_min >= floor_b) {
         merge(acc, (float)cnt, t_mean, t_m2);
       } else {  // clamped values inside the valid part: rare, recompute the column
         const float* col = xb + (int64_t)r_lo * F + f;
         float s = 0.f;
-        for (int r = 0; r < cnt; ++r) s += fmaxf(__ldg(col + (int64_t)r * F), floor_b);
+        for (int r = 0; r < cnt; ++r) s += fmaxf(col[(int64_t)r * F], floor_b);
         const float m = s / (float)cnt;
         float q = 0.f;
         for (int r = 0; r < cnt; ++r) {
-          const float d = fmaxf(__ldg(col + (int64_t)r * F), floor_b) - m;
+          const float d = fmaxf(col[(int64_t)r * F], floor_b) - m;
           q = fmaf(d, d, q);
         }
         merge(acc, (float)cnt, m, q);
       }
+    };
+#pragma unroll
+    for (int k = 0; k < kSpec; ++k) {
+      const int j = ty + k * kTileStatGroups;
+      if (j < whole) take(j, pm[k], pq[k], pn[k]);
+    }
+    for (int j = ty + kSpec * kTileStatGroups; j < whole; j += kTileStatGroups) {
+      const float* ts = tsb + (size_t)j * rec + f;
+      take(j, __ldg(ts), __ldg(ts + F), __ldg(ts + 2 * F));
     }
     if (cut) {  // sums about the cut tile's first row
       const float* col = xb + (int64_t)r_cut * F + f;
@@ -190,7 +221,7 @@ norm_stats_tiles_kernel(const float* __restrict__ x, const float* __restrict__ l
         }
       }
       for (int r = ty + kCutRows * kTileStatGroups; r < n - r_cut; r += kTileStatGroups, ++c) {
-        const float d = fmaxf(__ldg(col + (int64_t)r * F), floor_b) - pivot;  // tile > 32 rows only
+        const float d = fmaxf(col[(int64_t)r * F], floor_b) - pivot;  // tile > 32 rows only
         s1 += d;
         s2 = fmaf(d, d, s2);
       }
@@ -225,14 +256,18 @@ norm_stats_tiles_kernel(const float* __restrict__ x, const float* __restrict__ l
     mean[b * F + f] = mean_norm ? m : 0.f;
     stdv[b * F + f] = std_norm ? sd : 1.f;
   }
+  if (beside_clamp) {
+    pdl_wait();
+    pdl_launch_dependents();
+  }
 }
 
 // grid = ceil(F / 32) CTAs of 32 columns x 8 utterance groups
 __global__ void __launch_bounds__(256)
 norm_reduce_kernel(const float* __restrict__ mean, const float* __restrict__ stdv, int64_t B, int F,
                    float* __restrict__ cur) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   __shared__ float s_a[256], s_s[256];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int f = blockIdx.x * 32 + tx;
@@ -258,8 +293,8 @@ norm_reduce_kernel(const float* __restrict__ mean, const float* __restrict__ std
 
 __global__ void norm_update_kernel(const float* __restrict__ cur, int F, int first, float weight,
                                    float* __restrict__ gmean, float* __restrict__ gstd) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   const int f = blockIdx.x * blockDim.x + threadIdx.x;
   if (f >= F) return;
   const float n = cur[2 * F];
@@ -284,8 +319,8 @@ norm_apply_kernel(const float* x, int64_t T, int F, const float* __restrict__ me
                   const float* __restrict__ stdv, int per_utt,
                   const sbfe_maxkey_t* __restrict__ utt_max, float top_db, float* out,
                   unsigned chunks) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   extern __shared__ __align__(16) float s_ms[];  // mean[F] | std[F]
   const int64_t b = blockIdx.x / chunks;
   const int c = blockIdx.x - b * chunks;
@@ -378,7 +413,7 @@ int launch_norm_stats(const float* x, const float* lengths, int64_t B, int64_t T
 int launch_norm_stats_tiles(const float* x, const float* lengths, int64_t B, int64_t T, int F,
                             int mean_norm, int std_norm, float eps, const sbfe_maxkey_t* utt_max,
                             float top_db, const float* tile_stats, int tile, float* mean,
-                            float* stdv, cudaStream_t stream) {
+                            float* stdv, int beside_clamp, cudaStream_t stream) {
   if (B == 0 || F == 0) return 0;
   if (B > 0x7fffffff || T > 0x7fffffff) return SBFE_E_TOOBIG;
   const int tiles = (int)((T + tile - 1) / tile);
@@ -386,7 +421,7 @@ int launch_norm_stats_tiles(const float* x, const float* lengths, int64_t B, int
   const dim3 grid((unsigned)((F + kTileStatCols - 1) / kTileStatCols), (unsigned)B);
   return launch_pdl(norm_stats_tiles_kernel, grid, dim3(kTileStatThreads), 0, stream,
       x, lengths, T, F, tile, tiles, tile_stats, utt_max, top_db, mean_norm, std_norm, eps, mean,
-      stdv);
+      stdv, beside_clamp);
 }
 
 int launch_norm_reduce(const float* mean, const float* stdv, int64_t B, int F, float* cur,
@@ -432,8 +467,8 @@ __global__ void norm_speaker_update_kernel(const float* __restrict__ mean,
                                            const float* __restrict__ weight, float* tab_mean,
                                            float* tab_std, float* __restrict__ out_mean,
                                            float* __restrict__ out_std) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   const int f = blockIdx.x * blockDim.x + threadIdx.x;
   if (f >= F) return;
   for (int i = 0; i < B; ++i) {   // in batch order: a speaker may appear more than once

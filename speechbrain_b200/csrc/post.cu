@@ -13,8 +13,8 @@ namespace sbfe {
 __global__ void clamp_kernel(const float* __restrict__ x, int64_t per_utt,
                              const sbfe_maxkey_t* __restrict__ utt_max, float top_db,
                              float* __restrict__ out, unsigned chunks) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   const int64_t b = blockIdx.x / chunks;
   const int64_t c = blockIdx.x - b * chunks;
   const float floor_b = clamp_floor(utt_max, b, top_db);
@@ -51,8 +51,8 @@ __global__ void __launch_bounds__(kClampTileThreads)
 clamp_tiles_kernel(float* __restrict__ x, int64_t T, int F, int tile, unsigned tiles,
                    const sbfe_maxkey_t* __restrict__ utt_max, float top_db,
                    const float* __restrict__ tile_stats) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   const int64_t b = blockIdx.x / tiles;
   const int j = blockIdx.x - b * tiles;
   const float* mn = tile_stats + (size_t)blockIdx.x * tile_rec_words(F) + 2 * F;
@@ -106,8 +106,8 @@ struct PostParams {
 constexpr int kPostThreads = 256;
 
 __global__ void __launch_bounds__(kPostThreads) post_kernel(const PostParams p) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   extern __shared__ __align__(16) float smem[];
   const int n2 = p.deltas == 1 ? 2 * p.n : (p.deltas ? p.n : 0);  // base-feature halo per side
   const int n1 = p.deltas == 1 ? p.n : 0;                         // delta halo per side
@@ -204,8 +204,8 @@ __global__ void __launch_bounds__(kPostThreads) post_kernel(const PostParams p) 
 // output element (the generic kernel above is instruction-bound on exactly that: 660 outputs
 // per frame for the MFCC default).  Requires F_out % 4 == 0.
 __global__ void post_fast_kernel(const PostParams p) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   extern __shared__ __align__(16) float smem[];
   const int nthr = blockDim.x;
   const int n2 = p.deltas == 1 ? 2 * p.n : (p.deltas ? p.n : 0);

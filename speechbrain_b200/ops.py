@@ -9,6 +9,7 @@ import ctypes as C
 
 import torch
 
+from . import _lib
 from ._lib import FbankDesc, check, lib
 
 __all__ = [
@@ -147,11 +148,13 @@ class TileStats:
     """Per-tile column statistics emitted by the fused Fbank kernel (include/sbfe.h:
     sbfe_fbank_tile_frames) plus what is needed to use them later."""
 
-    __slots__ = ("stats", "frames", "utt_max", "top_db", "version")
+    __slots__ = ("stats", "frames", "utt_max", "top_db", "version", "clamp_mark", "ran_beside")
 
     def __init__(self, stats, frames, utt_max, top_db):
         self.stats, self.frames, self.utt_max, self.top_db = stats, frames, utt_max, top_db
         self.version = None
+        self.clamp_mark = None  # (launch count, stream, x) right after clamp_tiles
+        self.ran_beside = False  # the last norm_stats_tiles ran beside that clamp
 
 
 def ragged_supported(tables, device):
@@ -216,6 +219,7 @@ def clamp_tiles(x, ts, top_db):
         check(lib().sbfe_clamp_tiles(_ptr(x), B, T, F, _ptr(ts.utt_max), float(top_db),
                                      _ptr(ts.stats), ts.frames, _stream()))
     ts.top_db = float(top_db)
+    ts.clamp_mark = (_lib.launches, torch.cuda.current_stream().cuda_stream, x.data_ptr())
     return x
 
 
@@ -226,10 +230,14 @@ def norm_stats_tiles(x, lengths, ts, mean_norm=True, std_norm=True, eps=1e-10):
     mean = torch.empty((B, F), dtype=torch.float32, device=x.device)
     std = torch.empty((B, F), dtype=torch.float32, device=x.device)
     with torch.cuda.device(x.device):
+        # the clamp of this very tensor was the library's last launch on this stream: the
+        # statistics kernel may run beside it (include/sbfe.h: SBFE_STATS_BESIDE_CLAMP)
+        beside = ts.clamp_mark == (_lib.launches, torch.cuda.current_stream().cuda_stream, x.data_ptr())
         check(lib().sbfe_norm_stats_tiles(_ptr(x), _ptr(lengths), B, T, F, int(bool(mean_norm)),
                                           int(bool(std_norm)), float(eps), _ptr(ts.utt_max),
                                           float(ts.top_db), _ptr(ts.stats), ts.frames, _ptr(mean),
-                                          _ptr(std), _stream()))
+                                          _ptr(std), int(beside), _stream()))
+    ts.ran_beside = beside
     return mean, std
 
 

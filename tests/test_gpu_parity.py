@@ -276,6 +276,47 @@ def test_tile_stats_path_matches_generic_kernels(sb):
     assert torch.allclose(got, want, rtol=1e-4, atol=1e-4)
 
 
+def test_stats_beside_the_clamp_equal_stats_after_it(sb):
+    """norm_stats_tiles launched straight after clamp_tiles runs BESIDE it (no wait for the
+    clamp's writes, include/sbfe.h SBFE_STATS_BESIDE_CLAMP): bit-identical to running after
+    it, on a batch where most tiles are clamped and many are cut, every time."""
+    from speechbrain_b200 import ops
+
+    rng = np.random.default_rng(17)
+    B, L = 48, 16 * 16000
+    wav = (rng.standard_normal((B, L)) * 0.1).astype(np.float32)
+    n = rng.integers(800, L, B)
+    for i in range(B):
+        wav[i, n[i]:] = 0                        # silence tails: whole tiles sit below the floor
+        wav[i, n[i] // 2: n[i] // 2 + 4000] *= 1e-6   # and a quiet stretch inside the valid part
+    x = dev(wav)
+    lens = torch.from_numpy((n / L).astype(np.float32)).cuda()
+    tables = sb.Fbank(n_mels=80)._frontend_tables()
+    for trial in range(12):
+        raw, _, ts = ops.fbank_forward(tables, x, tile_stats=True)
+        a = raw.clone()
+        torch.cuda.synchronize()
+        ops.clamp_tiles(a, ts, 80.0)
+        m1, s1 = ops.norm_stats_tiles(a, lens, ts)
+        assert ts.ran_beside
+        out1 = ops.norm_apply(a, m1, s1, True)
+        b_ = raw.clone()
+        ops.clamp_tiles(b_, ts, 80.0)
+        torch.cuda.synchronize()
+        ts.clamp_mark = None
+        m2, s2 = ops.norm_stats_tiles(b_, lens, ts)
+        assert not ts.ran_beside
+        assert torch.equal(a, b_)
+        assert torch.equal(m1, m2) and torch.equal(s1, s2)
+        assert torch.equal(out1, ops.norm_apply(b_, m2, s2, True))   # what follows saw the clamp
+    # anything of the library launched in between withdraws the permission
+    raw, _, ts = ops.fbank_forward(tables, x, tile_stats=True)
+    ops.clamp_tiles(raw, ts, 80.0)
+    ops.tensor_mean(raw)
+    ops.norm_stats_tiles(raw, lens, ts)
+    assert not ts.ran_beside
+
+
 def test_ragged_ingest_is_bit_identical(sb):
     """RaggedBatch (packed valid samples, zero-fill in the kernel) == the padded batch."""
     rng = np.random.default_rng(9)
