@@ -21,6 +21,7 @@
 //    entries; both halves of a warp read the same entry (broadcast).
 #include <cmath>
 #include <cstring>
+#include <type_traits>
 
 #include "common.cuh"
 #include "fft_packed.cuh"
@@ -95,82 +96,68 @@ __device__ __forceinline__ void cp_async_wait() {
 // kThreads = 4*80 the thread's sample / smem offsets are base + k*{640, 648}: immediates.
 // Returns true when the staging used the aligned chunk mapping (thread -> chunks k*kThreads + tid),
 // which lets a thread look at its own copies before the barrier (all-zero tile detection).
+// Everything but `thr_src` (= wav + ibase - n_fft/2, per thread, loop-invariant) is uniform
+// over the CTA: the interior tile costs one 64-bit add per thread besides its copies.
 template <bool PCM16>
-__device__ __forceinline__ bool prefetch_tile(const Params& prm, int64_t b, int64_t t0, float* dst,
+__device__ __forceinline__ bool prefetch_tile(const Params& prm, unsigned b, unsigned j, float* dst,
                                               int tid, int ibase, int dbase) {
   static_assert(kThreads == 4 * (kHop / 2), "chunk mapping assumes 4 hops per pass");
-  const int64_t g0 = t0 * kHop - kNfft / 2;                 // even
-  const int64_t row0 = prm.offsets ? __ldg(prm.offsets + b) : b * prm.wav_stride;
+  using S = typename std::conditional<PCM16, int16_t, float>::type;
+  constexpr int kCp = PCM16 ? 4 : 8;                         // bytes per chunk (2 samples)
+  const int64_t row0 = prm.offsets ? __ldg(prm.offsets + b) : (int64_t)b * prm.wav_stride;
   const int64_t Lb = prm.nsamples ? (int64_t)__ldg(prm.nsamples + b) : prm.L;
-  const int lo = g0 < 0 ? (int)(-g0) : 0;                   // 0 or 200
-  const int64_t rem = Lb - g0;
-  const int hi = rem <= 0 ? 0 : (rem < kSpan ? (int)rem : kSpan);
-  if constexpr (PCM16) {
-    // same chunk mapping, 2 samples = 4 bytes per chunk; the staged span keeps the float
-    // layout's indices (pitch kPitch per hop) in 16-bit units
-    const int16_t* row = reinterpret_cast<const int16_t*>(prm.wav) + row0;
-    const int16_t* wsrc = row + g0;
-    int16_t* d16 = reinterpret_cast<int16_t*>(dst);
-    const bool al4 = (reinterpret_cast<uintptr_t>(row) & 3) == 0;
-    if (al4 && g0 >= 0 && g0 + kSpan <= Lb) {
-#pragma unroll
-      for (int k = 0; k < kCpIters; ++k)
-        if (k * kThreads + tid < kChunks)
-          cp_async4(d16 + dbase + k * (4 * kPitch), wsrc + ibase + k * (4 * kHop), 4);
-      return true;
-    }
-    if (al4) {
-#pragma unroll 1
-      for (int k = 0; k < kCpIters; ++k) {
-        if (k * kThreads + tid < kChunks) {
-          const int i = ibase + k * (4 * kHop);
-          int n = hi - i;
-          n = (i < lo || n < 0) ? 0 : (n > 2 ? 2 : n);
-          cp_async4(d16 + dbase + k * (4 * kPitch), n ? (const void*)(wsrc + i) : (const void*)prm.window,
-                    2 * n);
-        }
-      }
-    } else {  // odd sample offset: plain 16-bit copies (ordered by the barrier that opens the tile)
-      for (int i = tid; i < kSpan; i += kThreads)
-        d16[i + (i / kHop) * kPad] = (i >= lo && i < hi) ? wsrc[i] : (int16_t)0;
-    }
-    return al4;
-  } else {
-  const float* row = prm.wav + row0;
-  const float* wsrc = row + g0;                             // dereferenced inside [lo, hi) only
-  const bool al8 = (reinterpret_cast<uintptr_t>(row) & 7) == 0;
-  if (al8 && g0 >= 0 && g0 + kSpan <= Lb) {                 // interior tile: no guards at all
-    const float* src = wsrc + ibase;
-    float* d = dst + dbase;
+  const int64_t t0s = (int64_t)j * (kTile * kHop);            // first sample of frame t0, + n_fft/2
+  const S* row = reinterpret_cast<const S*>(prm.wav) + row0;
+  const bool al = (reinterpret_cast<uintptr_t>(row) & (kCp - 1)) == 0;
+  S* d = reinterpret_cast<S*>(dst) + dbase;
+  if (al && j != 0 && t0s + (kSpan - kNfft / 2) <= Lb) {     // interior tile: no guards at all
+    const S* src = row + t0s + (ibase - kNfft / 2);
 #pragma unroll
     for (int k = 0; k < kCpIters; ++k)
-      if (k * kThreads + tid < kChunks) cp_async8(d + k * (4 * kPitch), src + k * (4 * kHop), 8);
+      if (k * kThreads + tid < kChunks) {
+        if constexpr (PCM16) cp_async4(d + k * (4 * kPitch), src + k * (4 * kHop), 4);
+        else cp_async8(d + k * (4 * kPitch), src + k * (4 * kHop), 8);
+      }
     return true;
   }
-  if (al8) {
+  const int64_t g0 = t0s - kNfft / 2;                         // even
+  const S* wsrc = row + g0;                                   // dereferenced inside [lo, hi) only
+  const int lo = g0 < 0 ? (int)(-g0) : 0;                     // 0 or 200
+  const int64_t rem = Lb - g0;
+  const int hi = rem <= 0 ? 0 : (rem < kSpan ? (int)rem : kSpan);
+  if (al) {
 #pragma unroll 1
     for (int k = 0; k < kCpIters; ++k) {
       if (k * kThreads + tid < kChunks) {
         const int i = ibase + k * (4 * kHop);
         int n = hi - i;
         n = (i < lo || n < 0) ? 0 : (n > 2 ? 2 : n);
-        cp_async8(dst + dbase + k * (4 * kPitch), n ? wsrc + i : prm.window, 4 * n);
+        const void* g = n ? (const void*)(wsrc + i) : (const void*)prm.window;
+        if constexpr (PCM16) cp_async4(d + k * (4 * kPitch), g, 2 * n);
+        else cp_async8(d + k * (4 * kPitch), reinterpret_cast<const float*>(g), 4 * n);
       }
     }
+  } else if constexpr (PCM16) {
+    // odd sample offset: plain 16-bit copies (ordered by the barrier that opens the tile)
+    int16_t* d16 = reinterpret_cast<int16_t*>(dst);
+    for (int i = tid; i < kSpan; i += kThreads)
+      d16[i + (i / kHop) * kPad] = (i >= lo && i < hi) ? wsrc[i] : (int16_t)0;
   } else {
     for (int i = tid; i < kSpan; i += kThreads) {
       const bool ok = i >= lo && i < hi;
-      cp_async4(dst + i + (i / kHop) * kPad, ok ? wsrc + i : prm.window, ok ? 4 : 0);
+      cp_async4(dst + i + (i / kHop) * kPad, ok ? (const void*)(wsrc + i) : (const void*)prm.window,
+                ok ? 4 : 0);
     }
   }
-  return al8;
-  }
+  return al;
 }
 
 #ifndef SBFE_EXP_MINB
 #define SBFE_EXP_MINB 2
 #endif
-template <bool PCM16>
+// MC > 0: n_mels is the compile-time constant MC (every M-dependent index, walk and trip count
+// folds away: the recipes' 80 / 40 / 23 filters); MC == 0: any n_mels at run time
+template <bool PCM16, int MC>
 __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(const __grid_constant__ Params prm) {
   extern __shared__ __align__(16) float smem[];
   float* s_a = smem;                       // 2 x [staged waveform | P[bin][32]]
@@ -179,7 +166,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
   float* s_tt = s_tw + kTabW;              // [n2][20]: (re, im) of W400^(k1*n2), k1 = 1..9, 2 pad
   float* s_t2 = s_tt + kTabTw;             // [h][20]
   int2* s_meta = reinterpret_cast<int2*>(s_t2 + kTabT2);
-  const int M = prm.n_mels;
+  const int M = MC > 0 ? MC : prm.n_mels;
   float* s_w = reinterpret_cast<float*>(s_meta) + ((2 * M + 3) & ~3);  // 16-byte aligned
 
   __shared__ unsigned s_tile_key;  // max key of the current tile (tile records)
@@ -215,7 +202,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
   const unsigned step_j = gridDim.x - step_b * prm.tiles_per_utt;
   int nt0 = (int)nj * kTile;
   bool chunked = false, nxt_chunked = false;   // staging mode of the current / next tile (uniform)
-  if (tile < prm.n_tiles) nxt_chunked = prefetch_tile<PCM16>(prm, nb, nt0, s_a, tid, ibase, dbase);
+  if (tile < prm.n_tiles) nxt_chunked = prefetch_tile<PCM16>(prm, nb, nj, s_a, tid, ibase, dbase);
   cp_async_commit();
   float db_scale = prm.db.scale, db_amin = prm.db.amin, db_off = prm.db.offset,
         db_floor = prm.db.floor_db;
@@ -273,7 +260,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
       nt0 = (int)nj * kTile;
 #ifndef SBFE_EXP_NOPREFETCH
       if (nxt < prm.n_tiles)
-        nxt_chunked = prefetch_tile<PCM16>(prm, nb, nt0, s_a + ((it & 1) ^ 1) * kRegionA, tid, ibase, dbase);
+        nxt_chunked = prefetch_tile<PCM16>(prm, nb, nj, s_a + ((it & 1) ^ 1) * kRegionA, tid, ibase, dbase);
 #endif
       cp_async_commit();
     }
@@ -583,37 +570,45 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
       const int nvalid = left < kTile ? (int)left : kTile;
       float* ts = prm.tile_stats + (size_t)tile * tile_rec_words(M);
       // thread = (column, quarter of the rows): 4 partial sums about the column's first value,
-      // merged with two shuffles; lanes (8 columns x 4 quarters) hit 32 distinct banks
+      // merged with two shuffles; lanes (8 columns x 4 quarters) hit 32 distinct banks.
+      // FULL (all 32 frames exist: every tile but an utterance's last) carries no row guards.
       const int q = tid & 3;
-      for (int m0 = 0; m0 < M; m0 += kThreads / 4) {
-        const int m = m0 + (tid >> 2);
-        const bool live = m < M;
-        const float* col = s_o + (live ? m : 0);
-        const float x0 = col[0];
-        float s1 = 0.f, s2 = 0.f, mn = x0;
+      auto column_stats = [&](auto full_tag) {
+        constexpr bool FULL = decltype(full_tag)::value;
+        const float inv = FULL ? 1.f / kTile : 1.f / (float)nvalid;
+        for (int m0 = 0; m0 < M; m0 += kThreads / 4) {
+          const int m = m0 + (tid >> 2);
+          const bool live = m < M;
+          const float* col = s_o + (live ? m : 0);
+          const float x0 = col[0];
+          const float* cq = col + q * (kTile / 4) * opitch;
+          float v[kTile / 4];
 #pragma unroll
-        for (int r = 0; r < kTile / 4; ++r) {
-          const int row = q * (kTile / 4) + r;
-          if (row < nvalid) {
-            const float v = col[row * opitch], d = v - x0;
+          for (int r = 0; r < kTile / 4; ++r)
+            v[r] = (FULL || q * (kTile / 4) + r < nvalid) ? cq[r * opitch] : x0;  // x0: neutral
+          float s1 = 0.f, s2 = 0.f, mn = x0;
+#pragma unroll
+          for (int r = 0; r < kTile / 4; ++r) {
+            const float d = v[r] - x0;
             s1 += d;
             s2 = fmaf(d, d, s2);
-            mn = fminf(mn, v);
+            mn = fminf(mn, v[r]);
+          }
+#pragma unroll
+          for (int o = 1; o <= 2; o <<= 1) {
+            s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+            s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+            mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+          }
+          if (live && q < 3) {
+            const float r = q == 0 ? fmaf(s1, inv, x0)
+                                   : (q == 1 ? fmaxf(fmaf(-s1 * inv, s1, s2), 0.f) : mn);
+            ts[q * M + m] = r;
           }
         }
-#pragma unroll
-        for (int o = 1; o <= 2; o <<= 1) {
-          s1 += __shfl_xor_sync(0xffffffffu, s1, o);
-          s2 += __shfl_xor_sync(0xffffffffu, s2, o);
-          mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
-        }
-        if (live) {
-          const float inv = nvalid == kTile ? 1.f / kTile : 1.f / (float)nvalid;
-          if (q == 0) ts[m] = fmaf(s1, inv, x0);
-          if (q == 1) ts[M + m] = fmaxf(fmaf(-s1 * inv, s1, s2), 0.f);
-          if (q == 2) ts[2 * M + m] = mn;
-        }
-      }
+      };
+      if (nvalid == kTile) column_stats(std::true_type{});
+      else column_stats(std::false_type{});
     }
     // the barrier at the top of the next iteration orders these s_o reads before its stage 1
   }
@@ -621,6 +616,17 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
 }
 
 constexpr int kMaxSmem = 110 * 1024;  // two CTAs per SM
+
+using KernelFn = void (*)(Params);
+// the instantiation for this sample type / filter count (fixed-M builds for the recipes' sizes)
+inline KernelFn pick_kernel(int pcm16, int n_mels) {
+  switch (n_mels) {
+    case 80: return pcm16 ? fbank400_v3_kernel<true, 80> : fbank400_v3_kernel<false, 80>;
+    case 40: return pcm16 ? fbank400_v3_kernel<true, 40> : fbank400_v3_kernel<false, 40>;
+    case 23: return pcm16 ? fbank400_v3_kernel<true, 23> : fbank400_v3_kernel<false, 23>;
+    default: return pcm16 ? fbank400_v3_kernel<true, 0> : fbank400_v3_kernel<false, 0>;
+  }
+}
 
 }  // namespace v3
 
@@ -668,19 +674,20 @@ int launch_fbank400_v3(const sbfe_fbank_desc* d, const void* wav, int pcm16, flo
   cudaGetDevice(&dev);
   int sms = (dev >= 0 && dev < 64) ? n_sm[dev] : 0;
   if (sms == 0) {
-    cudaError_t e = cudaFuncSetAttribute(fbank400_v3_kernel<false>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem);
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(fbank400_v3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               kMaxSmem);
+    cudaError_t e = cudaSuccess;
+    for (int pcm = 0; pcm < 2; ++pcm)
+      for (int mc : {0, 80, 40, 23})
+        if (e == cudaSuccess)
+          e = cudaFuncSetAttribute(pick_kernel(pcm, mc), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   kMaxSmem);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (e != cudaSuccess) return (int)e;
     if (dev >= 0 && dev < 64) n_sm[dev] = sms;
   }
   // persistent: two CTAs per SM, each strides over the tiles
   const unsigned grid = prm.n_tiles < (unsigned)(2 * sms) ? prm.n_tiles : (unsigned)(2 * sms);
-  return launch_pdl(pcm16 ? fbank400_v3_kernel<true> : fbank400_v3_kernel<false>, dim3(grid),
-                    dim3(kThreads), (size_t)smem, stream, prm);
+  return launch_pdl(pick_kernel(pcm16, d->n_mels), dim3(grid), dim3(kThreads), (size_t)smem, stream,
+                    prm);
 }
 
 }  // namespace sbfe
