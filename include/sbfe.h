@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define SBFE_ABI_VERSION 5
+#define SBFE_ABI_VERSION 6
 
 #if defined(__GNUC__)
 #define SBFE_API __attribute__((visibility("default")))
@@ -134,7 +134,12 @@ SBFE_API int sbfe_fbank_forward_ragged_pcm16(const sbfe_fbank_desc* desc, const 
  * before this one is sbfe_clamp_tiles on the same d_x with the same records and top_db.  The
  * statistics do not depend on whether that clamp has landed yet (every value is read through
  * max(., floor)), so the kernel then runs beside it instead of after it; stream order for
- * everything that FOLLOWS is unchanged.  0 is always correct. */
+ * everything that FOLLOWS is unchanged.  0 is always correct.
+ * d_utt_max_out ([B], optional, may be NULL) receives the utterance maxima rebuilt from the
+ * records.  With them sbfe_norm_apply can apply the top_db clamp on the fly, so a caller that
+ * normalises d_x in place right away (InputNormalization "sentence" / "speaker") may pass the
+ * UN-clamped output of sbfe_fbank_forward here and skip sbfe_clamp_tiles altogether: every
+ * statistic is taken through max(., floor) whether or not the clamp was ever launched. */
 #define SBFE_STATS_BESIDE_CLAMP 1
 SBFE_API int32_t sbfe_fbank_tile_frames(const sbfe_fbank_desc* desc);
 SBFE_API int32_t sbfe_fbank_tile_stats_floats(const sbfe_fbank_desc* desc);
@@ -145,7 +150,7 @@ SBFE_API int sbfe_norm_stats_tiles(const float* d_x, const float* d_lengths, int
                           int32_t F, int32_t mean_norm, int32_t std_norm, float eps,
                           const sbfe_maxkey_t* d_utt_max, float top_db,
                           const float* d_tile_stats, int32_t tile_frames, float* d_mean,
-                          float* d_std, int32_t flags, void* stream);
+                          float* d_std, int32_t flags, sbfe_maxkey_t* d_utt_max_out, void* stream);
 
 /* STFT.forward for [B, L] input (processing/features.py:133-188):
  * out [B, T, bins, 2] (re, im), or, with power_only != 0, [B, T, bins] = re^2+im^2. */
@@ -195,10 +200,17 @@ SBFE_API int sbfe_norm_update(const float* d_cur, int32_t F, int32_t first, floa
 
 /* out = (x - mean) / std (processing/features.py:1035, 1088, 1116).
  * per_utt != 0: mean/std are [B, F]; else [F] shared.  In place when out == x.
- * d_utt_max != NULL applies the top_db clamp to x first. */
+ * d_utt_max != NULL applies the top_db clamp to x first.
+ * flags = SBFE_APPLY_X_STABLE: the caller states that the launch made on `stream` just before
+ * this one is a statistics call of this library on the same d_x (sbfe_norm_stats_tiles without
+ * SBFE_STATS_BESIDE_CLAMP, sbfe_norm_stats, sbfe_norm_speaker_update, ...: one that reads d_x
+ * at most).  The kernel then requests its share of d_x before it waits for that launch, so
+ * the reads overlap the statistics; d_mean / d_std / d_utt_max are read after it.  0 is always
+ * correct. */
+#define SBFE_APPLY_X_STABLE 1
 SBFE_API int sbfe_norm_apply(const float* d_x, int64_t B, int64_t T, int32_t F, const float* d_mean,
                     const float* d_std, int32_t per_utt, const sbfe_maxkey_t* d_utt_max,
-                    float top_db, float* d_out, void* stream);
+                    float top_db, float* d_out, int32_t flags, void* stream);
 
 /* ---- next row: speaker-mode statistics (processing/features.py:1037-1081) --
  * The speaker dictionary stays on the host (ids -> rows of d_table_mean / d_table_std [rows, F]);

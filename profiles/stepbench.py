@@ -19,18 +19,24 @@ tab = fb._frontend_tables()
 
 def step(w, upto):
     feats, _, ts = ops.fbank_forward(tab, w, tile_stats=True)
-    if upto >= 1:
+    if 1 <= upto <= 3:
         ops.clamp_tiles(feats, ts, 80.0)
     if upto == 2:
         mean, std = ops.norm_stats_tiles(feats, lens, ts)
     if upto == 3:
         mean, std = ops.norm_stats_tiles(feats, lens, ts)
-        ops.norm_apply(feats, mean, std, per_utt=True, out=feats)
+        ops.norm_apply(feats, mean, std, per_utt=True, out=feats, stats_mark=ops.stats_launch_mark(feats))
+    if upto == 4:   # pair(): no clamp launch, the normalisation clamps on the fly
+        ts.top_db = 80.0
+        mean, std, keys = ops.norm_stats_tiles(feats, lens, ts, want_max=True)
+        ops.norm_apply(feats, mean, std, per_utt=True, out=feats, utt_max=keys, top_db=80.0,
+                       stats_mark=ops.stats_launch_mark(feats))
     return feats
 
 
 prev = 0.0
-for upto, name in enumerate(["fbank400_v3 (+tile records)", "+ clamp_tiles", "+ norm_stats_tiles", "+ norm_apply"]):
+for upto, name in enumerate(["fbank400_v3 (+tile records)", "+ clamp_tiles", "+ norm_stats_tiles", "+ norm_apply",
+                             "paired: fbank + stats + apply(clamp)"]):
     for w in pool[:2]:
         step(w, upto)
     torch.cuda.synchronize()

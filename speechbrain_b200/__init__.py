@@ -8,7 +8,7 @@ behind a C ABI (include/sbfe.h).  See DESIGN.md / INTEGRATION.md.
 """
 from .dataio import RaggedBatch  # noqa: F401
 from .lobes.augment import SpecAugment  # noqa: F401
-from .lobes.features import MFCC, Fbank  # noqa: F401
+from .lobes.features import MFCC, Fbank, pair  # noqa: F401
 from .processing.features import (  # noqa: F401
     DCT, STFT, ContextWindow, Deltas, Filterbank, InputNormalization, spectral_magnitude)
 

@@ -56,6 +56,12 @@ def _tracing():
     return torch._C._get_tracing_state() is not None and not getattr(_local, "inside", 0)
 
 
+def plain_eager():
+    """True outside ``torch.jit.trace`` and outside a replay of a traced graph: only then can
+    python attributes on a returned tensor reach the next module (the tile-record hand-over)."""
+    return torch._C._get_tracing_state() is None and not getattr(_local, "inside", 0)
+
+
 def traceable(inplace_arg=None):
     """Decorate ``forward(self, *tensors, **constants)``.  ``inplace_arg`` = index of the tensor
     argument the eager ``forward`` overwrites and returns (None: returns a fresh tensor, or

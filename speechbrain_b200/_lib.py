@@ -55,7 +55,7 @@ SIGNATURES = {
     "sbfe_fbank_tile_stats_floats": (_I32, [_DESC]),
     "sbfe_clamp_tiles": (C.c_int, [_P, _I64, _I64, _I32, _P, _F, _P, _I32, _P]),
     "sbfe_norm_stats_tiles": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, _I32, _F, _P, _F, _P, _I32,
-                                        _P, _P, _I32, _P]),
+                                        _P, _P, _I32, _P, _P]),
     "sbfe_stft_forward": (C.c_int, [_DESC, _P, _I64, _I64, _I64, _P, _I32, _P]),
     "sbfe_spectral_magnitude": (C.c_int, [_P, _I64, _F, _I32, _F, _P, _P]),
     "sbfe_filterbank_forward": (C.c_int, [_DESC, _P, _I64, _I64, _P, _P, _P]),
@@ -66,7 +66,7 @@ SIGNATURES = {
                                   _I64, _P]),
     "sbfe_norm_reduce": (C.c_int, [_P, _P, _I64, _I32, _P, _P]),
     "sbfe_norm_update": (C.c_int, [_P, _I32, _I32, _F, _P, _P, _P]),
-    "sbfe_norm_apply": (C.c_int, [_P, _I64, _I64, _I32, _P, _P, _I32, _P, _F, _P, _P]),
+    "sbfe_norm_apply": (C.c_int, [_P, _I64, _I64, _I32, _P, _P, _I32, _P, _F, _P, _I32, _P]),
     "sbfe_norm_speaker_update": (C.c_int, [_P, _P, _I64, _I32, _P, _P, _P, _P, _P, _P, _P, _P]),
     "sbfe_specaugment_forward": (C.c_int, [_P, _I64, _I64, _I32, _I32, _I32, _I32, _P, _P, _I32, _P,
                                            _P, _I32, _P, _F, _P, _P]),
@@ -106,7 +106,7 @@ def lib():
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(handle, name)
             fn.restype, fn.argtypes = res, args
-        if handle.sbfe_abi_version() != 5:
+        if handle.sbfe_abi_version() != 6:
             raise SbfeUnavailable("libsbfe.so ABI version mismatch")
         _lib = handle
         return _lib

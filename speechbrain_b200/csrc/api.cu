@@ -13,7 +13,7 @@ int launch_clamp_tiles(float*, int64_t, int64_t, int, const sbfe_maxkey_t*, floa
                        cudaStream_t);
 int launch_norm_stats_tiles(const float*, const float*, int64_t, int64_t, int, int, int, float,
                             const sbfe_maxkey_t*, float, const float*, int, float*, float*, int,
-                            cudaStream_t);
+                            sbfe_maxkey_t*, cudaStream_t);
 int launch_stft_generic(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
                         int, cudaStream_t);
 int launch_spectral_magnitude(const float*, int64_t, float, int, float, float*, cudaStream_t);
@@ -27,7 +27,7 @@ int launch_norm_stats(const float*, const float*, int64_t, int64_t, int, int, in
 int launch_norm_reduce(const float*, const float*, int64_t, int, float*, cudaStream_t);
 int launch_norm_update(const float*, int, int, float, float*, float*, cudaStream_t);
 int launch_norm_apply(const float*, int64_t, int64_t, int, const float*, const float*, int,
-                      const sbfe_maxkey_t*, float, float*, cudaStream_t);
+                      const sbfe_maxkey_t*, float, float*, int, cudaStream_t);
 
 static bool desc_ok(const sbfe_fbank_desc* d, bool need_mel) {
   if (!d || d->n_fft < 2 || (d->n_fft & 1) || d->hop < 1 || !d->d_window || !d->h_window)
@@ -178,14 +178,15 @@ int sbfe_norm_stats_tiles(const float* d_x, const float* d_lengths, int64_t B, i
                           int32_t mean_norm, int32_t std_norm, float eps,
                           const sbfe_maxkey_t* d_utt_max, float top_db, const float* d_tile_stats,
                           int32_t tile_frames, float* d_mean, float* d_std, int32_t flags,
-                          void* stream) {
+                          sbfe_maxkey_t* d_utt_max_out, void* stream) {
   if (B < 0 || T < 0 || F < 0 || tile_frames < 1) return SBFE_E_INVAL;
   if (flags & ~SBFE_STATS_BESIDE_CLAMP) return SBFE_E_INVAL;
   if (B == 0 || F == 0) return 0;
   if (!d_x || !d_lengths || !d_mean || !d_std || !d_tile_stats) return SBFE_E_INVAL;
   return launch_norm_stats_tiles(d_x, d_lengths, B, T, F, mean_norm, std_norm, eps, d_utt_max,
                                  top_db, d_tile_stats, tile_frames, d_mean, d_std,
-                                 (flags & SBFE_STATS_BESIDE_CLAMP) != 0, (cudaStream_t)stream);
+                                 (flags & SBFE_STATS_BESIDE_CLAMP) != 0, d_utt_max_out,
+                                 (cudaStream_t)stream);
 }
 
 int64_t sbfe_norm_workspace_bytes(int64_t B, int64_t T, int32_t F) {
@@ -219,12 +220,12 @@ int sbfe_norm_update(const float* d_cur, int32_t F, int32_t first, float weight,
 
 int sbfe_norm_apply(const float* d_x, int64_t B, int64_t T, int32_t F, const float* d_mean,
                     const float* d_std, int32_t per_utt, const sbfe_maxkey_t* d_utt_max,
-                    float top_db, float* d_out, void* stream) {
-  if (B < 0 || T < 0 || F < 0) return SBFE_E_INVAL;
+                    float top_db, float* d_out, int32_t flags, void* stream) {
+  if (B < 0 || T < 0 || F < 0 || (flags & ~SBFE_APPLY_X_STABLE)) return SBFE_E_INVAL;
   if (B == 0 || T == 0 || F == 0) return 0;
   if (!d_x || !d_out || !d_mean || !d_std) return SBFE_E_INVAL;
   return launch_norm_apply(d_x, B, T, F, d_mean, d_std, per_utt, d_utt_max, top_db, d_out,
-                           (cudaStream_t)stream);
+                           (flags & SBFE_APPLY_X_STABLE) != 0, (cudaStream_t)stream);
 }
 
 int sbfe_norm_speaker_update(const float* d_mean, const float* d_std, int64_t B, int32_t F,

@@ -33,7 +33,8 @@ __host__ __device__ inline size_t tile_rec_words(int F) { return (size_t)3 * F +
 
 // top_db floor of utterance b from the tile records (whole CTA must call; uses one barrier pair)
 __device__ __forceinline__ float block_floor_from_tiles(const float* tile_stats, int64_t b, int tiles,
-                                                        int F, float top_db) {
+                                                        int F, float top_db,
+                                                        unsigned* key_out = nullptr) {
   __shared__ unsigned s_floor_key;
   if (threadIdx.x == 0) s_floor_key = 0u;
   __syncthreads();
@@ -48,6 +49,7 @@ __device__ __forceinline__ float block_floor_from_tiles(const float* tile_stats,
   if ((threadIdx.x & 31) == 0 && k) atomicMax(&s_floor_key, k);
   __syncthreads();
   const unsigned key = s_floor_key;
+  if (key_out != nullptr) *key_out = key;   // the utterance's max key (0: no record held one)
   return key ? max_key_decode(key) - top_db : -INFINITY;
 }
 

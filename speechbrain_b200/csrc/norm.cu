@@ -128,7 +128,7 @@ norm_stats_tiles_kernel(const float* x, const float* __restrict__ lengths, int64
                         int F, int tile, int tiles, const float* __restrict__ tile_stats,
                         const sbfe_maxkey_t* __restrict__ utt_max, float top_db, int mean_norm,
                         int std_norm, float eps, float* __restrict__ mean, float* __restrict__ stdv,
-                        int beside_clamp) {
+                        int beside_clamp, sbfe_maxkey_t* __restrict__ utt_max_out) {
   if (!beside_clamp) {
     pdl_wait();
     pdl_launch_dependents();
@@ -175,8 +175,13 @@ norm_stats_tiles_kernel(const float* x, const float* __restrict__ lengths, int64
       cv[i] = (r < n - r_cut) ? col[(int64_t)r * F] : NAN;
     }
   }
+  unsigned max_key = 0u;
   const float floor_b = utt_max ? clamp_floor(utt_max, b, top_db)
-                                : block_floor_from_tiles(tile_stats, b, tiles, F, top_db);
+                                : block_floor_from_tiles(tile_stats, b, tiles, F, top_db, &max_key);
+  // the utterance maximum rebuilt from the tile keys, for a consumer that clamps on the fly
+  // (norm_apply_kernel) instead of after a clamp_tiles launch
+  if (utt_max_out != nullptr && blockIdx.x == 0 && threadIdx.x == 0)
+    utt_max_out[b] = utt_max ? utt_max[b] : max_key;
   Moments acc{0.f, 0.f, 0.f};
   if (f < F) {
     int c = 0;
@@ -318,19 +323,18 @@ __global__ void __launch_bounds__(kNormThreads)
 norm_apply_kernel(const float* x, int64_t T, int F, const float* __restrict__ mean,
                   const float* __restrict__ stdv, int per_utt,
                   const sbfe_maxkey_t* __restrict__ utt_max, float top_db, float* out,
-                  unsigned chunks) {
-  pdl_wait();
-  pdl_launch_dependents();
+                  unsigned chunks, int x_stable) {
+  // x_stable: the launch directly before this one does not write x (it produces the
+  // statistics), and whatever wrote x completed before that launch triggered this one
+  // (common.cuh) - the vectors of x are then requested BEFORE the wait and fly while the
+  // statistics kernel finishes; mean / std / utt_max are read after it
+  if (!x_stable) {
+    pdl_wait();
+    pdl_launch_dependents();
+  }
   extern __shared__ __align__(16) float s_ms[];  // mean[F] | std[F]
   const int64_t b = blockIdx.x / chunks;
   const int c = blockIdx.x - b * chunks;
-  const float* m = mean + (per_utt ? b * F : 0);
-  const float* s = stdv + (per_utt ? b * F : 0);
-  for (int f = threadIdx.x; f < F; f += kNormThreads) {
-    s_ms[f] = __ldg(m + f);
-    s_ms[F + f] = __ldg(s + f);
-  }
-  const float floor_b = clamp_floor(utt_max, b, top_db);
   const int FV = F / VEC;
   const int64_t nvec = T * FV;
   const int64_t i0 = (int64_t)c * (kNormThreads * kApplyIters) + threadIdx.x;
@@ -338,13 +342,27 @@ norm_apply_kernel(const float* x, int64_t T, int F, const float* __restrict__ me
   float* ob = out + b * T * F;
   int col = (int)(i0 % FV);
   const int dcol = kNormThreads % FV;
+  float4 v4[VEC == 4 ? kApplyIters : 1];
   if (VEC == 4) {
-    float4 v[kApplyIters];
 #pragma unroll
     for (int k = 0; k < kApplyIters; ++k) {
       const int64_t i = i0 + (int64_t)k * kNormThreads;
-      if (i < nvec) v[k] = *reinterpret_cast<const float4*>(xb + 4 * i);
+      if (i < nvec) v4[k] = *reinterpret_cast<const float4*>(xb + 4 * i);
     }
+  }
+  if (x_stable) {
+    pdl_wait();
+    pdl_launch_dependents();
+  }
+  const float* m = mean + (per_utt ? b * F : 0);
+  const float* s = stdv + (per_utt ? b * F : 0);
+  for (int f = threadIdx.x; f < F; f += kNormThreads) {
+    s_ms[f] = __ldg(m + f);
+    s_ms[F + f] = __ldg(s + f);
+  }
+  const float floor_b = clamp_floor(utt_max, b, top_db);
+  if (VEC == 4) {
+    float4 (&v)[VEC == 4 ? kApplyIters : 1] = v4;
     __syncthreads();
 #pragma unroll
     for (int k = 0; k < kApplyIters; ++k) {
@@ -413,7 +431,8 @@ int launch_norm_stats(const float* x, const float* lengths, int64_t B, int64_t T
 int launch_norm_stats_tiles(const float* x, const float* lengths, int64_t B, int64_t T, int F,
                             int mean_norm, int std_norm, float eps, const sbfe_maxkey_t* utt_max,
                             float top_db, const float* tile_stats, int tile, float* mean,
-                            float* stdv, int beside_clamp, cudaStream_t stream) {
+                            float* stdv, int beside_clamp, sbfe_maxkey_t* utt_max_out,
+                            cudaStream_t stream) {
   if (B == 0 || F == 0) return 0;
   if (B > 0x7fffffff || T > 0x7fffffff) return SBFE_E_TOOBIG;
   const int tiles = (int)((T + tile - 1) / tile);
@@ -421,7 +440,7 @@ int launch_norm_stats_tiles(const float* x, const float* lengths, int64_t B, int
   const dim3 grid((unsigned)((F + kTileStatCols - 1) / kTileStatCols), (unsigned)B);
   return launch_pdl(norm_stats_tiles_kernel, grid, dim3(kTileStatThreads), 0, stream,
       x, lengths, T, F, tile, tiles, tile_stats, utt_max, top_db, mean_norm, std_norm, eps, mean,
-      stdv, beside_clamp);
+      stdv, beside_clamp, utt_max_out);
 }
 
 int launch_norm_reduce(const float* mean, const float* stdv, int64_t B, int F, float* cur,
@@ -438,7 +457,7 @@ int launch_norm_update(const float* cur, int F, int first, float weight, float* 
 
 int launch_norm_apply(const float* x, int64_t B, int64_t T, int F, const float* mean,
                       const float* stdv, int per_utt, const sbfe_maxkey_t* utt_max, float top_db,
-                      float* out, cudaStream_t stream) {
+                      float* out, int x_stable, cudaStream_t stream) {
   if (B == 0 || T == 0 || F == 0) return 0;
   const bool vec = (F % 4 == 0) &&
                    ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
@@ -450,7 +469,7 @@ int launch_norm_apply(const float* x, int64_t B, int64_t T, int F, const float* 
   if (smem > 48 * 1024) return SBFE_E_TOOBIG;
   return launch_pdl(vec ? norm_apply_kernel<4> : norm_apply_kernel<1>, dim3((unsigned)(chunks * B)),
                     dim3(kNormThreads), smem, stream, x, T, F, mean, stdv, per_utt, utt_max, top_db,
-                    out, (unsigned)chunks);
+                    out, (unsigned)chunks, x_stable);
 }
 
 // ---- speaker mode (processing/features.py:1037-1081): running per-speaker statistics ---------

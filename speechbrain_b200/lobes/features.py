@@ -11,10 +11,37 @@ ops:
 import torch
 
 from .. import ops
-from .._jit import traceable
+import weakref
+
+from .._jit import plain_eager, traceable
 from ..processing.features import DCT, STFT, ContextWindow, Deltas, Filterbank
 
-__all__ = ["Fbank", "MFCC"]
+__all__ = ["Fbank", "MFCC", "pair"]
+
+
+def pair(compute_features, normalizer):
+    """Declare that the output of ``compute_features`` (an ``Fbank``) goes straight into
+    ``normalizer`` (an ``InputNormalization``) and nowhere else, as in the recipes'
+    ``feats = self.modules.normalize(self.hparams.compute_features(wavs), wav_lens)``.
+
+    For the in-place modes (``sentence``, ``speaker``) the top_db clamp (reference:
+    processing/features.py:706-710) is then applied inside the normalisation pass instead of
+    by a launch of its own: same result, one kernel and one partial pass over the features
+    less.  Until the normaliser has run, the tensor ``compute_features`` returned holds the
+    UN-clamped dB values - that is the promise this call makes; any ``InputNormalization`` of
+    this package completes the clamp.  ``pair(compute_features, None)`` withdraws it.
+    Returns ``compute_features``."""
+    from ..processing.normalization import InputNormalization
+
+    if not isinstance(compute_features, _Lobe):
+        raise TypeError("pair() takes a speechbrain_b200 Fbank / MFCC")
+    if normalizer is None:
+        compute_features._paired = None
+        return compute_features
+    if not isinstance(normalizer, InputNormalization):
+        raise TypeError("pair() takes a speechbrain_b200 InputNormalization")
+    compute_features._paired = weakref.ref(normalizer)
+    return compute_features
 
 
 class _Lobe(torch.nn.Module):
@@ -35,6 +62,13 @@ class _Lobe(torch.nn.Module):
             param_change_factor=param_change_factor, param_rand_factor=param_rand_factor)
         self.context_window = ContextWindow(left_frames=left_frames, right_frames=right_frames)
         self._tables = None
+        self._paired = None   # weakref to the InputNormalization that takes the output (pair())
+
+    def _defers_clamp(self):
+        """pair(): the one consumer of the output is an in-place InputNormalization, which
+        applies the top_db clamp on the fly - no clamp launch here."""
+        norm = self._paired() if self._paired is not None else None
+        return (norm is not None and norm.norm_type in ("sentence", "speaker") and plain_eager())
 
     def _frontend_tables(self):
         fb = self.compute_fbanks
@@ -67,7 +101,10 @@ class _Lobe(torch.nn.Module):
             # statistics without another pass (handed over on the returned tensor)
             feats, utt_max, ts = ops.fbank_forward(self._frontend_tables(), wav, tile_stats=True)
             if ts is not None:
-                ops.clamp_tiles(feats, ts, fb.top_db)
+                if self._defers_clamp():
+                    ts.top_db, ts.pending_clamp = float(fb.top_db), True
+                else:
+                    ops.clamp_tiles(feats, ts, fb.top_db)
                 ts.version = feats._version
                 feats._sbfe_tile_stats = ts
                 return feats

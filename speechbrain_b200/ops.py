@@ -148,13 +148,15 @@ class TileStats:
     """Per-tile column statistics emitted by the fused Fbank kernel (include/sbfe.h:
     sbfe_fbank_tile_frames) plus what is needed to use them later."""
 
-    __slots__ = ("stats", "frames", "utt_max", "top_db", "version", "clamp_mark", "ran_beside")
+    __slots__ = ("stats", "frames", "utt_max", "top_db", "version", "clamp_mark", "ran_beside",
+                 "pending_clamp")
 
     def __init__(self, stats, frames, utt_max, top_db):
         self.stats, self.frames, self.utt_max, self.top_db = stats, frames, utt_max, top_db
         self.version = None
         self.clamp_mark = None  # (launch count, stream, x) right after clamp_tiles
         self.ran_beside = False  # the last norm_stats_tiles ran beside that clamp
+        self.pending_clamp = False  # the tensor is still UN-clamped (lobes/features.py: pair())
 
 
 def ragged_supported(tables, device):
@@ -223,12 +225,15 @@ def clamp_tiles(x, ts, top_db):
     return x
 
 
-def norm_stats_tiles(x, lengths, ts, mean_norm=True, std_norm=True, eps=1e-10):
-    """norm_stats from the fused kernel's tile partials (no pass over x)."""
+def norm_stats_tiles(x, lengths, ts, mean_norm=True, std_norm=True, eps=1e-10, want_max=False):
+    """norm_stats from the fused kernel's tile partials (no pass over x).  ``x`` may be clamped
+    or not (every value is read through max(., floor)); ``want_max=True`` also returns the
+    utterance max keys [B] for a ``norm_apply`` that clamps on the fly."""
     B, T, F = x.shape
     lengths = lengths.to(device=x.device, dtype=torch.float32).contiguous()
     mean = torch.empty((B, F), dtype=torch.float32, device=x.device)
     std = torch.empty((B, F), dtype=torch.float32, device=x.device)
+    keys = torch.empty((B,), dtype=torch.int32, device=x.device) if want_max else None
     with torch.cuda.device(x.device):
         # the clamp of this very tensor was the library's last launch on this stream: the
         # statistics kernel may run beside it (include/sbfe.h: SBFE_STATS_BESIDE_CLAMP)
@@ -236,9 +241,9 @@ def norm_stats_tiles(x, lengths, ts, mean_norm=True, std_norm=True, eps=1e-10):
         check(lib().sbfe_norm_stats_tiles(_ptr(x), _ptr(lengths), B, T, F, int(bool(mean_norm)),
                                           int(bool(std_norm)), float(eps), _ptr(ts.utt_max),
                                           float(ts.top_db), _ptr(ts.stats), ts.frames, _ptr(mean),
-                                          _ptr(std), int(beside), _stream()))
+                                          _ptr(std), int(beside), _ptr(keys), _stream()))
     ts.ran_beside = beside
-    return mean, std
+    return (mean, std, keys) if want_max else (mean, std)
 
 
 def stft_forward(tables, wav, power_only=False):
@@ -343,14 +348,25 @@ def norm_speaker_update(mean, std, row, mode, weight, table_mean, table_std):
     return out_m, out_s
 
 
-def norm_apply(x, mean, std, per_utt, out=None, utt_max=None, top_db=80.0):
+def norm_apply(x, mean, std, per_utt, out=None, utt_max=None, top_db=80.0, stats_mark=None):
+    """(max(x, floor) - mean) / std.  ``stats_mark`` = what ``stats_launch_mark(x)`` returned
+    right after the statistics call that produced ``mean`` / ``std``: when that call is still
+    the library's last launch on this stream, the kernel reads ``x`` while the statistics
+    finish (include/sbfe.h: SBFE_APPLY_X_STABLE)."""
     B, T, F = x.shape
     if out is None:
         out = torch.empty_like(x)
     with torch.cuda.device(x.device):
+        stable = stats_mark is not None and stats_mark == stats_launch_mark(x)
         check(lib().sbfe_norm_apply(_ptr(x), B, T, F, _ptr(mean), _ptr(std), int(bool(per_utt)),
-                                    _ptr(utt_max), float(top_db), _ptr(out), _stream()))
+                                    _ptr(utt_max), float(top_db), _ptr(out), int(stable), _stream()))
     return out
+
+
+def stats_launch_mark(x):
+    """(library launch count, stream, x) - identifies "the statistics call on x was the last
+    launch of the library on this stream" for ``norm_apply(stats_mark=...)``."""
+    return (_lib.launches, torch.cuda.current_stream().cuda_stream, x.data_ptr())
 
 
 def decode_utt_max(keys):

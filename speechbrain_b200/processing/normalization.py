@@ -81,21 +81,38 @@ class InputNormalization(torch.nn.Module):
         ops._require_cuda(x, "x")
         B, T, F = x.shape
         ts = getattr(x, "_sbfe_tile_stats", None)
+        clamp = {}  # top_db clamp still owed to x (lobes/features.py: pair()), applied on the fly
         if ts is not None:  # one-shot hand-over from the fused Fbank kernel (lobes/features.py)
             x._sbfe_tile_stats = None
             if ts.version != x._version or tuple(ts.stats.shape[::2]) != (B, 3 * F + 4):
+                if ts.pending_clamp:
+                    raise RuntimeError(
+                        "the output of a pair()-ed Fbank was modified before it reached "
+                        "InputNormalization: its top_db clamp is still pending")
                 ts = None
-        if ts is not None:
+        if ts is not None and ts.pending_clamp and self.norm_type not in ("sentence", "speaker"):
+            ops.clamp_tiles(x, ts, ts.top_db)  # these modes leave x behind: it must be complete
+            ts.pending_clamp = False
+        if ts is not None and ts.pending_clamp:
+            mean, std, keys = ops.norm_stats_tiles(x, lengths, ts, self.mean_norm, self.std_norm,
+                                                   self.eps, want_max=True)
+            clamp = {"utt_max": keys, "top_db": ts.top_db}
+            ts.pending_clamp = False
+        elif ts is not None:
             mean, std = ops.norm_stats_tiles(x, lengths, ts, self.mean_norm, self.std_norm, self.eps)
         else:
             mean, std = ops.norm_stats(x, lengths, self.mean_norm, self.std_norm, self.eps)
 
+        # "the statistics were the library's last launch": the apply kernel may then read x
+        # while they finish (include/sbfe.h: SBFE_APPLY_X_STABLE)
         if self.norm_type == "sentence":
-            return ops.norm_apply(x, mean, std, per_utt=True, out=x)  # in place (:1035)
+            return ops.norm_apply(x, mean, std, per_utt=True, out=x,  # in place (:1035)
+                                  stats_mark=ops.stats_launch_mark(x), **clamp)
 
         if self.norm_type == "speaker":
             s_mean, s_std = self._speaker_stats(mean, std, spk_ids)
-            return ops.norm_apply(x, s_mean, s_std, per_utt=True, out=x)  # in place (:1081)
+            return ops.norm_apply(x, s_mean, s_std, per_utt=True, out=x,  # in place (:1081)
+                                  stats_mark=ops.stats_launch_mark(x), **clamp)
 
         if self.norm_type not in ("batch", "global"):
             return x

@@ -317,6 +317,54 @@ def test_stats_beside_the_clamp_equal_stats_after_it(sb):
     assert not ts.ran_beside
 
 
+def test_paired_fbank_defers_the_clamp_to_the_normaliser(sb):
+    """pair(compute_features, normalize): no clamp launch, the in-place normalisation clamps on
+    the fly - bit-identical to the unpaired modules, for sentence and speaker mode; modes that
+    leave x behind complete the clamp first; a tensor modified in between is refused."""
+    rng = np.random.default_rng(31)
+    B, L = 6, 3 * 16000 + 77
+    wav = (rng.standard_normal((B, L)) * 0.1).astype(np.float32)
+    wav[1, L // 2:] = 0
+    wav[0, L // 4: L // 4 + 3000] *= 1e-6     # > 80 dB below the maximum inside the valid part
+    wav[3, :] = 0
+    x = dev(wav)
+    lens = torch.tensor([1.0, 0.5, 0.73, 0.4, 0.051, 0.9]).cuda()
+    spk = torch.tensor([3, 5, 3, 7, 5, 3])
+    for mode in ("sentence", "speaker", "global", "batch"):
+        fb0, n0 = sb.Fbank(n_mels=80), sb.InputNormalization(norm_type=mode)
+        fb1, n1 = sb.Fbank(n_mels=80), sb.InputNormalization(norm_type=mode)
+        assert sb.pair(fb1, n1) is fb1
+        for _ in range(2):   # second pass: running statistics of speaker / global mode
+            f0, f1 = fb0(x), fb1(x)
+            deferred = mode in ("sentence", "speaker")
+            assert f1._sbfe_tile_stats.pending_clamp == deferred
+            assert torch.equal(f0, f1) != deferred or not deferred   # un-clamped differs (tails)
+            want = n0(f0, lens, spk_ids=spk)
+            got = n1(f1, lens, spk_ids=spk)
+            assert torch.equal(got, want), mode
+            if not deferred:
+                assert torch.equal(f0, f1)   # x left behind complete
+    # a deferred tensor modified before it reaches the normaliser is refused, not mis-clamped
+    fb1, n1 = sb.Fbank(n_mels=80), sb.InputNormalization(norm_type="sentence")
+    sb.pair(fb1, n1)
+    f1 = fb1(x)
+    f1 += 1.0
+    with pytest.raises(RuntimeError):
+        n1(f1, lens)
+    # withdrawn pairing / dead normaliser: ordinary clamped output
+    sb.pair(fb1, None)
+    assert not fb1(x)._sbfe_tile_stats.pending_clamp
+    sb.pair(fb1, sb.InputNormalization(norm_type="sentence"))   # collected right away
+    import gc
+    gc.collect()
+    assert not fb1(x)._sbfe_tile_stats.pending_clamp
+    # any InputNormalization of the package completes a pending clamp
+    fb2, n2 = sb.Fbank(n_mels=80), sb.InputNormalization(norm_type="sentence")
+    sb.pair(fb2, n2)
+    other = sb.InputNormalization(norm_type="sentence")
+    assert torch.equal(other(fb2(x), lens), sb.InputNormalization(norm_type="sentence")(sb.Fbank(n_mels=80)(x), lens))
+
+
 def test_ragged_ingest_is_bit_identical(sb):
     """RaggedBatch (packed valid samples, zero-fill in the kernel) == the padded batch."""
     rng = np.random.default_rng(9)
