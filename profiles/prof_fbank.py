@@ -8,7 +8,9 @@ torch.manual_seed(0)
 wav = torch.randn(32, 256000, device="cuda") * 0.1
 lens = torch.ones(32, device="cuda")
 fb, norm = sb.Fbank(n_mels=80), sb.InputNormalization(norm_type="sentence")
-for _ in range(int(sys.argv[1]) if len(sys.argv) > 1 else 4):
+if "--unpaired" not in sys.argv:
+    sb.pair(fb, norm)
+for _ in range(int(sys.argv[1]) if len(sys.argv) > 1 and sys.argv[1].isdigit() else 4):
     out = norm(fb(wav), lens)
 torch.cuda.synchronize()
 print("ok", float(out.abs().mean()))
