@@ -180,16 +180,38 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
   const int ibase = kHop * (tid / (kHop / 2)) + 2 * (tid % (kHop / 2));
   const int dbase = ibase + kPad * (tid / (kHop / 2));
   unsigned tile = blockIdx.x;
-  for (int i = tid; i < kTabW; i += kThreads) {
-    const int n1 = i / 20, n2 = i - n1 * 20;   // window[i] is tap n1 of residue n2
-    s_tw[n2 * 20 + n1] = PCM16 ? __ldg(prm.window + i) * prm.scale : __ldg(prm.window + i);
-    s_tt[i] = kTw400[i];
+  // every table word this thread is responsible for is REQUESTED first and stored afterwards:
+  // one global-memory round trip for the whole prologue instead of one per table
+  {
+    static_assert(kTabW <= 2 * kThreads && kTabT2 <= kThreads, "two table words per thread");
+    const bool second = tid + kThreads < kTabW;
+    const float w0 = __ldg(prm.window + tid), w1 = second ? __ldg(prm.window + tid + kThreads) : 0.f;
+    const float c0 = kTw400[tid], c1 = second ? kTw400[tid + kThreads] : 0.f;
+    const float t2 = tid < kTabT2 ? kT2[tid] : 0.f;
+    int ms = 0, mc = 0, mo = 0;
+    if (tid < M) {
+      ms = __ldg(prm.mel_start + tid);
+      mc = __ldg(prm.mel_count + tid);
+      mo = __ldg(prm.mel_offset + tid);
+    }
+    const float g0 = tid < prm.mel_nnz ? __ldg(prm.mel_weight + tid) : 0.f;
+    const float g1 = tid + kThreads < prm.mel_nnz ? __ldg(prm.mel_weight + tid + kThreads) : 0.f;
+    auto put_w = [&](int i, float w, float c) {
+      const int n1 = i / 20, n2 = i - n1 * 20;   // window[i] is tap n1 of residue n2
+      s_tw[n2 * 20 + n1] = PCM16 ? w * prm.scale : w;
+      s_tt[i] = c;
+    };
+    put_w(tid, w0, c0);
+    if (second) put_w(tid + kThreads, w1, c1);
+    if (tid < kTabT2) s_t2[tid] = t2;
+    if (tid < M) s_meta[tid] = make_int2(ms | (mc << 16), mo);
+    if (tid < prm.mel_nnz) s_w[tid] = g0;
+    if (tid + kThreads < prm.mel_nnz) s_w[tid + kThreads] = g1;
   }
-  if (tid < kTabT2) s_t2[tid] = kT2[tid];
-  for (int m = tid; m < M; m += kThreads)
+  for (int m = tid + kThreads; m < M; m += kThreads)       // more than 320 filters
     s_meta[m] = make_int2(__ldg(prm.mel_start + m) | (__ldg(prm.mel_count + m) << 16),
                           __ldg(prm.mel_offset + m));
-  for (int i = tid; i < prm.mel_nnz; i += kThreads) s_w[i] = __ldg(prm.mel_weight + i);
+  for (int i = tid + 2 * kThreads; i < prm.mel_nnz; i += kThreads) s_w[i] = __ldg(prm.mel_weight + i);
   if (tid < 2 * (kPRows - kBins) * kTile) {
     const int r = tid / ((kPRows - kBins) * kTile), i = tid - r * (kPRows - kBins) * kTile;
     s_a[r * kRegionA + kBins * kTile + i] = 0.f;

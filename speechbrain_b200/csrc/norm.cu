@@ -155,6 +155,16 @@ norm_stats_tiles_kernel(const float* x, const float* __restrict__ lengths, int64
       pn[k] = __ldg(ts + 2 * F);
     }
   }
+  // the tile keys (-> top_db floor) are requested in the same round trip as well
+  __shared__ unsigned s_max_key;
+  unsigned my_key = 0u;
+  if (utt_max == nullptr) {
+    if (threadIdx.x == 0) s_max_key = 0u;
+    for (int i = threadIdx.x; i < tiles; i += kTileStatThreads) {
+      const unsigned k2 = __ldg(reinterpret_cast<const unsigned*>(tsb) + (size_t)i * rec + 3 * F);
+      my_key = k2 > my_key ? k2 : my_key;
+    }
+  }
   const int n = valid_frames(lengths, b, T);
   // tiles whose existing frames are all valid: [0, n / tile), plus the short last tile when
   // the whole utterance is valid
@@ -176,8 +186,17 @@ norm_stats_tiles_kernel(const float* x, const float* __restrict__ lengths, int64
     }
   }
   unsigned max_key = 0u;
-  const float floor_b = utt_max ? clamp_floor(utt_max, b, top_db)
-                                : block_floor_from_tiles(tile_stats, b, tiles, F, top_db, &max_key);
+  float floor_b;
+  if (utt_max != nullptr) {
+    floor_b = clamp_floor(utt_max, b, top_db);
+  } else {  // block maximum of the keys (common.cuh: block_floor_from_tiles, loads hoisted)
+    __syncthreads();
+    my_key = __reduce_max_sync(0xffffffffu, my_key);
+    if ((threadIdx.x & 31) == 0 && my_key) atomicMax(&s_max_key, my_key);
+    __syncthreads();
+    max_key = s_max_key;
+    floor_b = max_key ? max_key_decode(max_key) - top_db : -INFINITY;
+  }
   // the utterance maximum rebuilt from the tile keys, for a consumer that clamps on the fly
   // (norm_apply_kernel) instead of after a clamp_tiles launch
   if (utt_max_out != nullptr && blockIdx.x == 0 && threadIdx.x == 0)
