@@ -247,7 +247,29 @@ __global__ void post_fast_kernel_t(const PostParams p) {
   // division per thread and phase instead of one per element, 32-bit row arithmetic
   const int Ti = (int)T, base_lo_i = (int)base_lo, d_lo_i = (int)d_lo, o_lo_i = (int)o_lo;
   float* s_stage = dct ? s_in : s_base;
-  {
+  // the DCT matrix rides in the same memory round trip as the input rows
+  float dv[2] = {0.f, 0.f};
+  if (dct) {
+#pragma unroll
+    for (int k = 0; k < 2; ++k)
+      if (threadIdx.x + k * nthr < F_in * F0) dv[k] = __ldg(p.dct + threadIdx.x + k * nthr);
+  }
+  if (base_lo_i >= 0 && base_lo_i + fr_b <= Ti) {
+    // interior tile: the fr_b input rows are one contiguous run of the utterance - a flat copy,
+    // all of a thread's loads in flight before its first store
+    const float* src = xb + (int64_t)base_lo_i * F_in;
+    const int total = fr_b * F_in;
+    constexpr int kFlight = 4;
+    for (int i0 = threadIdx.x; i0 < total; i0 += kFlight * nthr) {
+      float v[kFlight];
+#pragma unroll
+      for (int k = 0; k < kFlight; ++k)
+        if (i0 + k * nthr < total) v[k] = __ldg(src + i0 + k * nthr);
+#pragma unroll
+      for (int k = 0; k < kFlight; ++k)
+        if (i0 + k * nthr < total) s_stage[i0 + k * nthr] = fmaxf(v[k], floor_b);
+    }
+  } else {
     int r = threadIdx.x / F_in, f = threadIdx.x - r * F_in;
     const int dr = nthr / F_in, df = nthr - dr * F_in;
     while (r < fr_b) {
@@ -258,8 +280,12 @@ __global__ void post_fast_kernel_t(const PostParams p) {
       if (f >= F_in) { f -= F_in; ++r; }
     }
   }
-  if (dct)
-    for (int i = threadIdx.x; i < F_in * F0; i += nthr) s_dct[i] = __ldg(p.dct + i);
+  if (dct) {
+#pragma unroll
+    for (int k = 0; k < 2; ++k)
+      if (threadIdx.x + k * nthr < F_in * F0) s_dct[threadIdx.x + k * nthr] = dv[k];
+    for (int i = threadIdx.x + 2 * nthr; i < F_in * F0; i += nthr) s_dct[i] = __ldg(p.dct + i);
+  }
   __syncthreads();
   if (dct) {
     if ((F0 & 3) == 0) {
@@ -429,9 +455,12 @@ int launch_post(const float* x, int64_t B, int64_t T, int F_in, const sbfe_maxke
         const int threads = rowthr >= 512 ? (rowthr > 1024 ? 1024 : rowthr) : rowthr * (512 / rowthr);
         // the MFCC default (23 mel -> 20 DCT, window 5, context 5 + 5) has its own instantiation
         const bool mfcc = dct && F_in == 23 && p.F0 == 20 && p.n == 2 && p.deltas == 1 && left == 5 &&
-                          right == 5 && tile == 32;
-        if (mfcc)
+                          right == 5;
+        if (mfcc && tile == 32)
           return launch_pdl(post_fast_kernel_t<23, 20, 2, 5, 5, 1, 1, 32>, dim3((unsigned)(tiles * B)),
+                            dim3(threads), smem, stream, p);
+        if (mfcc && tile == 64)
+          return launch_pdl(post_fast_kernel_t<23, 20, 2, 5, 5, 1, 1, 64>, dim3((unsigned)(tiles * B)),
                             dim3(threads), smem, stream, p);
         return launch_pdl(post_fast_kernel, dim3((unsigned)(tiles * B)), dim3(threads), smem, stream,
                           p);
