@@ -207,6 +207,12 @@ __global__ void __launch_bounds__(kPostThreads) post_kernel(const PostParams p) 
 // time): with the MFCC default <23, 20, 2, 5, 5, 1, 1, 32> every loop below unrolls and every
 // row / column index is a constant - the preparatory phases (staging, DCT, deltas, feature
 // rows) were 73 % of the generic kernel's instructions although they touch 3 % of its bytes.
+// Row pitch of the [frames][features] staging rows the context gather reads: the smallest
+// P >= nfeat with P % 4 == 2.  A lane's q-th source is (c, f) = ((4v + q) % C, (4v + q) / C) at
+// c * P + f; counted over all warps of the gather this pitch needs 1.5 - 2.0 shared-memory
+// wavefronts per load where an odd pitch needs 2.5 - 5.6 (MFCC default: 1.83 against 2.67).
+__host__ __device__ inline int post_feat_pitch(int nfeat) { return nfeat + ((6 - (nfeat & 3)) & 3); }
+
 template <int FIN, int F0C, int NC, int LC, int RC, int DELTAS, int DCTC, int TILE>
 __global__ void post_fast_kernel_t(const PostParams p) {
   const int F_in = FIN > 0 ? FIN : p.F_in;
@@ -227,12 +233,12 @@ __global__ void post_fast_kernel_t(const PostParams p) {
   const int fr_d = fr_out + 2 * n1;
   const int fr_b = fr_out + 2 * n2;
   const int nfeat = F0 * (deltas == 1 ? 3 : 1);
-  const int P = nfeat | 1;                               // odd row pitch of the feature rows
-  float* s_feat = smem;                                  // [fr_out][P]
+  const int P = post_feat_pitch(nfeat);                  // row pitch of the feature rows
+  float* s_dct = smem;                                   // [F_in][F0] first: read as float4
+  float* s_feat = s_dct + (dct ? F_in * F0 : 0);         // [fr_out][P]
   float* s_base = s_feat + fr_out * P;                   // [fr_b][F0]
   float* s_d = s_base + fr_b * F0;                     // [fr_d][F0]   (deltas only)
   float* s_in = s_d + (deltas ? fr_d * F0 : 0);      // [fr_b][F_in] (DCT only)
-  float* s_dct = s_in + (dct ? fr_b * F_in : 0);     // [F_in][F0]
 
   const int64_t b = blockIdx.x / p.tiles;
   const int64_t t0 = (int64_t)(blockIdx.x - b * p.tiles) * tile;
@@ -435,7 +441,7 @@ int launch_post(const float* x, int64_t B, int64_t T, int F_in, const sbfe_maxke
       // 64-frame tiles halve the halo work; 32-frame tiles when that leaves too few CTAs
       for (int tile = ((T + 63) / 64) * B >= 1184 ? 64 : 32; tile >= 8; tile /= 2) {
         const int fr_out = tile + left + right, fr_d = fr_out + 2 * n1, fr_b = fr_out + 2 * n2;
-        size_t fl = (size_t)fr_out * (nfeat | 1) + (size_t)fr_b * p.F0;
+        size_t fl = (size_t)fr_out * post_feat_pitch(nfeat) + (size_t)fr_b * p.F0;
         if (p.deltas) fl += (size_t)fr_d * p.F0;
         if (dct) fl += (size_t)fr_b * F_in + (size_t)F_in * p.F0;
         const size_t smem = fl * sizeof(float);
