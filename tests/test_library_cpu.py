@@ -173,3 +173,29 @@ def test_mel_layout_moves_a_filter_that_would_leave_the_spectrum():
         rebuilt[s:s + c, m] = w[o:o + c]
         assert torch.count_nonzero(w[o + c:o + int(stored[m])]) == 0
     assert torch.equal(rebuilt, mat)
+
+
+def test_pair_host_logic():
+    """pair() (lobes/features.py): type checks, weak reference, withdrawn / dead normaliser and
+    the modes that never defer - all host logic, no kernel involved."""
+    import gc as _gc
+
+    import speechbrain_b200 as sb
+
+    fb, norm = sb.Fbank(n_mels=80), sb.InputNormalization(norm_type="sentence")
+    assert not fb._defers_clamp()
+    assert sb.pair(fb, norm) is fb and fb._defers_clamp()
+    norm.norm_type = "global"          # modes that leave x behind never defer
+    assert not fb._defers_clamp()
+    norm.norm_type = "speaker"
+    assert fb._defers_clamp()
+    sb.pair(fb, None)
+    assert not fb._defers_clamp()
+    sb.pair(fb, sb.InputNormalization(norm_type="sentence"))   # nobody keeps the normaliser alive
+    _gc.collect()
+    assert not fb._defers_clamp()
+    with pytest.raises(TypeError):
+        sb.pair(torch.nn.Identity(), norm)
+    with pytest.raises(TypeError):
+        sb.pair(fb, torch.nn.Identity())
+    assert sb.pair(sb.MFCC(), norm) is not None   # accepted; MFCC never takes the log-mel-only path
