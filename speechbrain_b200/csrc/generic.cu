@@ -59,12 +59,95 @@ stft_generic_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride
   }
 }
 
+// ---- power-of-two n_fft (256 / 512 / 1024 ...): real FFT through a half-size complex FFT ------
+// z[n] = x[2n] + i x[2n+1] (windowed), radix-2 decimation in time in shared memory (bit-reversed
+// load, log2(N/2) butterfly stages), then the real-input untangle
+//   X[k] = (Z[k] + conj Z[M-k]) / 2 + W_N^k (Z[k] - conj Z[M-k]) / (2i),  M = N / 2.
+// O(N log N) where stft_generic_kernel is O(N^2); same frames-per-CTA tiling and outputs.
+// smem: W_N table cs[N/2] (cos, -sin) + kGenFrames complex buffers of N/2.
+__global__ void __launch_bounds__(kGenThreads)
+stft_pow2_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, int64_t T,
+                 const float* __restrict__ window, int n_fft, int log2m, int hop,
+                 float* __restrict__ out, int power_only, unsigned tiles) {
+  extern __shared__ __align__(16) float smem[];
+  const int M = n_fft >> 1;
+  float2* s_cs = reinterpret_cast<float2*>(smem);        // W_N^j, j < M
+  float2* s_z = s_cs + M;                                // [kGenFrames][M]
+  const int bins = M + 1;
+  const int64_t b = blockIdx.x / tiles;
+  const int64_t t0 = (int64_t)(blockIdx.x - b * tiles) * kGenFrames;
+  const float* w = wav + b * wav_stride;
+  for (int j = threadIdx.x; j < M; j += kGenThreads) {
+    float sn, cs;
+    sincospif(2.0f * (float)j / (float)n_fft, &sn, &cs);
+    s_cs[j] = make_float2(cs, -sn);
+  }
+  for (int i = threadIdx.x; i < kGenFrames * M; i += kGenThreads) {
+    const int f = i / M, n = i - f * M;
+    const int64_t g = (t0 + f) * hop - n_fft / 2 + 2 * n;
+    const float x0 = (g >= 0 && g < L) ? __ldg(w + g) * __ldg(window + 2 * n) : 0.f;
+    const float x1 = (g + 1 >= 0 && g + 1 < L) ? __ldg(w + g + 1) * __ldg(window + 2 * n + 1) : 0.f;
+    const int r = (int)(__brev((unsigned)n) >> (32 - log2m));
+    s_z[f * M + r] = make_float2(x0, x1);
+  }
+  __syncthreads();
+  for (int st = 0; st < log2m; ++st) {
+    const int half = 1 << st;
+    for (int i = threadIdx.x; i < kGenFrames * (M >> 1); i += kGenThreads) {
+      const int f = i / (M >> 1), j = i - f * (M >> 1);
+      const int pos = j & (half - 1);
+      const int i0 = ((j >> st) << (st + 1)) + pos;
+      const float2 tw = s_cs[pos << (log2m - st)];        // W_M^(pos * M / (2 half)) = W_N^(2 ...)
+      float2* z = s_z + f * M;
+      const float2 a = z[i0], c = z[i0 + half];
+      const float br = c.x * tw.x - c.y * tw.y, bi = c.x * tw.y + c.y * tw.x;
+      z[i0] = make_float2(a.x + br, a.y + bi);
+      z[i0 + half] = make_float2(a.x - br, a.y - bi);
+    }
+    __syncthreads();
+  }
+  for (int p = threadIdx.x; p < kGenFrames * bins; p += kGenThreads) {
+    const int f = p / bins, k = p - f * bins;
+    if (t0 + f >= T) continue;
+    const float2* z = s_z + f * M;
+    const float2 zk = z[k & (M - 1)], zm = z[(M - k) & (M - 1)];
+    const float er = 0.5f * (zk.x + zm.x), ei = 0.5f * (zk.y - zm.y);   // even part
+    const float orr = 0.5f * (zk.y + zm.y), oi = -0.5f * (zk.x - zm.x); // odd part: (Zk - conj Zm) / 2i
+    float twx, twy;
+    if (k < M) {
+      twx = s_cs[k].x;
+      twy = s_cs[k].y;
+    } else {  // W_N^(N/2) = -1
+      twx = -1.f;
+      twy = 0.f;
+    }
+    const float re = er + orr * twx - oi * twy, im = ei + orr * twy + oi * twx;
+    const int64_t o = ((b * T + t0 + f) * bins + k);
+    if (power_only) {
+      out[o] = re * re + im * im;
+    } else {
+      reinterpret_cast<float2*>(out)[o] = make_float2(re, im);
+    }
+  }
+}
+
 int launch_stft_generic(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64_t L,
                         int64_t wav_stride, float* out, int power_only, cudaStream_t stream) {
   const int64_t T = 1 + L / d->hop;
   const int64_t tiles = (T + kGenFrames - 1) / kGenFrames;
   if (tiles * B > 0x7fffffff) return SBFE_E_TOOBIG;
   if (d->n_fft > 4096) return SBFE_E_TOOBIG;
+  if (d->n_fft >= 16 && (d->n_fft & (d->n_fft - 1)) == 0) {   // power of two: the FFT kernel
+    int log2m = 0;
+    while ((2 << log2m) < d->n_fft) ++log2m;
+    const size_t smem2 = (size_t)(1 + kGenFrames) * d->n_fft * sizeof(float);
+    cudaError_t e2 = cudaFuncSetAttribute(stft_pow2_kernel,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+    if (e2 != cudaSuccess) return (int)e2;
+    stft_pow2_kernel<<<(unsigned)(tiles * B), kGenThreads, smem2, stream>>>(
+        wav, L, wav_stride, T, d->d_window, d->n_fft, log2m, d->hop, out, power_only, (unsigned)tiles);
+    return check_last();
+  }
   const size_t smem = (size_t)(2 + kGenFrames) * d->n_fft * sizeof(float);
   cudaError_t e = cudaFuncSetAttribute(stft_generic_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
