@@ -60,68 +60,94 @@ stft_generic_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride
 }
 
 // ---- power-of-two n_fft (256 / 512 / 1024 ...): real FFT through a half-size complex FFT ------
-// z[n] = x[2n] + i x[2n+1] (windowed), radix-2 decimation in time in shared memory (bit-reversed
-// load, log2(N/2) butterfly stages), then the real-input untangle
-//   X[k] = (Z[k] + conj Z[M-k]) / 2 + W_N^k (Z[k] - conj Z[M-k]) / (2i),  M = N / 2.
-// O(N log N) where stft_generic_kernel is O(N^2); same frames-per-CTA tiling and outputs.
-// smem: W_N table cs[N/2] (cos, -sin) + kGenFrames complex buffers of N/2.
+// z[n] = x[2n] + i x[2n+1] (windowed); Stockham autosort FFT of size M = N / 2 in shared memory
+// (ping-pong buffers, radix-4 passes and one radix-2 pass when log2 M is odd: natural order in
+// and out, no bit reversal), then the real-input untangle
+//   X[k] = (Z[k] + conj Z[M-k]) / 2 + W_N^k (Z[k] - conj Z[M-k]) / (2i).
+// O(N log N) where stft_generic_kernel is O(N^2); same outputs.
+// smem: W_N table cs[N] (cos, -sin) + 2 x kPow2Frames complex buffers of N/2.
+constexpr int kPow2Frames = 16;   // frames per CTA: four radix-4 butterflies per thread and pass
+
+__device__ __forceinline__ float2 cmulf(float2 a, float2 b) {
+  return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+}
+
 __global__ void __launch_bounds__(kGenThreads)
 stft_pow2_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, int64_t T,
                  const float* __restrict__ window, int n_fft, int log2m, int hop,
                  float* __restrict__ out, int power_only, unsigned tiles) {
   extern __shared__ __align__(16) float smem[];
   const int M = n_fft >> 1;
-  float2* s_cs = reinterpret_cast<float2*>(smem);        // W_N^j, j < M
-  float2* s_z = s_cs + M;                                // [kGenFrames][M]
+  float2* s_cs = reinterpret_cast<float2*>(smem);        // W_N^j, j < N
+  float2* s_a = s_cs + n_fft;                            // [kPow2Frames][M]
+  float2* s_b = s_a + kPow2Frames * M;                   // [kPow2Frames][M]
   const int bins = M + 1;
   const int64_t b = blockIdx.x / tiles;
-  const int64_t t0 = (int64_t)(blockIdx.x - b * tiles) * kGenFrames;
+  const int64_t t0 = (int64_t)(blockIdx.x - b * tiles) * kPow2Frames;
   const float* w = wav + b * wav_stride;
-  for (int j = threadIdx.x; j < M; j += kGenThreads) {
+  for (int j = threadIdx.x; j < n_fft; j += kGenThreads) {
     float sn, cs;
     sincospif(2.0f * (float)j / (float)n_fft, &sn, &cs);
     s_cs[j] = make_float2(cs, -sn);
   }
-  for (int i = threadIdx.x; i < kGenFrames * M; i += kGenThreads) {
-    const int f = i / M, n = i - f * M;
+  for (int i = threadIdx.x; i < kPow2Frames * M; i += kGenThreads) {
+    const int f = i >> log2m, n = i & (M - 1);
     const int64_t g = (t0 + f) * hop - n_fft / 2 + 2 * n;
     const float x0 = (g >= 0 && g < L) ? __ldg(w + g) * __ldg(window + 2 * n) : 0.f;
     const float x1 = (g + 1 >= 0 && g + 1 < L) ? __ldg(w + g + 1) * __ldg(window + 2 * n + 1) : 0.f;
-    const int r = (int)(__brev((unsigned)n) >> (32 - log2m));
-    s_z[f * M + r] = make_float2(x0, x1);
+    s_a[i] = make_float2(x0, x1);
   }
   __syncthreads();
-  for (int st = 0; st < log2m; ++st) {
-    const int half = 1 << st;
-    for (int i = threadIdx.x; i < kGenFrames * (M >> 1); i += kGenThreads) {
-      const int f = i / (M >> 1), j = i - f * (M >> 1);
-      const int pos = j & (half - 1);
-      const int i0 = ((j >> st) << (st + 1)) + pos;
-      const float2 tw = s_cs[pos << (log2m - st)];        // W_M^(pos * M / (2 half)) = W_N^(2 ...)
-      float2* z = s_z + f * M;
-      const float2 a = z[i0], c = z[i0 + half];
-      const float br = c.x * tw.x - c.y * tw.y, bi = c.x * tw.y + c.y * tw.x;
-      z[i0] = make_float2(a.x + br, a.y + bi);
-      z[i0 + half] = make_float2(a.x - br, a.y - bi);
+  float2* src = s_a;
+  float2* dst = s_b;
+  int ls = 0;                                            // log2 of Ns, the size already transformed
+  while (ls < log2m) {
+    if (log2m - ls >= 2) {                               // radix-4 pass
+      const int q = M >> 2, Ns = 1 << ls;
+      for (int i = threadIdx.x; i < kPow2Frames * q; i += kGenThreads) {
+        const int f = i >> (log2m - 2), j = i & (q - 1);
+        const int k = j & (Ns - 1);
+        const int tstep = k << (log2m + 1 - ls - 2);     // k * N / (4 Ns)
+        const float2* in = src + f * M + j;
+        float2 v0 = in[0], v1 = in[q], v2 = in[2 * q], v3 = in[3 * q];
+        v1 = cmulf(v1, s_cs[tstep]);
+        v2 = cmulf(v2, s_cs[2 * tstep]);
+        v3 = cmulf(v3, s_cs[3 * tstep]);
+        const float2 a0 = make_float2(v0.x + v2.x, v0.y + v2.y), a1 = make_float2(v0.x - v2.x, v0.y - v2.y);
+        const float2 a2 = make_float2(v1.x + v3.x, v1.y + v3.y);
+        const float2 a3 = make_float2(v1.y - v3.y, v3.x - v1.x);   // -i (v1 - v3)
+        float2* o = dst + f * M + (((j >> ls) << (ls + 2)) + k);
+        o[0] = make_float2(a0.x + a2.x, a0.y + a2.y);
+        o[Ns] = make_float2(a1.x + a3.x, a1.y + a3.y);
+        o[2 * Ns] = make_float2(a0.x - a2.x, a0.y - a2.y);
+        o[3 * Ns] = make_float2(a1.x - a3.x, a1.y - a3.y);
+      }
+      ls += 2;
+    } else {                                             // one radix-2 pass
+      const int h = M >> 1, Ns = 1 << ls;
+      for (int i = threadIdx.x; i < kPow2Frames * h; i += kGenThreads) {
+        const int f = i >> (log2m - 1), j = i & (h - 1);
+        const int k = j & (Ns - 1);
+        const float2* in = src + f * M + j;
+        const float2 v0 = in[0], v1 = cmulf(in[h], s_cs[k << (log2m + 1 - ls - 1)]);
+        float2* o = dst + f * M + (((j >> ls) << (ls + 1)) + k);
+        o[0] = make_float2(v0.x + v1.x, v0.y + v1.y);
+        o[Ns] = make_float2(v0.x - v1.x, v0.y - v1.y);
+      }
+      ls += 1;
     }
     __syncthreads();
+    float2* t = src; src = dst; dst = t;
   }
-  for (int p = threadIdx.x; p < kGenFrames * bins; p += kGenThreads) {
+  for (int p = threadIdx.x; p < kPow2Frames * bins; p += kGenThreads) {
     const int f = p / bins, k = p - f * bins;
     if (t0 + f >= T) continue;
-    const float2* z = s_z + f * M;
+    const float2* z = src + f * M;
     const float2 zk = z[k & (M - 1)], zm = z[(M - k) & (M - 1)];
     const float er = 0.5f * (zk.x + zm.x), ei = 0.5f * (zk.y - zm.y);   // even part
     const float orr = 0.5f * (zk.y + zm.y), oi = -0.5f * (zk.x - zm.x); // odd part: (Zk - conj Zm) / 2i
-    float twx, twy;
-    if (k < M) {
-      twx = s_cs[k].x;
-      twy = s_cs[k].y;
-    } else {  // W_N^(N/2) = -1
-      twx = -1.f;
-      twy = 0.f;
-    }
-    const float re = er + orr * twx - oi * twy, im = ei + orr * twy + oi * twx;
+    const float2 tw = s_cs[k];                                          // W_N^k (k = M: -1)
+    const float re = er + orr * tw.x - oi * tw.y, im = ei + orr * tw.y + oi * tw.x;
     const int64_t o = ((b * T + t0 + f) * bins + k);
     if (power_only) {
       out[o] = re * re + im * im;
@@ -137,15 +163,17 @@ int launch_stft_generic(const sbfe_fbank_desc* d, const float* wav, int64_t B, i
   const int64_t tiles = (T + kGenFrames - 1) / kGenFrames;
   if (tiles * B > 0x7fffffff) return SBFE_E_TOOBIG;
   if (d->n_fft > 4096) return SBFE_E_TOOBIG;
-  if (d->n_fft >= 16 && (d->n_fft & (d->n_fft - 1)) == 0) {   // power of two: the FFT kernel
+  // power of two (and the ping-pong buffers fit in shared memory): the FFT kernel
+  const size_t smem2 = (size_t)(2 + 2 * kPow2Frames) * d->n_fft * sizeof(float);
+  if (d->n_fft >= 16 && (d->n_fft & (d->n_fft - 1)) == 0 && smem2 <= 200 * 1024) {
     int log2m = 0;
     while ((2 << log2m) < d->n_fft) ++log2m;
-    const size_t smem2 = (size_t)(1 + kGenFrames) * d->n_fft * sizeof(float);
+    const int64_t tiles2 = (T + kPow2Frames - 1) / kPow2Frames;
     cudaError_t e2 = cudaFuncSetAttribute(stft_pow2_kernel,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
     if (e2 != cudaSuccess) return (int)e2;
-    stft_pow2_kernel<<<(unsigned)(tiles * B), kGenThreads, smem2, stream>>>(
-        wav, L, wav_stride, T, d->d_window, d->n_fft, log2m, d->hop, out, power_only, (unsigned)tiles);
+    stft_pow2_kernel<<<(unsigned)(tiles2 * B), kGenThreads, smem2, stream>>>(
+        wav, L, wav_stride, T, d->d_window, d->n_fft, log2m, d->hop, out, power_only, (unsigned)tiles2);
     return check_last();
   }
   const size_t smem = (size_t)(2 + kGenFrames) * d->n_fft * sizeof(float);
