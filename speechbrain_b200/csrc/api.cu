@@ -14,6 +14,9 @@ int launch_clamp_tiles(float*, int64_t, int64_t, int, const sbfe_maxkey_t*, floa
 int launch_norm_stats_tiles(const float*, const float*, int64_t, int64_t, int, int, int, float,
                             const sbfe_maxkey_t*, float, const float*, int, float*, float*, int,
                             sbfe_maxkey_t*, cudaStream_t);
+bool fbank_pow2_supported(const sbfe_fbank_desc*);
+int launch_fbank_pow2(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
+                      sbfe_maxkey_t*, cudaStream_t);
 int launch_stft_generic(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
                         int, cudaStream_t);
 int launch_spectral_magnitude(const float*, int64_t, float, int, float, float*, cudaStream_t);
@@ -75,7 +78,7 @@ int64_t sbfe_num_frames(int64_t n_samples, int32_t hop) {
 
 int64_t sbfe_fbank_workspace_bytes(const sbfe_fbank_desc* d, int64_t B, int64_t L) {
   if (!d || d->hop < 1 || B < 0 || L < 0) return SBFE_E_INVAL;
-  if (fused_ok(d)) return 0;
+  if (fused_ok(d) || fbank_pow2_supported(d)) return 0;
   return B * (1 + L / d->hop) * (int64_t)(d->n_fft / 2 + 1) * (int64_t)sizeof(float);
 }
 
@@ -99,6 +102,8 @@ int sbfe_fbank_forward(const sbfe_fbank_desc* d, const float* d_wav, int64_t B, 
                               d_tile_stats, s);
   if (d_tile_stats) return SBFE_E_INVAL;  // only where sbfe_fbank_tile_frames() != 0
   if (fused_ok(d)) return launch_fbank400(d, d_wav, B, L, wav_stride, d_out, d_utt_max, s);
+  if (fbank_pow2_supported(d))   // n_fft = 256 / 512 / 1024 ...: FFT + mel + dB in one launch
+    return launch_fbank_pow2(d, d_wav, B, L, wav_stride, d_out, d_utt_max, s);
   if (!d_ws || ws_bytes < sbfe_fbank_workspace_bytes(d, B, L)) return SBFE_E_NOSPACE;
   int rc = launch_stft_generic(d, d_wav, B, L, wav_stride, (float*)d_ws, 1, s);
   if (rc) return rc;

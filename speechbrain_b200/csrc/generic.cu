@@ -72,10 +72,24 @@ __device__ __forceinline__ float2 cmulf(float2 a, float2 b) {
   return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
 }
 
+// MEL: the Fbank path - the power spectrum stays in shared memory and goes straight through the
+// sparse mel projection + dB (Filterbank.forward :490-551, 701-702): nothing but the waveform is
+// read from and nothing but the [frames, n_mels] tile is written to HBM.
+struct MelArgs {
+  int M;
+  const int32_t* start;
+  const int32_t* count;
+  const int32_t* offset;
+  const float* weight;
+  DbParams db;
+  sbfe_maxkey_t* utt_max;
+};
+
+template <bool MEL>
 __global__ void __launch_bounds__(kGenThreads)
 stft_pow2_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, int64_t T,
                  const float* __restrict__ window, int n_fft, int log2m, int hop,
-                 float* __restrict__ out, int power_only, unsigned tiles) {
+                 float* __restrict__ out, int power_only, unsigned tiles, const MelArgs mel) {
   extern __shared__ __align__(16) float smem[];
   const int M = n_fft >> 1;
   float2* s_cs = reinterpret_cast<float2*>(smem);        // W_N^j, j < N
@@ -148,6 +162,10 @@ stft_pow2_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, i
     const float orr = 0.5f * (zk.y + zm.y), oi = -0.5f * (zk.x - zm.x); // odd part: (Zk - conj Zm) / 2i
     const float2 tw = s_cs[k];                                          // W_N^k (k = M: -1)
     const float re = er + orr * tw.x - oi * tw.y, im = ei + orr * tw.y + oi * tw.x;
+    if (MEL) {
+      reinterpret_cast<float*>(dst)[p] = re * re + im * im;   // [frame][bins] in the idle buffer
+      continue;
+    }
     const int64_t o = ((b * T + t0 + f) * bins + k);
     if (power_only) {
       out[o] = re * re + im * im;
@@ -155,6 +173,57 @@ stft_pow2_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, i
       reinterpret_cast<float2*>(out)[o] = make_float2(re, im);
     }
   }
+  if (MEL) {
+    __syncthreads();
+    const float* s_p = reinterpret_cast<const float*>(dst);
+    const int64_t left = T - t0;
+    const int nf = left < kPow2Frames ? (int)left : kPow2Frames;
+    float vmax = -INFINITY;
+    float* o = out + (b * T + t0) * mel.M;
+    for (int p = threadIdx.x; p < nf * mel.M; p += kGenThreads) {
+      const int f = p / mel.M, m = p - f * mel.M;
+      const int cnt = __ldg(mel.count + m);
+      const float* wt = mel.weight + __ldg(mel.offset + m);
+      const float* x = s_p + f * bins + __ldg(mel.start + m);
+      float acc = 0.f;
+      for (int i = 0; i < cnt; ++i) acc = fmaf(__ldg(wt + i), x[i], acc);
+      const float v = to_db(acc, mel.db);
+      o[p] = v;
+      vmax = fmaxf(vmax, v);
+    }
+    vmax = warp_max(vmax);
+    if ((threadIdx.x & 31) == 0 && vmax > -INFINITY && mel.utt_max != nullptr)
+      atomicMax(mel.utt_max + b, max_key_encode(vmax));
+  }
+}
+
+static bool pow2_fits(int n_fft) {
+  return n_fft >= 16 && (n_fft & (n_fft - 1)) == 0 &&
+         (size_t)(2 + 2 * kPow2Frames) * n_fft * sizeof(float) <= 200 * 1024;
+}
+
+// Fbank with a power-of-two n_fft in one launch (any hop, any filter shape: the CSR tables); the
+// idle frame buffer [16][N/2] float2 always holds the power tile [16][N/2 + 1] floats
+bool fbank_pow2_supported(const sbfe_fbank_desc* d) { return pow2_fits(d->n_fft) && d->n_mels >= 1; }
+
+int launch_fbank_pow2(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64_t L,
+                      int64_t wav_stride, float* out, sbfe_maxkey_t* utt_max, cudaStream_t stream) {
+  const int64_t T = 1 + L / d->hop;
+  const int64_t tiles = (T + kPow2Frames - 1) / kPow2Frames;
+  if (tiles * B > 0x7fffffff) return SBFE_E_TOOBIG;
+  int log2m = 0;
+  while ((2 << log2m) < d->n_fft) ++log2m;
+  const size_t smem = (size_t)(2 + 2 * kPow2Frames) * d->n_fft * sizeof(float);
+  cudaError_t e = cudaFuncSetAttribute(stft_pow2_kernel<true>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return (int)e;
+  MelArgs mel{d->n_mels, d->d_mel_start, d->d_mel_count, d->d_mel_offset, d->d_mel_weight,
+              DbParams{d->multiplier * 0.30102999566398120f, d->amin, d->db_offset, d->floor_db,
+                       d->log_mel},
+              utt_max};
+  stft_pow2_kernel<true><<<(unsigned)(tiles * B), kGenThreads, smem, stream>>>(
+      wav, L, wav_stride, T, d->d_window, d->n_fft, log2m, d->hop, out, 1, (unsigned)tiles, mel);
+  return check_last();
 }
 
 int launch_stft_generic(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64_t L,
@@ -165,15 +234,16 @@ int launch_stft_generic(const sbfe_fbank_desc* d, const float* wav, int64_t B, i
   if (d->n_fft > 4096) return SBFE_E_TOOBIG;
   // power of two (and the ping-pong buffers fit in shared memory): the FFT kernel
   const size_t smem2 = (size_t)(2 + 2 * kPow2Frames) * d->n_fft * sizeof(float);
-  if (d->n_fft >= 16 && (d->n_fft & (d->n_fft - 1)) == 0 && smem2 <= 200 * 1024) {
+  if (pow2_fits(d->n_fft)) {
     int log2m = 0;
     while ((2 << log2m) < d->n_fft) ++log2m;
     const int64_t tiles2 = (T + kPow2Frames - 1) / kPow2Frames;
-    cudaError_t e2 = cudaFuncSetAttribute(stft_pow2_kernel,
+    cudaError_t e2 = cudaFuncSetAttribute(stft_pow2_kernel<false>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
     if (e2 != cudaSuccess) return (int)e2;
-    stft_pow2_kernel<<<(unsigned)(tiles2 * B), kGenThreads, smem2, stream>>>(
-        wav, L, wav_stride, T, d->d_window, d->n_fft, log2m, d->hop, out, power_only, (unsigned)tiles2);
+    stft_pow2_kernel<false><<<(unsigned)(tiles2 * B), kGenThreads, smem2, stream>>>(
+        wav, L, wav_stride, T, d->d_window, d->n_fft, log2m, d->hop, out, power_only, (unsigned)tiles2,
+        MelArgs{});
     return check_last();
   }
   const size_t smem = (size_t)(2 + kGenFrames) * d->n_fft * sizeof(float);
