@@ -104,12 +104,17 @@ stft_pow2_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, i
     sincospif(2.0f * (float)j / (float)n_fft, &sn, &cs);
     s_cs[j] = make_float2(cs, -sn);
   }
-  for (int i = threadIdx.x; i < kPow2Frames * M; i += kGenThreads) {
-    const int f = i >> log2m, n = i & (M - 1);
-    const int64_t g = (t0 + f) * hop - n_fft / 2 + 2 * n;
-    const float x0 = (g >= 0 && g < L) ? __ldg(w + g) * __ldg(window + 2 * n) : 0.f;
-    const float x1 = (g + 1 >= 0 && g + 1 < L) ? __ldg(w + g + 1) * __ldg(window + 2 * n + 1) : 0.f;
-    s_a[i] = make_float2(x0, x1);
+  // thread = sample pair n (its two window taps are loaded once), loop over the frames: no
+  // division, no per-element window load
+  for (int n = threadIdx.x; n < M; n += kGenThreads) {
+    const float w0 = __ldg(window + 2 * n), w1 = __ldg(window + 2 * n + 1);
+    int64_t g = t0 * hop - n_fft / 2 + 2 * n;
+#pragma unroll 4
+    for (int f = 0; f < kPow2Frames; ++f, g += hop) {
+      const float x0 = (g >= 0 && g < L) ? __ldg(w + g) * w0 : 0.f;
+      const float x1 = (g + 1 >= 0 && g + 1 < L) ? __ldg(w + g + 1) * w1 : 0.f;
+      s_a[f * M + n] = make_float2(x0, x1);
+    }
   }
   __syncthreads();
   float2* src = s_a;
@@ -153,43 +158,57 @@ stft_pow2_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, i
     __syncthreads();
     float2* t = src; src = dst; dst = t;
   }
-  for (int p = threadIdx.x; p < kPow2Frames * bins; p += kGenThreads) {
-    const int f = p / bins, k = p - f * bins;
-    if (t0 + f >= T) continue;
-    const float2* z = src + f * M;
-    const float2 zk = z[k & (M - 1)], zm = z[(M - k) & (M - 1)];
-    const float er = 0.5f * (zk.x + zm.x), ei = 0.5f * (zk.y - zm.y);   // even part
-    const float orr = 0.5f * (zk.y + zm.y), oi = -0.5f * (zk.x - zm.x); // odd part: (Zk - conj Zm) / 2i
-    const float2 tw = s_cs[k];                                          // W_N^k (k = M: -1)
-    const float re = er + orr * tw.x - oi * tw.y, im = ei + orr * tw.y + oi * tw.x;
-    if (MEL) {
-      reinterpret_cast<float*>(dst)[p] = re * re + im * im;   // [frame][bins] in the idle buffer
-      continue;
+  // untangle: thread = bin k (its twiddle is loaded once), loop over the frames; the Nyquist
+  // bin k = M of frame f goes to thread f of the last pass
+  const int64_t left = T - t0;
+  const int nf = left < kPow2Frames ? (int)left : kPow2Frames;
+  for (int k0 = threadIdx.x; k0 < M + kGenThreads; k0 += kGenThreads) {
+    int k = k0, f_lo = 0, f_hi = nf;
+    if (k0 >= M) {                       // extra slots: (frame k0 - M, bin M)
+      if (k0 - M >= nf) break;
+      k = M;
+      f_lo = k0 - M;
+      f_hi = f_lo + 1;
     }
-    const int64_t o = ((b * T + t0 + f) * bins + k);
-    if (power_only) {
-      out[o] = re * re + im * im;
-    } else {
-      reinterpret_cast<float2*>(out)[o] = make_float2(re, im);
+    const float2 tw = s_cs[k];           // W_N^k (k = M: -1)
+    for (int f = f_lo; f < f_hi; ++f) {
+      const float2* z = src + f * M;
+      const float2 zk = z[k & (M - 1)], zm = z[(M - k) & (M - 1)];
+      const float er = 0.5f * (zk.x + zm.x), ei = 0.5f * (zk.y - zm.y);   // even part
+      const float orr = 0.5f * (zk.y + zm.y), oi = -0.5f * (zk.x - zm.x); // odd: (Zk - conj Zm) / 2i
+      const float re = er + orr * tw.x - oi * tw.y, im = ei + orr * tw.y + oi * tw.x;
+      if (MEL) {
+        reinterpret_cast<float*>(dst)[f * bins + k] = re * re + im * im;  // idle buffer: [frame][bins]
+        continue;
+      }
+      const int64_t o = ((b * T + t0 + f) * bins + k);
+      if (power_only) {
+        out[o] = re * re + im * im;
+      } else {
+        reinterpret_cast<float2*>(out)[o] = make_float2(re, im);
+      }
     }
   }
   if (MEL) {
     __syncthreads();
+    // thread = filter m (its table entry is loaded once) x frame group: lanes walk over m
     const float* s_p = reinterpret_cast<const float*>(dst);
-    const int64_t left = T - t0;
-    const int nf = left < kPow2Frames ? (int)left : kPow2Frames;
     float vmax = -INFINITY;
     float* o = out + (b * T + t0) * mel.M;
-    for (int p = threadIdx.x; p < nf * mel.M; p += kGenThreads) {
-      const int f = p / mel.M, m = p - f * mel.M;
+    const int fgroups = kGenThreads / mel.M > 0 ? kGenThreads / mel.M : 1;
+    const int fg = threadIdx.x / mel.M;
+    for (int m = threadIdx.x - fg * mel.M; m < mel.M && fg < fgroups; m += kGenThreads) {
       const int cnt = __ldg(mel.count + m);
       const float* wt = mel.weight + __ldg(mel.offset + m);
-      const float* x = s_p + f * bins + __ldg(mel.start + m);
-      float acc = 0.f;
-      for (int i = 0; i < cnt; ++i) acc = fmaf(__ldg(wt + i), x[i], acc);
-      const float v = to_db(acc, mel.db);
-      o[p] = v;
-      vmax = fmaxf(vmax, v);
+      const float* x0 = s_p + __ldg(mel.start + m);
+      for (int f = fg; f < nf; f += fgroups) {
+        const float* x = x0 + f * bins;
+        float acc = 0.f;
+        for (int i = 0; i < cnt; ++i) acc = fmaf(__ldg(wt + i), x[i], acc);
+        const float v = to_db(acc, mel.db);
+        o[f * mel.M + m] = v;
+        vmax = fmaxf(vmax, v);
+      }
     }
     vmax = warp_max(vmax);
     if ((threadIdx.x & 31) == 0 && vmax > -INFINITY && mel.utt_max != nullptr)
