@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define SBFE_ABI_VERSION 6
+#define SBFE_ABI_VERSION 7
 
 #if defined(__GNUC__)
 #define SBFE_API __attribute__((visibility("default")))
@@ -156,6 +156,19 @@ SBFE_API int sbfe_norm_stats_tiles(const float* d_x, const float* d_lengths, int
  * out [B, T, bins, 2] (re, im), or, with power_only != 0, [B, T, bins] = re^2+im^2. */
 SBFE_API int sbfe_stft_forward(const sbfe_fbank_desc* desc, const float* d_wav, int64_t B, int64_t L,
                       int64_t wav_stride, float* d_out, int32_t power_only, void* stream);
+
+/* ---- next row: ISTFT.forward (processing/features.py:283-324) = torch.istft
+ * for one-sided spectra: d_spec [B, T, n_fft/2 + 1, 2] -> d_out [B, out_len].  Per frame the
+ * inverse real DFT (1/n_fft; the imaginary parts of bins 0 and n_fft/2 are ignored), times
+ * d_window [n_fft] (the caller centres a shorter window inside n_fft), overlap-add at t * hop,
+ * division by the overlap-added squared window, then samples [start, start + out_len) with
+ * start = n_fft/2 if center else 0; samples past n_fft + hop * (T - 1) are zero.  The caller
+ * checks that the window envelope is non-zero over that range (torch.istft raises otherwise).
+ * Workspace: sbfe_istft_workspace_bytes (the windowed frames). */
+SBFE_API int64_t sbfe_istft_workspace_bytes(int64_t B, int64_t T, int32_t n_fft);
+SBFE_API int sbfe_istft_forward(const float* d_spec, int64_t B, int64_t T, int32_t n_fft, int32_t hop,
+                       const float* d_window, int32_t center, int64_t out_len, float* d_out,
+                       void* d_workspace, int64_t workspace_bytes, void* stream);
 
 /* spectral_magnitude (processing/features.py:327-356) on n complex pairs. */
 SBFE_API int sbfe_spectral_magnitude(const float* d_stft, int64_t n, float power, int32_t take_log,

@@ -119,6 +119,62 @@ def stft(
     return out
 
 
+def istft(
+    spec,
+    sample_rate=16000,
+    n_fft=None,
+    win_length=25,
+    hop_length=10,
+    window=None,
+    center=True,
+    sig_length=None,
+    dtype=_F32,
+):
+    """``ISTFT.forward`` (processing/features.py:283-324) = ``torch.istft``: per-frame inverse
+    real FFT (1/N), window, overlap-add, division by the overlap-added squared window, centre
+    trim of ``n_fft//2`` per side, cut / zero-pad to ``sig_length``.
+
+    spec ``[B, T, F, 2]`` -> ``[B, L]``; ``[B, T, F, 2, C]`` -> ``[B, L, C]`` (:300-307, 320-322).
+    ``normalized_stft`` and ``epsilon`` of the reference class never reach ``torch.istft``
+    (:309-318), so they have no counterpart here either."""
+    spec = np.asarray(spec, dtype=dtype)
+    multi = spec.ndim == 5
+    if multi:  # [B, T, F, 2, C] -> [B*C, T, F, 2]
+        b, t_, f_, _, c = spec.shape
+        spec = spec.transpose(0, 4, 1, 2, 3).reshape(b * c, t_, f_, 2)
+    if n_fft is None:
+        n_fft = (spec.shape[2] - 1) * 2
+    win = ms_to_samples(sample_rate, win_length)
+    hop = ms_to_samples(sample_rate, hop_length)
+    w = hamming_window(win, dtype) if window is None else np.asarray(window, dtype)
+    if win < n_fft:
+        left = (n_fft - win) // 2
+        w = np.pad(w, (left, n_fft - win - left))
+    z = spec[..., 0] + 1j * spec[..., 1]
+    frames = np.fft.irfft(z, n=n_fft, axis=-1).astype(dtype) * w  # [B, T, n_fft]
+    bsz, t = frames.shape[:2]
+    full = n_fft + hop * (t - 1)
+    y = np.zeros((bsz, full), dtype=dtype)
+    env = np.zeros((full,), dtype=dtype)
+    for i in range(t):
+        y[:, i * hop:i * hop + n_fft] += frames[:, i]
+        env[i * hop:i * hop + n_fft] += w * w
+    start = n_fft // 2 if center else 0
+    if sig_length is not None:
+        end = start + sig_length
+    else:
+        end = full - n_fft // 2 if center else full
+    y, env = y[:, start:min(end, full)], env[start:min(end, full)]
+    if np.abs(env).min() < 1e-11:
+        raise RuntimeError("istft: window overlap-add is zero somewhere (torch.istft raises too)")
+    y = y / env
+    if end > full:  # requested longer than what the frames cover: zero padding
+        y = np.pad(y, ((0, 0), (0, end - full)))
+    if multi:
+        y = y.reshape(b, c, -1).transpose(0, 2, 1)
+    return y.astype(dtype)
+
+
 def spectral_magnitude(stft_out, power=1, log=False, eps=1e-14):
     """``spectral_magnitude`` (processing/features.py:327-356): sum of squares
     over the LAST axis, ``eps`` added only when ``power < 1``."""

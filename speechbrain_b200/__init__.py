@@ -10,11 +10,11 @@ from .dataio import RaggedBatch  # noqa: F401
 from .lobes.augment import SpecAugment  # noqa: F401
 from .lobes.features import MFCC, Fbank, pair  # noqa: F401
 from .processing.features import (  # noqa: F401
-    DCT, STFT, ContextWindow, Deltas, Filterbank, InputNormalization, spectral_magnitude)
+    DCT, ISTFT, STFT, ContextWindow, Deltas, Filterbank, InputNormalization, spectral_magnitude)
 
 __version__ = "0.1.0"
 
-_PROCESSING = ("STFT", "spectral_magnitude", "Filterbank", "DCT", "Deltas", "ContextWindow",
+_PROCESSING = ("STFT", "ISTFT", "spectral_magnitude", "Filterbank", "DCT", "Deltas", "ContextWindow",
                "InputNormalization")
 _LOBES = ("Fbank", "MFCC")
 

@@ -57,6 +57,8 @@ SIGNATURES = {
     "sbfe_norm_stats_tiles": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, _I32, _F, _P, _F, _P, _I32,
                                         _P, _P, _I32, _P, _P]),
     "sbfe_stft_forward": (C.c_int, [_DESC, _P, _I64, _I64, _I64, _P, _I32, _P]),
+    "sbfe_istft_workspace_bytes": (_I64, [_I64, _I64, _I32]),
+    "sbfe_istft_forward": (C.c_int, [_P, _I64, _I64, _I32, _I32, _P, _I32, _I64, _P, _P, _I64, _P]),
     "sbfe_spectral_magnitude": (C.c_int, [_P, _I64, _F, _I32, _F, _P, _P]),
     "sbfe_filterbank_forward": (C.c_int, [_DESC, _P, _I64, _I64, _P, _P, _P]),
     "sbfe_post_forward": (C.c_int, [_P, _I64, _I64, _I32, _P, _F, _P, _I32, _I32, _I32, _I32,
@@ -106,7 +108,7 @@ def lib():
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(handle, name)
             fn.restype, fn.argtypes = res, args
-        if handle.sbfe_abi_version() != 6:
+        if handle.sbfe_abi_version() != 7:
             raise SbfeUnavailable("libsbfe.so ABI version mismatch")
         _lib = handle
         return _lib

@@ -14,6 +14,9 @@ int launch_clamp_tiles(float*, int64_t, int64_t, int, const sbfe_maxkey_t*, floa
 int launch_norm_stats_tiles(const float*, const float*, int64_t, int64_t, int, int, int, float,
                             const sbfe_maxkey_t*, float, const float*, int, float*, float*, int,
                             sbfe_maxkey_t*, cudaStream_t);
+int64_t istft_workspace_bytes(int64_t, int64_t, int);
+int launch_istft(const float*, int64_t, int64_t, int, int, const float*, int, int64_t, float*, void*,
+                 int64_t, cudaStream_t);
 bool fbank_pow2_supported(const sbfe_fbank_desc*);
 int launch_fbank_pow2(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
                       sbfe_maxkey_t*, cudaStream_t);
@@ -132,6 +135,21 @@ int sbfe_fbank_forward_ragged_pcm16(const sbfe_fbank_desc* d, const int16_t* d_p
   if (!fbank400_v3_supported(d)) return SBFE_E_INVAL;  // convert on the device and use sbfe_fbank_forward
   return launch_fbank400_v3(d, d_packed, 1, scale, d_offsets, d_nsamples, B, L, 0, d_out, d_utt_max,
                             d_tile_stats, (cudaStream_t)stream);
+}
+
+int64_t sbfe_istft_workspace_bytes(int64_t B, int64_t T, int32_t n_fft) {
+  if (B < 0 || T < 0 || n_fft < 2 || (n_fft & 1)) return SBFE_E_INVAL;
+  return istft_workspace_bytes(B, T, n_fft);
+}
+
+int sbfe_istft_forward(const float* d_spec, int64_t B, int64_t T, int32_t n_fft, int32_t hop,
+                       const float* d_window, int32_t center, int64_t out_len, float* d_out,
+                       void* d_ws, int64_t ws_bytes, void* stream) {
+  if (B < 0 || T < 1 || n_fft < 2 || (n_fft & 1) || hop < 1 || out_len < 0) return SBFE_E_INVAL;
+  if (B == 0 || out_len == 0) return 0;
+  if (!d_spec || !d_window || !d_out || !d_ws) return SBFE_E_INVAL;
+  return launch_istft(d_spec, B, T, n_fft, hop, d_window, center, out_len, d_out, d_ws, ws_bytes,
+                      (cudaStream_t)stream);
 }
 
 int sbfe_stft_forward(const sbfe_fbank_desc* d, const float* d_wav, int64_t B, int64_t L,

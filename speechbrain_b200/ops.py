@@ -13,7 +13,7 @@ from . import _lib
 from ._lib import FbankDesc, check, lib
 
 __all__ = [
-    "FrontendTables", "fbank_forward", "stft_forward", "spectral_magnitude",
+    "FrontendTables", "fbank_forward", "stft_forward", "istft_forward", "spectral_magnitude",
     "filterbank_forward", "post_forward", "norm_stats", "norm_stats_tiles", "clamp_tiles", "TileStats", "norm_reduce", "norm_update",
     "norm_apply", "decode_utt_max",
 ]
@@ -257,6 +257,24 @@ def stft_forward(tables, wav, power_only=False):
     with torch.cuda.device(wav.device):
         check(lib().sbfe_stft_forward(C.byref(desc), _ptr(wav), B, L, L, _ptr(out),
                                       int(power_only), _stream()))
+    return out
+
+
+def istft_forward(spec, n_fft, hop, window, center, out_len):
+    """spec [B, T, n_fft//2+1, 2] -> [B, out_len] (sbfe_istft_forward).  ``window``: device
+    float32 [n_fft]."""
+    spec = _f32c(spec, "stft")
+    if spec.dim() != 4 or spec.shape[-1] != 2 or spec.shape[2] != n_fft // 2 + 1:
+        raise ValueError("expected [batch, frames, n_fft//2+1, 2], got %s" % (tuple(spec.shape),))
+    B, T = spec.shape[:2]
+    out = torch.empty((B, out_len), dtype=torch.float32, device=spec.device)
+    L_ = lib()
+    ws = torch.empty((max(int(L_.sbfe_istft_workspace_bytes(B, T, n_fft)), 16),), dtype=torch.uint8,
+                     device=spec.device)
+    with torch.cuda.device(spec.device):
+        check(L_.sbfe_istft_forward(_ptr(spec), B, T, int(n_fft), int(hop), _ptr(window),
+                                    int(bool(center)), int(out_len), _ptr(out), _ptr(ws), ws.numel(),
+                                    _stream()))
     return out
 
 

@@ -16,7 +16,7 @@ from .._jit import traceable
 
 logger = logging.getLogger(__name__)
 
-__all__ = ["STFT", "spectral_magnitude", "Filterbank", "DCT", "Deltas", "ContextWindow",
+__all__ = ["STFT", "ISTFT", "spectral_magnitude", "Filterbank", "DCT", "Deltas", "ContextWindow",
            "InputNormalization"]
 
 
@@ -69,6 +69,77 @@ class STFT(torch.nn.Module):
             out = out.reshape(b, c, out.shape[1], out.shape[2], 2)
             return out.permute(0, 2, 3, 4, 1)  # [B, T, F, 2, C]    (:175-183)
         return ops.stft_forward(self.tables(), x)
+
+
+class ISTFT(torch.nn.Module):
+    """Inverse short-term Fourier transform; reference: processing/features.py:191-324
+    (``torch.istft``).  ``[B, T, F, 2]`` -> ``[B, L]``; ``[B, T, F, 2, C]`` -> ``[B, L, C]``.
+    ``L = sig_length`` or ``(T - 1) * hop``.  Like the reference, ``normalized_stft`` and
+    ``epsilon`` are accepted and never reach the transform (:309-318).  Supported natively:
+    ``center=True/False`` with ``onesided=True``."""
+
+    def __init__(self, sample_rate, n_fft=None, win_length=25, hop_length=10,
+                 window_fn=torch.hamming_window, normalized_stft=False, center=True,
+                 onesided=True, epsilon=1e-12):
+        super().__init__()
+        self.sample_rate = sample_rate
+        self.n_fft = n_fft
+        self.normalized_stft = normalized_stft
+        self.center = center
+        self.onesided = onesided
+        self.epsilon = epsilon
+        self.win_length = int(round((self.sample_rate / 1000.0) * win_length))
+        self.hop_length = int(round((self.sample_rate / 1000.0) * hop_length))
+        self.window = window_fn(self.win_length)
+        self._cache = {}
+
+    def _window_on(self, n_fft, device):
+        """The window centred inside n_fft (torch.istft pads it the same way), per device."""
+        key = (n_fft, device.type, device.index)
+        hit = self._cache.get(key)
+        if hit is None:
+            win = self.window.detach().to("cpu", torch.float32)
+            if win.numel() > n_fft:
+                raise ValueError("win_length (%d samples) > n_fft (%d)" % (win.numel(), n_fft))
+            left = (n_fft - win.numel()) // 2
+            win = torch.nn.functional.pad(win, (left, n_fft - win.numel() - left)).contiguous()
+            hit = self._cache[key] = (win, win.to(device))
+        return hit
+
+    def _check_envelope(self, h_win, n_fft, frames, start, out_len):
+        """torch.istft refuses a window whose overlap-add vanishes somewhere in the output."""
+        key = ("env", n_fft, frames, start, out_len)
+        if key not in self._cache:
+            full = n_fft + self.hop_length * (frames - 1)
+            env = torch.zeros(full)
+            w2 = h_win * h_win
+            for t in range(frames):
+                env[t * self.hop_length:t * self.hop_length + n_fft] += w2
+            seg = env[start:min(start + out_len, full)]
+            self._cache[key] = bool(seg.numel() == 0 or float(seg.abs().min()) >= 1e-11)
+        if not self._cache[key]:
+            raise RuntimeError("istft: window overlap add min is below 1e-11 (same check as torch.istft)")
+
+    def forward(self, x, sig_length=None):
+        if not self.onesided:
+            raise NotImplementedError("speechbrain_b200.ISTFT implements onesided=True")
+        or_shape = x.shape
+        n_fft = (x.shape[2] - 1) * 2 if self.n_fft is None else self.n_fft
+        if len(or_shape) == 5:  # [B, T, F, 2, C] -> [B*C, T, F, 2]   (:300-305)
+            x = x.permute(0, 4, 1, 2, 3).reshape(-1, or_shape[1], or_shape[2], 2)
+        elif len(or_shape) != 4:
+            raise ValueError("expected [batch, time, freq, 2(, channels)], got %s" % (tuple(or_shape),))
+        ops._require_cuda(x, "x")
+        frames = x.shape[1]
+        start = n_fft // 2 if self.center else 0
+        full = n_fft + self.hop_length * (frames - 1)
+        out_len = int(sig_length) if sig_length is not None else (full - 2 * start if self.center else full)
+        h_win, d_win = self._window_on(n_fft, x.device)
+        self._check_envelope(h_win, n_fft, frames, start, out_len)
+        out = ops.istft_forward(x, n_fft, self.hop_length, d_win, self.center, out_len)
+        if len(or_shape) == 5:  # back to [B, L, C]   (:320-322)
+            out = out.reshape(or_shape[0], or_shape[4], -1).transpose(1, 2)
+        return out
 
 
 def spectral_magnitude(stft, power=1, log=False, eps=1e-14):
