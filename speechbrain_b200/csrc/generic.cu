@@ -8,6 +8,7 @@
 #include <cmath>
 
 #include "common.cuh"
+#include "fft_packed.cuh"
 
 namespace sbfe {
 
@@ -85,10 +86,30 @@ struct MelArgs {
   sbfe_maxkey_t* utt_max;
 };
 
+// radices of the Stockham passes for M = n_fft / 2 = 2^a 5^b: 4 ... 4 [2] 5 ... 5
+struct FftPlan {
+  int n;
+  unsigned char radix[20];
+};
+
+static bool make_fft_plan(int n_fft, FftPlan* plan) {
+  int m = n_fft / 2;
+  plan->n = 0;
+  if (n_fft < 16 || (n_fft & 1)) return false;
+  int twos = 0, fives = 0;
+  while (m % 2 == 0) { m /= 2; ++twos; }
+  while (m % 5 == 0) { m /= 5; ++fives; }
+  if (m != 1) return false;
+  for (; twos >= 2; twos -= 2) plan->radix[plan->n++] = 4;
+  if (twos) plan->radix[plan->n++] = 2;
+  for (; fives > 0; --fives) plan->radix[plan->n++] = 5;
+  return true;
+}
+
 template <bool MEL>
 __global__ void __launch_bounds__(kGenThreads)
 stft_pow2_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, int64_t T,
-                 const float* __restrict__ window, int n_fft, int log2m, int hop,
+                 const float* __restrict__ window, int n_fft, const FftPlan plan, int hop,
                  float* __restrict__ out, int power_only, unsigned tiles, const MelArgs mel) {
   extern __shared__ __align__(16) float smem[];
   const int M = n_fft >> 1;
@@ -119,42 +140,72 @@ stft_pow2_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, i
   __syncthreads();
   float2* src = s_a;
   float2* dst = s_b;
-  int ls = 0;                                            // log2 of Ns, the size already transformed
-  while (ls < log2m) {
-    if (log2m - ls >= 2) {                               // radix-4 pass
-      const int q = M >> 2, Ns = 1 << ls;
-      for (int i = threadIdx.x; i < kPow2Frames * q; i += kGenThreads) {
-        const int f = i >> (log2m - 2), j = i & (q - 1);
-        const int k = j & (Ns - 1);
-        const int tstep = k << (log2m + 1 - ls - 2);     // k * N / (4 Ns)
-        const float2* in = src + f * M + j;
-        float2 v0 = in[0], v1 = in[q], v2 = in[2 * q], v3 = in[3 * q];
-        v1 = cmulf(v1, s_cs[tstep]);
-        v2 = cmulf(v2, s_cs[2 * tstep]);
-        v3 = cmulf(v3, s_cs[3 * tstep]);
-        const float2 a0 = make_float2(v0.x + v2.x, v0.y + v2.y), a1 = make_float2(v0.x - v2.x, v0.y - v2.y);
-        const float2 a2 = make_float2(v1.x + v3.x, v1.y + v3.y);
-        const float2 a3 = make_float2(v1.y - v3.y, v3.x - v1.x);   // -i (v1 - v3)
-        float2* o = dst + f * M + (((j >> ls) << (ls + 2)) + k);
-        o[0] = make_float2(a0.x + a2.x, a0.y + a2.y);
-        o[Ns] = make_float2(a1.x + a3.x, a1.y + a3.y);
-        o[2 * Ns] = make_float2(a0.x - a2.x, a0.y - a2.y);
-        o[3 * Ns] = make_float2(a1.x - a3.x, a1.y - a3.y);
-      }
-      ls += 2;
-    } else {                                             // one radix-2 pass
-      const int h = M >> 1, Ns = 1 << ls;
-      for (int i = threadIdx.x; i < kPow2Frames * h; i += kGenThreads) {
-        const int f = i >> (log2m - 1), j = i & (h - 1);
-        const int k = j & (Ns - 1);
-        const float2* in = src + f * M + j;
-        const float2 v0 = in[0], v1 = cmulf(in[h], s_cs[k << (log2m + 1 - ls - 1)]);
-        float2* o = dst + f * M + (((j >> ls) << (ls + 1)) + k);
-        o[0] = make_float2(v0.x + v1.x, v0.y + v1.y);
-        o[Ns] = make_float2(v0.x - v1.x, v0.y - v1.y);
-      }
-      ls += 1;
+  // Stockham passes: radix R with Ns = the size already transformed:
+  //   v[r] = in[j + r M/R] * W_(Ns R)^(k r), k = j mod Ns;  out[(j / Ns) Ns R + k + r Ns] = DFT_R(v)[r]
+  // The power-of-two passes come first (Ns is then a power of two: shifts), the radix-5 passes last.
+  int Ns = 1;
+  for (int ps = 0; ps < plan.n; ++ps) {
+    const int R = plan.radix[ps];
+    const int q = M / R;
+    const int tw1 = n_fft / (Ns * R);                    // table step of W_(Ns R)
+    // thread -> (frame slot, butterfly): with q < 256 butterflies per frame several frames run
+    // side by side (one division per thread and pass)
+    const int fpar = q >= kGenThreads ? 1 : kGenThreads / q;
+    const int f_first = q >= kGenThreads ? 0 : threadIdx.x / q;
+    const int j_first = threadIdx.x - f_first * q;
+    const int j_step = q >= kGenThreads ? kGenThreads : q;   // q < 256: one butterfly per frame
+    const int f_end = f_first < fpar ? kPow2Frames : 0;
+    if (R == 4) {
+      const int ls = 31 - __clz(Ns);
+      for (int f = f_first; f < f_end; f += fpar)
+        for (int j = j_first; j < q; j += j_step) {
+          const int k = j & (Ns - 1);
+          const int tstep = k * tw1;
+          const float2* in = src + f * M + j;
+          float2 v0 = in[0], v1 = in[q], v2 = in[2 * q], v3 = in[3 * q];
+          v1 = cmulf(v1, s_cs[tstep]);
+          v2 = cmulf(v2, s_cs[2 * tstep]);
+          v3 = cmulf(v3, s_cs[3 * tstep]);
+          const float2 a0 = make_float2(v0.x + v2.x, v0.y + v2.y), a1 = make_float2(v0.x - v2.x, v0.y - v2.y);
+          const float2 a2 = make_float2(v1.x + v3.x, v1.y + v3.y);
+          const float2 a3 = make_float2(v1.y - v3.y, v3.x - v1.x);   // -i (v1 - v3)
+          float2* o = dst + f * M + (((j >> ls) << (ls + 2)) + k);
+          o[0] = make_float2(a0.x + a2.x, a0.y + a2.y);
+          o[Ns] = make_float2(a1.x + a3.x, a1.y + a3.y);
+          o[2 * Ns] = make_float2(a0.x - a2.x, a0.y - a2.y);
+          o[3 * Ns] = make_float2(a1.x - a3.x, a1.y - a3.y);
+        }
+    } else if (R == 2) {
+      const int ls = 31 - __clz(Ns);
+      for (int f = f_first; f < f_end; f += fpar)
+        for (int j = j_first; j < q; j += j_step) {
+          const int k = j & (Ns - 1);
+          const float2* in = src + f * M + j;
+          const float2 v0 = in[0], v1 = cmulf(in[q], s_cs[k * tw1]);
+          float2* o = dst + f * M + (((j >> ls) << (ls + 1)) + k);
+          o[0] = make_float2(v0.x + v1.x, v0.y + v1.y);
+          o[Ns] = make_float2(v0.x - v1.x, v0.y - v1.y);
+        }
+    } else {  // R == 5
+      for (int f = f_first; f < f_end; f += fpar)
+        for (int j = j_first; j < q; j += j_step) {
+          const int jb = j / Ns, k = j - jb * Ns;
+          const int tstep = k * tw1;
+          const float2* in = src + f * M + j;
+          cx<float> v[5];
+#pragma unroll
+          for (int r = 0; r < 5; ++r) {
+            float2 t = in[r * q];
+            if (r) t = cmulf(t, s_cs[r * tstep]);
+            v[r] = cx<float>{t.x, t.y};
+          }
+          dft5(v[0], v[1], v[2], v[3], v[4]);
+          float2* o = dst + f * M + (jb * Ns * 5 + k);
+#pragma unroll
+          for (int r = 0; r < 5; ++r) o[r * Ns] = make_float2(v[r].re, v[r].im);
+        }
     }
+    Ns *= R;
     __syncthreads();
     float2* t = src; src = dst; dst = t;
   }
@@ -173,7 +224,7 @@ stft_pow2_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, i
     const float2 tw = s_cs[k];           // W_N^k (k = M: -1)
     for (int f = f_lo; f < f_hi; ++f) {
       const float2* z = src + f * M;
-      const float2 zk = z[k & (M - 1)], zm = z[(M - k) & (M - 1)];
+      const float2 zk = z[k == M ? 0 : k], zm = z[k == 0 ? 0 : M - k];
       const float er = 0.5f * (zk.x + zm.x), ei = 0.5f * (zk.y - zm.y);   // even part
       const float orr = 0.5f * (zk.y + zm.y), oi = -0.5f * (zk.x - zm.x); // odd: (Zk - conj Zm) / 2i
       const float re = er + orr * tw.x - oi * tw.y, im = ei + orr * tw.y + oi * tw.x;
@@ -216,8 +267,9 @@ stft_pow2_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, i
   }
 }
 
-static bool pow2_fits(int n_fft) {
-  return n_fft >= 16 && (n_fft & (n_fft - 1)) == 0 &&
+static bool pow2_fits(int n_fft) {   // n_fft / 2 = 2^a 5^b and the ping-pong buffers fit
+  FftPlan plan;
+  return make_fft_plan(n_fft, &plan) &&
          (size_t)(2 + 2 * kPow2Frames) * n_fft * sizeof(float) <= 200 * 1024;
 }
 
@@ -230,8 +282,8 @@ int launch_fbank_pow2(const sbfe_fbank_desc* d, const float* wav, int64_t B, int
   const int64_t T = 1 + L / d->hop;
   const int64_t tiles = (T + kPow2Frames - 1) / kPow2Frames;
   if (tiles * B > 0x7fffffff) return SBFE_E_TOOBIG;
-  int log2m = 0;
-  while ((2 << log2m) < d->n_fft) ++log2m;
+  FftPlan plan;
+  make_fft_plan(d->n_fft, &plan);
   const size_t smem = (size_t)(2 + 2 * kPow2Frames) * d->n_fft * sizeof(float);
   cudaError_t e = cudaFuncSetAttribute(stft_pow2_kernel<true>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -241,7 +293,7 @@ int launch_fbank_pow2(const sbfe_fbank_desc* d, const float* wav, int64_t B, int
                        d->log_mel},
               utt_max};
   stft_pow2_kernel<true><<<(unsigned)(tiles * B), kGenThreads, smem, stream>>>(
-      wav, L, wav_stride, T, d->d_window, d->n_fft, log2m, d->hop, out, 1, (unsigned)tiles, mel);
+      wav, L, wav_stride, T, d->d_window, d->n_fft, plan, d->hop, out, 1, (unsigned)tiles, mel);
   return check_last();
 }
 
@@ -254,14 +306,14 @@ int launch_stft_generic(const sbfe_fbank_desc* d, const float* wav, int64_t B, i
   // power of two (and the ping-pong buffers fit in shared memory): the FFT kernel
   const size_t smem2 = (size_t)(2 + 2 * kPow2Frames) * d->n_fft * sizeof(float);
   if (pow2_fits(d->n_fft)) {
-    int log2m = 0;
-    while ((2 << log2m) < d->n_fft) ++log2m;
+    FftPlan plan;
+    make_fft_plan(d->n_fft, &plan);
     const int64_t tiles2 = (T + kPow2Frames - 1) / kPow2Frames;
     cudaError_t e2 = cudaFuncSetAttribute(stft_pow2_kernel<false>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
     if (e2 != cudaSuccess) return (int)e2;
     stft_pow2_kernel<false><<<(unsigned)(tiles2 * B), kGenThreads, smem2, stream>>>(
-        wav, L, wav_stride, T, d->d_window, d->n_fft, log2m, d->hop, out, power_only, (unsigned)tiles2,
+        wav, L, wav_stride, T, d->d_window, d->n_fft, plan, d->hop, out, power_only, (unsigned)tiles2,
         MelArgs{});
     return check_last();
   }
