@@ -106,11 +106,17 @@ static bool make_fft_plan(int n_fft, FftPlan* plan) {
   return true;
 }
 
-template <bool MEL>
+// MODE 0: STFT (complex or power spectrum to HBM); 1: Fbank (power -> mel -> dB, MelArgs);
+// 2: INVERSE real FFT for ISTFT - `wav` is the one-sided spectrum [T][N/2 + 1][2] of T frames,
+//    `out` the windowed time frames [T][N]: Z[k] = E[k] + i O[k] is rebuilt from X (the inverse of
+//    the untangle step), conj(Z) goes through the SAME forward passes (IFFT(Z) = conj(FFT(conj Z)) / M)
+//    and x[2n] = Re z[n], x[2n+1] = Im z[n].
+template <int MODE>
 __global__ void __launch_bounds__(kGenThreads)
 stft_pow2_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, int64_t T,
                  const float* __restrict__ window, int n_fft, const FftPlan plan, int hop,
                  float* __restrict__ out, int power_only, unsigned tiles, const MelArgs mel) {
+  constexpr bool MEL = MODE == 1, INV = MODE == 2;
   extern __shared__ __align__(16) float smem[];
   const int M = n_fft >> 1;
   float2* s_cs = reinterpret_cast<float2*>(smem);        // W_N^j, j < N
@@ -125,9 +131,31 @@ stft_pow2_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, i
     sincospif(2.0f * (float)j / (float)n_fft, &sn, &cs);
     s_cs[j] = make_float2(cs, -sn);
   }
+  if (INV) {
+    // thread = bin k: Z[k] = E + i O with E = (X[k] + conj X[M-k]) / 2, O = conj(W^k) (X[k] - conj X[M-k]) / 2;
+    // conj(Z) is stored (the imaginary parts of X[0] and X[M] do not exist for a real signal)
+    const float2* spec = reinterpret_cast<const float2*>(wav);
+    for (int k = threadIdx.x; k < M; k += kGenThreads) {
+      float sn, cs;
+      sincospif(2.0f * (float)k / (float)n_fft, &sn, &cs);
+      for (int f = 0; f < kPow2Frames; ++f) {
+        float2 z = make_float2(0.f, 0.f);
+        if (t0 + f < T) {
+          const float2* x = spec + (t0 + f) * bins;
+          float2 a = __ldg(x + k), c = __ldg(x + (M - k));
+          if (k == 0) { a.y = 0.f; c.y = 0.f; }
+          const float ex = 0.5f * (a.x + c.x), ey = 0.5f * (a.y - c.y);
+          const float dx = 0.5f * (a.x - c.x), dy = 0.5f * (a.y + c.y);
+          const float ox = dx * cs - dy * sn, oy = dx * sn + dy * cs;   // (cos + i sin) * D
+          z = make_float2(ex - oy, -(ey + ox));                         // conj(E + i O)
+        }
+        s_a[f * M + k] = z;
+      }
+    }
+  }
   // thread = sample pair n (its two window taps are loaded once), loop over the frames: no
   // division, no per-element window load
-  for (int n = threadIdx.x; n < M; n += kGenThreads) {
+  for (int n = threadIdx.x; n < M && !INV; n += kGenThreads) {
     const float w0 = __ldg(window + 2 * n), w1 = __ldg(window + 2 * n + 1);
     int64_t g = t0 * hop - n_fft / 2 + 2 * n;
 #pragma unroll 4
@@ -209,10 +237,21 @@ stft_pow2_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, i
     __syncthreads();
     float2* t = src; src = dst; dst = t;
   }
-  // untangle: thread = bin k (its twiddle is loaded once), loop over the frames; the Nyquist
-  // bin k = M of frame f goes to thread f of the last pass
   const int64_t left = T - t0;
   const int nf = left < kPow2Frames ? (int)left : kPow2Frames;
+  if (INV) {   // x[2n] = Re z[n] / M, x[2n+1] = Im z[n] / M with z = conj(result); times the window
+    const float inv_m = 1.0f / (float)M;
+    for (int n = threadIdx.x; n < M; n += kGenThreads) {
+      const float w0 = __ldg(window + 2 * n) * inv_m, w1 = -__ldg(window + 2 * n + 1) * inv_m;
+      for (int f = 0; f < nf; ++f) {
+        const float2 r = src[f * M + n];
+        reinterpret_cast<float2*>(out + (t0 + f) * n_fft)[n] = make_float2(r.x * w0, r.y * w1);
+      }
+    }
+    return;
+  }
+  // untangle: thread = bin k (its twiddle is loaded once), loop over the frames; the Nyquist
+  // bin k = M of frame f goes to thread f of the last pass
   for (int k0 = threadIdx.x; k0 < M + kGenThreads; k0 += kGenThreads) {
     int k = k0, f_lo = 0, f_hi = nf;
     if (k0 >= M) {                       // extra slots: (frame k0 - M, bin M)
@@ -285,15 +324,34 @@ int launch_fbank_pow2(const sbfe_fbank_desc* d, const float* wav, int64_t B, int
   FftPlan plan;
   make_fft_plan(d->n_fft, &plan);
   const size_t smem = (size_t)(2 + 2 * kPow2Frames) * d->n_fft * sizeof(float);
-  cudaError_t e = cudaFuncSetAttribute(stft_pow2_kernel<true>,
+  cudaError_t e = cudaFuncSetAttribute(stft_pow2_kernel<1>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
   MelArgs mel{d->n_mels, d->d_mel_start, d->d_mel_count, d->d_mel_offset, d->d_mel_weight,
               DbParams{d->multiplier * 0.30102999566398120f, d->amin, d->db_offset, d->floor_db,
                        d->log_mel},
               utt_max};
-  stft_pow2_kernel<true><<<(unsigned)(tiles * B), kGenThreads, smem, stream>>>(
+  stft_pow2_kernel<1><<<(unsigned)(tiles * B), kGenThreads, smem, stream>>>(
       wav, L, wav_stride, T, d->d_window, d->n_fft, plan, d->hop, out, 1, (unsigned)tiles, mel);
+  return check_last();
+}
+
+// ISTFT step 1 through the FFT: spec [n_frames][n_fft/2+1][2] -> windowed frames [n_frames][n_fft]
+bool irfft_frames_supported(int n_fft) { return pow2_fits(n_fft); }
+
+int launch_irfft_frames(const float* spec, int64_t n_frames, int n_fft, const float* window,
+                        float* frames, cudaStream_t stream) {
+  if (n_frames == 0) return 0;
+  const int64_t tiles = (n_frames + kPow2Frames - 1) / kPow2Frames;
+  if (tiles > 0x7fffffff) return SBFE_E_TOOBIG;
+  FftPlan plan;
+  make_fft_plan(n_fft, &plan);
+  const size_t smem = (size_t)(2 + 2 * kPow2Frames) * n_fft * sizeof(float);
+  cudaError_t e = cudaFuncSetAttribute(stft_pow2_kernel<2>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return (int)e;
+  stft_pow2_kernel<2><<<(unsigned)tiles, kGenThreads, smem, stream>>>(
+      spec, 0, 0, n_frames, window, n_fft, plan, 1, frames, 0, (unsigned)tiles, MelArgs{});
   return check_last();
 }
 
@@ -309,10 +367,10 @@ int launch_stft_generic(const sbfe_fbank_desc* d, const float* wav, int64_t B, i
     FftPlan plan;
     make_fft_plan(d->n_fft, &plan);
     const int64_t tiles2 = (T + kPow2Frames - 1) / kPow2Frames;
-    cudaError_t e2 = cudaFuncSetAttribute(stft_pow2_kernel<false>,
+    cudaError_t e2 = cudaFuncSetAttribute(stft_pow2_kernel<0>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
     if (e2 != cudaSuccess) return (int)e2;
-    stft_pow2_kernel<false><<<(unsigned)(tiles2 * B), kGenThreads, smem2, stream>>>(
+    stft_pow2_kernel<0><<<(unsigned)(tiles2 * B), kGenThreads, smem2, stream>>>(
         wav, L, wav_stride, T, d->d_window, d->n_fft, plan, d->hop, out, power_only, (unsigned)tiles2,
         MelArgs{});
     return check_last();

@@ -1,8 +1,10 @@
 // ISTFT.forward (speechbrain/processing/features.py:283-324) = torch.istft for one-sided spectra:
 // per-frame inverse real DFT (1/N), window, overlap-add, division by the overlap-added squared
 // window, centre trim, cut / zero-pad to the requested length.  Next row N4 of SURVEY.md 8f.
-//   istft_frames_kernel  spec [B, T, F, 2] -> windowed frames [B, T, N] (workspace); direct
-//                        inverse DFT from a shared-memory twiddle table (general n_fft)
+//   frames               spec [B, T, F, 2] -> windowed frames [B, T, N] (workspace): the Stockham
+//                        FFT kernel of generic.cu in inverse mode when n_fft / 2 = 2^a 5^b (400,
+//                        512, ...), else istft_frames_kernel: direct inverse DFT from a
+//                        shared-memory twiddle table (any even n_fft)
 //   istft_ola_kernel     gather formulation of the overlap-add: every output sample sums the
 //                        <= ceil(N / hop) frames that cover it and divides by the window
 //                        envelope computed the same way (no atomics, deterministic)
@@ -11,6 +13,9 @@
 #include "common.cuh"
 
 namespace sbfe {
+
+bool irfft_frames_supported(int n_fft);   // generic.cu: the Stockham kernel in inverse mode
+int launch_irfft_frames(const float*, int64_t, int, const float*, float*, cudaStream_t);
 
 constexpr int kIstftFrames = 4;
 constexpr int kIstftThreads = 256;
@@ -109,7 +114,10 @@ int launch_istft(const float* spec, int64_t B, int64_t T, int n_fft, int hop, co
     if (e != cudaSuccess) return (int)e;
   }
   float* frames = reinterpret_cast<float*>(ws);
-  if (n_frames > 0) {
+  if (n_frames > 0 && irfft_frames_supported(n_fft)) {   // n_fft / 2 = 2^a 5^b: the FFT
+    int rc = launch_irfft_frames(spec, n_frames, n_fft, window, frames, stream);
+    if (rc) return rc;
+  } else if (n_frames > 0) {
     int rc = launch_pdl(istft_frames_kernel, dim3((unsigned)ctas), dim3(kIstftThreads), smem, stream,
                         reinterpret_cast<const float2*>(spec), n_frames, n_fft, window, frames);
     if (rc) return rc;

@@ -78,3 +78,25 @@ def test_cuda_roundtrip_at_full_size_and_errors():
         sb.ISTFT(sample_rate=16000)(spec.cpu())
     with pytest.raises(NotImplementedError):
         sb.ISTFT(sample_rate=16000, onesided=False)(spec)
+
+
+@pytest.mark.gpu
+def test_cuda_direct_dft_paths_for_other_n_fft():
+    """n_fft / 2 with a prime factor other than 2 and 5 (here 336 = 2^4 * 21) takes the direct-DFT
+    kernels, forward and inverse: checked against the float64 oracle."""
+    import speechbrain_b200 as sb
+
+    rng = np.random.default_rng(41)
+    wav = (rng.standard_normal((2, 3000)) * 0.1).astype(np.float32)
+    kw = dict(sample_rate=16000, n_fft=336, win_length=20, hop_length=10)
+    spec = sb.STFT(**kw)(torch.from_numpy(wav).cuda())
+    want = onp.stft(wav, dtype=np.float64, **kw)
+    assert spec.shape == want.shape
+    assert float(np.abs(spec.cpu().numpy() - want).max()) < 2e-5      # |X| up to ~10
+    x = rng.standard_normal((2, 9, 169, 2)).astype(np.float32)
+    got = sb.ISTFT(**kw)(torch.from_numpy(x).cuda()).cpu().numpy()
+    ref = onp.istft(x, dtype=np.float64, **kw)
+    assert got.shape == ref.shape
+    assert float(np.abs(got - ref).max()) < 2e-6 * max(1.0, float(np.abs(ref).max()))
+    back = sb.ISTFT(**kw)(spec).cpu().numpy()
+    assert float(np.abs(back - wav[:, :back.shape[1]]).max()) < 2e-6
