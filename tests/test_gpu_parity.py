@@ -243,6 +243,53 @@ def test_full_size_properties(sb, B, L, kw):
     assert (full.amax(dim=(1, 2)) - full.amin(dim=(1, 2)) <= 80.0 + 1e-4).all()
 
 
+def test_full_size_properties_cfg3_cfg4_cfg5(sb):
+    """The other BASELINE.json configs at their full sizes, through properties that do not need
+    the oracle: batch independence (bit for bit), linearity of the statistics, in-place
+    contract, zero mean / unit variance over the valid frames."""
+    g = torch.Generator(device="cuda").manual_seed(7)
+    # cfg3: MFCC (23 mel -> 20 DCT -> deltas -> context 5+5), 64 x 4 s
+    wav = torch.randn(64, 64000, device="cuda", generator=g) * 0.1
+    mf = sb.MFCC()
+    full = mf(wav)
+    assert full.shape == (64, 401, 660) and torch.isfinite(full).all()
+    assert torch.equal(mf(wav[5:6].clone())[0], full[5])
+    ctx = full.view(64, 401, 60, 11)                       # [.., feature, context]: f * C + c
+    assert torch.equal(ctx[:, 5:-5, :, 5 + 3], ctx[:, 8:-2, :, 5])   # window slot c = frame t + c - 5
+    assert bool((ctx[:, 0, :, :5] == 0).all()) and bool((ctx[:, -1, :, 6:] == 0).all())   # zero padding
+    # cfg4: Fbank-80 + sentence mean normalisation, 256 x 3 s, paired and un-paired agree bit for bit
+    wav = torch.randn(256, 48000, device="cuda", generator=g) * 0.1
+    lens = torch.linspace(0.5, 1.0, 256, device="cuda")
+    for i in range(256):
+        wav[i, int(round(float(lens[i]) * 48000)):] = 0
+    fb, norm = sb.Fbank(n_mels=80), sb.InputNormalization(norm_type="sentence", std_norm=False)
+    feats = fb(wav)
+    out = norm(feats, lens)
+    assert out.data_ptr() == feats.data_ptr() and out.shape == (256, 301, 80)
+    n_valid = torch.round(lens * 301).long()
+    for i in (0, 100, 255):
+        assert float(out[i, :n_valid[i]].mean(0).abs().max()) < 2e-5
+    fb2, norm2 = sb.Fbank(n_mels=80), sb.InputNormalization(norm_type="sentence", std_norm=False)
+    sb.pair(fb2, norm2)
+    assert torch.equal(norm2(fb2(wav), lens), out)
+    # cfg5 (one GPU's shard): Fbank-80 + global normalisation in training mode, 128 x 30 s
+    wav = torch.randn(128, 480000, device="cuda", generator=g) * 0.1
+    lens = torch.linspace(0.6, 1.0, 128, device="cuda")
+    fb, gn = sb.Fbank(n_mels=80), sb.InputNormalization(norm_type="global").train()
+    feats = fb(wav)
+    keep = feats.clone()
+    out = gn(feats, lens, epoch=0)
+    assert out.shape == (128, 3001, 80) and torch.equal(feats, keep)          # x is left intact
+    # the global statistics are the means of the per-sentence ones (features.py:1084-1085)
+    sn = sb.InputNormalization(norm_type="sentence")
+    from speechbrain_b200 import ops
+    m, sd = ops.norm_stats(keep, lens)
+    assert torch.allclose(gn.glob_mean, m.mean(0), rtol=1e-5, atol=1e-5)
+    assert torch.allclose(gn.glob_std, sd.mean(0), rtol=1e-5, atol=1e-5)
+    assert torch.allclose(out, (keep - gn.glob_mean) / gn.glob_std, rtol=1e-5, atol=1e-5)
+    assert gn.count == 1 and sn is not None
+
+
 def test_tile_stats_path_matches_generic_kernels(sb):
     """Fused-kernel tile statistics + tile-aware clamp == the generic clamp / stats kernels,
     with silence tails (values at the top_db floor), an all-zero utterance and valid lengths
