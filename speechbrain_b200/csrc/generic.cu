@@ -198,10 +198,16 @@ stft_pow2_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, i
           const float2 a2 = make_float2(v1.x + v3.x, v1.y + v3.y);
           const float2 a3 = make_float2(v1.y - v3.y, v3.x - v1.x);   // -i (v1 - v3)
           float2* o = dst + f * M + (((j >> ls) << (ls + 2)) + k);
-          o[0] = make_float2(a0.x + a2.x, a0.y + a2.y);
-          o[Ns] = make_float2(a1.x + a3.x, a1.y + a3.y);
-          o[2 * Ns] = make_float2(a0.x - a2.x, a0.y - a2.y);
-          o[3 * Ns] = make_float2(a1.x - a3.x, a1.y - a3.y);
+          if (Ns == 1) {   // first pass: the four outputs are adjacent - two 128-bit stores
+            float4* o4 = reinterpret_cast<float4*>(o);
+            o4[0] = make_float4(a0.x + a2.x, a0.y + a2.y, a1.x + a3.x, a1.y + a3.y);
+            o4[1] = make_float4(a0.x - a2.x, a0.y - a2.y, a1.x - a3.x, a1.y - a3.y);
+          } else {
+            o[0] = make_float2(a0.x + a2.x, a0.y + a2.y);
+            o[Ns] = make_float2(a1.x + a3.x, a1.y + a3.y);
+            o[2 * Ns] = make_float2(a0.x - a2.x, a0.y - a2.y);
+            o[3 * Ns] = make_float2(a1.x - a3.x, a1.y - a3.y);
+          }
         }
     } else if (R == 2) {
       const int ls = 31 - __clz(Ns);
