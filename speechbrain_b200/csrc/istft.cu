@@ -63,34 +63,40 @@ istft_frames_kernel(const float2* __restrict__ spec, int64_t n_frames, int n_fft
   }
 }
 
+// IDX = int32_t when every index of one utterance fits 31 bits (the usual case: the 64-bit
+// divisions otherwise cost more than the memory traffic), int64_t for the rest.
+template <typename IDX>
 __global__ void __launch_bounds__(256)
-istft_ola_kernel(const float* __restrict__ frames, int64_t T, int n_fft, int hop,
-                 const float* __restrict__ window, int64_t start, int64_t out_len,
+istft_ola_kernel(const float* __restrict__ frames, int64_t T64, int n_fft, int hop,
+                 const float* __restrict__ window, int64_t start64, int64_t out_len64,
                  float* __restrict__ out) {
   pdl_wait();
   pdl_launch_dependents();
   const int64_t b = blockIdx.y;
-  const int64_t full = (int64_t)n_fft + (int64_t)hop * (T - 1);
-  const float* fb = frames + b * T * n_fft;
-  for (int64_t s = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; s < out_len;
-       s += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t u = s + start;
+  const IDX T = (IDX)T64, start = (IDX)start64, out_len = (IDX)out_len64;
+  const IDX full = (IDX)n_fft + (IDX)hop * (T - 1);
+  const float* fb = frames + b * T64 * n_fft;
+  float* ob = out + b * out_len64;
+  for (IDX s = (IDX)(blockIdx.x * blockDim.x + threadIdx.x); s < out_len;
+       s += (IDX)(gridDim.x * blockDim.x)) {
+    const IDX u = s + start;
     float v = 0.f;
     if (u < full) {
-      int64_t t_hi = u / hop;
+      IDX t_hi = u / hop;
       if (t_hi > T - 1) t_hi = T - 1;
-      int64_t t_lo = (u - n_fft + hop) / hop;   // ceil((u - n_fft + 1) / hop) for u - n_fft + 1 > 0
-      if (u - n_fft + 1 <= 0) t_lo = 0;
+      // first frame that still covers u: ceil((u - n_fft + 1) / hop), 0 when that is negative
+      const IDX t_lo = u >= (IDX)n_fft ? (u - (IDX)n_fft + (IDX)hop) / (IDX)hop : 0;
       float acc = 0.f, env = 0.f;
-      for (int64_t t = t_lo; t <= t_hi; ++t) {
-        const int n = (int)(u - t * hop);
+      IDX n = u - t_lo * (IDX)hop;                 // position inside frame t_lo, then n - hop ...
+      const float* fr = fb + (int64_t)t_lo * n_fft;
+      for (IDX t = t_lo; t <= t_hi; ++t, n -= (IDX)hop, fr += n_fft) {
         const float w = __ldg(window + n);
-        acc += fb[t * n_fft + n];
+        acc += fr[n];
         env = fmaf(w, w, env);
       }
       v = acc / env;
     }
-    out[b * out_len + s] = v;
+    ob[s] = v;
   }
 }
 
@@ -124,9 +130,13 @@ int launch_istft(const float* spec, int64_t B, int64_t T, int n_fft, int hop, co
   }
   int64_t gx = (out_len + 255) / 256;
   if (gx > 148 * 8) gx = 148 * 8;
-  return launch_pdl(istft_ola_kernel, dim3((unsigned)gx, (unsigned)B), dim3(256), 0, stream,
-                    (const float*)frames, T, n_fft, hop, window,
-                    (int64_t)(center ? n_fft / 2 : 0), out_len, out);
+  const int64_t start = center ? n_fft / 2 : 0;
+  const bool small = (int64_t)n_fft + (int64_t)hop * T + out_len + start < 0x7fffffffLL;
+  if (small)
+    return launch_pdl(istft_ola_kernel<int32_t>, dim3((unsigned)gx, (unsigned)B), dim3(256), 0, stream,
+                      (const float*)frames, T, n_fft, hop, window, start, out_len, out);
+  return launch_pdl(istft_ola_kernel<int64_t>, dim3((unsigned)gx, (unsigned)B), dim3(256), 0, stream,
+                    (const float*)frames, T, n_fft, hop, window, start, out_len, out);
 }
 
 }  // namespace sbfe
