@@ -14,6 +14,8 @@ ncu --set full --import-source on --clock-control none -k regex:"fbank400_v3|nor
   python profiles/prof_fbank.py 4 >> $O/final_prof.log 2>&1
 python profiles/stepbench.py > $O/final_stepbench.txt 2>&1
 python profiles/configs_bench.py --json $O/final_configs.json > $O/final_configs.txt 2>&1
+(python profiles/istft_bench.py; python profiles/nfft512_bench.py) > $O/final_general.txt 2>&1
+python profiles/prof_cfg.py cfg3 > /dev/null 2>&1 && ncu --set full --clock-control none -k regex:"post_fast" -s 2 -c 1 -f -o $O/final_post python profiles/prof_cfg.py cfg3 > /dev/null 2>&1
 bash profiles/exp_v3.sh > $O/final_ablation.txt 2>&1
 python -m speechbrain_b200._build --force > /dev/null 2>&1
 cat $O/final_tests.txt $O/final_stepbench.txt $O/final_configs.txt $O/final_ablation.txt

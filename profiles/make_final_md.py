@@ -35,6 +35,8 @@ post = summ("kernel", "gpurun_out/final_post.ncu-rep") if os.path.exists(os.path
 step = open(os.path.join(G, "final_stepbench.txt")).read()
 cfgs = open(os.path.join(G, "final_configs.txt")).read()
 abl = open(os.path.join(G, "final_ablation.txt")).read()
+gen_path = os.path.join(G, "final_general.txt")
+general = open(gen_path).read() if os.path.exists(gen_path) else ""
 ro = d["roofline"]
 doc = f"""# Round 1, final kernels (cfg2 step = Fbank(80) + sentence InputNormalization, 32 x 16 s, B200)
 
@@ -80,6 +82,14 @@ start of the round: 41.2 full / 36.6 without stage 4 / 27.7 without stages 3-4):
 
 ```
 {abl}```
+
+## General path (Stockham FFT kernel: stand-alone STFT / ISTFT, Fbank with n_fft = 512), eager calls on the cfg2 batch
+
+`profiles/istft_bench.py`, `profiles/nfft512_bench.py` (the `n_fft=400` line of the second script is the fused
+kernel called eagerly, for scale):
+
+```
+{general}```
 
 ## ncu --set full (profiles/prof_fbank.py: one paired cfg2 step, lengths = 1)
 
