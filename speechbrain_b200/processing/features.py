@@ -111,10 +111,9 @@ class ISTFT(torch.nn.Module):
         key = ("env", n_fft, frames, start, out_len)
         if key not in self._cache:
             full = n_fft + self.hop_length * (frames - 1)
-            env = torch.zeros(full)
-            w2 = h_win * h_win
-            for t in range(frames):
-                env[t * self.hop_length:t * self.hop_length + n_fft] += w2
+            # overlap-add of the squared window = transposed convolution of an impulse train
+            env = torch.nn.functional.conv_transpose1d(
+                torch.ones(1, 1, frames), (h_win * h_win).view(1, 1, n_fft), stride=self.hop_length).view(-1)
             seg = env[start:min(start + out_len, full)]
             self._cache[key] = bool(seg.numel() == 0 or float(seg.abs().min()) >= 1e-11)
         if not self._cache[key]:
