@@ -152,66 +152,53 @@ def cpu_port_step(wav, lengths):
         return ot.fbank_sentence_norm(wav, lengths, n_mels=N_MELS)
 
 
-def time_cpu_port(n_utts, reps, warm=1):
-    """Times the torch-CPU port of the reference path on `n_utts` x 16 s with all
-    host threads; returns (audio-s/s from the best rep, threads, sample text)."""
+CPU_SAMPLE = ("full cfg2 batch (32 x 16 s) per step, mean over the timed steps, torch CPU ops "
+              "restating the reference chain (oracle/frontend_torch.py), all host threads")
+
+
+def time_cpu_port(steps, warm=1):
+    """Times the torch-CPU port of the reference path on the FULL cfg2 batch with all host
+    threads - the same sample and the same statistic (mean over `steps` steps after `warm`
+    warm-up steps) as the reference arm; returns (audio-s/s, threads, seconds per step)."""
     torch.set_num_threads(os.cpu_count() or 1)
     wav, lengths = synth_batch(0, "cpu")
-    wav, lengths = wav[:n_utts].contiguous(), lengths[:n_utts].contiguous()
-    for _ in range(warm):
+    for _ in range(max(1, warm)):
         cpu_port_step(wav, lengths)
-    best = float("inf")
-    for _ in range(reps):
-        t0 = time.perf_counter()
+    t0 = time.perf_counter()
+    for _ in range(steps):
         cpu_port_step(wav, lengths)
-        best = min(best, time.perf_counter() - t0)
-    sample = "%d x %d s utterances of the cfg2 batch, best of %d (torch CPU ops, %d threads)" % (
-        n_utts, SECONDS, reps, torch.get_num_threads())
-    return n_utts * SECONDS / best, torch.get_num_threads(), sample, best
+    dt = (time.perf_counter() - t0) / steps
+    return AUDIO_S_PER_STEP / dt, torch.get_num_threads(), dt
 
 
 def run_reference_arm(args, rank):
     if rank != 0:
         return
     steps = max(1, args.steps)
-    torch.set_num_threads(os.cpu_count() or 1)
-    wav, lengths = synth_batch(0, "cpu")
-    for _ in range(max(1, args.warmup)):
-        cpu_port_step(wav, lengths)
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        cpu_port_step(wav, lengths)
-    dt = (time.perf_counter() - t0) / steps
-    val = AUDIO_S_PER_STEP / dt
-    cores = torch.get_num_threads()
+    val, cores, dt = time_cpu_port(steps, args.warmup)
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": "audio-s/s",
         "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic", "config": CONFIG,
         "cpu_baseline": {"value": val, "unit": "audio-s/s", "cores": cores, "kind": "port",
-                         "sample": "full cfg2 batch (32 x 16 s) per step, torch CPU ops restating "
-                                   "the reference chain (oracle/frontend_torch.py)"},
+                         "sample": CPU_SAMPLE},
         "e2e": {"value": val, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
 
 
 # ------------------------------------------------------------------ GPU arm
-def build_frontend(paired=True):
-    """The recipe's two modules.  paired: speechbrain_b200.pair(compute_features, normalize) -
-    the one line a recipe adds to state that the features go straight into the normaliser, which
-    then applies the top_db clamp on the fly (3 launches per step instead of 4)."""
+def build_frontend():
+    """The recipe's two modules, constructed as its YAML does; nothing else is needed."""
     import speechbrain_b200 as sb
 
-    fb, norm = sb.Fbank(n_mels=N_MELS), sb.InputNormalization(norm_type="sentence")
-    if paired:
-        sb.pair(fb, norm)
-    return fb, norm
+    return sb.Fbank(n_mels=N_MELS), sb.InputNormalization(norm_type="sentence")
 
 
 def frontend_step(fb, norm, wav, lengths):
-    """The public API a recipe's compute_forward calls (train.py:66-68)."""
+    """What an unmodified recipe's compute_forward calls (LibriSpeech/ASR/transformer/train.py:
+    66-68): feats = compute_features(wavs); feats = normalize(feats, wav_lens)."""
     return norm(fb(wav), lengths)
 
 
@@ -277,8 +264,8 @@ def kernel_only_ms(fb, pool, reps):
     from speechbrain_b200 import ops
 
     tables = fb._frontend_tables()
-    # tile_stats=True: the variant the timed step launches (emits the tile records, needs no
-    # utt_max memset)
+    # tile_stats=True: the variant the timed step launches (finisher mode: clamp + prefix records
+    # inside the launch)
     for wav, _ in pool[:2]:
         ops.fbank_forward(tables, wav, tile_stats=True)
     torch.cuda.synchronize()
@@ -360,6 +347,59 @@ def time_e2e(fb, norm, host_pool, steps, warmup, barrier, padded=False):
     return dt, int(h2d), 4 * BATCH * T * N_MELS, float(h_out[(warmup + steps - 1) & 1].abs().mean())
 
 
+def time_cfg5(dev, world, rank, steps, barrier, max_over_ranks):
+    """BASELINE.json configs[4]: the sharded large-batch frontend - Fbank(80) + InputNormalization(
+    "global") in training mode (epoch 0: the running-average branch runs from the second step on)
+    on 128 x 30 s PER GPU.  With more than one rank the statistics are all-reduced over NCCL
+    (sync_stats=True: the path's ONE collective, 2F+1 = 161 floats per step; reference semantics:
+    processing/features.py:1083-1114 on the concatenated global batch) and the same loop is also
+    timed without the sync.  Eager launches (the collective is torch.distributed's), CUDA events,
+    max over ranks; 2 x 246 MB input buffers alternate (> L2)."""
+    import speechbrain_b200 as sb
+
+    B5, S5 = 128, 30
+    L5 = S5 * SR
+    g = torch.Generator(device=dev).manual_seed(4321 + rank)
+    pool = []
+    for _ in range(2):
+        wav = torch.randn(B5, L5, device=dev, generator=g) * 0.1
+        lens = torch.linspace(0.6, 1.0, B5, device=dev)[torch.randperm(B5, device=dev, generator=g)]
+        wav *= torch.arange(L5, device=dev)[None, :] < torch.round(lens * L5)[:, None]
+        pool.append((wav, lens))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    out = {"workload": "cfg5: Fbank n_mels=80 + global InputNormalization (training, epoch 0), "
+                       "128 x 30 s @16 kHz per GPU", "steps": steps, "unit": "audio-s/s",
+           "parallelism": "utterance-sharded x%d, %s" % (
+               world, "NCCL all-reduce (sum) of 2F+1 = 161 floats per step" if world > 1
+               else "single rank: nothing to reduce")}
+    ms_by = {}
+    for sync in ([False, True] if world > 1 else [False]):
+        fb = sb.Fbank(n_mels=N_MELS)
+        norm = sb.InputNormalization(norm_type="global", sync_stats=sync).train()
+        for i in range(3):
+            norm(fb(pool[i & 1][0]), pool[i & 1][1], epoch=0)
+        barrier()
+        e0.record()
+        for i in range(steps):
+            y = norm(fb(pool[i & 1][0]), pool[i & 1][1], epoch=0)
+        e1.record()
+        torch.cuda.synchronize()
+        barrier()
+        ms = max_over_ranks(e0.elapsed_time(e1))
+        ms_by[sync] = ms / steps
+        key = "with_sync" if sync else "no_sync"
+        out[key] = {"value": world * B5 * S5 * steps / (ms / 1e3), "ms_per_step": ms / steps,
+                    "count": norm.count, "checksum": float(y[0, 0, :4].sum())}
+    if True in ms_by:
+        out["exposed_allreduce_us_per_step"] = (ms_by[True] - ms_by[False]) * 1e3
+        out["value"] = out["with_sync"]["value"]
+    else:
+        out["value"] = out["no_sync"]["value"]
+    alg = 4 * B5 * L5 + 4 * B5 * (1 + L5 // HOP) * N_MELS
+    out["hbm_frac_per_gpu"] = alg / (ms_by[max(ms_by)] / 1e3) / 1e9 / peaks()[0]
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -368,6 +408,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of CUDA graphs")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cfg5", action="store_true", help="skip the cfg5 (global norm + all-reduce) leg")
     ap.add_argument("--e2e-padded", action="store_true",
                     help="diagnostic: upload the zero-padded float32 batch instead of the ragged one")
     args = ap.parse_args()
@@ -424,18 +465,6 @@ def main():
     ms = max_over_ranks(e0.elapsed_time(e1))
     value = world * AUDIO_S_PER_STEP * args.steps / (ms / 1e3)
 
-    # ---- supplementary: the same modules WITHOUT pair() (recipe untouched: 4 launches) ----
-    fb_u, norm_u = build_frontend(paired=False)
-    u_steps = min(args.steps, 10 * POOL)
-    run_u, _outs_u = time_device_resident(fb_u, norm_u, pool, u_steps, args.warmup, not args.no_graph)
-    barrier()
-    e0.record()
-    run_u(u_steps)
-    e1.record()
-    torch.cuda.synchronize()
-    barrier()
-    ms_u = max_over_ranks(e0.elapsed_time(e1))
-
     # ---- dominant kernel alone -> roofline ------------------------------------
     k_ms = kernel_only_ms(fb, pool, reps=max(4, args.steps // POOL))
     peak, peak_src = peaks()
@@ -472,10 +501,13 @@ def main():
         "metric": METRIC, "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": dict(CONFIG, launch="eager" if args.no_graph else "CUDA graphs: %d consecutive steps (one per pool slot) per graph, remainder one step per graph" % POOL,
-                       parallelism="utterance-sharded x%d, no collective" % world,
-                       api="norm(fb(wav), lens) with speechbrain_b200.pair(fb, norm): the normaliser "
-                           "applies Fbank's top_db clamp on the fly"),
+        "config": CONFIG,
+        "run": {"launch": "eager" if args.no_graph else "CUDA graphs: %d consecutive steps (one per pool slot) per graph, remainder one step per graph" % POOL,
+                "parallelism": "utterance-sharded x%d, no collective on this config (sentence "
+                               "statistics are per utterance); the path's one collective is "
+                               "measured in the cfg5 key" % world,
+                "api": "feats = Fbank(n_mels=80)(wav); feats = InputNormalization('sentence')(feats, "
+                       "lens) - the unmodified recipe flow, no extra call"},
         "clocks": clocks.summary(),
         "e2e": {"value": e2e_value, "unit": "audio-s/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "steps": e2e_steps,
@@ -484,21 +516,20 @@ def main():
                         "-> Fbank+norm via public API -> D2H features; copies pipelined on "
                         "separate streams; padded float32 batch would be %d B" % (4 * BATCH * L)},
         "e2e_pcm16": e2e16,
-        "gpu_launches": 3 * args.steps,  # fbank400_v3 + norm_stats_tiles + norm_apply (clamp on the fly)
-        "unpaired": {"value": world * AUDIO_S_PER_STEP * u_steps / (ms_u / 1e3), "unit": "audio-s/s",
-                     "ms_per_step": ms_u / u_steps, "steps": u_steps, "gpu_launches_per_step": 4,
-                     "note": "same modules without speechbrain_b200.pair(): Fbank launches its own "
-                             "clamp_tiles kernel"},
-        "roofline": {"bound": "hbm", "kernel": "v3::fbank400_v3_kernel (fused frame+window+rFFT400+power+mel+dB+tile records)",
+        # fbank400_v3 (FFT + mel + dB + clamp + prefix records) + norm_stats_prefix + norm_apply
+        "gpu_launches": 3 * args.steps,
+        "roofline": {"bound": "hbm", "kernel": "v3::fbank400_v3_kernel (fused frame+window+rFFT400+power+mel+dB+top_db clamp+prefix records)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "peak_source": peak_src, "us_per_launch": k_ms * 1e3,
                      "alg_bytes_per_launch": k_bytes, "traffic": traffic,
                      "step_frac": (ALG_BYTES_PER_STEP / (ms / args.steps / 1e3) / 1e9) / peak},
     }
+    if not args.no_cfg5:
+        line["cfg5"] = time_cfg5(dev, world, rank, max(3, min(args.steps, 10)), barrier, max_over_ranks)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        v, cores, sample, _ = time_cpu_port(8, reps=5)
+        v, cores, _ = time_cpu_port(steps=5)
         line["cpu_baseline"] = {"value": v, "unit": "audio-s/s", "cores": cores, "kind": "port",
-                                "sample": sample}
+                                "sample": CPU_SAMPLE}
     if rank == 0:
         print(json.dumps(line))
     if dist:

@@ -9,7 +9,9 @@
  *  - every pointer named d_* is a DEVICE pointer owned by the caller; h_* is host.
  *  - all tensors are contiguous float32 unless a stride argument is given.
  *  - `stream` is a cudaStream_t passed as void*; every call only enqueues work:
- *    no allocation, no synchronisation, no global mutable state (thread-safe).
+ *    no allocation, no synchronisation; thread-safe: no call reads state another call
+ *    wrote (the only process-wide data are immutable tables and a lock-free once-per-device
+ *    mark that an idempotent cudaFuncSetAttribute has been made).
  *  - return value: 0 ok; <0 invalid argument (SBFE_E_*); >0 a cudaError_t.
  *  - frame count T = 1 + L / hop (zero centre padding of n_fft/2 per side).
  */
@@ -22,7 +24,7 @@
 extern "C" {
 #endif
 
-#define SBFE_ABI_VERSION 7
+#define SBFE_ABI_VERSION 8
 
 #if defined(__GNUC__)
 #define SBFE_API __attribute__((visibility("default")))
@@ -84,14 +86,32 @@ SBFE_API int64_t sbfe_num_frames(int64_t n_samples, int32_t hop);
 SBFE_API int64_t sbfe_fbank_workspace_bytes(const sbfe_fbank_desc* desc, int64_t B, int64_t L);
 
 /* Fbank hot path = STFT.forward + spectral_magnitude(power=1) + Filterbank.forward
- * up to (not including) the per-utterance top_db clamp
- * (lobes/features.py:138-140; processing/features.py:133-188, 327-356, 490-551,
- * 691-702).  wav [B, L] (row stride wav_stride) -> out [B, T, M]; d_utt_max[b]
- * receives the key of max_{t,m} out[b] (must be zeroed by the caller first). */
+ * (lobes/features.py:138-140; processing/features.py:133-188, 327-356, 490-551, 691-712).
+ * wav [B, L] (row stride wav_stride) -> out [B, T, M].
+ *
+ * Two modes:
+ *  (a) d_tile_stats == NULL, d_sync == NULL: out holds the dB values WITHOUT the per-utterance
+ *      top_db clamp; d_utt_max[b] (zeroed by the caller first; may be NULL) receives the key of
+ *      max_{t,m} out[b] for a later clamp (sbfe_post_forward).  top_db is ignored.
+ *  (b) finisher mode, only where sbfe_fbank_tile_frames(desc) = R > 0 (fused n_fft 400 / hop 160
+ *      kernel): d_tile_stats = [B][ceil(T/R)] records of W = sbfe_fbank_tile_stats_floats(desc)
+ *      = 3*M + 4 words, d_sync = [B] uint32 counters that are ZERO on entry and zero again when
+ *      the call's work completes (the caller must not share them between calls that may be in
+ *      flight at the same time).  The CTA that completes an utterance's last tile finishes the
+ *      utterance inside the same launch: out IS top_db-clamped when the kernel ends
+ *      (x = max(x, max_b - top_db), features.py:706-710, the maximum taken over all T frames of
+ *      the padded utterance; top_db < 0: no clamp), and record j holds
+ *        [0, M)    mean  } of every feature column over the clamped frames [0, min(R (j+1), T))
+ *        [M, 2M)   M2    } (M2 = sum of squared deviations): PREFIX moments,
+ *        [2M, 3M)  the column minima of tile j before the clamp,
+ *        [3M]      max key of tile j, [3M+1] flags (bit 0: the tile's input was all zero).
+ *      sbfe_norm_stats_prefix / sbfe_norm_sentence_prefix turn these into InputNormalization
+ *      statistics for ANY valid length from one record and < R rows of out: no statistics pass
+ *      over the features, no clamp launch.  d_utt_max may be NULL. */
 SBFE_API int sbfe_fbank_forward(const sbfe_fbank_desc* desc, const float* d_wav, int64_t B, int64_t L,
                        int64_t wav_stride, float* d_out, sbfe_maxkey_t* d_utt_max,
-                       float* d_tile_stats, void* d_workspace, int64_t workspace_bytes,
-                       void* stream);
+                       float* d_tile_stats, uint32_t* d_sync, float top_db, void* d_workspace,
+                       int64_t workspace_bytes, void* stream);
 
 /* Ragged ingest (the step before the path: speechbrain/dataio/batch.py:20-190 pads on the CPU
  * and copies the padding over PCIe).  The batch arrives as ONE packed buffer holding only the
@@ -103,7 +123,7 @@ SBFE_API int sbfe_fbank_forward(const sbfe_fbank_desc* desc, const float* d_wav,
 SBFE_API int sbfe_fbank_forward_ragged(const sbfe_fbank_desc* desc, const float* d_packed,
                               const int64_t* d_offsets, const int32_t* d_nsamples, int64_t B,
                               int64_t L, float* d_out, sbfe_maxkey_t* d_utt_max,
-                              float* d_tile_stats, void* stream);
+                              float* d_tile_stats, uint32_t* d_sync, float top_db, void* stream);
 
 /* The same with 16-bit PCM samples (what a .wav / .flac file holds; the reference converts them
  * to float32 on the CPU, dataio/dataio.py read_audio via torchaudio.load, and ships 4 bytes per
@@ -114,43 +134,28 @@ SBFE_API int sbfe_fbank_forward_ragged(const sbfe_fbank_desc* desc, const float*
 SBFE_API int sbfe_fbank_forward_ragged_pcm16(const sbfe_fbank_desc* desc, const int16_t* d_packed,
                                     const int64_t* d_offsets, const int32_t* d_nsamples,
                                     int64_t B, int64_t L, float scale, float* d_out,
-                                    sbfe_maxkey_t* d_utt_max, float* d_tile_stats, void* stream);
+                                    sbfe_maxkey_t* d_utt_max, float* d_tile_stats,
+                                    uint32_t* d_sync, float top_db, void* stream);
 
-/* Per-tile column statistics.  When sbfe_fbank_tile_frames(desc) = R > 0 (fused n_fft 400 /
- * hop 160 kernel), sbfe_fbank_forward can also write d_tile_stats: [B][ceil(T/R)] records of
- * W = sbfe_fbank_tile_stats_floats(desc) = 3*M + 4 words: [3][M] floats = {mean, M2 = sum of
- * squared deviations, min} of every feature column over the frames of the R-frame tile
- * (un-clamped values), then the tile's max key (sbfe_maxkey_t) and 3 zero words; the maximum
- * of the keys over an utterance's records is the utterance maximum.  Pass NULL to skip.  With tile records
- * d_utt_max may be NULL in sbfe_fbank_forward (no atomics, no memset) and in the two consumers
- * below (the floor is rebuilt from the keys).  They let
- *   sbfe_clamp_tiles       apply the top_db clamp (features.py:706-710) in place, touching
- *                          only tiles that hold a value below the floor, and
- *   sbfe_norm_stats_tiles  produce the InputNormalization statistics (features.py:1020-1031,
- *                          1120-1145; same contract as sbfe_norm_stats) without a pass over x:
- *                          only tiles cut by the valid length or holding clamped values are
- *                          re-read.
- * flags = SBFE_STATS_BESIDE_CLAMP: the caller states that the launch made on `stream` just
- * before this one is sbfe_clamp_tiles on the same d_x with the same records and top_db.  The
- * statistics do not depend on whether that clamp has landed yet (every value is read through
- * max(., floor)), so the kernel then runs beside it instead of after it; stream order for
- * everything that FOLLOWS is unchanged.  0 is always correct.
- * d_utt_max_out ([B], optional, may be NULL) receives the utterance maxima rebuilt from the
- * records.  With them sbfe_norm_apply can apply the top_db clamp on the fly, so a caller that
- * normalises d_x in place right away (InputNormalization "sentence" / "speaker") may pass the
- * UN-clamped output of sbfe_fbank_forward here and skip sbfe_clamp_tiles altogether: every
- * statistic is taken through max(., floor) whether or not the clamp was ever launched. */
-#define SBFE_STATS_BESIDE_CLAMP 1
 SBFE_API int32_t sbfe_fbank_tile_frames(const sbfe_fbank_desc* desc);
 SBFE_API int32_t sbfe_fbank_tile_stats_floats(const sbfe_fbank_desc* desc);
-SBFE_API int sbfe_clamp_tiles(float* d_x, int64_t B, int64_t T, int32_t F,
-                     const sbfe_maxkey_t* d_utt_max, float top_db, const float* d_tile_stats,
-                     int32_t tile_frames, void* stream);
-SBFE_API int sbfe_norm_stats_tiles(const float* d_x, const float* d_lengths, int64_t B, int64_t T,
-                          int32_t F, int32_t mean_norm, int32_t std_norm, float eps,
-                          const sbfe_maxkey_t* d_utt_max, float top_db,
-                          const float* d_tile_stats, int32_t tile_frames, float* d_mean,
-                          float* d_std, int32_t flags, sbfe_maxkey_t* d_utt_max_out, void* stream);
+
+/* InputNormalization statistics (features.py:1020-1031, 1120-1145; same contract as
+ * sbfe_norm_stats) from the prefix records of a finisher-mode sbfe_fbank_forward whose output
+ * d_x has not been modified since: mean / std [B, F] over the first rint(lengths[b] * T) frames =
+ * record (n / R - 1) merged with the n % R rows of the tile the valid length cuts. */
+SBFE_API int sbfe_norm_stats_prefix(const float* d_x, const float* d_lengths, int64_t B, int64_t T,
+                           int32_t F, int32_t mean_norm, int32_t std_norm, float eps,
+                           const float* d_tile_stats, int32_t tile_frames, float* d_mean,
+                           float* d_std, void* stream);
+/* The same followed by out = (x - mean_b) / std_b over all T frames ("sentence" mode,
+ * features.py:1020-1035; in place when d_out == d_x): the statistics kernel and the
+ * normalisation kernel are launched back to back by this call, the second one fetching x while
+ * the first finishes.  d_mean / d_std [B, F] are scratch the caller provides (and may read). */
+SBFE_API int sbfe_norm_sentence_prefix(const float* d_x, const float* d_lengths, int64_t B, int64_t T,
+                              int32_t F, int32_t mean_norm, int32_t std_norm, float eps,
+                              const float* d_tile_stats, int32_t tile_frames, float* d_mean,
+                              float* d_std, float* d_out, void* stream);
 
 /* STFT.forward for [B, L] input (processing/features.py:133-188):
  * out [B, T, bins, 2] (re, im), or, with power_only != 0, [B, T, bins] = re^2+im^2. */
@@ -213,17 +218,10 @@ SBFE_API int sbfe_norm_update(const float* d_cur, int32_t F, int32_t first, floa
 
 /* out = (x - mean) / std (processing/features.py:1035, 1088, 1116).
  * per_utt != 0: mean/std are [B, F]; else [F] shared.  In place when out == x.
- * d_utt_max != NULL applies the top_db clamp to x first.
- * flags = SBFE_APPLY_X_STABLE: the caller states that the launch made on `stream` just before
- * this one is a statistics call of this library on the same d_x (sbfe_norm_stats_tiles without
- * SBFE_STATS_BESIDE_CLAMP, sbfe_norm_stats, sbfe_norm_speaker_update, ...: one that reads d_x
- * at most).  The kernel then requests its share of d_x before it waits for that launch, so
- * the reads overlap the statistics; d_mean / d_std / d_utt_max are read after it.  0 is always
- * correct. */
-#define SBFE_APPLY_X_STABLE 1
+ * d_utt_max != NULL applies the top_db clamp to x first. */
 SBFE_API int sbfe_norm_apply(const float* d_x, int64_t B, int64_t T, int32_t F, const float* d_mean,
                     const float* d_std, int32_t per_utt, const sbfe_maxkey_t* d_utt_max,
-                    float top_db, float* d_out, int32_t flags, void* stream);
+                    float top_db, float* d_out, void* stream);
 
 /* ---- next row: speaker-mode statistics (processing/features.py:1037-1081) --
  * The speaker dictionary stays on the host (ids -> rows of d_table_mean / d_table_std [rows, F]);

@@ -1,5 +1,6 @@
 """Cumulative timing of the cfg2 step's kernels (CUDA graphs over 8 rotating inputs):
-fbank | +clamp_tiles | +norm_stats_tiles | +norm_apply.  python profiles/stepbench.py"""
+fused kernel without / with its finisher | + statistics from the prefix records | + apply.
+python profiles/stepbench.py"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -18,25 +19,23 @@ tab = fb._frontend_tables()
 
 
 def step(w, upto):
-    feats, _, ts = ops.fbank_forward(tab, w, tile_stats=True)
-    if 1 <= upto <= 3:
-        ops.clamp_tiles(feats, ts, 80.0)
+    if upto == 0:     # mode (a): un-clamped output, utterance maxima via atomics (needs a memset)
+        return ops.fbank_forward(tab, w)[0]
+    feats, _, ts = ops.fbank_forward(tab, w, tile_stats=True, top_db=80.0)   # finisher mode
     if upto == 2:
-        mean, std = ops.norm_stats_tiles(feats, lens, ts)
+        ops.norm_stats_prefix(feats, lens, ts)
     if upto == 3:
-        mean, std = ops.norm_stats_tiles(feats, lens, ts)
-        ops.norm_apply(feats, mean, std, per_utt=True, out=feats, stats_mark=ops.stats_launch_mark(feats))
-    if upto == 4:   # pair(): no clamp launch, the normalisation clamps on the fly
-        ts.top_db = 80.0
-        mean, std, keys = ops.norm_stats_tiles(feats, lens, ts, want_max=True)
-        ops.norm_apply(feats, mean, std, per_utt=True, out=feats, utt_max=keys, top_db=80.0,
-                       stats_mark=ops.stats_launch_mark(feats))
+        ops.norm_sentence_prefix(feats, lens, ts, out=feats)
+    if upto == 4:     # the statistics the generic way (no records): 2 launches + apply
+        mean, std = ops.norm_stats(feats, lens)
+        ops.norm_apply(feats, mean, std, per_utt=True, out=feats)
     return feats
 
 
 prev = 0.0
-for upto, name in enumerate(["fbank400_v3 (+tile records)", "+ clamp_tiles", "+ norm_stats_tiles", "+ norm_apply",
-                             "paired: fbank + stats + apply(clamp)"]):
+for upto, name in enumerate(["fbank400_v3, no finisher (+memset)", "fbank400_v3 finisher (clamp+prefix)",
+                             "+ norm_stats_prefix", "+ stats_prefix + norm_apply (the step)",
+                             "finisher + generic stats + apply"]):
     for w in pool[:2]:
         step(w, upto)
     torch.cuda.synchronize()
@@ -55,5 +54,5 @@ for upto, name in enumerate(["fbank400_v3 (+tile records)", "+ clamp_tiles", "+ 
     e1.record()
     torch.cuda.synchronize()
     us = e0.elapsed_time(e1) / 160 * 1e3
-    print("%-30s %7.2f us/step  (+%.2f)" % (name, us, us - prev))
+    print("%-42s %7.2f us/step  (%+.2f)" % (name, us, us - prev))
     prev = us

@@ -48,14 +48,16 @@ SIGNATURES = {
     "sbfe_error_string": (C.c_char_p, [C.c_int]),
     "sbfe_num_frames": (_I64, [_I64, _I32]),
     "sbfe_fbank_workspace_bytes": (_I64, [_DESC, _I64, _I64]),
-    "sbfe_fbank_forward": (C.c_int, [_DESC, _P, _I64, _I64, _I64, _P, _P, _P, _P, _I64, _P]),
-    "sbfe_fbank_forward_ragged": (C.c_int, [_DESC, _P, _P, _P, _I64, _I64, _P, _P, _P, _P]),
-    "sbfe_fbank_forward_ragged_pcm16": (C.c_int, [_DESC, _P, _P, _P, _I64, _I64, _F, _P, _P, _P, _P]),
+    "sbfe_fbank_forward": (C.c_int, [_DESC, _P, _I64, _I64, _I64, _P, _P, _P, _P, _F, _P, _I64, _P]),
+    "sbfe_fbank_forward_ragged": (C.c_int, [_DESC, _P, _P, _P, _I64, _I64, _P, _P, _P, _P, _F, _P]),
+    "sbfe_fbank_forward_ragged_pcm16": (C.c_int, [_DESC, _P, _P, _P, _I64, _I64, _F, _P, _P, _P, _P,
+                                                  _F, _P]),
     "sbfe_fbank_tile_frames": (_I32, [_DESC]),
     "sbfe_fbank_tile_stats_floats": (_I32, [_DESC]),
-    "sbfe_clamp_tiles": (C.c_int, [_P, _I64, _I64, _I32, _P, _F, _P, _I32, _P]),
-    "sbfe_norm_stats_tiles": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, _I32, _F, _P, _F, _P, _I32,
-                                        _P, _P, _I32, _P, _P]),
+    "sbfe_norm_stats_prefix": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, _I32, _F, _P, _I32, _P, _P,
+                                         _P]),
+    "sbfe_norm_sentence_prefix": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, _I32, _F, _P, _I32, _P,
+                                            _P, _P, _P]),
     "sbfe_stft_forward": (C.c_int, [_DESC, _P, _I64, _I64, _I64, _P, _I32, _P]),
     "sbfe_istft_workspace_bytes": (_I64, [_I64, _I64, _I32]),
     "sbfe_istft_forward": (C.c_int, [_P, _I64, _I64, _I32, _I32, _P, _I32, _I64, _P, _P, _I64, _P]),
@@ -68,7 +70,7 @@ SIGNATURES = {
                                   _I64, _P]),
     "sbfe_norm_reduce": (C.c_int, [_P, _P, _I64, _I32, _P, _P]),
     "sbfe_norm_update": (C.c_int, [_P, _I32, _I32, _F, _P, _P, _P]),
-    "sbfe_norm_apply": (C.c_int, [_P, _I64, _I64, _I32, _P, _P, _I32, _P, _F, _P, _I32, _P]),
+    "sbfe_norm_apply": (C.c_int, [_P, _I64, _I64, _I32, _P, _P, _I32, _P, _F, _P, _P]),
     "sbfe_norm_speaker_update": (C.c_int, [_P, _P, _I64, _I32, _P, _P, _P, _P, _P, _P, _P, _P]),
     "sbfe_specaugment_forward": (C.c_int, [_P, _I64, _I64, _I32, _I32, _I32, _I32, _P, _P, _I32, _P,
                                            _P, _I32, _P, _F, _P, _P]),
@@ -76,6 +78,7 @@ SIGNATURES = {
     "sbfe_mean": (C.c_int, [_P, _I64, _P, _P, _I64, _P]),
 }
 
+ABI_VERSION = 8
 _lock = threading.Lock()
 _lib = None
 
@@ -108,17 +111,12 @@ def lib():
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(handle, name)
             fn.restype, fn.argtypes = res, args
-        if handle.sbfe_abi_version() != 7:
+        if handle.sbfe_abi_version() != ABI_VERSION:
             raise SbfeUnavailable("libsbfe.so ABI version mismatch")
         _lib = handle
         return _lib
 
 
-launches = 0  # library launches made by this process (ops.py: what was launched last)
-
-
 def check(rc):
-    global launches
-    launches += 1
     if rc != 0:
         raise RuntimeError("sbfe call failed (%d): %s" % (rc, lib().sbfe_error_string(rc).decode()))

@@ -95,7 +95,7 @@ inline int check_last(void) {
 // waits before it exits), and when a kernel starts, everything before its DIRECT predecessor
 // has completed (the predecessor triggered only after its own wait).  The second one lets a
 // kernel that reads nothing its direct predecessor writes run beside it and wait at its END
-// instead (norm_stats_tiles_kernel next to clamp_tiles_kernel, norm.cu).  Kernels of other
+// instead (norm_apply_kernel<., true> behind norm_stats_prefix_kernel, norm.cu).  Kernels of other
 // libraries never trigger early, so mixing with them degrades to ordinary stream order.
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() {

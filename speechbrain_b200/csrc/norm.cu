@@ -94,13 +94,7 @@ __global__ void norm_stats_final_kernel(const float* __restrict__ x,
   stdv[i] = std_norm ? sd : 1.f;
 }
 
-// ---- statistics from the per-tile column partials of the fused Fbank kernel ---------------
-// tile_stats [B][tiles][3][F] = mean, M2, min of every column over the tile's existing
-// frames (UN-clamped values).  A tile's partial is used as is when all of its frames are
-// inside the utterance's valid length and nothing in that column is below the top_db
-// floor; otherwise (at most the one tile straddling n_b, plus tiles with clamped values)
-// the column is recomputed from x.  Partials are merged with Chan's update (float: <= a few
-// hundred well-conditioned merges, error ~1e-6 relative).
+// Partial moments merged with Chan's update (float: <= a few hundred well-conditioned merges).
 struct Moments {
   float n, mean, m2;
 };
@@ -112,178 +106,97 @@ __device__ __forceinline__ void merge(Moments& a, float nb, float mb, float m2b)
   a.n = n;
 }
 
-constexpr int kTileStatCols = 32;     // feature columns per CTA (one 128-byte row segment)
-constexpr int kTileStatGroups = 16;   // tile groups per CTA
-constexpr int kTileStatThreads = kTileStatCols * kTileStatGroups;
 
-// grid = (ceil(F / 32), B); thread = (column, tile group)
-// beside_clamp: the kernel launched just before this one is clamp_tiles_kernel on the same x
-// (or anything else that leaves lengths and the records alone and writes x only as
-// x = max(x, floor) with the same floor).  Every read of x below goes through fmaxf(., floor),
-// which gives the same value before and after that write, so this kernel does not wait for
-// it: it runs beside the clamp and waits at its end, which keeps completion transitive for
-// whatever follows (common.cuh).
-__global__ void __launch_bounds__(kTileStatThreads)
-norm_stats_tiles_kernel(const float* x, const float* __restrict__ lengths, int64_t T,
-                        int F, int tile, int tiles, const float* __restrict__ tile_stats,
-                        const sbfe_maxkey_t* __restrict__ utt_max, float top_db, int mean_norm,
-                        int std_norm, float eps, float* __restrict__ mean, float* __restrict__ stdv,
-                        int beside_clamp, sbfe_maxkey_t* __restrict__ utt_max_out) {
-  if (!beside_clamp) {
-    pdl_wait();
-    pdl_launch_dependents();
-  }
-  __shared__ float s_red[3 * kTileStatThreads];
-  const int64_t b = blockIdx.y;
-  const int tx = threadIdx.x % kTileStatCols, ty = threadIdx.x / kTileStatCols;
-  const int f = blockIdx.x * kTileStatCols + tx;
-  const float* xb = x + b * T * F;
+// ---- statistics from the PREFIX records of the fused Fbank kernel ----------------------------
+// After sbfe_fbank_forward in finisher mode (fbank400_v3.cu: finish_utterance) record j of an
+// utterance holds {mean[F], M2[F]} of every column over the (already clamped) frames
+// [0, min(tile (j + 1), T)).  The statistics over the first n frames are then one record merged
+// (Chan) with the n % tile rows of the tile the valid length cuts: <= tile - 1 rows of x instead
+// of a pass over T rows, and no dependence on the batch.  Replaces the per-sentence Python loop of
+// processing/features.py:1020-1031 and _compute_current_stats :1120-1145.
+//
+// Whole CTA must call.  Thread = (column, row group); `s_red`: 3 * blockDim.x floats.  Writes
+// s_mean[F] / s_std[F] (shared or global) and ends with a barrier.
+__device__ __forceinline__ void prefix_stats_block(const float* __restrict__ xb, int n, int T, int F,
+                                                   int tile, int tiles,
+                                                   const float* __restrict__ tsb, int mean_norm,
+                                                   int std_norm, float eps, float* s_mean,
+                                                   float* s_std, float* s_red) {
+  const int nthr = blockDim.x;
+  const int CW = F < nthr ? F : nthr;            // columns per pass
+  const int G = nthr / CW;                       // row groups
+  const int col = threadIdx.x % CW, grp = threadIdx.x / CW;
   const size_t rec = tile_rec_words(F);
-  const float* tsb = tile_stats + (size_t)b * tiles * rec;
-  // the first kSpec records of this thread are requested before the valid length and the
-  // floor are known (which of them count is decided afterwards): one memory round trip for
-  // length, keys and records instead of two
-  constexpr int kSpec = 4;
-  float pm[kSpec], pq[kSpec], pn[kSpec];
-#pragma unroll
-  for (int k = 0; k < kSpec; ++k) {
-    const int j = ty + k * kTileStatGroups;
-    if (f < F && j < tiles) {
-      const float* ts = tsb + (size_t)j * rec + f;
-      pm[k] = __ldg(ts);
-      pq[k] = __ldg(ts + F);
-      pn[k] = __ldg(ts + 2 * F);
-    }
-  }
-  // the tile keys (-> top_db floor) are requested in the same round trip as well
-  __shared__ unsigned s_max_key;
-  unsigned my_key = 0u;
-  if (utt_max == nullptr) {
-    if (threadIdx.x == 0) s_max_key = 0u;
-    for (int i = threadIdx.x; i < tiles; i += kTileStatThreads) {
-      const unsigned k2 = __ldg(reinterpret_cast<const unsigned*>(tsb) + (size_t)i * rec + 3 * F);
-      my_key = k2 > my_key ? k2 : my_key;
-    }
-  }
-  const int n = valid_frames(lengths, b, T);
-  // tiles whose existing frames are all valid: [0, n / tile), plus the short last tile when
-  // the whole utterance is valid
+  // tiles whose existing frames are all valid: [0, whole)
   const int whole = (n >= T) ? tiles : n / tile;
-  // rows of the tile cut by the valid length, spread over the tile groups (at most
-  // ceil((tile - 1) / 16) per thread): requested as soon as the length is here, so that they
-  // fly while the floor is being rebuilt
   const int r_cut = whole * tile;
-  const bool cut = f < F && whole < tiles && r_cut < n;
-  constexpr int kCutRows = 2;
-  float cv[kCutRows], pivot = 0.f;
-  if (cut) {
-    const float* col = xb + (int64_t)r_cut * F + f;
-    pivot = col[0];
-#pragma unroll
-    for (int i = 0; i < kCutRows; ++i) {
-      const int r = ty + i * kTileStatGroups;
-      cv[i] = (r < n - r_cut) ? col[(int64_t)r * F] : NAN;
-    }
-  }
-  unsigned max_key = 0u;
-  float floor_b;
-  if (utt_max != nullptr) {
-    floor_b = clamp_floor(utt_max, b, top_db);
-  } else {  // block maximum of the keys (common.cuh: block_floor_from_tiles, loads hoisted)
-    __syncthreads();
-    my_key = __reduce_max_sync(0xffffffffu, my_key);
-    if ((threadIdx.x & 31) == 0 && my_key) atomicMax(&s_max_key, my_key);
-    __syncthreads();
-    max_key = s_max_key;
-    floor_b = max_key ? max_key_decode(max_key) - top_db : -INFINITY;
-  }
-  // the utterance maximum rebuilt from the tile keys, for a consumer that clamps on the fly
-  // (norm_apply_kernel) instead of after a clamp_tiles launch
-  if (utt_max_out != nullptr && blockIdx.x == 0 && threadIdx.x == 0)
-    utt_max_out[b] = utt_max ? utt_max[b] : max_key;
-  Moments acc{0.f, 0.f, 0.f};
-  if (f < F) {
+  const int ncut = (whole < tiles && r_cut < n) ? n - r_cut : 0;   // rows of the cut tile
+  const float na = whole > 0 ? (float)(r_cut < T ? r_cut : T) : 0.f;
+  for (int f0 = 0; f0 < F; f0 += CW) {
+    const int f = f0 + col;
+    const bool live = f < F && grp < G;
+    float pm = 0.f, pq = 0.f, s1 = 0.f, s2 = 0.f, pivot = 0.f;
     int c = 0;
-    auto take = [&](int j, float t_mean, float t_m2, float t_min) {
-      const int r_lo = j * tile;
-      const int cnt = T - r_lo < tile ? (int)(T - r_lo) : tile;
-      if (t_min >= floor_b) {
-        merge(acc, (float)cnt, t_mean, t_m2);
-      } else {  // clamped values inside the valid part: rare, recompute the column
-        const float* col = xb + (int64_t)r_lo * F + f;
-        float s = 0.f;
-        for (int r = 0; r < cnt; ++r) s += fmaxf(col[(int64_t)r * F], floor_b);
-        const float m = s / (float)cnt;
-        float q = 0.f;
-        for (int r = 0; r < cnt; ++r) {
-          const float d = fmaxf(col[(int64_t)r * F], floor_b) - m;
-          q = fmaf(d, d, q);
-        }
-        merge(acc, (float)cnt, m, q);
+    if (live) {
+      if (grp == 0 && whole > 0) {
+        const float* ts = tsb + (size_t)(whole - 1) * rec + f;
+        pm = __ldg(ts);
+        pq = __ldg(ts + F);
       }
-    };
-#pragma unroll
-    for (int k = 0; k < kSpec; ++k) {
-      const int j = ty + k * kTileStatGroups;
-      if (j < whole) take(j, pm[k], pq[k], pn[k]);
-    }
-    for (int j = ty + kSpec * kTileStatGroups; j < whole; j += kTileStatGroups) {
-      const float* ts = tsb + (size_t)j * rec + f;
-      take(j, __ldg(ts), __ldg(ts + F), __ldg(ts + 2 * F));
-    }
-    if (cut) {  // sums about the cut tile's first row
-      const float* col = xb + (int64_t)r_cut * F + f;
-      pivot = fmaxf(pivot, floor_b);
-      float s1 = 0.f, s2 = 0.f;
-#pragma unroll
-      for (int i = 0; i < kCutRows; ++i) {
-        if (ty + i * kTileStatGroups < n - r_cut) {
-          const float d = fmaxf(cv[i], floor_b) - pivot;
+      if (ncut > 0) {
+        const float* colp = xb + (size_t)r_cut * F + f;
+        pivot = colp[0];
+        for (int r = grp; r < ncut; r += G) {
+          const float d = colp[(size_t)r * F] - pivot;
           s1 += d;
           s2 = fmaf(d, d, s2);
           ++c;
         }
       }
-      for (int r = ty + kCutRows * kTileStatGroups; r < n - r_cut; r += kTileStatGroups, ++c) {
-        const float d = fmaxf(col[(int64_t)r * F], floor_b) - pivot;  // tile > 32 rows only
-        s1 += d;
-        s2 = fmaf(d, d, s2);
-      }
-      if (c > 0) {
-        const float mloc = s1 / (float)c;
-        merge(acc, (float)c, pivot + mloc, fmaxf(fmaf(-mloc, s1, s2), 0.f));
-      }
     }
-  }
-  // tree merge over the 16 tile groups (4 levels instead of a 15-long dependent chain)
-  float* s_n = s_red;
-  float* s_m = s_red + kTileStatThreads;
-  float* s_q = s_red + 2 * kTileStatThreads;
-#pragma unroll
-  for (int half = kTileStatGroups / 2; half >= 1; half >>= 1) {
-    if (ty >= half && ty < 2 * half) {
-      s_n[threadIdx.x] = acc.n;
-      s_m[threadIdx.x] = acc.mean;
-      s_q[threadIdx.x] = acc.m2;
+    if (G > 1) {
+      s_red[threadIdx.x] = s1;
+      s_red[nthr + threadIdx.x] = s2;
+      __syncthreads();
+      if (live && grp == 0)
+        for (int g = 1; g < G; ++g) {
+          s1 += s_red[g * CW + col];
+          s2 += s_red[nthr + g * CW + col];
+        }
+    }
+    if (live && grp == 0) {
+      Moments acc{na, pm, pq};
+      if (ncut > 0) {
+        const float mloc = s1 / (float)ncut;
+        merge(acc, (float)ncut, pivot + mloc, fmaxf(fmaf(-mloc, s1, s2), 0.f));
+      }
+      // n == 0: mean of an empty slice is NaN, n == 1: unbiased std is NaN (torch)
+      const float m = (acc.n > 0.f) ? acc.mean : NAN;
+      float sd = (acc.n > 1.f) ? sqrtf(fmaxf(acc.m2, 0.f) / (acc.n - 1.f)) : NAN;
+      if (sd == sd) sd = fmaxf(sd, eps);  // torch.max propagates NaN
+      s_mean[f] = mean_norm ? m : 0.f;
+      s_std[f] = std_norm ? sd : 1.f;
     }
     __syncthreads();
-    if (ty < half) {
-      const int o = threadIdx.x + half * kTileStatCols;
-      merge(acc, s_n[o], s_m[o], s_q[o]);
-    }
+    (void)c;
   }
-  if (ty == 0 && f < F) {
-    // n == 0: mean of an empty slice is NaN, n == 1: unbiased std is NaN (torch)
-    const float m = (acc.n > 0.f) ? acc.mean : NAN;
-    float sd = (acc.n > 1.f) ? sqrtf(fmaxf(acc.m2, 0.f) / (acc.n - 1.f)) : NAN;
-    if (sd == sd) sd = fmaxf(sd, eps);  // torch.max propagates NaN
-    mean[b * F + f] = mean_norm ? m : 0.f;
-    stdv[b * F + f] = std_norm ? sd : 1.f;
-  }
-  if (beside_clamp) {
-    pdl_wait();
-    pdl_launch_dependents();
-  }
+}
+
+
+// mean / std [B, F] from the prefix records: grid = B
+__global__ void __launch_bounds__(kNormThreads)
+norm_stats_prefix_kernel(const float* __restrict__ x, const float* __restrict__ lengths, int64_t T,
+                         int F, int tile, int tiles, const float* __restrict__ tile_stats,
+                         int mean_norm, int std_norm, float eps, float* __restrict__ mean,
+                         float* __restrict__ stdv) {
+  pdl_wait();
+  pdl_launch_dependents();
+  __shared__ float s_red[3 * kNormThreads];
+  const int64_t b = blockIdx.x;
+  const int n = valid_frames(lengths, b, T);
+  prefix_stats_block(x + b * T * F, n, (int)T, F, tile, tiles,
+                     tile_stats + (size_t)b * tiles * tile_rec_words(F), mean_norm, std_norm, eps,
+                     mean + b * F, stdv + b * F, s_red);
 }
 
 // grid = ceil(F / 32) CTAs of 32 columns x 8 utterance groups
@@ -335,19 +248,20 @@ __global__ void norm_update_kernel(const float* __restrict__ cur, int F, int fir
 // out = (max(x, floor_b) - mean) / std.  VEC = 4 when F % 4 == 0 and 16 B aligned.
 // An utterance is treated as a flat array of T*F/VEC vectors; a CTA takes kApplyIters
 // consecutive blocks of kNormThreads vectors, all loads issued before the first store.
+// X_STABLE (set only by launch_norm_sentence_prefix below, which launches the statistics kernel
+// and this one back to back itself): the direct predecessor in the stream does not write x and
+// everything before it had completed when it let this kernel start (common.cuh) - the vectors
+// of x are then requested BEFORE the wait and fly while the statistics finish; mean / std are
+// read after it.
 constexpr int kApplyIters = 8;
 
-template <int VEC>
+template <int VEC, bool X_STABLE>
 __global__ void __launch_bounds__(kNormThreads)
 norm_apply_kernel(const float* x, int64_t T, int F, const float* __restrict__ mean,
                   const float* __restrict__ stdv, int per_utt,
                   const sbfe_maxkey_t* __restrict__ utt_max, float top_db, float* out,
-                  unsigned chunks, int x_stable) {
-  // x_stable: the launch directly before this one does not write x (it produces the
-  // statistics), and whatever wrote x completed before that launch triggered this one
-  // (common.cuh) - the vectors of x are then requested BEFORE the wait and fly while the
-  // statistics kernel finishes; mean / std / utt_max are read after it
-  if (!x_stable) {
+                  unsigned chunks) {
+  if (!X_STABLE) {
     pdl_wait();
     pdl_launch_dependents();
   }
@@ -362,58 +276,46 @@ norm_apply_kernel(const float* x, int64_t T, int F, const float* __restrict__ me
   int col = (int)(i0 % FV);
   const int dcol = kNormThreads % FV;
   float4 v4[VEC == 4 ? kApplyIters : 1];
-  if (VEC == 4) {
+  float v1[VEC == 4 ? 1 : kApplyIters];
 #pragma unroll
-    for (int k = 0; k < kApplyIters; ++k) {
-      const int64_t i = i0 + (int64_t)k * kNormThreads;
-      if (i < nvec) v4[k] = *reinterpret_cast<const float4*>(xb + 4 * i);
+  for (int k = 0; k < kApplyIters; ++k) {
+    const int64_t i = i0 + (int64_t)k * kNormThreads;
+    if (i < nvec) {
+      if (VEC == 4) v4[k] = *reinterpret_cast<const float4*>(xb + 4 * i);
+      else v1[k] = xb[i];
     }
   }
-  if (x_stable) {
+  if (X_STABLE) {
     pdl_wait();
     pdl_launch_dependents();
   }
   const float* m = mean + (per_utt ? b * F : 0);
   const float* s = stdv + (per_utt ? b * F : 0);
   for (int f = threadIdx.x; f < F; f += kNormThreads) {
-    s_ms[f] = __ldg(m + f);
-    s_ms[F + f] = __ldg(s + f);
+    s_ms[f] = __ldcg(m + f);
+    s_ms[F + f] = __ldcg(s + f);
   }
   const float floor_b = clamp_floor(utt_max, b, top_db);
-  if (VEC == 4) {
-    float4 (&v)[VEC == 4 ? kApplyIters : 1] = v4;
-    __syncthreads();
+  __syncthreads();
 #pragma unroll
-    for (int k = 0; k < kApplyIters; ++k) {
-      const int64_t i = i0 + (int64_t)k * kNormThreads;
-      if (i < nvec) {
+  for (int k = 0; k < kApplyIters; ++k) {
+    const int64_t i = i0 + (int64_t)k * kNormThreads;
+    if (i < nvec) {
+      if (VEC == 4) {
         const float4 mm = *reinterpret_cast<const float4*>(s_ms + 4 * col);
         const float4 ss = *reinterpret_cast<const float4*>(s_ms + F + 4 * col);
         float4 r;
-        r.x = (fmaxf(v[k].x, floor_b) - mm.x) / ss.x;
-        r.y = (fmaxf(v[k].y, floor_b) - mm.y) / ss.y;
-        r.z = (fmaxf(v[k].z, floor_b) - mm.z) / ss.z;
-        r.w = (fmaxf(v[k].w, floor_b) - mm.w) / ss.w;
+        r.x = (fmaxf(v4[k].x, floor_b) - mm.x) / ss.x;
+        r.y = (fmaxf(v4[k].y, floor_b) - mm.y) / ss.y;
+        r.z = (fmaxf(v4[k].z, floor_b) - mm.z) / ss.z;
+        r.w = (fmaxf(v4[k].w, floor_b) - mm.w) / ss.w;
         *reinterpret_cast<float4*>(ob + 4 * i) = r;
+      } else {
+        ob[i] = (fmaxf(v1[k], floor_b) - s_ms[col]) / s_ms[F + col];
       }
-      col += dcol;
-      if (col >= FV) col -= FV;
     }
-  } else {
-    float v[kApplyIters];
-#pragma unroll
-    for (int k = 0; k < kApplyIters; ++k) {
-      const int64_t i = i0 + (int64_t)k * kNormThreads;
-      if (i < nvec) v[k] = xb[i];
-    }
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < kApplyIters; ++k) {
-      const int64_t i = i0 + (int64_t)k * kNormThreads;
-      if (i < nvec) ob[i] = (fmaxf(v[k], floor_b) - s_ms[col]) / s_ms[F + col];
-      col += dcol;
-      if (col >= FV) col -= FV;
-    }
+    col += dcol;
+    if (col >= FV) col -= FV;
   }
 }
 
@@ -447,19 +349,14 @@ int launch_norm_stats(const float* x, const float* lengths, int64_t B, int64_t T
                     (const double2*)ws, (unsigned)chunks, mean, stdv);
 }
 
-int launch_norm_stats_tiles(const float* x, const float* lengths, int64_t B, int64_t T, int F,
-                            int mean_norm, int std_norm, float eps, const sbfe_maxkey_t* utt_max,
-                            float top_db, const float* tile_stats, int tile, float* mean,
-                            float* stdv, int beside_clamp, sbfe_maxkey_t* utt_max_out,
-                            cudaStream_t stream) {
+int launch_norm_stats_prefix(const float* x, const float* lengths, int64_t B, int64_t T, int F,
+                             int mean_norm, int std_norm, float eps, const float* tile_stats,
+                             int tile, float* mean, float* stdv, cudaStream_t stream) {
   if (B == 0 || F == 0) return 0;
   if (B > 0x7fffffff || T > 0x7fffffff) return SBFE_E_TOOBIG;
   const int tiles = (int)((T + tile - 1) / tile);
-  if (B > 65535) return SBFE_E_TOOBIG;
-  const dim3 grid((unsigned)((F + kTileStatCols - 1) / kTileStatCols), (unsigned)B);
-  return launch_pdl(norm_stats_tiles_kernel, grid, dim3(kTileStatThreads), 0, stream,
-      x, lengths, T, F, tile, tiles, tile_stats, utt_max, top_db, mean_norm, std_norm, eps, mean,
-      stdv, beside_clamp, utt_max_out);
+  return launch_pdl(norm_stats_prefix_kernel, dim3((unsigned)B), dim3(kNormThreads), 0, stream, x,
+                    lengths, T, F, tile, tiles, tile_stats, mean_norm, std_norm, eps, mean, stdv);
 }
 
 int launch_norm_reduce(const float* mean, const float* stdv, int64_t B, int F, float* cur,
@@ -474,9 +371,9 @@ int launch_norm_update(const float* cur, int F, int first, float weight, float* 
                     weight, gmean, gstd);
 }
 
-int launch_norm_apply(const float* x, int64_t B, int64_t T, int F, const float* mean,
-                      const float* stdv, int per_utt, const sbfe_maxkey_t* utt_max, float top_db,
-                      float* out, int x_stable, cudaStream_t stream) {
+static int launch_apply_any(const float* x, int64_t B, int64_t T, int F, const float* mean,
+                            const float* stdv, int per_utt, const sbfe_maxkey_t* utt_max,
+                            float top_db, float* out, bool x_stable, cudaStream_t stream) {
   if (B == 0 || T == 0 || F == 0) return 0;
   const bool vec = (F % 4 == 0) &&
                    ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
@@ -486,9 +383,29 @@ int launch_norm_apply(const float* x, int64_t B, int64_t T, int F, const float* 
   if (chunks * B > 0x7fffffff) return SBFE_E_TOOBIG;
   const size_t smem = (size_t)2 * F * sizeof(float);
   if (smem > 48 * 1024) return SBFE_E_TOOBIG;
-  return launch_pdl(vec ? norm_apply_kernel<4> : norm_apply_kernel<1>, dim3((unsigned)(chunks * B)),
-                    dim3(kNormThreads), smem, stream, x, T, F, mean, stdv, per_utt, utt_max, top_db,
-                    out, (unsigned)chunks, x_stable);
+  auto k = x_stable ? (vec ? norm_apply_kernel<4, true> : norm_apply_kernel<1, true>)
+                    : (vec ? norm_apply_kernel<4, false> : norm_apply_kernel<1, false>);
+  return launch_pdl(k, dim3((unsigned)(chunks * B)), dim3(kNormThreads), smem, stream, x, T, F, mean,
+                    stdv, per_utt, utt_max, top_db, out, (unsigned)chunks);
+}
+
+int launch_norm_apply(const float* x, int64_t B, int64_t T, int F, const float* mean,
+                      const float* stdv, int per_utt, const sbfe_maxkey_t* utt_max, float top_db,
+                      float* out, cudaStream_t stream) {
+  return launch_apply_any(x, B, T, F, mean, stdv, per_utt, utt_max, top_db, out, false, stream);
+}
+
+// sentence normalisation from the prefix records: statistics kernel + apply kernel, launched
+// back to back HERE, so that "the apply kernel's direct predecessor only reads x" holds by
+// construction and the apply kernel may fetch x while the statistics finish
+int launch_norm_sentence_prefix(const float* x, const float* lengths, int64_t B, int64_t T, int F,
+                                int mean_norm, int std_norm, float eps, const float* tile_stats,
+                                int tile, float* mean, float* stdv, float* out,
+                                cudaStream_t stream) {
+  int rc = launch_norm_stats_prefix(x, lengths, B, T, F, mean_norm, std_norm, eps, tile_stats, tile,
+                                    mean, stdv, stream);
+  if (rc) return rc;
+  return launch_apply_any(x, B, T, F, mean, stdv, 1, nullptr, 0.f, out, pdl_enabled(), stream);
 }
 
 // ---- speaker mode (processing/features.py:1037-1081): running per-speaker statistics ---------

@@ -40,55 +40,6 @@ __global__ void clamp_kernel(const float* __restrict__ x, int64_t per_utt,
   }
 }
 
-// ---- tile-aware clamp: only tiles that hold a value below the floor are touched -----------
-// (tile records of the fused Fbank kernel, common.cuh: plane 2 = column minima; utt_max NULL:
-// the utterance maximum is rebuilt from the records' keys)
-constexpr int kClampTileThreads = 128;
-// one CTA per tile: the tiles that need clamping cluster at the utterance tails, so anything
-// coarser serialises them (8 tiles per CTA measured 3x slower on padded batches).  The floor
-// costs one key per tile of the utterance (a single load per thread).
-__global__ void __launch_bounds__(kClampTileThreads)
-clamp_tiles_kernel(float* __restrict__ x, int64_t T, int F, int tile, unsigned tiles,
-                   const sbfe_maxkey_t* __restrict__ utt_max, float top_db,
-                   const float* __restrict__ tile_stats) {
-  pdl_wait();
-  pdl_launch_dependents();
-  const int64_t b = blockIdx.x / tiles;
-  const int j = blockIdx.x - b * tiles;
-  const float* mn = tile_stats + (size_t)blockIdx.x * tile_rec_words(F) + 2 * F;
-  // the tile's column minima are requested before the floor is rebuilt (one memory round trip,
-  // not two): min over this thread's columns first, compared once the floor is known
-  float lo = INFINITY;
-  for (int f = threadIdx.x; f < F; f += kClampTileThreads) lo = fminf(lo, __ldg(mn + f));
-  const float floor_b = utt_max ? clamp_floor(utt_max, b, top_db)
-                                : block_floor_from_tiles(tile_stats, b, (int)tiles, F, top_db);
-  if (!__syncthreads_or(lo < floor_b)) return;
-  const int64_t r_lo = (int64_t)j * tile;
-  const int64_t rows = T - r_lo < tile ? T - r_lo : tile;
-  float* p = x + (b * T + r_lo) * F;
-  const int64_t n = rows * F;
-  if ((F & 3) == 0 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) {
-    float4* p4 = reinterpret_cast<float4*>(p);
-    for (int64_t i = threadIdx.x; i < n / 4; i += kClampTileThreads) {
-      float4 v = p4[i];
-      v.x = fmaxf(v.x, floor_b); v.y = fmaxf(v.y, floor_b);
-      v.z = fmaxf(v.z, floor_b); v.w = fmaxf(v.w, floor_b);
-      p4[i] = v;
-    }
-  } else {
-    for (int64_t i = threadIdx.x; i < n; i += kClampTileThreads) p[i] = fmaxf(p[i], floor_b);
-  }
-}
-
-int launch_clamp_tiles(float* x, int64_t B, int64_t T, int F, const sbfe_maxkey_t* utt_max,
-                       float top_db, const float* tile_stats, int tile, cudaStream_t stream) {
-  if (B == 0 || T == 0 || F == 0) return 0;
-  const int64_t tiles = (T + tile - 1) / tile;
-  if (tiles * B > 0x7fffffff || tiles > 0x7fffffff / kTileKeys) return SBFE_E_TOOBIG;
-  return launch_pdl(clamp_tiles_kernel, dim3((unsigned)(tiles * B)), dim3(kClampTileThreads), 0,
-                    stream, x, T, F, tile, (unsigned)tiles, utt_max, top_db, tile_stats);
-}
-
 struct PostParams {
   const float* x;
   float* out;

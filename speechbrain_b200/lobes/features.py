@@ -3,16 +3,15 @@
 Same constructors, sub-module names (``compute_STFT``, ``compute_fbanks``,
 ``compute_dct``, ``compute_deltas``, ``context_window``), ``state_dict`` keys and
 ``[batch, time, features]`` output as the reference (speechbrain/lobes/features.py:
-22-281), but ``forward`` is two kernel launches instead of a chain of 15-25 ATen
-ops:
-  1. sbfe_fbank_forward  wav -> un-clamped log-mel + per-utterance max
-  2. sbfe_post_forward   top_db clamp [-> DCT] [-> deltas] [-> context window]
+22-281), but ``forward`` is one or two kernel launches instead of a chain of 15-25
+ATen ops:
+  plain log-mel   sbfe_fbank_forward (finisher mode): wav -> final, clamped log-mel
+  otherwise       sbfe_fbank_forward  wav -> un-clamped log-mel + per-utterance max
+                  sbfe_post_forward   top_db clamp [-> DCT] [-> deltas] [-> context window]
 """
 import torch
 
 from .. import ops
-import weakref
-
 from .._jit import plain_eager, traceable
 from ..processing.features import DCT, STFT, ContextWindow, Deltas, Filterbank
 
@@ -20,27 +19,15 @@ __all__ = ["Fbank", "MFCC", "pair"]
 
 
 def pair(compute_features, normalizer):
-    """Declare that the output of ``compute_features`` (an ``Fbank``) goes straight into
-    ``normalizer`` (an ``InputNormalization``) and nowhere else, as in the recipes'
-    ``feats = self.modules.normalize(self.hparams.compute_features(wavs), wav_lens)``.
+    """Kept for source compatibility with round-1 recipes: a no-op.
 
-    For the in-place modes (``sentence``, ``speaker``) the top_db clamp (reference:
-    processing/features.py:706-710) is then applied inside the normalisation pass instead of
-    by a launch of its own: same result, one kernel and one partial pass over the features
-    less.  Until the normaliser has run, the tensor ``compute_features`` returned holds the
-    UN-clamped dB values - that is the promise this call makes; any ``InputNormalization`` of
-    this package completes the clamp.  ``pair(compute_features, None)`` withdraws it.
-    Returns ``compute_features``."""
-    from ..processing.normalization import InputNormalization
-
+    It used to declare that the features go straight into ``normalizer`` so that the top_db
+    clamp could be deferred to it.  The fused kernel now finishes every utterance itself (clamp
+    + prefix moments inside the producing launch, csrc/fbank400_v3.cu: finish_utterance), so an
+    unmodified recipe - ``normalize(compute_features(wavs), wav_lens)`` - already gets the
+    shortest chain and the tensor ``compute_features`` returns is always final."""
     if not isinstance(compute_features, _Lobe):
         raise TypeError("pair() takes a speechbrain_b200 Fbank / MFCC")
-    if normalizer is None:
-        compute_features._paired = None
-        return compute_features
-    if not isinstance(normalizer, InputNormalization):
-        raise TypeError("pair() takes a speechbrain_b200 InputNormalization")
-    compute_features._paired = weakref.ref(normalizer)
     return compute_features
 
 
@@ -62,13 +49,6 @@ class _Lobe(torch.nn.Module):
             param_change_factor=param_change_factor, param_rand_factor=param_rand_factor)
         self.context_window = ContextWindow(left_frames=left_frames, right_frames=right_frames)
         self._tables = None
-        self._paired = None   # weakref to the InputNormalization that takes the output (pair())
-
-    def _defers_clamp(self):
-        """pair(): the one consumer of the output is an in-place InputNormalization, which
-        applies the top_db clamp on the fly - no clamp launch here."""
-        norm = self._paired() if self._paired is not None else None
-        return (norm is not None and norm.norm_type in ("sentence", "speaker") and plain_eager())
 
     def _frontend_tables(self):
         fb = self.compute_fbanks
@@ -96,17 +76,15 @@ class _Lobe(torch.nn.Module):
         fb = self.compute_fbanks
         ctx = self.context and self.context_window.context_len > 1
         if dct is None and not self.deltas and not ctx and fb.log_mel:
-            # plain log-mel: the fused kernel also emits per-tile column statistics; the clamp
-            # then only touches tiles that need it and a following InputNormalization gets its
-            # statistics without another pass (handed over on the returned tensor)
-            feats, utt_max, ts = ops.fbank_forward(self._frontend_tables(), wav, tile_stats=True)
+            # plain log-mel: ONE launch.  The fused kernel finishes each utterance itself (top_db
+            # clamp + prefix moments); a following InputNormalization gets its statistics from
+            # the records handed over on the returned tensor instead of a pass over it
+            feats, utt_max, ts = ops.fbank_forward(self._frontend_tables(), wav, tile_stats=True,
+                                                   top_db=fb.top_db)
             if ts is not None:
-                if self._defers_clamp():
-                    ts.top_db, ts.pending_clamp = float(fb.top_db), True
-                else:
-                    ops.clamp_tiles(feats, ts, fb.top_db)
-                ts.version = feats._version
-                feats._sbfe_tile_stats = ts
+                ts.version = ops.version_of(feats)
+                if ts.version is not None and plain_eager():
+                    feats._sbfe_tile_stats = ts
                 return feats
         else:
             feats, utt_max = ops.fbank_forward(self._frontend_tables(), wav)

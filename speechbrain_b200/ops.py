@@ -14,8 +14,8 @@ from ._lib import FbankDesc, check, lib
 
 __all__ = [
     "FrontendTables", "fbank_forward", "stft_forward", "istft_forward", "spectral_magnitude",
-    "filterbank_forward", "post_forward", "norm_stats", "norm_stats_tiles", "clamp_tiles", "TileStats", "norm_reduce", "norm_update",
-    "norm_apply", "decode_utt_max",
+    "filterbank_forward", "post_forward", "norm_stats", "norm_stats_prefix", "norm_sentence_prefix",
+    "TileStats", "norm_reduce", "norm_update", "norm_apply", "decode_utt_max", "mark_written", "version_of",
 ]
 
 
@@ -144,19 +144,58 @@ def _wav2d(wav):
     return wav
 
 
+def mark_written(t):
+    """Tell torch that ``t`` was written in place by a kernel launched through ctypes (which
+    autograd's version counter cannot see): bumps ``t._version``, so that anything keyed on it -
+    the one-shot prefix records handed from Fbank to InputNormalization - sees the change."""
+    torch.autograd.graph.increment_version(t)
+    return t
+
+
+def version_of(t):
+    """``t._version``, or None where torch keeps none (inference tensors)."""
+    try:
+        return t._version
+    except RuntimeError:
+        return None
+
+
 class TileStats:
-    """Per-tile column statistics emitted by the fused Fbank kernel (include/sbfe.h:
-    sbfe_fbank_tile_frames) plus what is needed to use them later."""
+    """Prefix records emitted by the fused Fbank kernel in finisher mode (include/sbfe.h:
+    sbfe_fbank_forward (b)): record j = per-column {mean, M2} of the final (clamped) features over
+    frames [0, min(frames * (j + 1), T)).  ``version`` = ``_version`` of the feature tensor they
+    describe; they are void once that tensor is written to."""
 
-    __slots__ = ("stats", "frames", "utt_max", "top_db", "version", "clamp_mark", "ran_beside",
-                 "pending_clamp")
+    __slots__ = ("stats", "frames", "version")
 
-    def __init__(self, stats, frames, utt_max, top_db):
-        self.stats, self.frames, self.utt_max, self.top_db = stats, frames, utt_max, top_db
-        self.version = None
-        self.clamp_mark = None  # (launch count, stream, x) right after clamp_tiles
-        self.ran_beside = False  # the last norm_stats_tiles ran beside that clamp
-        self.pending_clamp = False  # the tensor is still UN-clamped (lobes/features.py: pair())
+    def __init__(self, stats, frames):
+        self.stats, self.frames, self.version = stats, frames, None
+
+
+# Tiles-done counters of the finisher (sbfe.h: d_sync): zero on entry, zero again when the kernel
+# ends.  One zeroed ring per device, handed out slice by slice: calls that may be in flight at the
+# same time (other streams, other captured graphs) get different slices unless 2^16 counters'
+# worth of calls lie between them; nothing is allocated or memset per call (a memset would be
+# one more node in every captured step).
+_SYNC_RING = {}
+_SYNC_SLOTS = 1 << 16
+
+
+def _sync_counters(device, B):
+    if B > _SYNC_SLOTS // 4:
+        return torch.zeros((B,), dtype=torch.int32, device=device)
+    key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
+    ring = _SYNC_RING.get(key)
+    if ring is None:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("first speechbrain_b200 Fbank call on this device happens inside a "
+                               "CUDA graph capture: run one eager step first")
+        ring = _SYNC_RING[key] = [torch.zeros((_SYNC_SLOTS,), dtype=torch.int32, device=device), 0]
+    buf, cur = ring
+    if cur + B > _SYNC_SLOTS:
+        cur = 0
+    ring[1] = cur + B
+    return buf[cur:cur + B]
 
 
 def ragged_supported(tables, device):
@@ -165,9 +204,13 @@ def ragged_supported(tables, device):
     return int(lib().sbfe_fbank_tile_frames(C.byref(desc))) > 0
 
 
-def fbank_forward(tables, wav, tile_stats=False):
-    """wav [B, L] (or a dataio.RaggedBatch) -> (dB or linear mel [B, T, M] WITHOUT the top_db
-    clamp, utt_max keys [B] int32[, TileStats or None]).  sbfe_fbank_forward[_ragged]."""
+def fbank_forward(tables, wav, tile_stats=False, top_db=80.0):
+    """wav [B, L] (or a dataio.RaggedBatch) -> mel features [B, T, M].
+
+    tile_stats=False: (dB or linear mel WITHOUT the top_db clamp, utt_max keys [B] int32).
+    tile_stats=True (finisher mode where the configuration has one): (FINAL features - clamped
+    to ``top_db`` below each utterance's maximum (None: no clamp) -, None, TileStats); where it
+    has none: (un-clamped, utt_max, None).  sbfe_fbank_forward[_ragged[_pcm16]]."""
     ragged = None
     if hasattr(wav, "packed"):
         ragged = wav
@@ -187,63 +230,68 @@ def fbank_forward(tables, wav, tile_stats=False):
     L_ = lib()
     ws_bytes = L_.sbfe_fbank_workspace_bytes(C.byref(desc), B, L)
     ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=wav.device) if ws_bytes > 0 else None
-    ts, frames = None, 0
+    ts, frames, sync = None, 0, None
     if tile_stats and B > 0:
         frames = int(L_.sbfe_fbank_tile_frames(C.byref(desc)))
         if frames > 0:
             words = int(L_.sbfe_fbank_tile_stats_floats(C.byref(desc)))
             ts = torch.empty((B, (T + frames - 1) // frames, words), dtype=torch.float32,
                              device=wav.device)
-    # with tile records the utterance maximum travels in them: no atomics, no memset
+            sync = _sync_counters(wav.device, B)
+    # in finisher mode the utterance maximum travels in the records: no atomics, no memset
     utt_max = None if ts is not None else torch.zeros((B,), dtype=torch.int32, device=wav.device)
+    db = -1.0 if top_db is None else float(top_db)
     with torch.cuda.device(wav.device):
         if ragged is not None and wav.dtype == torch.int16:
             check(L_.sbfe_fbank_forward_ragged_pcm16(C.byref(desc), _ptr(wav), _ptr(ragged.offsets),
                                                      _ptr(ragged.nsamples), B, L, ragged.scale,
-                                                     _ptr(out), _ptr(utt_max), _ptr(ts), _stream()))
+                                                     _ptr(out), _ptr(utt_max), _ptr(ts), _ptr(sync),
+                                                     db, _stream()))
         elif ragged is not None:
             check(L_.sbfe_fbank_forward_ragged(C.byref(desc), _ptr(wav), _ptr(ragged.offsets),
                                                _ptr(ragged.nsamples), B, L, _ptr(out),
-                                               _ptr(utt_max), _ptr(ts), _stream()))
+                                               _ptr(utt_max), _ptr(ts), _ptr(sync), db, _stream()))
         else:
             check(L_.sbfe_fbank_forward(C.byref(desc), _ptr(wav), B, L, L, _ptr(out),
-                                        _ptr(utt_max), _ptr(ts), _ptr(ws), max(ws_bytes, 0),
-                                        _stream()))
+                                        _ptr(utt_max), _ptr(ts), _ptr(sync), db, _ptr(ws),
+                                        max(ws_bytes, 0), _stream()))
     if tile_stats:
-        return out, utt_max, (TileStats(ts, frames, None, 0.0) if ts is not None else None)
+        return out, utt_max, (TileStats(ts, frames) if ts is not None else None)
     return out, utt_max
 
 
-def clamp_tiles(x, ts, top_db):
-    """In-place top_db clamp that only touches tiles holding a value below the floor."""
-    B, T, F = x.shape
-    with torch.cuda.device(x.device):
-        check(lib().sbfe_clamp_tiles(_ptr(x), B, T, F, _ptr(ts.utt_max), float(top_db),
-                                     _ptr(ts.stats), ts.frames, _stream()))
-    ts.top_db = float(top_db)
-    ts.clamp_mark = (_lib.launches, torch.cuda.current_stream().cuda_stream, x.data_ptr())
-    return x
-
-
-def norm_stats_tiles(x, lengths, ts, mean_norm=True, std_norm=True, eps=1e-10, want_max=False):
-    """norm_stats from the fused kernel's tile partials (no pass over x).  ``x`` may be clamped
-    or not (every value is read through max(., floor)); ``want_max=True`` also returns the
-    utterance max keys [B] for a ``norm_apply`` that clamps on the fly."""
+def _stats_out(x, lengths):
     B, T, F = x.shape
     lengths = lengths.to(device=x.device, dtype=torch.float32).contiguous()
     mean = torch.empty((B, F), dtype=torch.float32, device=x.device)
     std = torch.empty((B, F), dtype=torch.float32, device=x.device)
-    keys = torch.empty((B,), dtype=torch.int32, device=x.device) if want_max else None
+    return lengths, mean, std
+
+
+def norm_stats_prefix(x, lengths, ts, mean_norm=True, std_norm=True, eps=1e-10):
+    """norm_stats from the fused kernel's prefix records (one record + the rows of the tile the
+    valid length cuts; no pass over x).  sbfe_norm_stats_prefix."""
+    B, T, F = x.shape
+    lengths, mean, std = _stats_out(x, lengths)
     with torch.cuda.device(x.device):
-        # the clamp of this very tensor was the library's last launch on this stream: the
-        # statistics kernel may run beside it (include/sbfe.h: SBFE_STATS_BESIDE_CLAMP)
-        beside = ts.clamp_mark == (_lib.launches, torch.cuda.current_stream().cuda_stream, x.data_ptr())
-        check(lib().sbfe_norm_stats_tiles(_ptr(x), _ptr(lengths), B, T, F, int(bool(mean_norm)),
-                                          int(bool(std_norm)), float(eps), _ptr(ts.utt_max),
-                                          float(ts.top_db), _ptr(ts.stats), ts.frames, _ptr(mean),
-                                          _ptr(std), int(beside), _ptr(keys), _stream()))
-    ts.ran_beside = beside
-    return (mean, std, keys) if want_max else (mean, std)
+        check(lib().sbfe_norm_stats_prefix(_ptr(x), _ptr(lengths), B, T, F, int(bool(mean_norm)),
+                                           int(bool(std_norm)), float(eps), _ptr(ts.stats), ts.frames,
+                                           _ptr(mean), _ptr(std), _stream()))
+    return mean, std
+
+
+def norm_sentence_prefix(x, lengths, ts, mean_norm=True, std_norm=True, eps=1e-10, out=None):
+    """Sentence normalisation straight from the prefix records: statistics + (x - mean) / std in
+    one library call (sbfe_norm_sentence_prefix).  In place when ``out is x``."""
+    B, T, F = x.shape
+    lengths, mean, std = _stats_out(x, lengths)
+    if out is None:
+        out = torch.empty_like(x)
+    with torch.cuda.device(x.device):
+        check(lib().sbfe_norm_sentence_prefix(_ptr(x), _ptr(lengths), B, T, F, int(bool(mean_norm)),
+                                              int(bool(std_norm)), float(eps), _ptr(ts.stats),
+                                              ts.frames, _ptr(mean), _ptr(std), _ptr(out), _stream()))
+    return mark_written(out)
 
 
 def stft_forward(tables, wav, power_only=False):
@@ -319,7 +367,7 @@ def post_forward(x, utt_max=None, top_db=80.0, dct=None, deltas=False, delta_win
                                       int(F0 if dct is not None else 0), int(deltas),
                                       int(delta_window), int(bool(context)), int(left), int(right),
                                       _ptr(out), _stream()))
-    return out
+    return mark_written(out) if out is x else out
 
 
 def norm_stats(x, lengths, mean_norm=True, std_norm=True, eps=1e-10, utt_max=None, top_db=80.0):
@@ -366,25 +414,15 @@ def norm_speaker_update(mean, std, row, mode, weight, table_mean, table_std):
     return out_m, out_s
 
 
-def norm_apply(x, mean, std, per_utt, out=None, utt_max=None, top_db=80.0, stats_mark=None):
-    """(max(x, floor) - mean) / std.  ``stats_mark`` = what ``stats_launch_mark(x)`` returned
-    right after the statistics call that produced ``mean`` / ``std``: when that call is still
-    the library's last launch on this stream, the kernel reads ``x`` while the statistics
-    finish (include/sbfe.h: SBFE_APPLY_X_STABLE)."""
+def norm_apply(x, mean, std, per_utt, out=None, utt_max=None, top_db=80.0):
+    """(max(x, floor) - mean) / std (sbfe_norm_apply); in place when ``out is x``."""
     B, T, F = x.shape
     if out is None:
         out = torch.empty_like(x)
     with torch.cuda.device(x.device):
-        stable = stats_mark is not None and stats_mark == stats_launch_mark(x)
         check(lib().sbfe_norm_apply(_ptr(x), B, T, F, _ptr(mean), _ptr(std), int(bool(per_utt)),
-                                    _ptr(utt_max), float(top_db), _ptr(out), int(stable), _stream()))
-    return out
-
-
-def stats_launch_mark(x):
-    """(library launch count, stream, x) - identifies "the statistics call on x was the last
-    launch of the library on this stream" for ``norm_apply(stats_mark=...)``."""
-    return (_lib.launches, torch.cuda.current_stream().cuda_stream, x.data_ptr())
+                                    _ptr(utt_max), float(top_db), _ptr(out), _stream()))
+    return mark_written(out) if out is x else out
 
 
 def decode_utt_max(keys):
@@ -441,4 +479,4 @@ def specaugment_forward(x, warp=None, warp_mode="bicubic", freq_masks=None, time
         check(lib().sbfe_specaugment_forward(_ptr(x), B, T, F, c, w, modes.get(warp_mode, 0),
                                              _ptr(fpos), _ptr(flen), nf, _ptr(tpos), _ptr(tlen),
                                              nt, _ptr(d_fill), f_fill, _ptr(out), _stream()))
-    return out
+    return mark_written(out) if out is x else out

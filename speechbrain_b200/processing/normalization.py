@@ -1,10 +1,11 @@
 """``InputNormalization`` drop-in (reference: speechbrain/processing/features.py:940-1231).
 
 The reference loops over sentences in Python (one host sync and >= 5 tiny kernels
-per sentence).  Here the statistics of the whole batch come from two kernel
-launches and the normalisation from one; nothing is read back to the host except
-in ``speaker`` mode, whose dictionary is keyed by host integers in the reference
-as well.
+per sentence).  Here the statistics of the whole batch come from one or two kernel
+launches (one tiny one when the features come straight from this package's Fbank,
+whose kernel leaves prefix moments behind) and the normalisation from one; nothing
+is read back to the host except in ``speaker`` mode, whose dictionary is keyed by
+host integers in the reference as well.
 """
 import torch
 
@@ -49,6 +50,7 @@ class InputNormalization(torch.nn.Module):
     def __init__(self, mean_norm=True, std_norm=True, norm_type="global", avg_factor=None,
                  requires_grad=False, update_until_epoch=3, sync_stats=False):
         super().__init__()
+        register_checkpoint_hooks_if_available(import_it=False)
         self.mean_norm = mean_norm
         self.std_norm = std_norm
         self.norm_type = norm_type
@@ -80,39 +82,31 @@ class InputNormalization(torch.nn.Module):
             x = x.float().contiguous()
         ops._require_cuda(x, "x")
         B, T, F = x.shape
+        # one-shot hand-over from the fused Fbank kernel (lobes/features.py): prefix records of
+        # this very tensor, void as soon as anything has written to it (version counter; the
+        # package's own in-place ops bump it, ops.mark_written)
         ts = getattr(x, "_sbfe_tile_stats", None)
-        clamp = {}  # top_db clamp still owed to x (lobes/features.py: pair()), applied on the fly
-        if ts is not None:  # one-shot hand-over from the fused Fbank kernel (lobes/features.py)
+        if ts is not None:
             x._sbfe_tile_stats = None
-            if ts.version != x._version or tuple(ts.stats.shape[::2]) != (B, 3 * F + 4):
-                if ts.pending_clamp:
-                    raise RuntimeError(
-                        "the output of a pair()-ed Fbank was modified before it reached "
-                        "InputNormalization: its top_db clamp is still pending")
+            if (ops.version_of(x) != ts.version or ts.version is None
+                    or tuple(ts.stats.shape[::2]) != (B, 3 * F + 4)):
                 ts = None
-        if ts is not None and ts.pending_clamp and self.norm_type not in ("sentence", "speaker"):
-            ops.clamp_tiles(x, ts, ts.top_db)  # these modes leave x behind: it must be complete
-            ts.pending_clamp = False
-        if ts is not None and ts.pending_clamp:
-            mean, std, keys = ops.norm_stats_tiles(x, lengths, ts, self.mean_norm, self.std_norm,
-                                                   self.eps, want_max=True)
-            clamp = {"utt_max": keys, "top_db": ts.top_db}
-            ts.pending_clamp = False
-        elif ts is not None:
-            mean, std = ops.norm_stats_tiles(x, lengths, ts, self.mean_norm, self.std_norm, self.eps)
+
+        if self.norm_type == "sentence" and ts is not None:
+            # statistics + normalisation in one library call, in place (:1020-1035)
+            return ops.norm_sentence_prefix(x, lengths, ts, self.mean_norm, self.std_norm, self.eps,
+                                            out=x)
+        if ts is not None:
+            mean, std = ops.norm_stats_prefix(x, lengths, ts, self.mean_norm, self.std_norm, self.eps)
         else:
             mean, std = ops.norm_stats(x, lengths, self.mean_norm, self.std_norm, self.eps)
 
-        # "the statistics were the library's last launch": the apply kernel may then read x
-        # while they finish (include/sbfe.h: SBFE_APPLY_X_STABLE)
         if self.norm_type == "sentence":
-            return ops.norm_apply(x, mean, std, per_utt=True, out=x,  # in place (:1035)
-                                  stats_mark=ops.stats_launch_mark(x), **clamp)
+            return ops.norm_apply(x, mean, std, per_utt=True, out=x)  # in place (:1035)
 
         if self.norm_type == "speaker":
             s_mean, s_std = self._speaker_stats(mean, std, spk_ids)
-            return ops.norm_apply(x, s_mean, s_std, per_utt=True, out=x,  # in place (:1081)
-                                  stats_mark=ops.stats_launch_mark(x), **clamp)
+            return ops.norm_apply(x, s_mean, s_std, per_utt=True, out=x)  # in place (:1081)
 
         if self.norm_type not in ("batch", "global"):
             return x
@@ -261,16 +255,30 @@ class InputNormalization(torch.nn.Module):
         self._load_statistics_dict(stats)
 
 
-def register_checkpoint_hooks_if_available():
-    """Registers ``_save`` / ``_load`` with SpeechBrain's checkpointer when the
-    reference package is importable (utils/checkpoints.py:197-328); a no-op
-    otherwise.  Called by ``speechbrain_b200.install()``."""
-    try:
-        from speechbrain.utils import checkpoints as ck
-    except Exception:
+def register_checkpoint_hooks_if_available(import_it=True):
+    """Registers ``_save`` / ``_load`` with SpeechBrain's checkpointer (utils/checkpoints.py:
+    197-328) - the reference does it with decorators at class definition (:940, 1205-1231).
+    ``import_it=True`` (``speechbrain_b200.install()``) imports ``speechbrain.utils.checkpoints``;
+    ``False`` (every construction, and the import of this module) only looks whether the
+    application has imported it already, so that the class used directly with a reference
+    ``Checkpointer`` - without ``install()`` - saves its statistics and not an empty
+    ``state_dict``.  A no-op when the reference package is absent."""
+    import sys
+
+    ck = sys.modules.get("speechbrain.utils.checkpoints")
+    if ck is None and import_it:
+        try:
+            from speechbrain.utils import checkpoints as ck
+        except Exception:
+            return False
+    if ck is None:
         return False
     cls = InputNormalization
-    ck.DEFAULT_SAVE_HOOKS[cls] = cls._save
-    ck.DEFAULT_LOAD_HOOKS[cls] = cls._load
-    ck.DEFAULT_TRANSFER_HOOKS[cls] = cls._load
+    if ck.DEFAULT_SAVE_HOOKS.get(cls) is not cls._save:
+        ck.DEFAULT_SAVE_HOOKS[cls] = cls._save
+        ck.DEFAULT_LOAD_HOOKS[cls] = cls._load
+        ck.DEFAULT_TRANSFER_HOOKS[cls] = cls._load
     return True
+
+
+register_checkpoint_hooks_if_available(import_it=False)

@@ -155,3 +155,58 @@ _case("norm_speaker", kind="norm_seq", shape=SEQ_SHAPE, norm={"norm_type": "spea
 def input_checksum(x):
     x = np.asarray(x, dtype=np.float64)
     return np.array([x.sum(), np.abs(x).sum(), x.reshape(-1)[:: max(1, x.size // 97)].sum()])
+
+
+# ---- round 2 additions: a second fixture file (frontend_golden_r2.npz, tests/make_golden_r2.py)
+# so that the round-1 file keeps regenerating bit for bit -------------------------------------
+GOLDEN_R2_NPZ = os.path.join(GOLDEN_DIR, "frontend_golden_r2.npz")
+REF_CKPT_GLOBAL = os.path.join(GOLDEN_DIR, "ref_normalizer_global.ckpt")
+REF_CKPT_SPEAKER = os.path.join(GOLDEN_DIR, "ref_normalizer_speaker.ckpt")
+JITTER_SEED = 77
+
+CASES_R2 = {}
+
+
+def _case2(name, **spec):
+    CASES_R2[name] = spec
+
+
+# Filterbank jitter (processing/features.py:525-532): training mode, torch.manual_seed(JITTER_SEED)
+# right before forward - the product draws the same torch.rand(2)
+_case2("fbank_jitter_train", kind="fbank", train_seed=JITTER_SEED,
+       make_input=lambda: synth_wav(301, 2, 8000),
+       kwargs={"n_mels": 40, "param_rand_factor": 0.15})
+_case2("mfcc_jitter_train", kind="mfcc", train_seed=JITTER_SEED + 1,
+       make_input=lambda: synth_wav(302, 2, 4000),
+       kwargs={"param_rand_factor": 0.3, "deltas": False, "context": False})
+# n_fft = 400 with hop != 160: the scalar fused kernel (csrc/fbank400.cu)
+_case2("fbank_hop128", kind="fbank", make_input=lambda: synth_wav(303, 3, 8000 + 37),
+       kwargs={"n_mels": 40, "hop_length": 8})
+_case2("fbank_hop200_80mel", kind="fbank", make_input=lambda: synth_wav(304, 2, 9000),
+       kwargs={"n_mels": 80, "hop_length": 12.5})
+# the power-of-two kernels at sizes that span several tiles
+_case2("fbank_nfft512_80mel_3x1s", kind="fbank",
+       make_input=lambda: synth_wav(305, 3, 16000 + 91, rel_lengths=[1.0, 0.55, 0.8]),
+       kwargs={"n_fft": 512, "n_mels": 80})
+_case2("fbank_nfft512_hop256", kind="fbank", make_input=lambda: synth_wav(306, 2, 12000),
+       kwargs={"n_fft": 512, "n_mels": 40, "win_length": 32, "hop_length": 16})
+_case2("mfcc_nfft512", kind="mfcc", make_input=lambda: synth_wav(307, 2, 6000),
+       kwargs={"n_fft": 512})
+# dense filters (the tensor-core contraction)
+_case2("fbank_gaussian80_2x1s", kind="fbank", make_input=lambda: synth_wav(308, 2, 16000),
+       kwargs={"filter_shape": "gaussian", "n_mels": 80})
+_case2("fbank_gaussian_nfft512", kind="fbank", make_input=lambda: synth_wav(309, 2, 8000),
+       kwargs={"filter_shape": "gaussian", "n_mels": 64, "n_fft": 512})
+_case2("stft_normalized", kind="stft", make_input=lambda: synth_wav(310, 2, 4000),
+       kwargs={"sample_rate": 16000, "normalized_stft": True})
+_case2("stft_normalized_nfft512", kind="stft", make_input=lambda: synth_wav(311, 2, 3000),
+       kwargs={"sample_rate": 16000, "n_fft": 512, "normalized_stft": True})
+_case2("filterbank_gaussian_spec", kind="filterbank",
+       make_input=lambda: np.abs(synth_feats(312, (3, 50, 201), 5.0, 0.0)),
+       kwargs={"filter_shape": "gaussian", "n_mels": 40})
+
+# InputNormalization state written by the REFERENCE's _save (normalizer.ckpt): the steps that
+# build the state, then one eval step whose output is stored
+CKPT_SHAPE = (4, 37, 12)
+CKPT_STEPS = _seq(400, [0, 0, 0], [True, True, True], spk=[[3, 5, 3, 9], [5, 5, 9, 3], [3, 7, 3, 3]])
+CKPT_EVAL = dict(seed=450, lengths=SEQ_LENS[3], spk_ids=[3, 11, 9, 5])

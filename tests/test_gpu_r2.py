@@ -1,0 +1,205 @@
+"""Round-2 GPU parity: the product against the round-2 reference fixtures (jitter, other hops,
+n_fft 512, gaussian filters, normalized STFT, reference-written checkpoints) and - at the FULL
+sizes of BASELINE.json's configs - directly against the numpy oracle in float64 with the
+SURVEY.md 8c protocol (the product may be at most twice as far from the float64 anchor as the
+float32 restatement of the reference is)."""
+import numpy as np
+import pytest
+import torch
+
+import golden_cases as gc
+from oracle import frontend_np as onp
+
+pytestmark = pytest.mark.gpu
+ULP = 1e-5
+LOBES_R2 = [n for n, s in gc.CASES_R2.items() if s["kind"] in ("fbank", "mfcc")]
+
+
+@pytest.fixture(scope="module")
+def sb():
+    assert torch.cuda.is_available(), "these tests need the B200"
+    import speechbrain_b200
+
+    return speechbrain_b200
+
+
+@pytest.fixture(scope="module")
+def golden2():
+    return np.load(gc.GOLDEN_R2_NPZ)
+
+
+def dev(x):
+    return torch.from_numpy(np.ascontiguousarray(x)).cuda()
+
+
+@pytest.mark.parametrize("name", LOBES_R2)
+def test_lobe_vs_reference_r2(sb, golden2, name):
+    spec = gc.CASES_R2[name]
+    x = spec["make_input"]()
+    mod = (sb.MFCC if spec["kind"] == "mfcc" else sb.Fbank)(**spec["kwargs"])
+    assert np.array_equal(mod.compute_fbanks.f_central.numpy(), golden2[f"{name}/fc"])
+    assert np.array_equal(mod.compute_STFT.window.numpy(), golden2[f"{name}/window"])
+    if "train_seed" in spec:      # jitter: training mode, same default-generator draw
+        mod.train()
+        torch.manual_seed(spec["train_seed"])
+    else:
+        mod.eval()
+    got = mod(dev(x)).cpu().numpy()
+    ref32 = golden2[f"{name}/ref32"]
+    assert got.shape == ref32.shape and np.isfinite(got).all()
+    mult = 30.0 if spec["kind"] == "mfcc" else 1.0
+    if f"{name}/ref64" in golden2.files:
+        ref64 = golden2[f"{name}/ref64"]
+        noise = np.abs(ref32 - ref64).max()
+        err = np.abs(got - ref64).max()
+        assert err <= 2 * noise + mult * ULP, (err, noise)
+        assert np.abs(got - ref64).mean() <= 2 * np.abs(ref32 - ref64).mean() + ULP
+    assert np.abs(got - ref32).max() < 2e-3 * mult
+    if "train_seed" in spec:      # and a second call draws again: different filters
+        again = mod(dev(x)).cpu().numpy()
+        assert np.abs(again - got).max() > 1e-3
+        mod.eval()
+        base = (sb.MFCC if spec["kind"] == "mfcc" else sb.Fbank)(
+            **{k: v for k, v in spec["kwargs"].items() if k != "param_rand_factor"})
+        assert torch.equal(mod(dev(x)), base(dev(x)))   # eval mode: no jitter
+
+
+def test_stft_normalized_vs_reference(sb, golden2):
+    for name in ("stft_normalized", "stft_normalized_nfft512"):
+        spec = gc.CASES_R2[name]
+        got = sb.STFT(**spec["kwargs"])(dev(spec["make_input"]())).cpu().numpy()
+        ref = golden2[f"{name}/ref32"]
+        assert got.shape == ref.shape
+        assert np.abs(got - ref).max() <= 2e-4 * np.abs(ref).max()
+
+
+def test_filterbank_gaussian_module_vs_reference(sb, golden2):
+    spec = gc.CASES_R2["filterbank_gaussian_spec"]
+    got = sb.Filterbank(**spec["kwargs"])(dev(spec["make_input"]())).cpu().numpy()
+    ref = golden2["filterbank_gaussian_spec/ref32"]
+    assert got.shape == ref.shape and np.abs(got - ref).max() < 1e-4
+
+
+@pytest.mark.parametrize("norm_type,path", [("global", gc.REF_CKPT_GLOBAL), ("speaker", gc.REF_CKPT_SPEAKER)])
+def test_reference_written_checkpoint_drives_the_kernels(sb, golden2, norm_type, path):
+    """normalizer.ckpt written by the reference's _save, loaded by the product (as the
+    Checkpointer does: _load(path, end_of_epoch, device)), then an eval step on the GPU ==
+    the reference's eval step after the same state."""
+    norm = sb.InputNormalization(norm_type=norm_type)
+    norm._load(path, end_of_epoch=False, device="cuda")
+    norm.eval()
+    x = dev(gc.synth_feats(gc.CKPT_EVAL["seed"], gc.CKPT_SHAPE))
+    y = norm(x, torch.tensor(gc.CKPT_EVAL["lengths"]).cuda(),
+             spk_ids=torch.tensor(gc.CKPT_EVAL["spk_ids"]).unsqueeze(1))
+    ref = golden2[f"ckpt_{norm_type}/eval"]
+    assert np.abs(y.cpu().numpy() - ref).max() < 2e-5 * max(1.0, np.abs(ref).max())
+    assert norm.count == int(golden2[f"ckpt_{norm_type}/count"])
+
+
+# ---- BASELINE.json configs at FULL size against the oracle -----------------
+def _protocol(got, ref64, ref32, mult=1.0):
+    """no less accurate than twice the float32 restatement of the reference."""
+    noise = np.abs(ref32 - ref64).max()
+    err = np.abs(got - ref64).max()
+    assert err <= 2 * noise + mult * ULP, (err, noise)
+    assert np.abs(got - ref64).mean() <= 2 * np.abs(ref32 - ref64).mean() + mult * ULP
+    return err, noise
+
+
+def _oracle_fbank(fb, wav, dtype, n_mels=80):
+    consts = (fb.compute_fbanks.f_central.numpy(), fb.compute_fbanks.band.numpy())
+    return onp.fbank(wav, n_mels=n_mels, dtype=dtype, mel_params=consts,
+                     window=fb.compute_STFT.window.numpy())
+
+
+def _check_sentence_norm(out, ref64, lens, std_norm=True):
+    """Normalised output against the oracle normalising the float64 features; columns the
+    top_db clamp made constant over the valid frames (zero variance) are not compared - there
+    (rounding noise) / eps is arbitrary in every implementation, the reference included."""
+    want = onp.InputNormalizationOracle(norm_type="sentence", std_norm=std_norm)(ref64.copy(), lens)
+    T = ref64.shape[1]
+    for b in range(ref64.shape[0]):
+        n = int(np.rint(np.float32(lens[b]) * np.float32(T)))
+        live = ref64[b, :n].std(axis=0) > 1e-3 if std_norm else np.ones(ref64.shape[2], bool)
+        assert live.mean() > 0.9
+        d = np.abs(out[b][:, live] - want[b][:, live])
+        assert d.max() < 1e-3, (b, d.max())
+        assert d.mean() < 2e-5
+
+
+def test_cfg2_full_size_vs_oracle(sb):
+    """32 x 16 s, lengths 0.6-1.0 with zero-padded tails: exactly bench.py's synth_batch."""
+    import bench
+
+    wav_t, lens_t = bench.synth_batch(0, "cpu")
+    wav, lens = wav_t.numpy(), lens_t.numpy()
+    fb, norm = sb.Fbank(n_mels=80), sb.InputNormalization(norm_type="sentence")
+    feats = fb(wav_t.cuda())
+    got = feats.cpu().numpy()
+    assert got.shape == (32, 1601, 80)
+    ref64 = _oracle_fbank(fb, wav, np.float64)
+    ref32 = _oracle_fbank(fb, wav, np.float32)
+    _protocol(got, ref64, ref32)
+    out = norm(feats, lens_t.cuda())
+    assert out.data_ptr() == feats.data_ptr()
+    _check_sentence_norm(out.cpu().numpy(), ref64, lens)
+
+
+def test_cfg3_full_size_vs_oracle(sb):
+    """64 x 4 s MFCC: 23 mel -> 20 DCT -> deltas -> context 5+5 = 660."""
+    wav = gc.synth_wav(703, 64, 64000)
+    mf = sb.MFCC()
+    got = mf(dev(wav)).cpu().numpy()
+    assert got.shape == (64, 401, 660)
+    consts = (mf.compute_fbanks.f_central.numpy(), mf.compute_fbanks.band.numpy())
+    kw = dict(mel_params=consts, window=mf.compute_STFT.window.numpy())
+    ref64 = onp.mfcc(wav, dtype=np.float64, **kw)
+    ref32 = onp.mfcc(wav, dtype=np.float32, **kw)
+    _protocol(got, ref64, ref32, mult=30.0)
+
+
+def test_cfg4_full_size_vs_oracle(sb):
+    """256 x 3 s crops, Fbank-80 + sentence MEAN normalisation."""
+    rng = np.random.default_rng(704)
+    lens = rng.uniform(0.5, 1.0, 256).astype(np.float32)
+    lens[:3] = [1.0, 0.5, 32 * 5 / 301]
+    wav = gc.synth_wav(704, 256, 48000, rel_lengths=lens)
+    fb = sb.Fbank(n_mels=80)
+    norm = sb.InputNormalization(norm_type="sentence", std_norm=False)
+    feats = fb(dev(wav))
+    got = feats.cpu().numpy()
+    ref64 = _oracle_fbank(fb, wav, np.float64)
+    ref32 = _oracle_fbank(fb, wav, np.float32)
+    _protocol(got, ref64, ref32)
+    out = norm(feats, torch.from_numpy(lens).cuda()).cpu().numpy()
+    _check_sentence_norm(out, ref64, lens, std_norm=False)
+
+
+def test_cfg5_shard_vs_oracle(sb):
+    """One GPU's shard of cfg5: 128 x 30 s, Fbank-80 + global normalisation in training mode,
+    two steps (first-call copy, then the running average).  Features of a slice of the shard
+    against the float64 oracle; the normalisation of the WHOLE shard against the oracle
+    normalising the product's own features (isolates the statistics / update / apply kernels)."""
+    g = torch.Generator().manual_seed(705)
+    fb = sb.Fbank(n_mels=80)
+    gn = sb.InputNormalization(norm_type="global").train()
+    ref = onp.InputNormalizationOracle(norm_type="global")
+    for step in range(2):
+        wav = torch.randn(128, 480000, generator=g) * 0.1
+        lens = torch.linspace(0.6, 1.0, 128)[torch.randperm(128, generator=g)]
+        for i in range(128):
+            wav[i, int(round(float(lens[i]) * 480000)):] = 0
+        feats = fb(wav.cuda())
+        keep = feats.cpu().numpy()
+        assert keep.shape == (128, 3001, 80)
+        if step == 0:
+            sl = [0, 17, 127]
+            w = wav[sl].numpy()
+            _protocol(keep[sl], _oracle_fbank(fb, w, np.float64), _oracle_fbank(fb, w, np.float32))
+        out = gn(feats, lens.cuda(), epoch=0)
+        assert torch.equal(feats.cpu(), torch.from_numpy(keep))          # x is left intact
+        want = ref(keep.astype(np.float64), lens.numpy(), epoch=0)
+        assert np.abs(out.cpu().numpy() - want).max() < 2e-4, step
+        np.testing.assert_allclose(gn.glob_mean.cpu().numpy(), ref.glob_mean, rtol=1e-5, atol=2e-5)
+        np.testing.assert_allclose(gn.glob_std.cpu().numpy(), ref.glob_std, rtol=2e-5, atol=2e-5)
+    assert gn.count == ref.count == 2
