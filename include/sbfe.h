@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define SBFE_ABI_VERSION 8
+#define SBFE_ABI_VERSION 9
 
 #if defined(__GNUC__)
 #define SBFE_API __attribute__((visibility("default")))
@@ -35,6 +35,7 @@ extern "C" {
 #define SBFE_E_INVAL (-1)    /* bad size / null pointer / unsupported combination */
 #define SBFE_E_TOOBIG (-2)   /* a dimension exceeds what the kernels index */
 #define SBFE_E_NOSPACE (-3)  /* workspace too small */
+#define SBFE_E_STATIC_LIMIT (-4) /* sbfe_norm_stats_static: needs more than SBFE_NORM_STATIC_WS_BYTES */
 
 /* Utterance-maximum keys: order-preserving uint32 encoding of a float so that
  * atomicMax works for negative dB values.  0 == "no value yet". */
@@ -207,6 +208,24 @@ SBFE_API int sbfe_norm_stats(const float* d_x, const float* d_lengths, int64_t B
                     int32_t mean_norm, int32_t std_norm, float eps,
                     const sbfe_maxkey_t* d_utt_max, float top_db, float* d_mean, float* d_std,
                     void* d_workspace, int64_t workspace_bytes, void* stream);
+
+/* sbfe_norm_stats without a workspace argument and without any allocation.  No counterpart in
+ * the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same kernels, same results as sbfe_norm_stats; the partial sums go to a device array built into
+ * the library (SBFE_NORM_STATIC_WS_BYTES, held by every GPU that loads the library until the
+ * process exits).  Limit: sbfe_norm_workspace_bytes(B, T, F) = 16 * B * ceil(T / 256) * F must
+ * not exceed SBFE_NORM_STATIC_WS_BYTES (e.g. 32 x 16 s x 80 mel = 280 KiB, 128 x 30 s x 80 mel =
+ * 1.9 MiB), else SBFE_E_STATIC_LIMIT and nothing is launched.  The call makes no cudaMalloc /
+ * cudaFree / allocating library call (first use on a device resolves the array's address with
+ * cudaGetSymbolAddress).  All calls share the one array: calls whose kernels may overlap on the
+ * GPU (different streams, no ordering between them) race; calls on one stream are safe.  Nothing
+ * in the array has to be cleared between calls (every slot read was written by the same call). */
+#define SBFE_NORM_STATIC_WS_BYTES (2 * 1024 * 1024)
+SBFE_API int sbfe_norm_stats_static(const float* d_x, const float* d_lengths, int64_t B, int64_t T,
+                           int32_t F, int32_t mean_norm, int32_t std_norm, float eps,
+                           const sbfe_maxkey_t* d_utt_max, float top_db, float* d_mean,
+                           float* d_std, void* stream);
 
 /* batch / global statistics (processing/features.py:1083-1114):
  * d_cur[2F+1] = {sum_b mean_b, sum_b std_b, B} (the all-reduce payload).  */

@@ -68,6 +68,7 @@ SIGNATURES = {
     "sbfe_norm_workspace_bytes": (_I64, [_I64, _I64, _I32]),
     "sbfe_norm_stats": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, _I32, _F, _P, _F, _P, _P, _P,
                                   _I64, _P]),
+    "sbfe_norm_stats_static": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, _I32, _F, _P, _F, _P, _P, _P]),
     "sbfe_norm_reduce": (C.c_int, [_P, _P, _I64, _I32, _P, _P]),
     "sbfe_norm_update": (C.c_int, [_P, _I32, _I32, _F, _P, _P, _P]),
     "sbfe_norm_apply": (C.c_int, [_P, _I64, _I64, _I32, _P, _P, _I32, _P, _F, _P, _P]),
@@ -78,7 +79,7 @@ SIGNATURES = {
     "sbfe_mean": (C.c_int, [_P, _I64, _P, _P, _I64, _P]),
 }
 
-ABI_VERSION = 8
+ABI_VERSION = 9
 _lock = threading.Lock()
 _lib = None
 

@@ -29,6 +29,8 @@ int launch_post(const float*, int64_t, int64_t, int, const sbfe_maxkey_t*, float
 int64_t norm_workspace_bytes(int64_t, int64_t, int);
 int launch_norm_stats(const float*, const float*, int64_t, int64_t, int, int, int, float,
                       const sbfe_maxkey_t*, float, float*, float*, void*, int64_t, cudaStream_t);
+int launch_norm_stats_static(const float*, const float*, int64_t, int64_t, int, int, int, float,
+                             const sbfe_maxkey_t*, float, float*, float*, cudaStream_t);
 int launch_norm_reduce(const float*, const float*, int64_t, int, float*, cudaStream_t);
 int launch_norm_update(const float*, int, int, float, float*, float*, cudaStream_t);
 int launch_norm_apply(const float*, int64_t, int64_t, int, const float*, const float*, int,
@@ -70,6 +72,9 @@ const char* sbfe_error_string(int code) {
   if (code == SBFE_E_INVAL) return "sbfe: invalid argument";
   if (code == SBFE_E_TOOBIG) return "sbfe: dimension too large for the kernels";
   if (code == SBFE_E_NOSPACE) return "sbfe: workspace too small";
+  if (code == SBFE_E_STATIC_LIMIT)
+    return "sbfe: request needs more scratch than the built-in array of the no-allocation entry "
+           "point holds (SBFE_NORM_STATIC_WS_BYTES); use the variant that takes a workspace";
   if (code > 0) return cudaGetErrorString((cudaError_t)code);
   return "sbfe: unknown error";
 }
@@ -233,6 +238,17 @@ int sbfe_norm_stats(const float* d_x, const float* d_lengths, int64_t B, int64_t
   if (!d_x || !d_lengths || !d_mean || !d_std || !d_ws) return SBFE_E_INVAL;
   return launch_norm_stats(d_x, d_lengths, B, T, F, mean_norm, std_norm, eps, d_utt_max, top_db,
                            d_mean, d_std, d_ws, ws_bytes, (cudaStream_t)stream);
+}
+
+int sbfe_norm_stats_static(const float* d_x, const float* d_lengths, int64_t B, int64_t T, int32_t F,
+                           int32_t mean_norm, int32_t std_norm, float eps,
+                           const sbfe_maxkey_t* d_utt_max, float top_db, float* d_mean,
+                           float* d_std, void* stream) {
+  if (B < 0 || T < 0 || F < 0) return SBFE_E_INVAL;
+  if (B == 0 || F == 0) return 0;
+  if (!d_x || !d_lengths || !d_mean || !d_std) return SBFE_E_INVAL;
+  return launch_norm_stats_static(d_x, d_lengths, B, T, F, mean_norm, std_norm, eps, d_utt_max,
+                                  top_db, d_mean, d_std, (cudaStream_t)stream);
 }
 
 int sbfe_norm_reduce(const float* d_mean, const float* d_std, int64_t B, int32_t F, float* d_cur,

@@ -6,6 +6,8 @@
 //   apply   : (x - mean) / std over ALL T frames, padding too     (:1035, 1088, 1116)
 // The reference does this with a Python loop over sentences (a host sync per
 // sentence); here nothing leaves the device.
+#include <atomic>
+
 #include "common.cuh"
 
 namespace sbfe {
@@ -347,6 +349,36 @@ int launch_norm_stats(const float* x, const float* lengths, int64_t B, int64_t T
   return launch_pdl(norm_stats_final_kernel, dim3((unsigned)((B * F + 255) / 256)), dim3(256), 0,
                     stream, x, lengths, B, T, F, mean_norm, std_norm, eps, utt_max, top_db,
                     (const double2*)ws, (unsigned)chunks, mean, stdv);
+}
+
+// ---- the no-allocation variant of launch_norm_stats ---------------------------------------------
+// Same two kernels; the partial sums live in a file-scope device array instead of a caller-provided
+// workspace, for callers that cannot allocate (CUDA graph capture, serving loops).  Every GPU that
+// loads the library holds these SBFE_NORM_STATIC_WS_BYTES until the process exits.  The array's
+// name is a host-side stand-in, not a device address: the address comes from
+// cudaGetSymbolAddress, once per device, with that device current.  Nothing has to start at zero:
+// norm_stats_partial_kernel writes every (utterance, chunk, column) slot that
+// norm_stats_final_kernel reads.  All calls share the array, so two calls that overlap on the
+// GPU (different streams) race; calls on one stream are ordered.
+static __device__ __align__(256) unsigned char g_norm_static_ws[SBFE_NORM_STATIC_WS_BYTES];
+
+int launch_norm_stats_static(const float* x, const float* lengths, int64_t B, int64_t T, int F,
+                             int mean_norm, int std_norm, float eps, const sbfe_maxkey_t* utt_max,
+                             float top_db, float* mean, float* stdv, cudaStream_t stream) {
+  if (B == 0 || F == 0) return 0;
+  if (norm_workspace_bytes(B, T, F) > (int64_t)SBFE_NORM_STATIC_WS_BYTES) return SBFE_E_STATIC_LIMIT;
+  static std::atomic<void*> addr[64];   // per device; the only transition is null -> the address
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  void* ws = (dev >= 0 && dev < 64) ? addr[dev].load(std::memory_order_acquire) : nullptr;
+  if (ws == nullptr) {
+    e = cudaGetSymbolAddress(&ws, g_norm_static_ws);
+    if (e != cudaSuccess || ws == nullptr) return e != cudaSuccess ? (int)e : (int)cudaErrorInvalidSymbol;
+    if (dev >= 0 && dev < 64) addr[dev].store(ws, std::memory_order_release);
+  }
+  return launch_norm_stats(x, lengths, B, T, F, mean_norm, std_norm, eps, utt_max, top_db, mean,
+                           stdv, ws, (int64_t)SBFE_NORM_STATIC_WS_BYTES, stream);
 }
 
 int launch_norm_stats_prefix(const float* x, const float* lengths, int64_t B, int64_t T, int F,
