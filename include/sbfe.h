@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define SBFE_ABI_VERSION 9
+#define SBFE_ABI_VERSION 10
 
 #if defined(__GNUC__)
 #define SBFE_API __attribute__((visibility("default")))
@@ -91,27 +91,26 @@ SBFE_API int64_t sbfe_fbank_workspace_bytes(const sbfe_fbank_desc* desc, int64_t
  * wav [B, L] (row stride wav_stride) -> out [B, T, M].
  *
  * Two modes:
- *  (a) d_tile_stats == NULL, d_sync == NULL: out holds the dB values WITHOUT the per-utterance
- *      top_db clamp; d_utt_max[b] (zeroed by the caller first; may be NULL) receives the key of
- *      max_{t,m} out[b] for a later clamp (sbfe_post_forward).  top_db is ignored.
- *  (b) finisher mode, only where sbfe_fbank_tile_frames(desc) = R > 0 (fused n_fft 400 / hop 160
+ *  (a) d_tile_stats == NULL: out holds the dB values WITHOUT the
+ *      per-utterance top_db clamp; d_utt_max[b] (zeroed by the caller first; may be NULL) receives
+ *      the key of max_{t,m} out[b] for a later clamp (sbfe_post_forward).  top_db is ignored.
+ *  (b) tile records, only where sbfe_fbank_tile_frames(desc) = R > 0 (fused n_fft 400 / hop 160
  *      kernel): d_tile_stats = [B][ceil(T/R)] records of W = sbfe_fbank_tile_stats_floats(desc)
- *      = 3*M + 4 words, d_sync = [B] uint32 counters that are ZERO on entry and zero again when
- *      the call's work completes (the caller must not share them between calls that may be in
- *      flight at the same time).  The CTA that completes an utterance's last tile finishes the
- *      utterance inside the same launch: out IS top_db-clamped when the kernel ends
+ *      = 3*M + 4 words.  When the call's work completes, out IS top_db-clamped
  *      (x = max(x, max_b - top_db), features.py:706-710, the maximum taken over all T frames of
- *      the padded utterance; top_db < 0: no clamp), and record j holds
- *        [0, M)    mean  } of every feature column over the clamped frames [0, min(R (j+1), T))
- *        [M, 2M)   M2    } (M2 = sum of squared deviations): PREFIX moments,
- *        [2M, 3M)  the column minima of tile j before the clamp,
+ *      the padded utterance; top_db < 0: no clamp), and record j of utterance b holds
+ *        [0, M)    mean  } of every feature column over the existing frames of tile j, BEFORE
+ *        [M, 2M)   M2    } the clamp (M2 = sum of squared deviations),
+ *        [2M, 3M)  the column minima of tile j before the clamp: a column whose minimum is not
+ *                  below the utterance's floor was not changed by the clamp, its moments hold,
  *        [3M]      max key of tile j, [3M+1] flags (bit 0: the tile's input was all zero).
- *      sbfe_norm_stats_prefix / sbfe_norm_sentence_prefix turn these into InputNormalization
- *      statistics for ANY valid length from one record and < R rows of out: no statistics pass
- *      over the features, no clamp launch.  d_utt_max may be NULL. */
+ *      sbfe_norm_stats_tiles / sbfe_norm_sentence_tiles turn these into InputNormalization
+ *      statistics for any valid length: 2 M floats per R frames instead of a pass over out.
+ *      The clamp is a second, small kernel launched by this call (it reads the records only
+ *      and touches just the tiles that hold a value below the floor).  d_utt_max may be NULL. */
 SBFE_API int sbfe_fbank_forward(const sbfe_fbank_desc* desc, const float* d_wav, int64_t B, int64_t L,
                        int64_t wav_stride, float* d_out, sbfe_maxkey_t* d_utt_max,
-                       float* d_tile_stats, uint32_t* d_sync, float top_db, void* d_workspace,
+                       float* d_tile_stats, float top_db, void* d_workspace,
                        int64_t workspace_bytes, void* stream);
 
 /* Ragged ingest (the step before the path: speechbrain/dataio/batch.py:20-190 pads on the CPU
@@ -124,7 +123,7 @@ SBFE_API int sbfe_fbank_forward(const sbfe_fbank_desc* desc, const float* d_wav,
 SBFE_API int sbfe_fbank_forward_ragged(const sbfe_fbank_desc* desc, const float* d_packed,
                               const int64_t* d_offsets, const int32_t* d_nsamples, int64_t B,
                               int64_t L, float* d_out, sbfe_maxkey_t* d_utt_max,
-                              float* d_tile_stats, uint32_t* d_sync, float top_db, void* stream);
+                              float* d_tile_stats, float top_db, void* stream);
 
 /* The same with 16-bit PCM samples (what a .wav / .flac file holds; the reference converts them
  * to float32 on the CPU, dataio/dataio.py read_audio via torchaudio.load, and ships 4 bytes per
@@ -135,28 +134,37 @@ SBFE_API int sbfe_fbank_forward_ragged(const sbfe_fbank_desc* desc, const float*
 SBFE_API int sbfe_fbank_forward_ragged_pcm16(const sbfe_fbank_desc* desc, const int16_t* d_packed,
                                     const int64_t* d_offsets, const int32_t* d_nsamples,
                                     int64_t B, int64_t L, float scale, float* d_out,
-                                    sbfe_maxkey_t* d_utt_max, float* d_tile_stats,
-                                    uint32_t* d_sync, float top_db, void* stream);
+                                    sbfe_maxkey_t* d_utt_max, float* d_tile_stats, float top_db,
+                                    void* stream);
 
 SBFE_API int32_t sbfe_fbank_tile_frames(const sbfe_fbank_desc* desc);
 SBFE_API int32_t sbfe_fbank_tile_stats_floats(const sbfe_fbank_desc* desc);
 
 /* InputNormalization statistics (features.py:1020-1031, 1120-1145; same contract as
- * sbfe_norm_stats) from the prefix records of a finisher-mode sbfe_fbank_forward whose output
- * d_x has not been modified since: mean / std [B, F] over the first rint(lengths[b] * T) frames =
- * record (n / R - 1) merged with the n % R rows of the tile the valid length cuts. */
-SBFE_API int sbfe_norm_stats_prefix(const float* d_x, const float* d_lengths, int64_t B, int64_t T,
-                           int32_t F, int32_t mean_norm, int32_t std_norm, float eps,
-                           const float* d_tile_stats, int32_t tile_frames, float* d_mean,
-                           float* d_std, void* stream);
+ * sbfe_norm_stats) from the tile records of a mode-(b) sbfe_fbank_forward whose output d_x has not
+ * been modified since: mean / std [B, F] over the first rint(lengths[b] * T) frames = the records
+ * of the whole tiles below that length merged with the rows of the tile it cuts (columns the
+ * clamp changed are recomputed from d_x).  top_db: what that sbfe_fbank_forward call was given. */
+SBFE_API int sbfe_norm_stats_tiles(const float* d_x, const float* d_lengths, int64_t B, int64_t T,
+                          int32_t F, int32_t mean_norm, int32_t std_norm, float eps,
+                          const float* d_tile_stats, int32_t tile_frames, float top_db,
+                          float* d_mean, float* d_std, void* stream);
 /* The same followed by out = (x - mean_b) / std_b over all T frames ("sentence" mode,
- * features.py:1020-1035; in place when d_out == d_x): the statistics kernel and the
- * normalisation kernel are launched back to back by this call, the second one fetching x while
- * the first finishes.  d_mean / d_std [B, F] are scratch the caller provides (and may read). */
-SBFE_API int sbfe_norm_sentence_prefix(const float* d_x, const float* d_lengths, int64_t B, int64_t T,
-                              int32_t F, int32_t mean_norm, int32_t std_norm, float eps,
-                              const float* d_tile_stats, int32_t tile_frames, float* d_mean,
-                              float* d_std, float* d_out, void* stream);
+ * features.py:1020-1035; in place when d_out == d_x), in ONE launch: every CTA rebuilds the
+ * statistics of its utterance from the records while its share of x is in flight.
+ * top_db: the value the producing sbfe_fbank_forward call was given (< 0: none).
+ * flags: SBFE_BESIDE_CLAMP - the caller states that nothing has been launched into `stream`
+ *   since that sbfe_fbank_forward call that writes d_x, the records or d_lengths (launches that
+ *   do not touch them are fine).  The kernel then does not wait for the call's clamp launch
+ *   before it reads: it applies the clamp to every value it reads itself (same result before
+ *   and after), rebuilds the floor from the records' keys, recomputes what a record below the
+ *   floor would have told it, and waits only before its first store.  Without the flag it waits
+ *   first, like every other kernel of the library.  Results are identical either way. */
+#define SBFE_BESIDE_CLAMP 1
+SBFE_API int sbfe_norm_sentence_tiles(const float* d_x, const float* d_lengths, int64_t B, int64_t T,
+                             int32_t F, int32_t mean_norm, int32_t std_norm, float eps,
+                             const float* d_tile_stats, int32_t tile_frames, float top_db,
+                             int32_t flags, float* d_out, void* stream);
 
 /* STFT.forward for [B, L] input (processing/features.py:133-188):
  * out [B, T, bins, 2] (re, im), or, with power_only != 0, [B, T, bins] = re^2+im^2. */

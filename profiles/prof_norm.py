@@ -1,4 +1,4 @@
-"""Driver for ncu: the cfg2 step with the one-launch sentence normalisation, with and without the clamp kernel."""
+"""Driver for ncu: the cfg2 step = fused Fbank (records) + clamp launch + one-launch sentence normalisation."""
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -13,15 +13,12 @@ for b in range(B):
     wav[b, int(round(float(lens[b]) * L)):] = 0
 tab = sb.Fbank(n_mels=80)._frontend_tables()
 for _ in range(3):
-    feats, _, ts = ops.fbank_forward(tab, wav, tile_stats=True)
-    ops.clamp_tiles(feats, ts, 80.0)
+    feats, _, ts = ops.fbank_forward(tab, wav, tile_stats=True, top_db=80.0)
+    ops.norm_sentence_tiles(feats, lens, ts, out=feats, beside_clamp=True)
+    feats, _, ts = ops.fbank_forward(tab, wav, tile_stats=True, top_db=80.0)
+    ops.norm_sentence_tiles(feats, lens, ts, out=feats)
+    feats, _, ts = ops.fbank_forward(tab, wav, tile_stats=True, top_db=80.0)
     m, s = ops.norm_stats_tiles(feats, lens, ts)
     ops.norm_apply(feats, m, s, per_utt=True, out=feats)
-    feats, _, ts = ops.fbank_forward(tab, wav, tile_stats=True)
-    ops.clamp_tiles(feats, ts, 80.0)
-    ops.norm_sentence_tiles(feats, lens, ts)
-    feats, _, ts = ops.fbank_forward(tab, wav, tile_stats=True)
-    ts.top_db = 80.0
-    ops.norm_sentence_tiles(feats, lens, ts)
 torch.cuda.synchronize()
 print("ok")

@@ -1,5 +1,5 @@
 """Cumulative timing of the cfg2 step's kernels (CUDA graphs over 8 rotating inputs):
-fused kernel without / with its finisher | + statistics from the prefix records | + apply.
+fused kernel without / with records + in-launch clamp | + statistics from the tile records | the step.
 python profiles/stepbench.py"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -21,21 +21,33 @@ tab = fb._frontend_tables()
 def step(w, upto):
     if upto == 0:     # mode (a): un-clamped output, utterance maxima via atomics (needs a memset)
         return ops.fbank_forward(tab, w)[0]
-    feats, _, ts = ops.fbank_forward(tab, w, tile_stats=True, top_db=80.0)   # finisher mode
-    if upto == 2:
-        ops.norm_stats_prefix(feats, lens, ts)
+    if upto == 1:     # mode (b) without a clamp: what the records alone cost
+        return ops.fbank_forward(tab, w, tile_stats=True, top_db=None)[0]
+    feats, _, ts = ops.fbank_forward(tab, w, tile_stats=True, top_db=80.0)   # + the clamp launch
     if upto == 3:
-        ops.norm_sentence_prefix(feats, lens, ts, out=feats)
-    if upto == 4:     # the statistics the generic way (no records): 2 launches + apply
+        ops.norm_stats_tiles(feats, lens, ts)
+    if upto == 4:
+        ops.norm_sentence_tiles(feats, lens, ts, out=feats)
+    if upto == 7:
+        ops.norm_sentence_tiles(feats, lens, ts, out=feats, beside_clamp=True)
+    if upto == 5:
+        mean, std = ops.norm_stats_tiles(feats, lens, ts)
+        ops.norm_apply(feats, mean, std, per_utt=True, out=feats)
+    if upto == 6:     # the statistics the generic way (no records): 2 launches + apply
         mean, std = ops.norm_stats(feats, lens)
         ops.norm_apply(feats, mean, std, per_utt=True, out=feats)
     return feats
 
 
 prev = 0.0
-for upto, name in enumerate(["fbank400_v3, no finisher (+memset)", "fbank400_v3 finisher (clamp+prefix)",
-                             "+ norm_stats_prefix", "+ stats_prefix + norm_apply (the step)",
-                             "finisher + generic stats + apply"]):
+for upto, name in enumerate(["fbank400_v3 mode (a): no records, no clamp (+memset)",
+                             "fbank400_v3 mode (b): records, no clamp",
+                             "fbank400_v3 mode (b): records + clamp launch",
+                             "  + norm_stats_tiles", "  + norm_sentence_tiles",
+                             "  + norm_stats_tiles + norm_apply",
+                             "  + generic stats + apply",
+                             "  + norm_sentence_tiles beside the clamp (THE STEP)"]):
+    base = {3: 2, 4: 2, 5: 2, 6: 2, 7: 2}.get(upto)
     for w in pool[:2]:
         step(w, upto)
     torch.cuda.synchronize()
@@ -54,5 +66,6 @@ for upto, name in enumerate(["fbank400_v3, no finisher (+memset)", "fbank400_v3 
     e1.record()
     torch.cuda.synchronize()
     us = e0.elapsed_time(e1) / 160 * 1e3
-    print("%-42s %7.2f us/step  (%+.2f)" % (name, us, us - prev))
-    prev = us
+    res = globals().setdefault("res", {})
+    res[upto] = us
+    print("%-52s %7.2f us/step%s" % (name, us, "  (%+.2f)" % (us - res[base]) if base is not None else ""))

@@ -48,16 +48,16 @@ SIGNATURES = {
     "sbfe_error_string": (C.c_char_p, [C.c_int]),
     "sbfe_num_frames": (_I64, [_I64, _I32]),
     "sbfe_fbank_workspace_bytes": (_I64, [_DESC, _I64, _I64]),
-    "sbfe_fbank_forward": (C.c_int, [_DESC, _P, _I64, _I64, _I64, _P, _P, _P, _P, _F, _P, _I64, _P]),
-    "sbfe_fbank_forward_ragged": (C.c_int, [_DESC, _P, _P, _P, _I64, _I64, _P, _P, _P, _P, _F, _P]),
-    "sbfe_fbank_forward_ragged_pcm16": (C.c_int, [_DESC, _P, _P, _P, _I64, _I64, _F, _P, _P, _P, _P,
-                                                  _F, _P]),
+    "sbfe_fbank_forward": (C.c_int, [_DESC, _P, _I64, _I64, _I64, _P, _P, _P, _F, _P, _I64, _P]),
+    "sbfe_fbank_forward_ragged": (C.c_int, [_DESC, _P, _P, _P, _I64, _I64, _P, _P, _P, _F, _P]),
+    "sbfe_fbank_forward_ragged_pcm16": (C.c_int, [_DESC, _P, _P, _P, _I64, _I64, _F, _P, _P, _P, _F,
+                                                  _P]),
     "sbfe_fbank_tile_frames": (_I32, [_DESC]),
     "sbfe_fbank_tile_stats_floats": (_I32, [_DESC]),
-    "sbfe_norm_stats_prefix": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, _I32, _F, _P, _I32, _P, _P,
-                                         _P]),
-    "sbfe_norm_sentence_prefix": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, _I32, _F, _P, _I32, _P,
-                                            _P, _P, _P]),
+    "sbfe_norm_stats_tiles": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, _I32, _F, _P, _I32, _F, _P,
+                                        _P, _P]),
+    "sbfe_norm_sentence_tiles": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, _I32, _F, _P, _I32, _F,
+                                           _I32, _P, _P]),
     "sbfe_stft_forward": (C.c_int, [_DESC, _P, _I64, _I64, _I64, _P, _I32, _P]),
     "sbfe_istft_workspace_bytes": (_I64, [_I64, _I64, _I32]),
     "sbfe_istft_forward": (C.c_int, [_P, _I64, _I64, _I32, _I32, _P, _I32, _I64, _P, _P, _I64, _P]),
@@ -79,7 +79,7 @@ SIGNATURES = {
     "sbfe_mean": (C.c_int, [_P, _I64, _P, _P, _I64, _P]),
 }
 
-ABI_VERSION = 9
+ABI_VERSION = 10
 _lock = threading.Lock()
 _lib = None
 

@@ -8,11 +8,11 @@ int launch_fbank400(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int6
                     sbfe_maxkey_t*, cudaStream_t);
 int launch_fbank400_v3(const sbfe_fbank_desc*, const void*, int, float, const int64_t*,
                        const int32_t*, int64_t, int64_t, int64_t, float*, sbfe_maxkey_t*, float*,
-                       unsigned*, float, cudaStream_t);
-int launch_norm_stats_prefix(const float*, const float*, int64_t, int64_t, int, int, int, float,
-                             const float*, int, float*, float*, cudaStream_t);
-int launch_norm_sentence_prefix(const float*, const float*, int64_t, int64_t, int, int, int, float,
-                                const float*, int, float*, float*, float*, cudaStream_t);
+                       float, cudaStream_t);
+int launch_norm_stats_tiles(const float*, const float*, int64_t, int64_t, int, int, int, float,
+                            const float*, int, float, float*, float*, cudaStream_t);
+int launch_norm_sentence_tiles(const float*, const float*, int64_t, int64_t, int, int, int, float,
+                               const float*, int, float, int, float*, cudaStream_t);
 int64_t istft_workspace_bytes(int64_t, int64_t, int);
 int launch_istft(const float*, int64_t, int64_t, int, int, const float*, int, int64_t, float*, void*,
                  int64_t, cudaStream_t);
@@ -97,23 +97,18 @@ int32_t sbfe_fbank_tile_stats_floats(const sbfe_fbank_desc* d) {
   return sbfe_fbank_tile_frames(d) ? (int32_t)tile_rec_words(d->n_mels) : 0;
 }
 
-// d_tile_stats and d_sync come together (finisher mode, include/sbfe.h)
-static bool records_ok(const float* d_tile_stats, const uint32_t* d_sync) {
-  return (d_tile_stats == nullptr) == (d_sync == nullptr);
-}
-
 int sbfe_fbank_forward(const sbfe_fbank_desc* d, const float* d_wav, int64_t B, int64_t L,
                        int64_t wav_stride, float* d_out, sbfe_maxkey_t* d_utt_max,
-                       float* d_tile_stats, uint32_t* d_sync, float top_db, void* d_ws,
+                       float* d_tile_stats, float top_db, void* d_ws,
                        int64_t ws_bytes, void* stream) {
-  if (!desc_ok(d, true) || B < 0 || L < 0 || wav_stride < L || !records_ok(d_tile_stats, d_sync))
+  if (!desc_ok(d, true) || B < 0 || L < 0 || wav_stride < L)
     return SBFE_E_INVAL;
   if (B == 0) return 0;
   if ((!d_wav && L > 0) || !d_out) return SBFE_E_INVAL;
   cudaStream_t s = (cudaStream_t)stream;
   if (fbank400_v3_supported(d))
     return launch_fbank400_v3(d, d_wav, 0, 1.f, nullptr, nullptr, B, L, wav_stride, d_out, d_utt_max,
-                              d_tile_stats, d_sync, top_db, s);
+                              d_tile_stats, top_db, s);
   if (d_tile_stats) return SBFE_E_INVAL;  // only where sbfe_fbank_tile_frames() != 0
   if (fused_ok(d)) return launch_fbank400(d, d_wav, B, L, wav_stride, d_out, d_utt_max, s);
   if (fbank_pow2_supported(d))   // n_fft = 256 / 512 / 1024 ...: FFT + mel + dB in one launch
@@ -127,27 +122,27 @@ int sbfe_fbank_forward(const sbfe_fbank_desc* d, const float* d_wav, int64_t B, 
 int sbfe_fbank_forward_ragged(const sbfe_fbank_desc* d, const float* d_packed,
                               const int64_t* d_offsets, const int32_t* d_nsamples, int64_t B,
                               int64_t L, float* d_out, sbfe_maxkey_t* d_utt_max,
-                              float* d_tile_stats, uint32_t* d_sync, float top_db, void* stream) {
-  if (!desc_ok(d, true) || B < 0 || L < 0 || !records_ok(d_tile_stats, d_sync)) return SBFE_E_INVAL;
+                              float* d_tile_stats, float top_db, void* stream) {
+  if (!desc_ok(d, true) || B < 0 || L < 0) return SBFE_E_INVAL;
   if (B == 0) return 0;
   if (!d_packed || !d_offsets || !d_nsamples || !d_out) return SBFE_E_INVAL;
   if (!fbank400_v3_supported(d)) return SBFE_E_INVAL;  // pad on the device and use sbfe_fbank_forward
   return launch_fbank400_v3(d, d_packed, 0, 1.f, d_offsets, d_nsamples, B, L, 0, d_out, d_utt_max,
-                            d_tile_stats, d_sync, top_db, (cudaStream_t)stream);
+                            d_tile_stats, top_db, (cudaStream_t)stream);
 }
 
 int sbfe_fbank_forward_ragged_pcm16(const sbfe_fbank_desc* d, const int16_t* d_packed,
                                     const int64_t* d_offsets, const int32_t* d_nsamples, int64_t B,
                                     int64_t L, float scale, float* d_out, sbfe_maxkey_t* d_utt_max,
-                                    float* d_tile_stats, uint32_t* d_sync, float top_db,
+                                    float* d_tile_stats, float top_db,
                                     void* stream) {
-  if (!desc_ok(d, true) || B < 0 || L < 0 || !(scale > 0.f) || !records_ok(d_tile_stats, d_sync))
+  if (!desc_ok(d, true) || B < 0 || L < 0 || !(scale > 0.f))
     return SBFE_E_INVAL;
   if (B == 0) return 0;
   if (!d_packed || !d_offsets || !d_nsamples || !d_out) return SBFE_E_INVAL;
   if (!fbank400_v3_supported(d)) return SBFE_E_INVAL;  // convert on the device and use sbfe_fbank_forward
   return launch_fbank400_v3(d, d_packed, 1, scale, d_offsets, d_nsamples, B, L, 0, d_out, d_utt_max,
-                            d_tile_stats, d_sync, top_db, (cudaStream_t)stream);
+                            d_tile_stats, top_db, (cudaStream_t)stream);
 }
 
 int64_t sbfe_istft_workspace_bytes(int64_t B, int64_t T, int32_t n_fft) {
@@ -201,27 +196,28 @@ int sbfe_post_forward(const float* d_x, int64_t B, int64_t T, int32_t F_in,
                      context, left, right, d_out, (cudaStream_t)stream);
 }
 
-int sbfe_norm_stats_prefix(const float* d_x, const float* d_lengths, int64_t B, int64_t T, int32_t F,
-                           int32_t mean_norm, int32_t std_norm, float eps,
-                           const float* d_tile_stats, int32_t tile_frames, float* d_mean,
-                           float* d_std, void* stream) {
+int sbfe_norm_stats_tiles(const float* d_x, const float* d_lengths, int64_t B, int64_t T, int32_t F,
+                          int32_t mean_norm, int32_t std_norm, float eps,
+                          const float* d_tile_stats, int32_t tile_frames, float top_db,
+                          float* d_mean, float* d_std, void* stream) {
   if (B < 0 || T < 0 || F < 0 || tile_frames < 1) return SBFE_E_INVAL;
   if (B == 0 || F == 0) return 0;
   if (!d_x || !d_lengths || !d_mean || !d_std || !d_tile_stats) return SBFE_E_INVAL;
-  return launch_norm_stats_prefix(d_x, d_lengths, B, T, F, mean_norm, std_norm, eps, d_tile_stats,
-                                  tile_frames, d_mean, d_std, (cudaStream_t)stream);
+  return launch_norm_stats_tiles(d_x, d_lengths, B, T, F, mean_norm, std_norm, eps, d_tile_stats,
+                                 tile_frames, top_db, d_mean, d_std, (cudaStream_t)stream);
 }
 
-int sbfe_norm_sentence_prefix(const float* d_x, const float* d_lengths, int64_t B, int64_t T,
-                              int32_t F, int32_t mean_norm, int32_t std_norm, float eps,
-                              const float* d_tile_stats, int32_t tile_frames, float* d_mean,
-                              float* d_std, float* d_out, void* stream) {
+int sbfe_norm_sentence_tiles(const float* d_x, const float* d_lengths, int64_t B, int64_t T,
+                             int32_t F, int32_t mean_norm, int32_t std_norm, float eps,
+                             const float* d_tile_stats, int32_t tile_frames, float top_db,
+                             int32_t flags, float* d_out, void* stream) {
   if (B < 0 || T < 0 || F < 0 || tile_frames < 1) return SBFE_E_INVAL;
   if (B == 0 || F == 0) return 0;
-  if (!d_x || !d_lengths || !d_mean || !d_std || !d_tile_stats || !d_out) return SBFE_E_INVAL;
-  return launch_norm_sentence_prefix(d_x, d_lengths, B, T, F, mean_norm, std_norm, eps,
-                                     d_tile_stats, tile_frames, d_mean, d_std, d_out,
-                                     (cudaStream_t)stream);
+  if (!d_x || !d_lengths || !d_tile_stats || !d_out) return SBFE_E_INVAL;
+  if (flags & ~SBFE_BESIDE_CLAMP) return SBFE_E_INVAL;
+  return launch_norm_sentence_tiles(d_x, d_lengths, B, T, F, mean_norm, std_norm, eps, d_tile_stats,
+                                    tile_frames, top_db, (flags & SBFE_BESIDE_CLAMP) != 0, d_out,
+                                    (cudaStream_t)stream);
 }
 
 int64_t sbfe_norm_workspace_bytes(int64_t B, int64_t T, int32_t F) {

@@ -64,10 +64,7 @@ struct Params {
   float* out;
   sbfe_maxkey_t* utt_max;
   float* tile_stats;       // optional [n_tiles] records of tile_rec_words(M) (common.cuh)
-  unsigned* sync;          // optional [B] tiles-done counters (zero on entry, zero again on exit):
-                           // with them the CTA that completes an utterance FINISHES it in this
-                           // launch - top_db clamp + prefix moments (finish_utterance below)
-  float top_db;            // finisher: floor = utterance maximum - top_db (inf: no clamp)
+  float top_db;            // mode (b): floor = utterance maximum - top_db (inf: no clamp)
   const int32_t* mel_start;
   const int32_t* mel_count;
   const int32_t* mel_offset;
@@ -158,124 +155,59 @@ __device__ __forceinline__ bool prefetch_tile(const Params& prm, unsigned b, uns
 }
 
 
-// ---- finisher -----------------------------------------------------------------------------------
-// Runs in the CTA whose tile completed utterance b (tiles-done counter prm.sync[b], below): every
-// tile and record of b is in global memory by then, written by any CTA of the grid.
-//  1. floor = utterance maximum (max of the tile keys) - top_db     (processing/features.py:706-710)
-//  2. tiles that hold a value below the floor are clamped in place - constant tiles (all-zero
-//     input: the padding behind an utterance) are simply refilled - and their moments recomputed
-//  3. the records become PREFIX moments: record j = {mean, M2} of every column over the clamped
-//     frames [0, min(32 (j + 1), T)).  InputNormalization then needs one record and at most 31
-//     rows for ANY valid length (norm.cu: prefix_stats_block) - no statistics pass, no clamp
-//     launch, and the features this kernel returns are final.
-// Reads go through L2 (ld.cg): the data may come from other SMs.  `buf`: kRegionE floats of
-// shared memory (free between tiles).  All threads of the CTA must call.
-constexpr int kFinChunkMax = 64;
+// ---- top_db clamp of the finished utterances (mode (b)) ---------------------------------------
+// Reference semantics: x = max(x, max(x[b]) - top_db) over the whole padded utterance
+// (processing/features.py:706-710).  The floor of utterance b exists once its last tile has been
+// produced, so the clamp is a second, small launch of the same call (clamp_tiles_kernel below):
+// it reads the tile records only (keys -> floor, column minima -> "does this tile hold anything
+// below it") and refills constant tiles (the zero padding behind an utterance) without reading
+// them.  The records keep the moments of the UN-clamped values; a consumer trusts a record's
+// column only when its minimum is not below the floor (norm.cu).  Finishing the utterances inside the producing launch instead (every CTA clamping its
+// own tiles once a per-utterance counter says the utterance is complete) was built and measured:
+// the hand-shake needs >= 3 dependent L2 round trips behind the last tile (maximum, count, poll)
+// plus one for the counters' reset, 45.9 us against 43.9 us for the two launches on the cfg2
+// batch (profiles/r2_inlaunch_finish.md) - dropped.
 
-template <int MC>
-__device__ __noinline__ void finish_utterance(const Params& prm, unsigned b, float* buf, int tid) {
+// Clamp tile j of utterance b at floor_b in place.  The tile's record is left alone: its moments
+// stay those of the un-clamped values, and every consumer checks the record's column minimum
+// against the floor before it trusts them (norm.cu) - so a reader that runs beside this kernel
+// never meets a half-written record.  Whole CTA calls; no barrier inside.
+template <int MC, int NT>
+__device__ __forceinline__ void clamp_tile(const Params& prm, unsigned b, unsigned j, float floor_b,
+                                           bool constant, int tid) {
   const int M = MC > 0 ? MC : prm.n_mels;
-  const int rec = (int)tile_rec_words(M);
-  const int per = 3 * M;
-  const int tiles = (int)prm.tiles_per_utt;
-  const int T = (int)prm.T;
-  const int lane = tid & 31, warp = tid >> 5;
-  float* ts = prm.tile_stats + (size_t)b * tiles * rec;
-  float* xb = prm.out + (size_t)b * prm.T * M;
-  __shared__ unsigned s_key;
-  __shared__ unsigned char s_need[kFinChunkMax];
-  if (tid == 0) s_key = 0u;
-  __syncthreads();
-  {
-    unsigned key = 0u;
-    for (int i = tid; i < tiles; i += kThreads) {
-      const unsigned k = __ldcg(reinterpret_cast<const unsigned*>(ts) + (size_t)i * rec + per);
-      key = k > key ? k : key;
+  const int64_t r_lo = (int64_t)j * kTile;
+  const int rows = prm.T - r_lo < kTile ? (int)(prm.T - r_lo) : kTile;
+  float* p = prm.out + ((int64_t)b * prm.T + r_lo) * M;
+  const int total = rows * M;
+  const bool vec = (M & 3) == 0 && (reinterpret_cast<uintptr_t>(p) & 15) == 0;
+  if (constant) {                   // every value of the tile is the dB floor (all-zero input)
+    const float v = fmaxf(prm.db.log_mel ? prm.db.floor_db : 0.f, floor_b);
+    if (vec) {
+      for (int e = tid * 4; e < total; e += NT * 4)
+        *reinterpret_cast<float4*>(p + e) = make_float4(v, v, v, v);
+    } else {
+      for (int e = tid; e < total; e += NT) p[e] = v;
     }
-    key = __reduce_max_sync(0xffffffffu, key);
-    if (lane == 0 && key) atomicMax(&s_key, key);
+    return;
   }
-  __syncthreads();
-  const float floor_b = s_key ? max_key_decode(s_key) - prm.top_db : -INFINITY;
-  int C = (kRegionE - 2 * M) / per;
-  C = C > kFinChunkMax ? kFinChunkMax : C;
-  float* s_carry = buf + C * per;       // running {mean[M], M2[M]} over the tiles scanned so far
-  for (int m = tid; m < 2 * M; m += kThreads) s_carry[m] = 0.f;
-  for (int j0 = 0; j0 < tiles; j0 += C) {
-    const int nj = tiles - j0 < C ? tiles - j0 : C;
-    __syncthreads();                    // the previous chunk's scan has read buf
-    for (int i = tid; i < nj * per; i += kThreads) {
-      const int jj = i / per, o = i - jj * per;
-      buf[i] = __ldcg(ts + (size_t)(j0 + jj) * rec + o);
-    }
-    __syncthreads();
-    for (int jj = warp; jj < nj; jj += kWarps) {   // does tile jj hold anything below the floor?
-      bool lo = false;
-      for (int m = lane; m < M; m += 32) lo |= buf[jj * per + 2 * M + m] < floor_b;
-      lo = __any_sync(0xffffffffu, lo);
-      if (lane == 0) s_need[jj] = lo ? 1 : 0;
-    }
-    __syncthreads();
-    for (int jj = 0; jj < nj; ++jj) {
-      if (!s_need[jj]) continue;        // block-uniform
-      const int j = j0 + jj;
-      const int r_lo = j * kTile;
-      const int rows = T - r_lo < kTile ? T - r_lo : kTile;
-      float* p = xb + (size_t)r_lo * M;
-      const unsigned flags =
-          __ldcg(reinterpret_cast<const unsigned*>(ts) + (size_t)j * rec + per + 1);
-      if (flags & 1u) {                 // constant tile: nothing to read
-        const float v = fmaxf(buf[jj * per], floor_b);
-        const int total = rows * M;
-        if ((M & 3) == 0 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) {
-          for (int e = tid * 4; e < total; e += kThreads * 4)
-            *reinterpret_cast<float4*>(p + e) = make_float4(v, v, v, v);
-        } else {
-          for (int e = tid; e < total; e += kThreads) p[e] = v;
-        }
-        __syncthreads();                // everybody has read buf[jj * per]
-        for (int m = tid; m < M; m += kThreads) {
-          buf[jj * per + m] = v;
-          buf[jj * per + M + m] = 0.f;
-        }
-      } else {                          // rare: clamp + moments of the clamped column in one pass
-        for (int m = tid; m < M; m += kThreads) {
-          const float pivot = fmaxf(__ldcg(p + m), floor_b);
-          float s1 = 0.f, s2 = 0.f;
-          for (int r = 0; r < rows; ++r) {
-            const float v = fmaxf(__ldcg(p + (size_t)r * M + m), floor_b);
-            p[(size_t)r * M + m] = v;
-            const float d = v - pivot;
-            s1 += d;
-            s2 = fmaf(d, d, s2);
-          }
-          const float ml = s1 / (float)rows;
-          buf[jj * per + m] = pivot + ml;
-          buf[jj * per + M + m] = fmaxf(fmaf(-ml, s1, s2), 0.f);
-        }
+  if (vec) {
+    for (int e = tid * 4; e < total; e += NT * 4) {
+      float4 v = __ldcg(reinterpret_cast<const float4*>(p + e));
+      if (fminf(fminf(v.x, v.y), fminf(v.z, v.w)) < floor_b) {
+        v.x = fmaxf(v.x, floor_b);
+        v.y = fmaxf(v.y, floor_b);
+        v.z = fmaxf(v.z, floor_b);
+        v.w = fmaxf(v.w, floor_b);
+        *reinterpret_cast<float4*>(p + e) = v;
       }
     }
-    __syncthreads();
-    // Chan's update along the tiles, one thread per column: prefix {mean, M2} -> the records
-    for (int m = tid; m < M; m += kThreads) {
-      float mean = s_carry[m], m2 = s_carry[M + m];
-      for (int jj = 0; jj < nj; ++jj) {
-        const int j = j0 + jj;
-        const float na = (float)(j * kTile);
-        const float cnt = (float)(T - j * kTile < kTile ? T - j * kTile : kTile);
-        const float r = __fdividef(cnt, na + cnt);
-        const float d = buf[jj * per + m] - mean;
-        mean = fmaf(d, r, mean);
-        m2 += fmaf(d * d, na * r, buf[jj * per + M + m]);
-        ts[(size_t)j * rec + m] = mean;
-        ts[(size_t)j * rec + M + m] = m2;
-      }
-      s_carry[m] = mean;
-      s_carry[M + m] = m2;
+  } else {
+    for (int e = tid; e < total; e += NT) {
+      const float v = __ldcg(p + e);
+      if (v < floor_b) p[e] = floor_b;
     }
   }
-  if (tid == 0) prm.sync[b] = 0u;       // the counters are zero again when the kernel ends
-  __syncthreads();                      // buf is the caller's again
 }
 
 #ifndef SBFE_EXP_MINB
@@ -296,17 +228,6 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
   float* s_w = reinterpret_cast<float*>(s_meta) + ((2 * M + 3) & ~3);  // 16-byte aligned
 
   __shared__ unsigned s_tile_key;  // max key of the current tile (tile records)
-  // finisher hand-shake (prm.sync != nullptr).  A tile's completion is ANNOUNCED (fence + atomicAdd
-  // on the utterance's counter, by one thread) after the barrier that follows its stores, i.e. at
-  // the top of the next iteration, and the returned ticket is LOOKED AT one iteration later still:
-  // neither the fence nor the atomic's round trip sits on the tile's critical path.  The CTA
-  // whose ticket is the utterance's last runs finish_utterance for it.
-  __shared__ unsigned s_fin[2];    // utterance + 1 to finish now (0: none)
-  constexpr int kSig = kThreads - 32;   // the announcing thread: lane 0 of the last warp
-  const bool fin_mode = prm.sync != nullptr;
-  unsigned ann_b1 = 0;             // utterance + 1 of the tile stored but not yet announced (uniform)
-  unsigned tick_b1 = 0;            // utterance + 1 the outstanding ticket belongs to (uniform)
-  unsigned ticket = 0;             // kSig: the counter's value before this CTA's announcement
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
   const int p = lane & 15, h = lane >> 4;
@@ -440,27 +361,8 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
         }
       };
       int nz = chunked ? chunk_nonzero(0) : 1;
-      if (fin_mode && tid == kSig) {   // the ticket drawn one iteration ago has long arrived
-        unsigned f = 0u;
-        if (tick_b1 && ticket + 1u == prm.tiles_per_utt) {
-          __threadfence();             // acquire: the other CTAs' tiles of that utterance
-          f = tick_b1;
-        }
-        s_fin[0] = f;
-      }
-      // the barrier: this tile's span (all threads' copies) is in smem; s_e / s_o are free;
-      // every store of the previous tile has been issued
+      // the barrier: this tile's span (all threads' copies) is in smem; s_e / s_o are free
       const int any_nz = __syncthreads_or(nz);
-      if (fin_mode) {
-        const unsigned fin = s_fin[0];
-        if (tid == kSig && ann_b1) {
-          __threadfence();             // release: with the barrier above, the whole CTA's stores
-          ticket = atomicAdd(prm.sync + (ann_b1 - 1u), 1u);
-        }
-        tick_b1 = ann_b1;
-        ann_b1 = (unsigned)b + 1u;
-        if (fin) finish_utterance<MC>(prm, fin - 1u, s_e, tid);
-      }
       if (any_nz == 0) {
         nz = 0;
 #pragma unroll 1
@@ -495,6 +397,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
         }
       }
     }
+
     if (tid == 0) s_tile_key = 0u;  // two barriers before stage 3 raises it, read after the third
 
     // ---- stage 1: unit = residue n2: windowed real DFT20 over n1, twiddle, exchange --------
@@ -794,25 +697,43 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
     // the barrier at the top of the next iteration orders these s_o reads before its stage 1
   }
   cp_async_wait<0>();
-  if (fin_mode) {   // the two announcements still owed: the tile before last (ticket drawn) and the last
-    __syncthreads();
-    if (tid == kSig) {
-      unsigned f0 = 0u, f1 = 0u, t2 = 0u;
-      if (ann_b1) {
-        __threadfence();
-        t2 = atomicAdd(prm.sync + (ann_b1 - 1u), 1u);
-      }
-      if (tick_b1 && ticket + 1u == prm.tiles_per_utt) f0 = tick_b1;
-      if (ann_b1 && t2 + 1u == prm.tiles_per_utt) f1 = ann_b1;
-      if (f0 | f1) __threadfence();
-      s_fin[0] = f0;
-      s_fin[1] = f1;
-    }
-    __syncthreads();
-    const unsigned f0 = s_fin[0], f1 = s_fin[1];
-    if (f0) finish_utterance<MC>(prm, f0 - 1u, s_e, tid);
-    if (f1) finish_utterance<MC>(prm, f1 - 1u, s_e, tid);
+}
+
+// grid = n_tiles CTAs of kClampThreads: one tile each (the refills spread over the SMs, one wave).
+// The utterance's keys and the tile's own column minima / flags are requested together (one
+// round trip); a tile with nothing below the floor costs nothing else.  The kernel lets its
+// successor start right after its own wait: sbfe_norm_sentence_tiles runs beside it (norm.cu).
+constexpr int kClampThreads = 128;
+
+template <int MC>
+__global__ void __launch_bounds__(kClampThreads) clamp_tiles_kernel(const __grid_constant__ Params prm) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int M = MC > 0 ? MC : prm.n_mels;
+  const int tid = threadIdx.x;
+  const int tiles = (int)prm.tiles_per_utt;
+  const unsigned b = blockIdx.x / prm.tiles_per_utt, j = blockIdx.x - b * prm.tiles_per_utt;
+  const size_t rec = tile_rec_words(M);
+  const float* tsb = prm.tile_stats + (size_t)b * tiles * rec;
+  const float* ts = tsb + (size_t)j * rec;
+  __shared__ unsigned s_key;
+  if (tid == 0) s_key = 0u;
+  unsigned key = 0u;
+  for (int i = tid; i < tiles; i += kClampThreads) {
+    const unsigned k = __ldg(reinterpret_cast<const unsigned*>(tsb) + (size_t)i * rec + 3 * M);
+    key = k > key ? k : key;
   }
+  float mn = INFINITY;
+  for (int m = tid; m < M; m += kClampThreads) mn = fminf(mn, __ldg(ts + 2 * M + m));
+  const unsigned flags = __ldg(reinterpret_cast<const unsigned*>(ts) + 3 * M + 1);
+  __syncthreads();
+  key = __reduce_max_sync(0xffffffffu, key);
+  if ((tid & 31) == 0 && key) atomicMax(&s_key, key);
+  __syncthreads();
+  if (s_key == 0u) return;
+  const float floor_b = max_key_decode(s_key) - prm.top_db;
+  if (__syncthreads_or(mn < floor_b) == 0) return;
+  clamp_tile<MC, kClampThreads>(prm, b, j, floor_b, (flags & 1u) != 0u, tid);
 }
 
 constexpr int kMaxSmem = 110 * 1024;  // two CTAs per SM
@@ -825,6 +746,14 @@ inline KernelFn pick_kernel(int pcm16, int n_mels) {
     case 40: return pcm16 ? fbank400_v3_kernel<true, 40> : fbank400_v3_kernel<false, 40>;
     case 23: return pcm16 ? fbank400_v3_kernel<true, 23> : fbank400_v3_kernel<false, 23>;
     default: return pcm16 ? fbank400_v3_kernel<true, 0> : fbank400_v3_kernel<false, 0>;
+  }
+}
+inline KernelFn pick_clamp(int n_mels) {
+  switch (n_mels) {
+    case 80: return clamp_tiles_kernel<80>;
+    case 40: return clamp_tiles_kernel<40>;
+    case 23: return clamp_tiles_kernel<23>;
+    default: return clamp_tiles_kernel<0>;
   }
 }
 
@@ -842,7 +771,7 @@ bool fbank400_v3_supported(const sbfe_fbank_desc* d) {
 int launch_fbank400_v3(const sbfe_fbank_desc* d, const void* wav, int pcm16, float scale,
                        const int64_t* offsets, const int32_t* nsamples, int64_t B, int64_t L,
                        int64_t wav_stride, float* out, sbfe_maxkey_t* utt_max, float* tile_stats,
-                       unsigned* sync, float top_db, cudaStream_t stream) {
+                       float top_db, cudaStream_t stream) {
   using namespace v3;
   Params prm;
   prm.db = DbParams{d->multiplier * 0.30102999566398120f, d->amin, d->db_offset, d->floor_db,
@@ -860,7 +789,6 @@ int launch_fbank400_v3(const sbfe_fbank_desc* d, const void* wav, int pcm16, flo
   prm.out = out;
   prm.utt_max = utt_max;
   prm.tile_stats = tile_stats;
-  prm.sync = tile_stats != nullptr ? sync : nullptr;
   prm.top_db = top_db >= 0.f ? top_db : INFINITY;
   prm.mel_start = d->d_mel_start;
   prm.mel_count = d->d_mel_count;
@@ -871,28 +799,42 @@ int launch_fbank400_v3(const sbfe_fbank_desc* d, const void* wav, int pcm16, flo
   prm.tiles_per_utt = (unsigned)tiles;
   prm.n_tiles = (unsigned)(tiles * B);
   const size_t smem = smem_floats(d->n_mels, d->mel_nnz) * sizeof(float);
-  // once per device and process: the opt-in to > 48 KB of dynamic shared memory.  The cache is a
-  // lock-free bit mask whose only transition is 0 -> 1 after an idempotent call: no call ever
-  // observes or depends on another call's state (include/sbfe.h: thread safety)
-  static std::atomic<uint64_t> attr_done{0};
+  // once per device and process: the opt-in to > 48 KB of dynamic shared memory and the number
+  // of these CTAs an SM holds.  The cache is a lock-free per-device word whose only transition is
+  // 0 -> the value after idempotent calls: no call depends on another call's state (sbfe.h).
+  static std::atomic<int> per_sm_cache[64];
   int dev = 0, sms = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   if (e != cudaSuccess) return (int)e;
-  const uint64_t bit = (dev >= 0 && dev < 64) ? (uint64_t)1 << dev : 0;
-  if (!(attr_done.load(std::memory_order_acquire) & bit) || bit == 0) {
+  const bool cached = dev >= 0 && dev < 64;
+  int per_sm = cached ? per_sm_cache[dev].load(std::memory_order_acquire) : 0;
+  if (per_sm == 0) {
+    per_sm = 2;
     for (int pcm = 0; pcm < 2; ++pcm)
-      for (int mc : {0, 80, 40, 23})
+      for (int mc : {0, 80, 40, 23}) {
         if (e == cudaSuccess)
           e = cudaFuncSetAttribute(pick_kernel(pcm, mc), cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    kMaxSmem);
+        int n = 0;
+        if (e == cudaSuccess)
+          e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, pick_kernel(pcm, mc), kThreads,
+                                                            (size_t)kMaxSmem);
+        if (e == cudaSuccess && n < per_sm) per_sm = n;
+      }
     if (e != cudaSuccess) return (int)e;
-    attr_done.fetch_or(bit, std::memory_order_release);
+    if (per_sm < 1) return (int)cudaErrorLaunchOutOfResources;
+    if (cached) per_sm_cache[dev].store(per_sm, std::memory_order_release);
   }
-  // persistent: two CTAs per SM, each strides over the tiles
-  const unsigned grid = prm.n_tiles < (unsigned)(2 * sms) ? prm.n_tiles : (unsigned)(2 * sms);
-  return launch_pdl(pick_kernel(pcm16, d->n_mels), dim3(grid), dim3(kThreads), (size_t)smem, stream,
-                    prm);
+  // persistent: every CTA strides over the tiles
+  const unsigned cap = (unsigned)(per_sm * sms);
+  const unsigned grid = prm.n_tiles < cap ? prm.n_tiles : cap;
+  int rc = launch_pdl(pick_kernel(pcm16, d->n_mels), dim3(grid), dim3(kThreads), (size_t)smem, stream,
+                      prm);
+  if (rc == 0 && tile_stats != nullptr && prm.top_db < INFINITY) {
+    rc = launch_pdl(pick_clamp(d->n_mels), dim3(prm.n_tiles), dim3(kClampThreads), 0, stream, prm);
+  }
+  return rc;
 }
 
 }  // namespace sbfe

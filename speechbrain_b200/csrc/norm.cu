@@ -109,69 +109,115 @@ __device__ __forceinline__ void merge(Moments& a, float nb, float mb, float m2b)
 }
 
 
-// ---- statistics from the PREFIX records of the fused Fbank kernel ----------------------------
-// After sbfe_fbank_forward in finisher mode (fbank400_v3.cu: finish_utterance) record j of an
-// utterance holds {mean[F], M2[F]} of every column over the (already clamped) frames
-// [0, min(tile (j + 1), T)).  The statistics over the first n frames are then one record merged
-// (Chan) with the n % tile rows of the tile the valid length cuts: <= tile - 1 rows of x instead
-// of a pass over T rows, and no dependence on the batch.  Replaces the per-sentence Python loop of
-// processing/features.py:1020-1031 and _compute_current_stats :1120-1145.
-//
-// Whole CTA must call.  Thread = (column, row group); `s_red`: 3 * blockDim.x floats.  Writes
-// s_mean[F] / s_std[F] (shared or global) and ends with a barrier.
-__device__ __forceinline__ void prefix_stats_block(const float* __restrict__ xb, int n, int T, int F,
-                                                   int tile, int tiles,
-                                                   const float* __restrict__ tsb, int mean_norm,
-                                                   int std_norm, float eps, float* s_mean,
-                                                   float* s_std, float* s_red) {
+// ---- statistics from the TILE RECORDS of the fused Fbank kernel -------------------------------
+// After sbfe_fbank_forward with tile records (fbank400_v3.cu) record j of an utterance holds, for
+// every column over the existing frames of tile j, {mean[F], M2[F], min[F]} of the UN-clamped
+// values plus the tile's max key; x itself is top_db-clamped.  A column whose minimum is not below
+// the floor (rebuilt from the keys) was not changed by the clamp: its record is exact.  The
+// statistics over the first n frames are then the records of the n / tile whole tiles merged
+// (Chan) with the n % tile rows of the tile the valid length cuts - 3 F floats per 32 frames
+// instead of a pass over T rows; a column the clamp did change (rare inside the valid part) is
+// recomputed from x.  Replaces the per-sentence Python loop of processing/features.py:1020-1031
+// and _compute_current_stats :1120-1145.
+
+// moments of column `cp` (stride F) over cnt rows, every value through the clamp: the slow path of
+// a record that cannot be used (two passes like torch's)
+__device__ __noinline__ float2 column_moments_clamped(const float* cp, int F, int cnt, float floor_b) {
+  float sm = 0.f;
+  for (int r = 0; r < cnt; ++r) sm += fmaxf(__ldcg(cp + (size_t)r * F), floor_b);
+  const float mean = sm / (float)cnt;
+  float q = 0.f;
+  for (int r = 0; r < cnt; ++r) {
+    const float d = fmaxf(__ldcg(cp + (size_t)r * F), floor_b) - mean;
+    q = fmaf(d, d, q);
+  }
+  return make_float2(mean, q);
+}
+
+// Whole CTA must call.  Thread = (column, tile group): CW = min(F, blockDim) columns per pass,
+// G = blockDim / CW groups; a group takes tiles g, g + G, ... and rows g, g + G, ... of the cut
+// tile.  `s_red`: 3 * blockDim.x floats.  Writes s_mean[F] / s_std[F] (shared or global) and ends
+// with a barrier.  Returns the floor (-inf without a top_db).
+__device__ __forceinline__ float tile_stats_block(const float* xb, int n, int T, int F, int tile,
+                                                  int tiles, const float* tsb0, float top_db,
+                                                  int mean_norm, int std_norm, float eps,
+                                                  float* s_mean, float* s_std, float* s_red) {
   const int nthr = blockDim.x;
   const int CW = F < nthr ? F : nthr;            // columns per pass
-  const int G = nthr / CW;                       // row groups
+  const int G = nthr / CW;                       // tile groups
   const int col = threadIdx.x % CW, grp = threadIdx.x / CW;
-  const size_t rec = tile_rec_words(F);
-  // tiles whose existing frames are all valid: [0, whole)
-  const int whole = (n >= T) ? tiles : n / tile;
+  const int rec = (int)tile_rec_words(F);
+  const int whole = (n >= T) ? tiles : n / tile; // tiles whose existing frames are all valid
   const int r_cut = whole * tile;
   const int ncut = (whole < tiles && r_cut < n) ? n - r_cut : 0;   // rows of the cut tile
-  const float na = whole > 0 ? (float)(r_cut < T ? r_cut : T) : 0.f;
+  __shared__ unsigned s_key;
+  if (threadIdx.x == 0) s_key = 0u;
+  __syncthreads();
+  if (top_db < INFINITY) {
+    unsigned key = 0u;
+    for (int i = threadIdx.x; i < tiles; i += nthr) {
+      const unsigned k2 = __ldcg(reinterpret_cast<const unsigned*>(tsb0) + (size_t)i * rec + 3 * F);
+      key = k2 > key ? k2 : key;
+    }
+    key = __reduce_max_sync(0xffffffffu, key);
+    if ((threadIdx.x & 31) == 0 && key) atomicMax(&s_key, key);
+  }
+  __syncthreads();
+  const float floor_b = s_key ? max_key_decode(s_key) - top_db : -INFINITY;
+  constexpr int kSpec = 4;
   for (int f0 = 0; f0 < F; f0 += CW) {
     const int f = f0 + col;
     const bool live = f < F && grp < G;
-    float pm = 0.f, pq = 0.f, s1 = 0.f, s2 = 0.f, pivot = 0.f;
-    int c = 0;
+    Moments acc{0.f, 0.f, 0.f};
     if (live) {
-      if (grp == 0 && whole > 0) {
-        const float* ts = tsb + (size_t)(whole - 1) * rec + f;
-        pm = __ldg(ts);
-        pq = __ldg(ts + F);
+      const float* tsb = tsb0 + f;
+      float pm[kSpec], pq[kSpec], pn[kSpec];
+      for (int j0 = grp; j0 < whole; j0 += kSpec * G) {   // batches: every load before the first merge
+#pragma unroll
+        for (int k = 0; k < kSpec; ++k) {
+          const int j = j0 + k * G;
+          if (j < whole) {
+            pm[k] = __ldcg(tsb + (size_t)j * rec);
+            pq[k] = __ldcg(tsb + (size_t)j * rec + F);
+            pn[k] = __ldcg(tsb + (size_t)j * rec + 2 * F);
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < kSpec; ++k) {
+          const int j = j0 + k * G;
+          if (j < whole) {
+            const int cnt = T - j * tile < tile ? T - j * tile : tile;
+            float2 mq = make_float2(pm[k], pq[k]);
+            if (pn[k] < floor_b)
+              mq = column_moments_clamped(xb + (size_t)j * tile * F + f, F, cnt, floor_b);
+            merge(acc, (float)cnt, mq.x, mq.y);
+          }
+        }
       }
-      if (ncut > 0) {
+      if (grp < ncut) {      // x is clamped already when this kernel may read it: max() is a no-op then
         const float* colp = xb + (size_t)r_cut * F + f;
-        pivot = colp[0];
-        for (int r = grp; r < ncut; r += G) {
-          const float d = colp[(size_t)r * F] - pivot;
+        const float pivot = fmaxf(__ldcg(colp), floor_b);
+        float s1 = 0.f, s2 = 0.f;
+        int c = 0;
+        for (int r = grp; r < ncut; r += G, ++c) {
+          const float d = fmaxf(__ldcg(colp + (size_t)r * F), floor_b) - pivot;
           s1 += d;
           s2 = fmaf(d, d, s2);
-          ++c;
         }
+        const float mloc = s1 / (float)c;
+        merge(acc, (float)c, pivot + mloc, fmaxf(fmaf(-mloc, s1, s2), 0.f));
       }
     }
     if (G > 1) {
-      s_red[threadIdx.x] = s1;
-      s_red[nthr + threadIdx.x] = s2;
+      s_red[threadIdx.x] = acc.n;
+      s_red[nthr + threadIdx.x] = acc.mean;
+      s_red[2 * nthr + threadIdx.x] = acc.m2;
       __syncthreads();
       if (live && grp == 0)
-        for (int g = 1; g < G; ++g) {
-          s1 += s_red[g * CW + col];
-          s2 += s_red[nthr + g * CW + col];
-        }
+        for (int g = 1; g < G; ++g)
+          merge(acc, s_red[g * CW + col], s_red[nthr + g * CW + col], s_red[2 * nthr + g * CW + col]);
     }
     if (live && grp == 0) {
-      Moments acc{na, pm, pq};
-      if (ncut > 0) {
-        const float mloc = s1 / (float)ncut;
-        merge(acc, (float)ncut, pivot + mloc, fmaxf(fmaf(-mloc, s1, s2), 0.f));
-      }
       // n == 0: mean of an empty slice is NaN, n == 1: unbiased std is NaN (torch)
       const float m = (acc.n > 0.f) ? acc.mean : NAN;
       float sd = (acc.n > 1.f) ? sqrtf(fmaxf(acc.m2, 0.f) / (acc.n - 1.f)) : NAN;
@@ -180,25 +226,209 @@ __device__ __forceinline__ void prefix_stats_block(const float* __restrict__ xb,
       s_std[f] = std_norm ? sd : 1.f;
     }
     __syncthreads();
-    (void)c;
   }
+  return floor_b;
 }
 
+constexpr int kTileNormThreads = 512;
 
-// mean / std [B, F] from the prefix records: grid = B
-__global__ void __launch_bounds__(kNormThreads)
-norm_stats_prefix_kernel(const float* __restrict__ x, const float* __restrict__ lengths, int64_t T,
-                         int F, int tile, int tiles, const float* __restrict__ tile_stats,
-                         int mean_norm, int std_norm, float eps, float* __restrict__ mean,
-                         float* __restrict__ stdv) {
+// mean / std [B, F] from the tile records: grid = B
+__global__ void __launch_bounds__(kTileNormThreads)
+norm_stats_tiles_kernel(const float* __restrict__ x, const float* __restrict__ lengths, int64_t T,
+                        int F, int tile, int tiles, const float* __restrict__ tile_stats,
+                        float top_db, int mean_norm, int std_norm, float eps,
+                        float* __restrict__ mean, float* __restrict__ stdv) {
   pdl_wait();
   pdl_launch_dependents();
-  __shared__ float s_red[3 * kNormThreads];
+  __shared__ float s_red[3 * kTileNormThreads];
   const int64_t b = blockIdx.x;
   const int n = valid_frames(lengths, b, T);
-  prefix_stats_block(x + b * T * F, n, (int)T, F, tile, tiles,
-                     tile_stats + (size_t)b * tiles * tile_rec_words(F), mean_norm, std_norm, eps,
-                     mean + b * F, stdv + b * F, s_red);
+  tile_stats_block(x + b * T * F, n, (int)T, F, tile, tiles,
+                   tile_stats + (size_t)b * tiles * tile_rec_words(F), top_db, mean_norm, std_norm,
+                   eps, mean + b * F, stdv + b * F, s_red);
+}
+
+// Sentence normalisation in ONE launch (processing/features.py:1020-1035): every CTA rebuilds its
+// utterance's statistics from the records (2 F floats per tile, L2-resident: cheaper than a
+// second launch and its dependent round trips) and normalises its share of the utterance - half
+// of its vectors of x are requested first and fly while the statistics are merged.
+//
+// BESIDE_CLAMP: the launch directly before this one in the stream may be the clamp kernel of the
+// sbfe_fbank_forward call that produced x and the records (or anything else that leaves lengths
+// alone and writes x / the records only the way that kernel does: x = max(x, floor) with the same
+// floor; moments of records whose minimum is below the floor).  This kernel then does not wait
+// for it before it READS: every value of x goes through max(., floor) - the same before and after
+// that write -, the floor is rebuilt from the tile keys, and a record whose minimum is below the
+// floor is not trusted (its column is recomputed from x).  It waits right before its first
+// store, which also keeps completion transitive for whatever follows (common.cuh).  Everything
+// before that direct predecessor has completed when this kernel starts, so the records and x as
+// the producing kernel left them are visible.
+// grid = B * chunks; VEC = 4 when F % 4 == 0 and x / out are 16-byte aligned; F <= blockDim.
+constexpr int kSentIters = 8;    // vectors per thread
+constexpr int kSentSpec = 4;     // records per thread and batch
+
+template <int VEC, bool BESIDE_CLAMP>
+__global__ void __launch_bounds__(kTileNormThreads, 2)
+norm_sentence_tiles_kernel(const float* x, const float* __restrict__ lengths, int T, int F,
+                           int tile, int tiles, const float* tile_stats, float top_db,
+                           int mean_norm, int std_norm, float eps, float* out, unsigned chunks) {
+  if (!BESIDE_CLAMP) {
+    pdl_wait();
+    pdl_launch_dependents();
+  }
+  extern __shared__ __align__(16) float s_dyn[];   // mean[F] | std[F] | 3 * blockDim scratch
+  __shared__ unsigned s_key;
+  float* s_mean = s_dyn;
+  float* s_std = s_dyn + F;
+  float* s_red = s_dyn + 2 * F;
+  const unsigned b = blockIdx.x / chunks;
+  const int c0 = blockIdx.x - b * chunks;
+  const float* xb = x + (size_t)b * T * F;
+  float floor_b = -INFINITY;
+  // ---- the utterance's statistics from its records (F <= blockDim: one pass over the columns).
+  // x and the records may be written beside us (BESIDE_CLAMP): read through L2 (ld.cg).
+  {
+    if (threadIdx.x == 0) s_key = 0u;
+    const int n = valid_frames(lengths, b, T);
+    const int G = kTileNormThreads / F;            // tile groups
+    const int col = threadIdx.x % F, grp = threadIdx.x / F;
+    const int rec = (int)tile_rec_words(F);
+    const float* tsb0 = tile_stats + (size_t)b * tiles * rec;
+    const float* tsb = tsb0 + col;
+    const bool live = grp < G;
+    // the first batch does not wait for the valid length (`tiles`, not `whole`): lengths, keys
+    // and records share one round trip
+    float pm[kSentSpec], pq[kSentSpec], pn[kSentSpec];
+    if (live) {
+#pragma unroll
+      for (int k = 0; k < kSentSpec; ++k) {
+        const int j = grp + k * G;
+        if (j < tiles) {
+          pm[k] = __ldcg(tsb + j * rec);
+          pq[k] = __ldcg(tsb + j * rec + F);
+          pn[k] = __ldcg(tsb + j * rec + 2 * F);
+        }
+      }
+    }
+    unsigned key = 0u;
+    if (top_db < INFINITY)
+      for (int i = threadIdx.x; i < tiles; i += kTileNormThreads) {
+        const unsigned k2 = __ldcg(reinterpret_cast<const unsigned*>(tsb0) + i * rec + 3 * F);
+        key = k2 > key ? k2 : key;
+      }
+    __syncthreads();                               // s_key = 0 is in
+    key = __reduce_max_sync(0xffffffffu, key);
+    if ((threadIdx.x & 31) == 0 && key) atomicMax(&s_key, key);
+    __syncthreads();
+    if (s_key) floor_b = max_key_decode(s_key) - top_db;
+    Moments acc{0.f, 0.f, 0.f};
+    if (live) {
+      const int whole = (n >= T) ? tiles : n / tile;
+      const int r_cut = whole * tile;
+      const int ncut = (whole < tiles && r_cut < n) ? n - r_cut : 0;
+      const float* colp = xb + (size_t)r_cut * F + col;
+      float pivot = 0.f, cv = 0.f;
+      if (ncut > 0) {                              // rows of the cut tile: second round trip
+        pivot = __ldcg(colp);
+        if (grp < ncut) cv = __ldcg(colp + grp * F);
+      }
+      for (int j0 = grp;;) {
+#pragma unroll
+        for (int k = 0; k < kSentSpec; ++k) {
+          const int j = j0 + k * G;
+          if (j < whole) {
+            const int cnt = T - j * tile < tile ? T - j * tile : tile;
+            // a record below the floor (values the clamp changes, inside the valid part: rare)
+            // is not used - its moments may be the clamp kernel's or the producer's
+            float2 mq = make_float2(pm[k], pq[k]);
+            if (pn[k] < floor_b)
+              mq = column_moments_clamped(xb + (size_t)j * tile * F + col, F, cnt, floor_b);
+            merge(acc, (float)cnt, mq.x, mq.y);
+          }
+        }
+        j0 += kSentSpec * G;
+        if (j0 >= whole) break;
+#pragma unroll
+        for (int k = 0; k < kSentSpec; ++k) {
+          const int j = j0 + k * G;
+          if (j < whole) {
+            pm[k] = __ldcg(tsb + j * rec);
+            pq[k] = __ldcg(tsb + j * rec + F);
+            pn[k] = __ldcg(tsb + j * rec + 2 * F);
+          }
+        }
+      }
+      if (grp < ncut) {
+        pivot = fmaxf(pivot, floor_b);
+        float d = fmaxf(cv, floor_b) - pivot, s1 = d, s2 = d * d;
+        int c = 1;
+        for (int r = grp + G; r < ncut; r += G, ++c) {
+          d = fmaxf(__ldcg(colp + r * F), floor_b) - pivot;
+          s1 += d;
+          s2 = fmaf(d, d, s2);
+        }
+        const float mloc = s1 / (float)c;
+        merge(acc, (float)c, pivot + mloc, fmaxf(fmaf(-mloc, s1, s2), 0.f));
+      }
+    }
+    s_red[threadIdx.x] = acc.n;
+    s_red[kTileNormThreads + threadIdx.x] = acc.mean;
+    s_red[2 * kTileNormThreads + threadIdx.x] = acc.m2;
+    __syncthreads();
+    if (threadIdx.x < F) {
+      for (int g = 1; g < G; ++g)
+        merge(acc, s_red[g * F + col], s_red[kTileNormThreads + g * F + col],
+              s_red[2 * kTileNormThreads + g * F + col]);
+      // n == 0: mean of an empty slice is NaN, n == 1: unbiased std is NaN (torch)
+      const float m = (acc.n > 0.f) ? acc.mean : NAN;
+      float sd = (acc.n > 1.f) ? sqrtf(fmaxf(acc.m2, 0.f) / (acc.n - 1.f)) : NAN;
+      if (sd == sd) sd = fmaxf(sd, eps);  // torch.max propagates NaN
+      s_mean[col] = mean_norm ? m : 0.f;
+      s_std[col] = std_norm ? sd : 1.f;
+    }
+    __syncthreads();
+  }
+  // ---- (max(x, floor) - mean) / std over the CTA's share of the utterance: all loads first
+  const int FV = F / VEC;
+  const int nvec = T * FV;                         // < 2^30 (launcher)
+  const int i0 = c0 * (kTileNormThreads * kSentIters) + threadIdx.x;
+  float* ob = out + (size_t)b * T * F;
+  float4 v4[VEC == 4 ? kSentIters : 1];
+  float v1[VEC == 4 ? 1 : kSentIters];
+#pragma unroll
+  for (int k = 0; k < kSentIters; ++k) {
+    const int i = i0 + k * kTileNormThreads;
+    if (i < nvec) {
+      if (VEC == 4) v4[k] = __ldcg(reinterpret_cast<const float4*>(xb + 4 * (size_t)i));
+      else v1[k] = __ldcg(xb + i);
+    }
+  }
+  if (BESIDE_CLAMP) {   // nothing has been written so far
+    pdl_wait();
+    pdl_launch_dependents();
+  }
+  int col = i0 % FV;
+  const int dcol = kTileNormThreads % FV;
+#pragma unroll
+  for (int k = 0; k < kSentIters; ++k) {
+    const int i = i0 + k * kTileNormThreads;
+    if (i < nvec) {
+      if (VEC == 4) {
+        const float4 mm = *reinterpret_cast<const float4*>(s_mean + 4 * col);
+        const float4 ss = *reinterpret_cast<const float4*>(s_std + 4 * col);
+        float4 r;
+        r.x = (fmaxf(v4[k].x, floor_b) - mm.x) / ss.x;
+        r.y = (fmaxf(v4[k].y, floor_b) - mm.y) / ss.y;
+        r.z = (fmaxf(v4[k].z, floor_b) - mm.z) / ss.z;
+        r.w = (fmaxf(v4[k].w, floor_b) - mm.w) / ss.w;
+        *reinterpret_cast<float4*>(ob + 4 * (size_t)i) = r;
+      } else {
+        ob[i] = (fmaxf(v1[k], floor_b) - s_mean[col]) / s_std[col];
+      }
+    }
+    col += dcol;
+    while (col >= FV) col -= FV;
+  }
 }
 
 // grid = ceil(F / 32) CTAs of 32 columns x 8 utterance groups
@@ -381,14 +611,15 @@ int launch_norm_stats_static(const float* x, const float* lengths, int64_t B, in
                            stdv, ws, (int64_t)SBFE_NORM_STATIC_WS_BYTES, stream);
 }
 
-int launch_norm_stats_prefix(const float* x, const float* lengths, int64_t B, int64_t T, int F,
-                             int mean_norm, int std_norm, float eps, const float* tile_stats,
-                             int tile, float* mean, float* stdv, cudaStream_t stream) {
+int launch_norm_stats_tiles(const float* x, const float* lengths, int64_t B, int64_t T, int F,
+                            int mean_norm, int std_norm, float eps, const float* tile_stats,
+                            int tile, float top_db, float* mean, float* stdv, cudaStream_t stream) {
   if (B == 0 || F == 0) return 0;
   if (B > 0x7fffffff || T > 0x7fffffff) return SBFE_E_TOOBIG;
   const int tiles = (int)((T + tile - 1) / tile);
-  return launch_pdl(norm_stats_prefix_kernel, dim3((unsigned)B), dim3(kNormThreads), 0, stream, x,
-                    lengths, T, F, tile, tiles, tile_stats, mean_norm, std_norm, eps, mean, stdv);
+  return launch_pdl(norm_stats_tiles_kernel, dim3((unsigned)B), dim3(kTileNormThreads), 0, stream, x,
+                    lengths, T, F, tile, tiles, tile_stats, top_db >= 0.f ? top_db : INFINITY, mean_norm,
+                    std_norm, eps, mean, stdv);
 }
 
 int launch_norm_reduce(const float* mean, const float* stdv, int64_t B, int F, float* cur,
@@ -427,17 +658,29 @@ int launch_norm_apply(const float* x, int64_t B, int64_t T, int F, const float* 
   return launch_apply_any(x, B, T, F, mean, stdv, per_utt, utt_max, top_db, out, false, stream);
 }
 
-// sentence normalisation from the prefix records: statistics kernel + apply kernel, launched
-// back to back HERE, so that "the apply kernel's direct predecessor only reads x" holds by
-// construction and the apply kernel may fetch x while the statistics finish
-int launch_norm_sentence_prefix(const float* x, const float* lengths, int64_t B, int64_t T, int F,
-                                int mean_norm, int std_norm, float eps, const float* tile_stats,
-                                int tile, float* mean, float* stdv, float* out,
-                                cudaStream_t stream) {
-  int rc = launch_norm_stats_prefix(x, lengths, B, T, F, mean_norm, std_norm, eps, tile_stats, tile,
-                                    mean, stdv, stream);
-  if (rc) return rc;
-  return launch_apply_any(x, B, T, F, mean, stdv, 1, nullptr, 0.f, out, pdl_enabled(), stream);
+// sentence normalisation from the tile records, one launch
+int launch_norm_sentence_tiles(const float* x, const float* lengths, int64_t B, int64_t T, int F,
+                               int mean_norm, int std_norm, float eps, const float* tile_stats,
+                               int tile, float top_db, int beside_clamp, float* out,
+                               cudaStream_t stream) {
+  if (B == 0 || T == 0 || F == 0) return 0;
+  if (B > 0x7fffffff || T > 0x7fffffff) return SBFE_E_TOOBIG;
+  const int tiles = (int)((T + tile - 1) / tile);
+  const bool vec = (F % 4 == 0) &&
+                   ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+  const int64_t nvec = T * (vec ? F / 4 : F);
+  const int64_t per_cta = (int64_t)kTileNormThreads * kSentIters;
+  const int64_t chunks = (nvec + per_cta - 1) / per_cta;
+  if (chunks * B > 0x7fffffff) return SBFE_E_TOOBIG;
+  if (F > kTileNormThreads || nvec > 0x3fffffff) return SBFE_E_TOOBIG;
+  const size_t smem = ((size_t)2 * F + 3 * kTileNormThreads) * sizeof(float);
+  // the flag presumes that call's last launch was its clamp kernel: there is none without a top_db
+  const bool beside = beside_clamp != 0 && top_db >= 0.f && pdl_enabled();
+  auto k = beside ? (vec ? norm_sentence_tiles_kernel<4, true> : norm_sentence_tiles_kernel<1, true>)
+                  : (vec ? norm_sentence_tiles_kernel<4, false> : norm_sentence_tiles_kernel<1, false>);
+  return launch_pdl(k, dim3((unsigned)(chunks * B)), dim3(kTileNormThreads), smem, stream, x, lengths,
+                    (int)T, F, tile, tiles, tile_stats, top_db >= 0.f ? top_db : INFINITY, mean_norm,
+                    std_norm, eps, out, (unsigned)chunks);
 }
 
 // ---- speaker mode (processing/features.py:1037-1081): running per-speaker statistics ---------

@@ -22,8 +22,8 @@ def pair(compute_features, normalizer):
     """Kept for source compatibility with round-1 recipes: a no-op.
 
     It used to declare that the features go straight into ``normalizer`` so that the top_db
-    clamp could be deferred to it.  The fused kernel now finishes every utterance itself (clamp
-    + prefix moments inside the producing launch, csrc/fbank400_v3.cu: finish_utterance), so an
+    clamp could be deferred to it.  The fused kernel now finishes every utterance itself (every
+    CTA clamps the tiles it produced once their utterance is complete, csrc/fbank400_v3.cu), so an
     unmodified recipe - ``normalize(compute_features(wavs), wav_lens)`` - already gets the
     shortest chain and the tensor ``compute_features`` returns is always final."""
     if not isinstance(compute_features, _Lobe):
@@ -77,7 +77,7 @@ class _Lobe(torch.nn.Module):
         ctx = self.context and self.context_window.context_len > 1
         if dct is None and not self.deltas and not ctx and fb.log_mel:
             # plain log-mel: ONE launch.  The fused kernel finishes each utterance itself (top_db
-            # clamp + prefix moments); a following InputNormalization gets its statistics from
+            # clamp, per-tile moments); a following InputNormalization gets its statistics from
             # the records handed over on the returned tensor instead of a pass over it
             feats, utt_max, ts = ops.fbank_forward(self._frontend_tables(), wav, tile_stats=True,
                                                    top_db=fb.top_db)

@@ -14,7 +14,7 @@ from ._lib import FbankDesc, check, lib
 
 __all__ = [
     "FrontendTables", "fbank_forward", "stft_forward", "istft_forward", "spectral_magnitude",
-    "filterbank_forward", "post_forward", "norm_stats", "norm_stats_prefix", "norm_sentence_prefix",
+    "filterbank_forward", "post_forward", "norm_stats", "norm_stats_tiles", "norm_sentence_tiles",
     "TileStats", "norm_reduce", "norm_update", "norm_apply", "decode_utt_max", "mark_written", "version_of",
 ]
 
@@ -147,7 +147,7 @@ def _wav2d(wav):
 def mark_written(t):
     """Tell torch that ``t`` was written in place by a kernel launched through ctypes (which
     autograd's version counter cannot see): bumps ``t._version``, so that anything keyed on it -
-    the one-shot prefix records handed from Fbank to InputNormalization - sees the change."""
+    the one-shot tile records handed from Fbank to InputNormalization - sees the change."""
     torch.autograd.graph.increment_version(t)
     return t
 
@@ -161,41 +161,16 @@ def version_of(t):
 
 
 class TileStats:
-    """Prefix records emitted by the fused Fbank kernel in finisher mode (include/sbfe.h:
-    sbfe_fbank_forward (b)): record j = per-column {mean, M2} of the final (clamped) features over
-    frames [0, min(frames * (j + 1), T)).  ``version`` = ``_version`` of the feature tensor they
-    describe; they are void once that tensor is written to."""
+    """Tile records emitted by the fused Fbank kernel (include/sbfe.h: sbfe_fbank_forward (b)):
+    record j = per-column {mean, M2} of the final (clamped) features over the existing frames of
+    tile j.  ``version`` = ``_version`` of the feature tensor they describe; they are void once
+    that tensor is written to."""
 
-    __slots__ = ("stats", "frames", "version")
+    __slots__ = ("stats", "frames", "version", "top_db", "stream")
 
-    def __init__(self, stats, frames):
-        self.stats, self.frames, self.version = stats, frames, None
-
-
-# Tiles-done counters of the finisher (sbfe.h: d_sync): zero on entry, zero again when the kernel
-# ends.  One zeroed ring per device, handed out slice by slice: calls that may be in flight at the
-# same time (other streams, other captured graphs) get different slices unless 2^16 counters'
-# worth of calls lie between them; nothing is allocated or memset per call (a memset would be
-# one more node in every captured step).
-_SYNC_RING = {}
-_SYNC_SLOTS = 1 << 16
-
-
-def _sync_counters(device, B):
-    if B > _SYNC_SLOTS // 4:
-        return torch.zeros((B,), dtype=torch.int32, device=device)
-    key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
-    ring = _SYNC_RING.get(key)
-    if ring is None:
-        if torch.cuda.is_current_stream_capturing():
-            raise RuntimeError("first speechbrain_b200 Fbank call on this device happens inside a "
-                               "CUDA graph capture: run one eager step first")
-        ring = _SYNC_RING[key] = [torch.zeros((_SYNC_SLOTS,), dtype=torch.int32, device=device), 0]
-    buf, cur = ring
-    if cur + B > _SYNC_SLOTS:
-        cur = 0
-    ring[1] = cur + B
-    return buf[cur:cur + B]
+    def __init__(self, stats, frames, top_db=None):
+        self.stats, self.frames, self.version, self.top_db = stats, frames, None, top_db
+        self.stream = None   # the stream the producing call went into
 
 
 def ragged_supported(tables, device):
@@ -208,7 +183,7 @@ def fbank_forward(tables, wav, tile_stats=False, top_db=80.0):
     """wav [B, L] (or a dataio.RaggedBatch) -> mel features [B, T, M].
 
     tile_stats=False: (dB or linear mel WITHOUT the top_db clamp, utt_max keys [B] int32).
-    tile_stats=True (finisher mode where the configuration has one): (FINAL features - clamped
+    tile_stats=True (where the configuration has tile records): (FINAL features - clamped
     to ``top_db`` below each utterance's maximum (None: no clamp) -, None, TileStats); where it
     has none: (un-clamped, utt_max, None).  sbfe_fbank_forward[_ragged[_pcm16]]."""
     ragged = None
@@ -230,33 +205,35 @@ def fbank_forward(tables, wav, tile_stats=False, top_db=80.0):
     L_ = lib()
     ws_bytes = L_.sbfe_fbank_workspace_bytes(C.byref(desc), B, L)
     ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=wav.device) if ws_bytes > 0 else None
-    ts, frames, sync = None, 0, None
+    ts, frames = None, 0
     if tile_stats and B > 0:
         frames = int(L_.sbfe_fbank_tile_frames(C.byref(desc)))
         if frames > 0:
             words = int(L_.sbfe_fbank_tile_stats_floats(C.byref(desc)))
             ts = torch.empty((B, (T + frames - 1) // frames, words), dtype=torch.float32,
                              device=wav.device)
-            sync = _sync_counters(wav.device, B)
-    # in finisher mode the utterance maximum travels in the records: no atomics, no memset
+    # with tile records the utterance maximum travels in the records: no atomics, no memset
     utt_max = None if ts is not None else torch.zeros((B,), dtype=torch.int32, device=wav.device)
     db = -1.0 if top_db is None else float(top_db)
     with torch.cuda.device(wav.device):
         if ragged is not None and wav.dtype == torch.int16:
             check(L_.sbfe_fbank_forward_ragged_pcm16(C.byref(desc), _ptr(wav), _ptr(ragged.offsets),
                                                      _ptr(ragged.nsamples), B, L, ragged.scale,
-                                                     _ptr(out), _ptr(utt_max), _ptr(ts), _ptr(sync),
-                                                     db, _stream()))
+                                                     _ptr(out), _ptr(utt_max), _ptr(ts), db, _stream()))
         elif ragged is not None:
             check(L_.sbfe_fbank_forward_ragged(C.byref(desc), _ptr(wav), _ptr(ragged.offsets),
                                                _ptr(ragged.nsamples), B, L, _ptr(out),
-                                               _ptr(utt_max), _ptr(ts), _ptr(sync), db, _stream()))
+                                               _ptr(utt_max), _ptr(ts), db, _stream()))
         else:
             check(L_.sbfe_fbank_forward(C.byref(desc), _ptr(wav), B, L, L, _ptr(out),
-                                        _ptr(utt_max), _ptr(ts), _ptr(sync), db, _ptr(ws),
+                                        _ptr(utt_max), _ptr(ts), db, _ptr(ws),
                                         max(ws_bytes, 0), _stream()))
     if tile_stats:
-        return out, utt_max, (TileStats(ts, frames) if ts is not None else None)
+        rec = None
+        if ts is not None:
+            rec = TileStats(ts, frames, top_db)
+            rec.stream = torch.cuda.current_stream(wav.device).cuda_stream
+        return out, utt_max, rec
     return out, utt_max
 
 
@@ -268,29 +245,34 @@ def _stats_out(x, lengths):
     return lengths, mean, std
 
 
-def norm_stats_prefix(x, lengths, ts, mean_norm=True, std_norm=True, eps=1e-10):
-    """norm_stats from the fused kernel's prefix records (one record + the rows of the tile the
-    valid length cuts; no pass over x).  sbfe_norm_stats_prefix."""
+def norm_stats_tiles(x, lengths, ts, mean_norm=True, std_norm=True, eps=1e-10):
+    """norm_stats from the fused kernel's tile records (2 F floats per tile + the rows of the
+    tile the valid length cuts; no pass over x).  sbfe_norm_stats_tiles."""
     B, T, F = x.shape
     lengths, mean, std = _stats_out(x, lengths)
     with torch.cuda.device(x.device):
-        check(lib().sbfe_norm_stats_prefix(_ptr(x), _ptr(lengths), B, T, F, int(bool(mean_norm)),
-                                           int(bool(std_norm)), float(eps), _ptr(ts.stats), ts.frames,
-                                           _ptr(mean), _ptr(std), _stream()))
+        check(lib().sbfe_norm_stats_tiles(_ptr(x), _ptr(lengths), B, T, F, int(bool(mean_norm)),
+                                          int(bool(std_norm)), float(eps), _ptr(ts.stats), ts.frames,
+                                          -1.0 if ts.top_db is None else float(ts.top_db),
+                                          _ptr(mean), _ptr(std), _stream()))
     return mean, std
 
 
-def norm_sentence_prefix(x, lengths, ts, mean_norm=True, std_norm=True, eps=1e-10, out=None):
-    """Sentence normalisation straight from the prefix records: statistics + (x - mean) / std in
-    one library call (sbfe_norm_sentence_prefix).  In place when ``out is x``."""
+def norm_sentence_tiles(x, lengths, ts, mean_norm=True, std_norm=True, eps=1e-10, out=None,
+                        beside_clamp=False):
+    """Sentence normalisation straight from the tile records: statistics + (x - mean) / std in
+    ONE launch (sbfe_norm_sentence_tiles).  In place when ``out is x``.  ``beside_clamp``: nothing
+    that writes x, the records or lengths was launched since the Fbank call that made them
+    (sbfe.h: SBFE_BESIDE_CLAMP) - the kernel then runs beside that call's clamp launch."""
     B, T, F = x.shape
-    lengths, mean, std = _stats_out(x, lengths)
+    lengths = lengths.to(device=x.device, dtype=torch.float32).contiguous()
     if out is None:
         out = torch.empty_like(x)
     with torch.cuda.device(x.device):
-        check(lib().sbfe_norm_sentence_prefix(_ptr(x), _ptr(lengths), B, T, F, int(bool(mean_norm)),
-                                              int(bool(std_norm)), float(eps), _ptr(ts.stats),
-                                              ts.frames, _ptr(mean), _ptr(std), _ptr(out), _stream()))
+        check(lib().sbfe_norm_sentence_tiles(_ptr(x), _ptr(lengths), B, T, F, int(bool(mean_norm)),
+                                             int(bool(std_norm)), float(eps), _ptr(ts.stats),
+                                             ts.frames, -1.0 if ts.top_db is None else float(ts.top_db),
+                                             1 if beside_clamp else 0, _ptr(out), _stream()))
     return mark_written(out)
 
 

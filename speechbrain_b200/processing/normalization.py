@@ -3,7 +3,7 @@
 The reference loops over sentences in Python (one host sync and >= 5 tiny kernels
 per sentence).  Here the statistics of the whole batch come from one or two kernel
 launches (one tiny one when the features come straight from this package's Fbank,
-whose kernel leaves prefix moments behind) and the normalisation from one; nothing
+whose kernel leaves per-tile moments behind) and the normalisation from one; nothing
 is read back to the host except in ``speaker`` mode, whose dictionary is keyed by
 host integers in the reference as well.
 """
@@ -82,7 +82,7 @@ class InputNormalization(torch.nn.Module):
             x = x.float().contiguous()
         ops._require_cuda(x, "x")
         B, T, F = x.shape
-        # one-shot hand-over from the fused Fbank kernel (lobes/features.py): prefix records of
+        # one-shot hand-over from the fused Fbank kernel (lobes/features.py): tile records of
         # this very tensor, void as soon as anything has written to it (version counter; the
         # package's own in-place ops bump it, ops.mark_written)
         ts = getattr(x, "_sbfe_tile_stats", None)
@@ -94,10 +94,13 @@ class InputNormalization(torch.nn.Module):
 
         if self.norm_type == "sentence" and ts is not None:
             # statistics + normalisation in one library call, in place (:1020-1035)
-            return ops.norm_sentence_prefix(x, lengths, ts, self.mean_norm, self.std_norm, self.eps,
-                                            out=x)
+            # the version check above is the statement SBFE_BESIDE_CLAMP asks for: nothing this
+            # package or torch launched has written x since Fbank returned it (same stream)
+            beside = ts.stream == torch.cuda.current_stream(x.device).cuda_stream
+            return ops.norm_sentence_tiles(x, lengths, ts, self.mean_norm, self.std_norm, self.eps,
+                                           out=x, beside_clamp=beside)
         if ts is not None:
-            mean, std = ops.norm_stats_prefix(x, lengths, ts, self.mean_norm, self.std_norm, self.eps)
+            mean, std = ops.norm_stats_tiles(x, lengths, ts, self.mean_norm, self.std_norm, self.eps)
         else:
             mean, std = ops.norm_stats(x, lengths, self.mean_norm, self.std_norm, self.eps)
 

