@@ -7,7 +7,7 @@
 //
 // What changed against v2 (profiles/r1_baseline.md: 31.5 M warp-instructions, only
 // 31 % of them FP32; ALU pipe > FMA pipe):
-//  * PACKED f32x2 MATH: a thread owns TWO frames (p, p+16) of the 32-frame tile and
+//  * PACKED f32x2 MATH: a thread owns TWO frames (2p, 2p+1) of the 32-frame tile and
 //    every add/mul/fma is one FADD2/FMUL2/FFMA2 on a 64-bit register pair.
 //  * 20 EQUAL WORK UNITS IN BOTH FFT STAGES: thread = (frame pair p = lane & 15,
 //    unit s = 2*warp + (lane >> 4)); stage 1 unit = residue n2, stage 2 unit =
@@ -34,13 +34,18 @@ namespace v3 {
 #include "fbank400_tables.inc"
 
 constexpr int kTile = 32;            // frames per tile
-constexpr int kPairs = 16;           // frame pairs (p, p + 16)
+constexpr int kPairs = 16;           // frame pairs (2p, 2p + 1)
 constexpr int kUnits = 20;           // work units per stage
 constexpr int kWarps = kUnits / 2;
 constexpr int kThreads = kWarps * 32;
 constexpr int kHop = 160;
-constexpr int kPad = 2;              // (kHop + kPad) % 32 == 2: conflict-free scalar reads
-constexpr int kPitch = kHop + kPad;
+// staged waveform: hops (2q, 2q + 1) back to back, 2 floats of padding behind every PAIR of hops:
+// sample i of the span sits at i + 2 * (i / 320).  A thread's frame pair is (2p, 2p + 1) - adjacent
+// frames share 12 of their 20 samples per residue (hop = 8 * 20) - and lane p starts at p * 322:
+// banks 2p (+1 for the other half-warp's residue), conflict-free scalar reads.
+constexpr int kPad2 = 2;
+constexpr int kPitch2 = 2 * kHop + kPad2;       // 322 floats per pair of hops
+constexpr int kPass = 2 * kPitch2;              // 4 hops = one pass of the staging copy
 constexpr int kNfft = 400;
 constexpr int kBins = 201;
 constexpr int kSpan = (kTile - 1) * kHop + kNfft;                // 5360 samples per tile
@@ -92,7 +97,7 @@ __device__ __forceinline__ void cp_async_wait() {
   asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory");
 }
 
-// asynchronous copy of one tile's waveform span into `dst` (pitch kPitch per hop); samples
+// asynchronous copy of one tile's waveform span into `dst` (layout above); samples
 // outside [0, L) are zero-filled by the copy engine (src-size < cp-size).
 // Chunk c = k*kThreads + tid covers samples i = 2c, 2c+1: with 80 chunks per hop and
 // kThreads = 4*80 the thread's sample / smem offsets are base + k*{640, 648}: immediates.
@@ -117,8 +122,8 @@ __device__ __forceinline__ bool prefetch_tile(const Params& prm, unsigned b, uns
 #pragma unroll
     for (int k = 0; k < kCpIters; ++k)
       if (k * kThreads + tid < kChunks) {
-        if constexpr (PCM16) cp_async4(d + k * (4 * kPitch), src + k * (4 * kHop), 4);
-        else cp_async8(d + k * (4 * kPitch), src + k * (4 * kHop), 8);
+        if constexpr (PCM16) cp_async4(d + k * kPass, src + k * (4 * kHop), 4);
+        else cp_async8(d + k * kPass, src + k * (4 * kHop), 8);
       }
     return true;
   }
@@ -135,19 +140,19 @@ __device__ __forceinline__ bool prefetch_tile(const Params& prm, unsigned b, uns
         int n = hi - i;
         n = (i < lo || n < 0) ? 0 : (n > 2 ? 2 : n);
         const void* g = n ? (const void*)(wsrc + i) : (const void*)prm.window;
-        if constexpr (PCM16) cp_async4(d + k * (4 * kPitch), g, 2 * n);
-        else cp_async8(d + k * (4 * kPitch), reinterpret_cast<const float*>(g), 4 * n);
+        if constexpr (PCM16) cp_async4(d + k * kPass, g, 2 * n);
+        else cp_async8(d + k * kPass, reinterpret_cast<const float*>(g), 4 * n);
       }
     }
   } else if constexpr (PCM16) {
     // odd sample offset: plain 16-bit copies (ordered by the barrier that opens the tile)
     int16_t* d16 = reinterpret_cast<int16_t*>(dst);
     for (int i = tid; i < kSpan; i += kThreads)
-      d16[i + (i / kHop) * kPad] = (i >= lo && i < hi) ? wsrc[i] : (int16_t)0;
+      d16[i + (i / (2 * kHop)) * kPad2] = (i >= lo && i < hi) ? wsrc[i] : (int16_t)0;
   } else {
     for (int i = tid; i < kSpan; i += kThreads) {
       const bool ok = i >= lo && i < hi;
-      cp_async4(dst + i + (i / kHop) * kPad, ok ? (const void*)(wsrc + i) : (const void*)prm.window,
+      cp_async4(dst + i + (i / (2 * kHop)) * kPad2, ok ? (const void*)(wsrc + i) : (const void*)prm.window,
                 ok ? 4 : 0);
     }
   }
@@ -236,7 +241,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
   // ---- once per CTA: the constant tables (they are not produced by the preceding kernel, so
   // this part may overlap its tail: see pdl_wait in common.cuh), then the first prefetch ------
   const int ibase = kHop * (tid / (kHop / 2)) + 2 * (tid % (kHop / 2));
-  const int dbase = ibase + kPad * (tid / (kHop / 2));
+  const int dbase = ibase + kPad2 * (tid / kHop);   // tid / 160 = hop pair of the pass
   unsigned tile = blockIdx.x;
   // every table word this thread is responsible for is REQUESTED first and stored afterwards:
   // one global-memory round trip for the whole prologue instead of one per table
@@ -295,15 +300,8 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
   // stage-4 walk of this thread over the [frames][M] tile (vector / scalar), tile-invariant
   const int st_t4 = (tid * 4) / M, st_m4 = tid * 4 - st_t4 * M;
   const int st_dt4 = (kThreads * 4) / M, st_dm4 = kThreads * 4 - st_dt4 * M;
-  // M <= 80 (at most two vectors per thread): their shared-memory offsets, resolved once
-  const bool st_two = (M & 3) == 0 && kTile * M <= 8 * kThreads;
-  int st_so0 = st_t4 * opitch + st_m4, st_so1;
-  {
-    int t = st_t4 + st_dt4, m = st_m4 + st_dm4;
-    if (m >= M) { m -= M; ++t; }
-    st_so1 = t * opitch + m;
-  }
   const int st_t1 = tid / M, st_m1 = tid - st_t1 * M;
+  const int st_so_lin = tid + st_t1;   // M | 1 == M + 1 for the even compile-time sizes
   const int st_dt1 = kThreads / M, st_dm1 = kThreads - st_dt1 * M;
 
   // stage-3 plan of this thread (tile-invariant): its four filters' group counts, weight and
@@ -354,9 +352,9 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
       auto chunk_nonzero = [&](int k) -> int {
         if constexpr (PCM16) {
           return *reinterpret_cast<const int*>(reinterpret_cast<const int16_t*>(s_wave) + dbase +
-                                               k * (4 * kPitch)) != 0;
+                                               k * kPass) != 0;
         } else {
-          const float2 v = *reinterpret_cast<const float2*>(s_wave + dbase + k * (4 * kPitch));
+          const float2 v = *reinterpret_cast<const float2*>(s_wave + dbase + k * kPass);
           return (v.x != 0.f) | (v.y != 0.f);
         }
       };
@@ -414,21 +412,22 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
           tw[4 * q] = c.x; tw[4 * q + 1] = c.y; tw[4 * q + 2] = c.z; tw[4 * q + 3] = c.w;
         }
       }
+      // frames (2p, 2p + 1): tap n1 of the second is sample 20 (n1 + 8) + n2 of the first's span,
+      // so 28 loads serve both (not 40)
       f2 x[20];
-      if constexpr (PCM16) {   // int16 -> float is exact; the 2^-15 scale sits in the window taps
-        const int16_t* xa = reinterpret_cast<const int16_t*>(s_wave) + p * kPitch + n2;
+      {
+        float xs[28];
+        if constexpr (PCM16) {   // int16 -> float is exact; the 2^-15 scale sits in the window taps
+          const int16_t* xa = reinterpret_cast<const int16_t*>(s_wave) + p * kPitch2 + n2;
 #pragma unroll
-        for (int n1 = 0; n1 < 20; ++n1) {
-          const int off = 20 * n1 + ((20 * n1) / kHop) * kPad;
-          x[n1] = mk2((float)xa[off], (float)xa[off + kPairs * kPitch]);
-        }
-      } else {
-        const float* xa = s_wave + p * kPitch + n2;
+          for (int m = 0; m < 28; ++m) xs[m] = (float)xa[20 * m + (m >= 16 ? kPad2 : 0)];
+        } else {
+          const float* xa = s_wave + p * kPitch2 + n2;
 #pragma unroll
-        for (int n1 = 0; n1 < 20; ++n1) {
-          const int off = 20 * n1 + ((20 * n1) / kHop) * kPad;  // n2 < 20 never crosses a hop boundary
-          x[n1] = mk2(xa[off], xa[off + kPairs * kPitch]);
+          for (int m = 0; m < 28; ++m) xs[m] = xa[20 * m + (m >= 16 ? kPad2 : 0)];  // 20 m + n2 >= 320 <=> m >= 16
         }
+#pragma unroll
+        for (int n1 = 0; n1 < 20; ++n1) x[n1] = mk2(xs[n1], xs[n1 + 8]);
       }
       cx<f2> Y[11];
       rdft20<true>(x, wv, Y);
@@ -578,16 +577,16 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
             v1 = (v1 > db_amin) ? l1 : db_floor;
           }
           if (m < M) {
-            s_o[p * opitch + m] = v0;
-            s_o[(p + kPairs) * opitch + m] = v1;
+            s_o[(2 * p) * opitch + m] = v0;
+            s_o[(2 * p + 1) * opitch + m] = v1;
             vmax0 = fmaxf(vmax0, v0);
             vmax1 = fmaxf(vmax1, v1);
           }
         }
       }
       {
-        const float vmax = fmaxf((t0 + p) < prm.T ? vmax0 : -INFINITY,
-                                 (t0 + p + kPairs) < prm.T ? vmax1 : -INFINITY);
+        const float vmax = fmaxf((t0 + 2 * p) < prm.T ? vmax0 : -INFINITY,
+                                 (t0 + 2 * p + 1) < prm.T ? vmax1 : -INFINITY);
         const unsigned key = vmax > -INFINITY ? max_key_encode(vmax) : 0u;
         // one warp reduction, then one atomic per warp: the tile maximum via a shared word
         // (stored with the tile record after the barrier) and / or the utterance maximum
@@ -610,16 +609,18 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
       const int nvalid = left < kTile ? (int)left : kTile;
       float* o = prm.out + (b * prm.T + t0) * M;
       const int total = nvalid * M;
-      if (st_two && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
-        const int e0 = tid * 4, e1 = e0 + kThreads * 4;
-        if (e0 < total) {
-          const float* s = s_o + st_so0;
-          *reinterpret_cast<float4*>(o + e0) = make_float4(s[0], s[1], s[2], s[3]);
-        }
-        if (e1 < total) {
-          const float* s = s_o + st_so1;
-          *reinterpret_cast<float4*>(o + e1) = make_float4(s[0], s[1], s[2], s[3]);
-        }
+      if (MC > 0 && kThreads % MC == 0) {
+        // a pass of the CTA covers whole rows: element e = tid + k * kThreads sits at smem offset
+        // e + e / M = (tid + tid / M) + k * (kThreads + kThreads / M).  One float per lane:
+        // consecutive lanes read consecutive banks (the row pitch M | 1 only shifts by one per
+        // row) and a warp stores 128 contiguous bytes - the float4 walk below reads its four
+        // floats at a lane stride of 4 words, 2.75 wavefronts per load on this tile shape
+        constexpr int kRowsPass = MC > 0 ? kThreads / MC : 1;
+        constexpr int kPasses = MC > 0 ? (kTile * MC) / kThreads : 1;
+        const float* s = s_o + st_so_lin;
+#pragma unroll
+        for (int k = 0; k < kPasses; ++k)
+          if (tid + k * kThreads < total) o[tid + k * kThreads] = s[k * (kThreads + kRowsPass)];
       } else if ((M & 3) == 0 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
         int e = tid * 4;
         int t = st_t4, m = st_m4;
