@@ -74,6 +74,12 @@ typedef struct sbfe_fbank_desc {
                                    mel_start[m] + 4*G <= 4*ceil(bins / 4) for both.  Needed by the
                                    fused n_fft = 400 / hop = 160 kernel (128-bit weight loads,
                                    warp-uniform trip counts). */
+  int32_t mel_precision;        /* dense filterbanks only (gaussian: at least half of the
+                                   [bins, M] matrix is stored): they run as a tensor-core GEMM
+                                   (mma.sync TF32, fp32 accumulation).  0: 3xTF32 split, inside
+                                   the fp32 tolerance of the path (max-abs 1e-4 dB).  1: one TF32
+                                   pass - inputs rounded to 10-bit mantissas: |err| <= 2e-2 dB
+                                   stated bound (typically 3e-3).  Sparse filterbanks ignore it. */
 } sbfe_fbank_desc;
 
 SBFE_API int sbfe_abi_version(void);
@@ -159,12 +165,16 @@ SBFE_API int sbfe_norm_stats_tiles(const float* d_x, const float* d_lengths, int
  *   before it reads: it applies the clamp to every value it reads itself (same result before
  *   and after), rebuilds the floor from the records' keys, recomputes what a record below the
  *   floor would have told it, and waits only before its first store.  Without the flag it waits
- *   first, like every other kernel of the library.  Results are identical either way. */
+ *   first, like every other kernel of the library.  Results are identical either way.
+ *   SBFE_OUT_BF16 - d_out is a bfloat16 [B, T, F] tensor (must not be d_x): the opt-in
+ *   reduced-precision output, rounded to nearest even from the float32 result, i.e. relative
+ *   error <= 2^-8 of each normalised value (stated bound; the statistics stay float32). */
 #define SBFE_BESIDE_CLAMP 1
+#define SBFE_OUT_BF16 2
 SBFE_API int sbfe_norm_sentence_tiles(const float* d_x, const float* d_lengths, int64_t B, int64_t T,
                              int32_t F, int32_t mean_norm, int32_t std_norm, float eps,
                              const float* d_tile_stats, int32_t tile_frames, float top_db,
-                             int32_t flags, float* d_out, void* stream);
+                             int32_t flags, void* d_out, void* stream);
 
 /* STFT.forward for [B, L] input (processing/features.py:133-188):
  * out [B, T, bins, 2] (re, im), or, with power_only != 0, [B, T, bins] = re^2+im^2. */
@@ -245,10 +255,11 @@ SBFE_API int sbfe_norm_update(const float* d_cur, int32_t F, int32_t first, floa
 
 /* out = (x - mean) / std (processing/features.py:1035, 1088, 1116).
  * per_utt != 0: mean/std are [B, F]; else [F] shared.  In place when out == x.
- * d_utt_max != NULL applies the top_db clamp to x first. */
+ * d_utt_max != NULL applies the top_db clamp to x first.  flags: 0 or SBFE_OUT_BF16 (d_out is
+ * bfloat16 [B, T, F], not d_x). */
 SBFE_API int sbfe_norm_apply(const float* d_x, int64_t B, int64_t T, int32_t F, const float* d_mean,
                     const float* d_std, int32_t per_utt, const sbfe_maxkey_t* d_utt_max,
-                    float top_db, float* d_out, void* stream);
+                    float top_db, int32_t flags, void* d_out, void* stream);
 
 /* ---- next row: speaker-mode statistics (processing/features.py:1037-1081) --
  * The speaker dictionary stays on the host (ids -> rows of d_table_mean / d_table_std [rows, F]);

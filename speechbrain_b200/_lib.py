@@ -36,6 +36,7 @@ class FbankDesc(C.Structure):
         ("d_mel_weight", C.c_void_p),
         ("mel_nnz", C.c_int32),
         ("mel_pad4", C.c_int32),
+        ("mel_precision", C.c_int32),
     ]
 
 
@@ -71,7 +72,7 @@ SIGNATURES = {
     "sbfe_norm_stats_static": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, _I32, _F, _P, _F, _P, _P, _P]),
     "sbfe_norm_reduce": (C.c_int, [_P, _P, _I64, _I32, _P, _P]),
     "sbfe_norm_update": (C.c_int, [_P, _I32, _I32, _F, _P, _P, _P]),
-    "sbfe_norm_apply": (C.c_int, [_P, _I64, _I64, _I32, _P, _P, _I32, _P, _F, _P, _P]),
+    "sbfe_norm_apply": (C.c_int, [_P, _I64, _I64, _I32, _P, _P, _I32, _P, _F, _I32, _P, _P]),
     "sbfe_norm_speaker_update": (C.c_int, [_P, _P, _I64, _I32, _P, _P, _P, _P, _P, _P, _P, _P]),
     "sbfe_specaugment_forward": (C.c_int, [_P, _I64, _I64, _I32, _I32, _I32, _I32, _P, _P, _I32, _P,
                                            _P, _I32, _P, _F, _P, _P]),

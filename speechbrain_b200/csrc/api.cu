@@ -12,11 +12,12 @@ int launch_fbank400_v3(const sbfe_fbank_desc*, const void*, int, float, const in
 int launch_norm_stats_tiles(const float*, const float*, int64_t, int64_t, int, int, int, float,
                             const float*, int, float, float*, float*, cudaStream_t);
 int launch_norm_sentence_tiles(const float*, const float*, int64_t, int64_t, int, int, int, float,
-                               const float*, int, float, int, float*, cudaStream_t);
+                               const float*, int, float, int, int, void*, cudaStream_t);
 int64_t istft_workspace_bytes(int64_t, int64_t, int);
 int launch_istft(const float*, int64_t, int64_t, int, int, const float*, int, int64_t, float*, void*,
                  int64_t, cudaStream_t);
 bool fbank_pow2_supported(const sbfe_fbank_desc*);
+bool mel_dense_mma(const sbfe_fbank_desc*);
 int launch_fbank_pow2(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
                       sbfe_maxkey_t*, cudaStream_t);
 int launch_stft_generic(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
@@ -34,7 +35,7 @@ int launch_norm_stats_static(const float*, const float*, int64_t, int64_t, int, 
 int launch_norm_reduce(const float*, const float*, int64_t, int, float*, cudaStream_t);
 int launch_norm_update(const float*, int, int, float, float*, float*, cudaStream_t);
 int launch_norm_apply(const float*, int64_t, int64_t, int, const float*, const float*, int,
-                      const sbfe_maxkey_t*, float, float*, cudaStream_t);
+                      const sbfe_maxkey_t*, float, int, void*, cudaStream_t);
 
 static bool desc_ok(const sbfe_fbank_desc* d, bool need_mel) {
   if (!d || d->n_fft < 2 || (d->n_fft & 1) || d->hop < 1 || !d->d_window || !d->h_window)
@@ -85,12 +86,13 @@ int64_t sbfe_num_frames(int64_t n_samples, int32_t hop) {
 
 int64_t sbfe_fbank_workspace_bytes(const sbfe_fbank_desc* d, int64_t B, int64_t L) {
   if (!d || d->hop < 1 || B < 0 || L < 0) return SBFE_E_INVAL;
-  if (fused_ok(d) || fbank_pow2_supported(d)) return 0;
+  if (!mel_dense_mma(d) && (fused_ok(d) || fbank_pow2_supported(d))) return 0;
   return B * (1 + L / d->hop) * (int64_t)(d->n_fft / 2 + 1) * (int64_t)sizeof(float);
 }
 
 int32_t sbfe_fbank_tile_frames(const sbfe_fbank_desc* d) {
-  return (d && desc_ok(d, true) && fbank400_v3_supported(d)) ? 32 : 0;
+  // a dense filterbank goes through the tensor-core projection, not the fused kernel
+  return (d && desc_ok(d, true) && fbank400_v3_supported(d) && !mel_dense_mma(d)) ? 32 : 0;
 }
 
 int32_t sbfe_fbank_tile_stats_floats(const sbfe_fbank_desc* d) {
@@ -106,13 +108,16 @@ int sbfe_fbank_forward(const sbfe_fbank_desc* d, const float* d_wav, int64_t B, 
   if (B == 0) return 0;
   if ((!d_wav && L > 0) || !d_out) return SBFE_E_INVAL;
   cudaStream_t s = (cudaStream_t)stream;
-  if (fbank400_v3_supported(d))
+  if (fbank400_v3_supported(d) && !mel_dense_mma(d))
     return launch_fbank400_v3(d, d_wav, 0, 1.f, nullptr, nullptr, B, L, wav_stride, d_out, d_utt_max,
                               d_tile_stats, top_db, s);
   if (d_tile_stats) return SBFE_E_INVAL;  // only where sbfe_fbank_tile_frames() != 0
-  if (fused_ok(d)) return launch_fbank400(d, d_wav, B, L, wav_stride, d_out, d_utt_max, s);
-  if (fbank_pow2_supported(d))   // n_fft = 256 / 512 / 1024 ...: FFT + mel + dB in one launch
-    return launch_fbank_pow2(d, d_wav, B, L, wav_stride, d_out, d_utt_max, s);
+  // dense (gaussian) filterbank: power spectrum to the workspace, projection on the tensor cores
+  if (!mel_dense_mma(d)) {
+    if (fused_ok(d)) return launch_fbank400(d, d_wav, B, L, wav_stride, d_out, d_utt_max, s);
+    if (fbank_pow2_supported(d))   // n_fft = 256 / 512 / 1024 ...: FFT + mel + dB in one launch
+      return launch_fbank_pow2(d, d_wav, B, L, wav_stride, d_out, d_utt_max, s);
+  }
   if (!d_ws || ws_bytes < sbfe_fbank_workspace_bytes(d, B, L)) return SBFE_E_NOSPACE;
   int rc = launch_stft_generic(d, d_wav, B, L, wav_stride, (float*)d_ws, 1, s);
   if (rc) return rc;
@@ -126,7 +131,7 @@ int sbfe_fbank_forward_ragged(const sbfe_fbank_desc* d, const float* d_packed,
   if (!desc_ok(d, true) || B < 0 || L < 0) return SBFE_E_INVAL;
   if (B == 0) return 0;
   if (!d_packed || !d_offsets || !d_nsamples || !d_out) return SBFE_E_INVAL;
-  if (!fbank400_v3_supported(d)) return SBFE_E_INVAL;  // pad on the device and use sbfe_fbank_forward
+  if (!sbfe_fbank_tile_frames(d)) return SBFE_E_INVAL;  // pad on the device and use sbfe_fbank_forward
   return launch_fbank400_v3(d, d_packed, 0, 1.f, d_offsets, d_nsamples, B, L, 0, d_out, d_utt_max,
                             d_tile_stats, top_db, (cudaStream_t)stream);
 }
@@ -140,7 +145,7 @@ int sbfe_fbank_forward_ragged_pcm16(const sbfe_fbank_desc* d, const int16_t* d_p
     return SBFE_E_INVAL;
   if (B == 0) return 0;
   if (!d_packed || !d_offsets || !d_nsamples || !d_out) return SBFE_E_INVAL;
-  if (!fbank400_v3_supported(d)) return SBFE_E_INVAL;  // convert on the device and use sbfe_fbank_forward
+  if (!sbfe_fbank_tile_frames(d)) return SBFE_E_INVAL;  // convert on the device and use sbfe_fbank_forward
   return launch_fbank400_v3(d, d_packed, 1, scale, d_offsets, d_nsamples, B, L, 0, d_out, d_utt_max,
                             d_tile_stats, top_db, (cudaStream_t)stream);
 }
@@ -210,14 +215,15 @@ int sbfe_norm_stats_tiles(const float* d_x, const float* d_lengths, int64_t B, i
 int sbfe_norm_sentence_tiles(const float* d_x, const float* d_lengths, int64_t B, int64_t T,
                              int32_t F, int32_t mean_norm, int32_t std_norm, float eps,
                              const float* d_tile_stats, int32_t tile_frames, float top_db,
-                             int32_t flags, float* d_out, void* stream) {
+                             int32_t flags, void* d_out, void* stream) {
   if (B < 0 || T < 0 || F < 0 || tile_frames < 1) return SBFE_E_INVAL;
   if (B == 0 || F == 0) return 0;
   if (!d_x || !d_lengths || !d_tile_stats || !d_out) return SBFE_E_INVAL;
-  if (flags & ~SBFE_BESIDE_CLAMP) return SBFE_E_INVAL;
+  if (flags & ~(SBFE_BESIDE_CLAMP | SBFE_OUT_BF16)) return SBFE_E_INVAL;
+  if ((flags & SBFE_OUT_BF16) && d_out == (const void*)d_x) return SBFE_E_INVAL;
   return launch_norm_sentence_tiles(d_x, d_lengths, B, T, F, mean_norm, std_norm, eps, d_tile_stats,
-                                    tile_frames, top_db, (flags & SBFE_BESIDE_CLAMP) != 0, d_out,
-                                    (cudaStream_t)stream);
+                                    tile_frames, top_db, (flags & SBFE_BESIDE_CLAMP) != 0,
+                                    (flags & SBFE_OUT_BF16) != 0, d_out, (cudaStream_t)stream);
 }
 
 int64_t sbfe_norm_workspace_bytes(int64_t B, int64_t T, int32_t F) {
@@ -262,12 +268,13 @@ int sbfe_norm_update(const float* d_cur, int32_t F, int32_t first, float weight,
 
 int sbfe_norm_apply(const float* d_x, int64_t B, int64_t T, int32_t F, const float* d_mean,
                     const float* d_std, int32_t per_utt, const sbfe_maxkey_t* d_utt_max,
-                    float top_db, float* d_out, void* stream) {
-  if (B < 0 || T < 0 || F < 0) return SBFE_E_INVAL;
+                    float top_db, int32_t flags, void* d_out, void* stream) {
+  if (B < 0 || T < 0 || F < 0 || (flags & ~SBFE_OUT_BF16)) return SBFE_E_INVAL;
   if (B == 0 || T == 0 || F == 0) return 0;
   if (!d_x || !d_out || !d_mean || !d_std) return SBFE_E_INVAL;
-  return launch_norm_apply(d_x, B, T, F, d_mean, d_std, per_utt, d_utt_max, top_db, d_out,
-                           (cudaStream_t)stream);
+  if ((flags & SBFE_OUT_BF16) && d_out == (const void*)d_x) return SBFE_E_INVAL;
+  return launch_norm_apply(d_x, B, T, F, d_mean, d_std, per_utt, d_utt_max, top_db,
+                           (flags & SBFE_OUT_BF16) != 0, d_out, (cudaStream_t)stream);
 }
 
 int sbfe_norm_speaker_update(const float* d_mean, const float* d_std, int64_t B, int32_t F,

@@ -446,7 +446,239 @@ mel_db_kernel(const float* __restrict__ spec, int64_t T, int bins, int M,
     atomicMax(utt_max + b, max_key_encode(vmax));
 }
 
+static int launch_mel_db_sparse(const sbfe_fbank_desc* d, const float* spec, int64_t B, int64_t T,
+                                float* out, sbfe_maxkey_t* utt_max, cudaStream_t stream);
+
+// ---- dense filterbanks on the tensor cores ------------------------------------------------------
+// Gaussian filters (speechbrain/processing/features.py:637-658) make Filterbank.forward's matmul
+// (:548) a genuinely dense [frames x bins] . [bins x M] contraction (triangular / rectangular
+// ones are ~2 % dense and stay on the sparse loops).  mma.sync.m16n8k8 TF32 with fp32 accumulators;
+// SPLIT = 3 is the 3xTF32 scheme (x = hi + lo, both TF32: hi*hi + hi*lo + lo*hi, error ~2^-21
+// relative: inside the fp32 tolerance), SPLIT = 1 a single TF32 pass (10-bit mantissas: the
+// stated looser bound, include/sbfe.h mel_precision).
+// Why mma.sync and not tcgen05 / TMEM: K = bins (201) and N = M (<= 128) are tiny and the kernel
+// reads 4 * bins and writes 4 * M bytes per frame - it is bound by HBM (or L2), not by the tensor
+// pipe (3 x 2 * bins * M flop per frame = 0.1 MFLOP against 1.1 KB: 87 flop/byte, a B200 is at
+// > 280); a UMMA tile needs 128 rows in shared memory through descriptors, its accumulator comes
+// back through tcgen05.ld for an epilogue that is one lg2 and a store.  Warp-level MMA fed from a
+// conflict-free fp32 tile does the same work with none of that and the same memory time.
+// Persistent CTAs (one per SM): the [M][bins] weights stay in shared memory, frame tiles are
+// double-buffered with cp.async.
+constexpr int kMmaRows = 64;       // frames per tile
+constexpr int kMmaThreads = 512;   // 16 warps = 4 row groups of 16 x 4 column groups
+constexpr int kMmaColGroups = 4;
+constexpr int kMmaMaxNT = 4;       // n-tiles of 8 filters per warp: M <= 128
+constexpr int kMmaDensity = 2;     // stored weights >= 1 / kMmaDensity of the matrix: "dense"
+constexpr int kMmaDensitySlowPath = 10;
+bool fbank400_supported(const sbfe_fbank_desc* d);   // fbank400.cu
+
+__device__ __forceinline__ uint32_t to_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
+      "{%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+template <int SPLIT, int NT>      // NT: n-tiles of 8 filters per warp (ceil(M / 32))
+__global__ void __launch_bounds__(kMmaThreads, 1)
+mel_mma_kernel(const float* __restrict__ spec, int64_t rows_total, int64_t T, int bins, int M,
+               int kpad, int npad, const int32_t* __restrict__ mel_start,
+               const int32_t* __restrict__ mel_count, const int32_t* __restrict__ mel_offset,
+               const float* __restrict__ mel_weight, DbParams db, float* __restrict__ out,
+               sbfe_maxkey_t* utt_max, int nbuf) {
+  extern __shared__ __align__(16) float s_mma[];
+  const int pitch = kpad + 4;                      // = 4 mod 8: fragment loads hit 32 distinct banks
+  float* s_w = s_mma;                              // [npad][pitch]: W^T, zero outside each filter
+  float* s_a = s_w + (size_t)npad * pitch;         // 2 x [kMmaRows][pitch]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  __shared__ unsigned s_um[kMmaRows];              // max keys of the utterances a tile meets
+  if (tid < kMmaRows) s_um[tid] = 0u;
+  for (int i = tid; i < npad * pitch; i += kMmaThreads) s_w[i] = 0.f;
+  for (int i = tid; i < nbuf * kMmaRows * pitch; i += kMmaThreads) s_a[i] = 0.f;   // k >= bins stays 0
+  __syncthreads();
+  for (int m = warp; m < M; m += kMmaThreads / 32) {
+    const int st = __ldg(mel_start + m), cnt = __ldg(mel_count + m);
+    const float* wt = mel_weight + __ldg(mel_offset + m);
+    for (int i = lane; i < cnt; i += 32) s_w[m * pitch + st + i] = __ldg(wt + i);
+  }
+  const int64_t n_tiles = (rows_total + kMmaRows - 1) / kMmaRows;
+  auto stage = [&](int64_t tile, float* dst) {     // rows of a tile are one contiguous block of spec
+    const int64_t r0 = tile * kMmaRows;
+    const int nr = rows_total - r0 < kMmaRows ? (int)(rows_total - r0) : kMmaRows;
+    const float* src = spec + r0 * bins;
+    const int total = nr * bins;
+    int r = tid / bins, k = tid - r * bins;
+    const int dr = kMmaThreads / bins, dk = kMmaThreads - dr * bins;
+    for (int i = tid; i < total; i += kMmaThreads) {
+      const unsigned d = (unsigned)__cvta_generic_to_shared(dst + r * pitch + k);
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(d), "l"(src + i) : "memory");
+      r += dr;
+      k += dk;
+      if (k >= bins) { k -= bins; ++r; }
+    }
+  };
+  int64_t tile = blockIdx.x;
+  if (tile < n_tiles) stage(tile, s_a);
+  asm volatile("cp.async.commit_group;\n" ::: "memory");
+  const int rg = warp & 3, ch = warp >> 2;
+  const int nt0 = ch * NT;                         // npad = 32 NT: every warp has NT n-tiles
+  constexpr int my_nt = NT;
+  for (int it = 0; tile < n_tiles; ++it, tile += gridDim.x) {
+    // nbuf == 2: the next tile flies while this one is multiplied; 1 (large n_fft: the second
+    // buffer does not fit): it is requested once this one is done
+    float* a_buf = s_a + (size_t)(nbuf == 2 ? (it & 1) : 0) * kMmaRows * pitch;
+    if (nbuf == 2 && tile + gridDim.x < n_tiles)
+      stage(tile + gridDim.x, s_a + (size_t)((it & 1) ^ 1) * kMmaRows * pitch);
+    asm volatile("cp.async.commit_group;\n" ::: "memory");
+    if (nbuf == 2) asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+    else asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+    __syncthreads();                               // this tile (and, first time, the weights) is in
+    float acc[NT][4];
+#pragma unroll
+    for (int n = 0; n < NT; ++n) acc[n][0] = acc[n][1] = acc[n][2] = acc[n][3] = 0.f;
+    const float* ap = a_buf + (rg * 16 + g) * pitch + t;
+    const float* ap8 = ap + 8 * pitch;
+    const float* bp = s_w + (nt0 * 8 + g) * pitch + t;
+    const int bstep = 8 * pitch;
+#pragma unroll 2
+    for (int k0 = 0; k0 < kpad; k0 += 8) {
+      const float af[4] = {ap[k0], ap8[k0], ap[k0 + 4], ap8[k0 + 4]};
+      uint32_t ah[4], al[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        ah[i] = to_tf32(af[i]);
+        if (SPLIT == 3) al[i] = to_tf32(af[i] - __uint_as_float(ah[i]));
+      }
+#pragma unroll
+      for (int n = 0; n < NT; ++n) {
+        if (n < my_nt) {
+          const float bf[2] = {bp[n * bstep + k0], bp[n * bstep + k0 + 4]};
+          uint32_t bh[2], bl[2];
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            bh[i] = to_tf32(bf[i]);
+            if (SPLIT == 3) bl[i] = to_tf32(bf[i] - __uint_as_float(bh[i]));
+          }
+          if (SPLIT == 3) {                        // the small terms first
+            mma_tf32(acc[n], al, bh);
+            mma_tf32(acc[n], ah, bl);
+          }
+          mma_tf32(acc[n], ah, bh);
+        }
+      }
+    }
+    // epilogue: dB, store, utterance maxima.  c0 c1: row g, filters 2t, 2t+1; c2 c3: row g + 8
+    const int64_t row_a = tile * kMmaRows + rg * 16 + g, row_b = row_a + 8;
+    float vmax_a = -INFINITY, vmax_b = -INFINITY;
+#pragma unroll
+    for (int n = 0; n < NT; ++n) {
+      if (n < my_nt) {
+        const int m0 = (nt0 + n) * 8 + 2 * t;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int m = m0 + (i & 1);
+          const int64_t row = (i & 2) ? row_b : row_a;
+          if (m < M && row < rows_total) {
+            const float v = to_db(acc[n][i], db);
+            out[row * M + m] = v;
+            if (i & 2) vmax_b = fmaxf(vmax_b, v);
+            else vmax_a = fmaxf(vmax_a, v);
+          }
+        }
+      }
+    }
+    // utterance maxima: through shared memory first (a tile of 64 rows meets one or two
+    // utterances; same-address global atomics from every quad would serialise in L2)
+    if (utt_max != nullptr) {
+#pragma unroll
+      for (int o = 1; o <= 2; o <<= 1) {           // the four lanes of a row
+        vmax_a = fmaxf(vmax_a, __shfl_xor_sync(0xffffffffu, vmax_a, o));
+        vmax_b = fmaxf(vmax_b, __shfl_xor_sync(0xffffffffu, vmax_b, o));
+      }
+      const int64_t b_first = (tile * kMmaRows) / T;
+      if (t == 0) {
+        if (vmax_a > -INFINITY) atomicMax(&s_um[row_a / T - b_first], max_key_encode(vmax_a));
+        if (vmax_b > -INFINITY) atomicMax(&s_um[row_b / T - b_first], max_key_encode(vmax_b));
+      }
+      __syncthreads();
+      if (tid < kMmaRows) {
+        const unsigned k = s_um[tid];
+        if (k) {
+          atomicMax(utt_max + b_first + tid, k);
+          s_um[tid] = 0u;
+        }
+      }
+    }
+    __syncthreads();                               // a_buf is free for the tile after next
+    if (nbuf == 1 && tile + gridDim.x < n_tiles) stage(tile + gridDim.x, s_a);
+  }
+  asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+}
+
+// dense enough for the tensor-core kernel, and its weights + two frame tiles fit in shared memory
+static bool mel_mma_ok(const sbfe_fbank_desc* d, size_t* smem_out, int* nbuf_out = nullptr) {
+  const int bins = d->n_fft / 2 + 1;
+  const int kpad = (bins + 7) & ~7, npad = (d->n_mels + 31) & ~31;   // 4 column groups x NT x 8
+  size_t smem = ((size_t)npad + 2 * kMmaRows) * (kpad + 4) * sizeof(float);
+  int nbuf = 2;
+  if (smem > 220 * 1024) {
+    nbuf = 1;
+    smem = ((size_t)npad + kMmaRows) * (kpad + 4) * sizeof(float);
+  }
+  if (nbuf_out) *nbuf_out = nbuf;
+  if (smem_out) *smem_out = smem;
+  const char* sw = getenv("SBFE_MEL_MMA");          // 0: never, 2: whenever it fits (experiments)
+  if (sw != nullptr && sw[0] == '0') return false;
+  if (npad > 8 * kMmaColGroups * kMmaMaxNT || smem > 220 * 1024) return false;
+  if (sw != nullptr && sw[0] == '2') return true;
+  // where a fused n_fft = 400 kernel takes the configuration its sparse loops win unless the
+  // matrix is really dense (gaussian-80 at 18 % stored weights: 96 us fused against STFT +
+  // projection = 91 + 40 us on the cfg2 batch); elsewhere (n_fft 512 ...) 10 % is enough
+  const int density = fbank400_supported(d) ? kMmaDensity : kMmaDensitySlowPath;
+  return (int64_t)density * d->mel_nnz >= (int64_t)bins * d->n_mels;
+}
+
+// Fbank with a dense filterbank = STFT power spectrum (workspace) + the tensor-core projection
+bool mel_dense_mma(const sbfe_fbank_desc* d) { return mel_mma_ok(d, nullptr); }
+
 int launch_mel_db(const sbfe_fbank_desc* d, const float* spec, int64_t B, int64_t T, float* out,
+                  sbfe_maxkey_t* utt_max, cudaStream_t stream) {
+  if (B == 0 || T == 0) return 0;
+  size_t smem_mma = 0;
+  int nbuf = 2;
+  if (mel_mma_ok(d, &smem_mma, &nbuf)) {
+    const int bins = d->n_fft / 2 + 1;
+    const int kpad = (bins + 7) & ~7, npad = (d->n_mels + 31) & ~31;
+    const int nt = npad / (8 * kMmaColGroups);                       // 1 .. kMmaMaxNT
+    using Kern = decltype(&mel_mma_kernel<3, 1>);
+    static const Kern table[2][kMmaMaxNT] = {
+        {mel_mma_kernel<3, 1>, mel_mma_kernel<3, 2>, mel_mma_kernel<3, 3>, mel_mma_kernel<3, 4>},
+        {mel_mma_kernel<1, 1>, mel_mma_kernel<1, 2>, mel_mma_kernel<1, 3>, mel_mma_kernel<1, 4>}};
+    Kern k = table[d->mel_precision == 1 ? 1 : 0][nt - 1];
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_mma);
+    int dev = 0, sms = 0;
+    if (e == cudaSuccess) e = cudaGetDevice(&dev);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) return (int)e;
+    const int64_t rows = B * T, n_tiles = (rows + kMmaRows - 1) / kMmaRows;
+    const DbParams db{d->multiplier * 0.30102999566398120f, d->amin, d->db_offset, d->floor_db,
+                      d->log_mel};
+    k<<<(unsigned)(n_tiles < sms ? n_tiles : sms), kMmaThreads, smem_mma, stream>>>(
+        spec, rows, T, bins, d->n_mels, kpad, npad, d->d_mel_start, d->d_mel_count, d->d_mel_offset,
+        d->d_mel_weight, db, out, utt_max, nbuf);
+    return check_last();
+  }
+  return launch_mel_db_sparse(d, spec, B, T, out, utt_max, stream);
+}
+
+static int launch_mel_db_sparse(const sbfe_fbank_desc* d, const float* spec, int64_t B, int64_t T, float* out,
                   sbfe_maxkey_t* utt_max, cudaStream_t stream) {
   if (B == 0 || T == 0) return 0;
   const int bins = d->n_fft / 2 + 1;

@@ -8,11 +8,33 @@
 // sentence); here nothing leaves the device.
 #include <atomic>
 
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 
 namespace sbfe {
 
 constexpr int kNormThreads = 256;
+
+// feature stores: float32, or bfloat16 (round to nearest even) for the opt-in reduced-precision
+// output (sbfe.h: SBFE_OUT_BF16) - half the bytes for the consumer and for a device -> host copy
+template <bool BF16>
+__device__ __forceinline__ void store4(void* out, size_t i4, float4 r) {
+  if (BF16) {
+    const __nv_bfloat162 lo = __floats2bfloat162_rn(r.x, r.y), hi = __floats2bfloat162_rn(r.z, r.w);
+    uint2 v;
+    v.x = *reinterpret_cast<const unsigned*>(&lo);
+    v.y = *reinterpret_cast<const unsigned*>(&hi);
+    reinterpret_cast<uint2*>(out)[i4] = v;
+  } else {
+    reinterpret_cast<float4*>(out)[i4] = r;
+  }
+}
+template <bool BF16>
+__device__ __forceinline__ void store1(void* out, size_t i, float r) {
+  if (BF16) reinterpret_cast<__nv_bfloat16*>(out)[i] = __float2bfloat16_rn(r);
+  else reinterpret_cast<float*>(out)[i] = r;
+}
 constexpr int kStatChunk = 256;  // frames per CTA in the statistics pass
 
 __device__ __forceinline__ int valid_frames(const float* lengths, int64_t b, int64_t T) {
@@ -267,11 +289,11 @@ norm_stats_tiles_kernel(const float* __restrict__ x, const float* __restrict__ l
 constexpr int kSentIters = 8;    // vectors per thread
 constexpr int kSentSpec = 4;     // records per thread and batch
 
-template <int VEC, bool BESIDE_CLAMP>
+template <int VEC, bool BESIDE_CLAMP, bool BF16OUT>
 __global__ void __launch_bounds__(kTileNormThreads, 2)
 norm_sentence_tiles_kernel(const float* x, const float* __restrict__ lengths, int T, int F,
                            int tile, int tiles, const float* tile_stats, float top_db,
-                           int mean_norm, int std_norm, float eps, float* out, unsigned chunks) {
+                           int mean_norm, int std_norm, float eps, void* out, unsigned chunks) {
   if (!BESIDE_CLAMP) {
     pdl_wait();
     pdl_launch_dependents();
@@ -392,7 +414,7 @@ norm_sentence_tiles_kernel(const float* x, const float* __restrict__ lengths, in
   const int FV = F / VEC;
   const int nvec = T * FV;                         // < 2^30 (launcher)
   const int i0 = c0 * (kTileNormThreads * kSentIters) + threadIdx.x;
-  float* ob = out + (size_t)b * T * F;
+  const size_t ob = (size_t)b * T * F;            // element offset of the utterance in out
   float4 v4[VEC == 4 ? kSentIters : 1];
   float v1[VEC == 4 ? 1 : kSentIters];
 #pragma unroll
@@ -421,9 +443,9 @@ norm_sentence_tiles_kernel(const float* x, const float* __restrict__ lengths, in
         r.y = (fmaxf(v4[k].y, floor_b) - mm.y) / ss.y;
         r.z = (fmaxf(v4[k].z, floor_b) - mm.z) / ss.z;
         r.w = (fmaxf(v4[k].w, floor_b) - mm.w) / ss.w;
-        *reinterpret_cast<float4*>(ob + 4 * (size_t)i) = r;
+        store4<BF16OUT>(out, ob / 4 + (size_t)i, r);
       } else {
-        ob[i] = (fmaxf(v1[k], floor_b) - s_mean[col]) / s_std[col];
+        store1<BF16OUT>(out, ob + (size_t)i, (fmaxf(v1[k], floor_b) - s_mean[col]) / s_std[col]);
       }
     }
     col += dcol;
@@ -480,23 +502,16 @@ __global__ void norm_update_kernel(const float* __restrict__ cur, int F, int fir
 // out = (max(x, floor_b) - mean) / std.  VEC = 4 when F % 4 == 0 and 16 B aligned.
 // An utterance is treated as a flat array of T*F/VEC vectors; a CTA takes kApplyIters
 // consecutive blocks of kNormThreads vectors, all loads issued before the first store.
-// X_STABLE (set only by launch_norm_sentence_prefix below, which launches the statistics kernel
-// and this one back to back itself): the direct predecessor in the stream does not write x and
-// everything before it had completed when it let this kernel start (common.cuh) - the vectors
-// of x are then requested BEFORE the wait and fly while the statistics finish; mean / std are
-// read after it.
 constexpr int kApplyIters = 8;
 
-template <int VEC, bool X_STABLE>
+template <int VEC, bool BF16OUT>
 __global__ void __launch_bounds__(kNormThreads)
 norm_apply_kernel(const float* x, int64_t T, int F, const float* __restrict__ mean,
                   const float* __restrict__ stdv, int per_utt,
-                  const sbfe_maxkey_t* __restrict__ utt_max, float top_db, float* out,
+                  const sbfe_maxkey_t* __restrict__ utt_max, float top_db, void* out,
                   unsigned chunks) {
-  if (!X_STABLE) {
-    pdl_wait();
-    pdl_launch_dependents();
-  }
+  pdl_wait();
+  pdl_launch_dependents();
   extern __shared__ __align__(16) float s_ms[];  // mean[F] | std[F]
   const int64_t b = blockIdx.x / chunks;
   const int c = blockIdx.x - b * chunks;
@@ -504,7 +519,7 @@ norm_apply_kernel(const float* x, int64_t T, int F, const float* __restrict__ me
   const int64_t nvec = T * FV;
   const int64_t i0 = (int64_t)c * (kNormThreads * kApplyIters) + threadIdx.x;
   const float* xb = x + b * T * F;
-  float* ob = out + b * T * F;
+  const size_t ob = (size_t)b * T * F;
   int col = (int)(i0 % FV);
   const int dcol = kNormThreads % FV;
   float4 v4[VEC == 4 ? kApplyIters : 1];
@@ -516,10 +531,6 @@ norm_apply_kernel(const float* x, int64_t T, int F, const float* __restrict__ me
       if (VEC == 4) v4[k] = *reinterpret_cast<const float4*>(xb + 4 * i);
       else v1[k] = xb[i];
     }
-  }
-  if (X_STABLE) {
-    pdl_wait();
-    pdl_launch_dependents();
   }
   const float* m = mean + (per_utt ? b * F : 0);
   const float* s = stdv + (per_utt ? b * F : 0);
@@ -541,9 +552,9 @@ norm_apply_kernel(const float* x, int64_t T, int F, const float* __restrict__ me
         r.y = (fmaxf(v4[k].y, floor_b) - mm.y) / ss.y;
         r.z = (fmaxf(v4[k].z, floor_b) - mm.z) / ss.z;
         r.w = (fmaxf(v4[k].w, floor_b) - mm.w) / ss.w;
-        *reinterpret_cast<float4*>(ob + 4 * i) = r;
+        store4<BF16OUT>(out, ob / 4 + (size_t)i, r);
       } else {
-        ob[i] = (fmaxf(v1[k], floor_b) - s_ms[col]) / s_ms[F + col];
+        store1<BF16OUT>(out, ob + (size_t)i, (fmaxf(v1[k], floor_b) - s_ms[col]) / s_ms[F + col]);
       }
     }
     col += dcol;
@@ -634,34 +645,29 @@ int launch_norm_update(const float* cur, int F, int first, float weight, float* 
                     weight, gmean, gstd);
 }
 
-static int launch_apply_any(const float* x, int64_t B, int64_t T, int F, const float* mean,
-                            const float* stdv, int per_utt, const sbfe_maxkey_t* utt_max,
-                            float top_db, float* out, bool x_stable, cudaStream_t stream) {
+int launch_norm_apply(const float* x, int64_t B, int64_t T, int F, const float* mean,
+                      const float* stdv, int per_utt, const sbfe_maxkey_t* utt_max, float top_db,
+                      int out_bf16, void* out, cudaStream_t stream) {
   if (B == 0 || T == 0 || F == 0) return 0;
   const bool vec = (F % 4 == 0) &&
-                   ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+                   ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 15) == 0 &&
+                   (B == 1 || (T * F) % 4 == 0);
   const int64_t nvec = T * (vec ? F / 4 : F);
   const int64_t per_cta = (int64_t)kNormThreads * kApplyIters;
   const int64_t chunks = (nvec + per_cta - 1) / per_cta;
   if (chunks * B > 0x7fffffff) return SBFE_E_TOOBIG;
   const size_t smem = (size_t)2 * F * sizeof(float);
   if (smem > 48 * 1024) return SBFE_E_TOOBIG;
-  auto k = x_stable ? (vec ? norm_apply_kernel<4, true> : norm_apply_kernel<1, true>)
+  auto k = out_bf16 ? (vec ? norm_apply_kernel<4, true> : norm_apply_kernel<1, true>)
                     : (vec ? norm_apply_kernel<4, false> : norm_apply_kernel<1, false>);
   return launch_pdl(k, dim3((unsigned)(chunks * B)), dim3(kNormThreads), smem, stream, x, T, F, mean,
                     stdv, per_utt, utt_max, top_db, out, (unsigned)chunks);
 }
 
-int launch_norm_apply(const float* x, int64_t B, int64_t T, int F, const float* mean,
-                      const float* stdv, int per_utt, const sbfe_maxkey_t* utt_max, float top_db,
-                      float* out, cudaStream_t stream) {
-  return launch_apply_any(x, B, T, F, mean, stdv, per_utt, utt_max, top_db, out, false, stream);
-}
-
 // sentence normalisation from the tile records, one launch
 int launch_norm_sentence_tiles(const float* x, const float* lengths, int64_t B, int64_t T, int F,
                                int mean_norm, int std_norm, float eps, const float* tile_stats,
-                               int tile, float top_db, int beside_clamp, float* out,
+                               int tile, float top_db, int beside_clamp, int out_bf16, void* out,
                                cudaStream_t stream) {
   if (B == 0 || T == 0 || F == 0) return 0;
   if (B > 0x7fffffff || T > 0x7fffffff) return SBFE_E_TOOBIG;
@@ -676,8 +682,13 @@ int launch_norm_sentence_tiles(const float* x, const float* lengths, int64_t B, 
   const size_t smem = ((size_t)2 * F + 3 * kTileNormThreads) * sizeof(float);
   // the flag presumes that call's last launch was its clamp kernel: there is none without a top_db
   const bool beside = beside_clamp != 0 && top_db >= 0.f && pdl_enabled();
-  auto k = beside ? (vec ? norm_sentence_tiles_kernel<4, true> : norm_sentence_tiles_kernel<1, true>)
-                  : (vec ? norm_sentence_tiles_kernel<4, false> : norm_sentence_tiles_kernel<1, false>);
+  using Kern = decltype(&norm_sentence_tiles_kernel<4, true, false>);
+  static const Kern table[8] = {
+      norm_sentence_tiles_kernel<1, false, false>, norm_sentence_tiles_kernel<4, false, false>,
+      norm_sentence_tiles_kernel<1, true, false>,  norm_sentence_tiles_kernel<4, true, false>,
+      norm_sentence_tiles_kernel<1, false, true>,  norm_sentence_tiles_kernel<4, false, true>,
+      norm_sentence_tiles_kernel<1, true, true>,   norm_sentence_tiles_kernel<4, true, true>};
+  Kern k = table[(out_bf16 ? 4 : 0) + (beside ? 2 : 0) + (vec ? 1 : 0)];
   return launch_pdl(k, dim3((unsigned)(chunks * B)), dim3(kTileNormThreads), smem, stream, x, lengths,
                     (int)T, F, tile, tiles, tile_stats, top_db >= 0.f ? top_db : INFINITY, mean_norm,
                     std_norm, eps, out, (unsigned)chunks);

@@ -61,7 +61,7 @@ class _Lobe(torch.nn.Module):
             if st.normalized_stft:
                 win = win * (float(st.n_fft) ** -0.5)
             tab = ops.FrontendTables(st.n_fft, st.hop_length, win, None, fb.log_mel, fb.multiplier,
-                                     fb.amin, fb.db_multiplier)
+                                     fb.amin, fb.db_multiplier, mel_precision=mel.mel_precision)
             tab.n_mels, tab._h_mel, tab.nnz = mel.n_mels, mel._h_mel, mel.nnz
             if jitter:
                 return tab

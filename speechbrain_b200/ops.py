@@ -56,7 +56,8 @@ class FrontendTables:
     processing/features.py:166, 534-536)."""
 
     def __init__(self, n_fft, hop, window, fbank_matrix=None, log_mel=True, multiplier=10.0,
-                 amin=1e-10, db_multiplier=0.0):
+                 amin=1e-10, db_multiplier=0.0, mel_precision=0):
+        self.mel_precision = int(mel_precision)   # sbfe.h: 0 = 3xTF32 (fp32 grade), 1 = TF32
         self.n_fft, self.hop = int(n_fft), int(hop)
         self.bins = self.n_fft // 2 + 1
         win = window.detach().to("cpu", torch.float32)
@@ -132,6 +133,7 @@ class FrontendTables:
             desc.d_mel_offset, desc.d_mel_weight = dev[2].data_ptr(), dev[3].data_ptr()
             desc.mel_nnz = self.nnz
             desc.mel_pad4 = 2
+            desc.mel_precision = self.mel_precision
         entry = (desc, keep)
         self._dev[key] = entry
         return entry
@@ -259,20 +261,22 @@ def norm_stats_tiles(x, lengths, ts, mean_norm=True, std_norm=True, eps=1e-10):
 
 
 def norm_sentence_tiles(x, lengths, ts, mean_norm=True, std_norm=True, eps=1e-10, out=None,
-                        beside_clamp=False):
+                        beside_clamp=False, out_dtype=None):
     """Sentence normalisation straight from the tile records: statistics + (x - mean) / std in
     ONE launch (sbfe_norm_sentence_tiles).  In place when ``out is x``.  ``beside_clamp``: nothing
     that writes x, the records or lengths was launched since the Fbank call that made them
     (sbfe.h: SBFE_BESIDE_CLAMP) - the kernel then runs beside that call's clamp launch."""
     B, T, F = x.shape
     lengths = lengths.to(device=x.device, dtype=torch.float32).contiguous()
-    if out is None:
-        out = torch.empty_like(x)
+    bf16 = out_dtype == torch.bfloat16
+    if out is None or bf16:   # a bfloat16 result (sbfe.h: SBFE_OUT_BF16) is always a new tensor
+        out = torch.empty_like(x, dtype=torch.bfloat16 if bf16 else None)
     with torch.cuda.device(x.device):
         check(lib().sbfe_norm_sentence_tiles(_ptr(x), _ptr(lengths), B, T, F, int(bool(mean_norm)),
                                              int(bool(std_norm)), float(eps), _ptr(ts.stats),
                                              ts.frames, -1.0 if ts.top_db is None else float(ts.top_db),
-                                             1 if beside_clamp else 0, _ptr(out), _stream()))
+                                             (1 if beside_clamp else 0) | (2 if bf16 else 0),
+                                             _ptr(out), _stream()))
     return mark_written(out)
 
 
@@ -396,14 +400,17 @@ def norm_speaker_update(mean, std, row, mode, weight, table_mean, table_std):
     return out_m, out_s
 
 
-def norm_apply(x, mean, std, per_utt, out=None, utt_max=None, top_db=80.0):
-    """(max(x, floor) - mean) / std (sbfe_norm_apply); in place when ``out is x``."""
+def norm_apply(x, mean, std, per_utt, out=None, utt_max=None, top_db=80.0, out_dtype=None):
+    """(max(x, floor) - mean) / std (sbfe_norm_apply); in place when ``out is x``;
+    ``out_dtype=torch.bfloat16``: a new bfloat16 tensor (sbfe.h: SBFE_OUT_BF16)."""
     B, T, F = x.shape
-    if out is None:
-        out = torch.empty_like(x)
+    bf16 = out_dtype == torch.bfloat16
+    if out is None or bf16:
+        out = torch.empty_like(x, dtype=torch.bfloat16 if bf16 else None)
     with torch.cuda.device(x.device):
         check(lib().sbfe_norm_apply(_ptr(x), B, T, F, _ptr(mean), _ptr(std), int(bool(per_utt)),
-                                    _ptr(utt_max), float(top_db), _ptr(out), _stream()))
+                                    _ptr(utt_max), float(top_db), 2 if bf16 else 0, _ptr(out),
+                                    _stream()))
     return mark_written(out) if out is x else out
 
 

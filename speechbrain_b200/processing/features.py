@@ -151,8 +151,15 @@ class Filterbank(torch.nn.Module):
 
     def __init__(self, n_mels=40, log_mel=True, filter_shape="triangular", f_min=0, f_max=8000,
                  n_fft=400, sample_rate=16000, power_spectrogram=2, amin=1e-10, ref_value=1.0,
-                 top_db=80.0, param_change_factor=1.0, param_rand_factor=0.0, freeze=True):
+                 top_db=80.0, param_change_factor=1.0, param_rand_factor=0.0, freeze=True,
+                 mel_precision="fp32"):
         super().__init__()
+        # not in the reference: dense (gaussian) filterbanks run as a tensor-core GEMM;
+        # "fp32" = 3xTF32 split (inside the fp32 tolerance), "tf32" = one TF32 pass (looser
+        # stated bound, include/sbfe.h: mel_precision).  May be changed before the first call.
+        if mel_precision not in ("fp32", "tf32"):
+            raise ValueError("mel_precision must be 'fp32' or 'tf32'")
+        self.mel_precision = mel_precision
         self.n_mels = n_mels
         self.log_mel = log_mel
         self.filter_shape = filter_shape
@@ -215,7 +222,8 @@ class Filterbank(torch.nn.Module):
             fc, bw = fc * jitter[0], bw * jitter[1]
         mat = self._create_fbank_matrix(fc, bw)
         return ops.FrontendTables(self.n_fft, 1, torch.ones(self.n_fft), mat, self.log_mel,
-                                  self.multiplier, self.amin, self.db_multiplier)
+                                  self.multiplier, self.amin, self.db_multiplier,
+                                  mel_precision=1 if self.mel_precision == "tf32" else 0)
 
     def tables(self):
         """Tables for this call: cached, or re-drawn when the reference would

@@ -48,8 +48,15 @@ class InputNormalization(torch.nn.Module):
     spk_dict_count: Dict[int, int]
 
     def __init__(self, mean_norm=True, std_norm=True, norm_type="global", avg_factor=None,
-                 requires_grad=False, update_until_epoch=3, sync_stats=False):
+                 requires_grad=False, update_until_epoch=3, sync_stats=False, output_dtype=None):
         super().__init__()
+        # not in the reference (opt-in, like sync_stats): torch.bfloat16 makes forward return a
+        # NEW bfloat16 tensor (the float32 result rounded to nearest even: relative error <= 2^-8
+        # per value; statistics stay float32) - half the bytes for the model's first layer and
+        # for a device -> host copy.  The in-place modes then leave x untouched.
+        if output_dtype not in (None, torch.float32, torch.bfloat16):
+            raise ValueError("output_dtype must be None, torch.float32 or torch.bfloat16")
+        self.output_dtype = None if output_dtype == torch.float32 else output_dtype
         register_checkpoint_hooks_if_available(import_it=False)
         self.mean_norm = mean_norm
         self.std_norm = std_norm
@@ -98,18 +105,20 @@ class InputNormalization(torch.nn.Module):
             # package or torch launched has written x since Fbank returned it (same stream)
             beside = ts.stream == torch.cuda.current_stream(x.device).cuda_stream
             return ops.norm_sentence_tiles(x, lengths, ts, self.mean_norm, self.std_norm, self.eps,
-                                           out=x, beside_clamp=beside)
+                                           out=x, beside_clamp=beside, out_dtype=self.output_dtype)
         if ts is not None:
             mean, std = ops.norm_stats_tiles(x, lengths, ts, self.mean_norm, self.std_norm, self.eps)
         else:
             mean, std = ops.norm_stats(x, lengths, self.mean_norm, self.std_norm, self.eps)
 
         if self.norm_type == "sentence":
-            return ops.norm_apply(x, mean, std, per_utt=True, out=x)  # in place (:1035)
+            return ops.norm_apply(x, mean, std, per_utt=True, out=x,  # in place (:1035)
+                                  out_dtype=self.output_dtype)
 
         if self.norm_type == "speaker":
             s_mean, s_std = self._speaker_stats(mean, std, spk_ids)
-            return ops.norm_apply(x, s_mean, s_std, per_utt=True, out=x)  # in place (:1081)
+            return ops.norm_apply(x, s_mean, s_std, per_utt=True, out=x,  # in place (:1081)
+                                  out_dtype=self.output_dtype)
 
         if self.norm_type not in ("batch", "global"):
             return x
@@ -121,7 +130,7 @@ class InputNormalization(torch.nn.Module):
             g_mean = torch.empty((F,), dtype=torch.float32, device=x.device)
             g_std = torch.empty((F,), dtype=torch.float32, device=x.device)
             ops.norm_update(cur, g_mean, g_std, first=True, weight=1.0)
-            return ops.norm_apply(x, g_mean, g_std, per_utt=False)
+            return ops.norm_apply(x, g_mean, g_std, per_utt=False, out_dtype=self.output_dtype)
 
         # global (:1090-1116)
         if self.training:
@@ -135,7 +144,8 @@ class InputNormalization(torch.nn.Module):
                 ops.norm_update(cur, self.glob_mean, self.glob_std, first=False, weight=self.weight)
             self.count = self.count + 1
         self._stats_to(x.device, F)
-        return ops.norm_apply(x, self.glob_mean, self.glob_std, per_utt=False)
+        return ops.norm_apply(x, self.glob_mean, self.glob_std, per_utt=False,
+                              out_dtype=self.output_dtype)
 
     def _stats_to(self, device, F):
         """Global stats as float32 [F] on ``device`` (the never-initialised

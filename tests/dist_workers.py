@@ -74,7 +74,7 @@ def install_cpu_kernels():
             gm.copy_((1 - weight) * gm + weight * (cur[:f] / n))
             gs.copy_((1 - weight) * gs + weight * (cur[f:2 * f] / n))
 
-    def norm_apply(x, mean, std, per_utt, out=None, utt_max=None, top_db=80.0):
+    def norm_apply(x, mean, std, per_utt, out=None, utt_max=None, top_db=80.0, out_dtype=None):
         y = (x - mean[:, None, :]) / std[:, None, :] if per_utt else (x - mean) / std
         if out is None:
             return y
