@@ -296,6 +296,34 @@ SBFE_API int sbfe_specaugment_forward(const float* d_x, int64_t B, int64_t T, in
                              const int64_t* d_tpos, const int64_t* d_tlen, int32_t n_tmask,
                              const float* d_fill, float fill, float* d_out, void* stream);
 
+/* ---- next row (second half): time-domain augmentation ------------------------
+ * speechbrain/processing/speech_augmentation.py; lobes/augment.py:204-299 (TimeDomainSpecAugment)
+ * chains SpeedPerturb -> DropFreq -> DropChunk right before compute_features.  The random draws
+ * are the caller's (the reference's torch calls); these are the data movements. */
+
+/* DropChunk (:1013-1173).  d_out [B, L, channels] already holds a copy of the input; chunk i =
+ * d_chunks[4 i ..] = {utterance, start, length (time steps), offset into d_noise (time steps)}
+ * is zeroed, or, with d_noise / d_noise_max [B] given, filled with
+ * 2 * noise_max[b] * d_noise[...] - noise_max[b] (:1163-1170; d_noise: the uniform draws).
+ * Chunks of one call must belong to different utterances or not overlap (the caller issues one
+ * call per round of overlapping chunks, in the reference's order). */
+SBFE_API int sbfe_wav_drop_chunks(float* d_out, int64_t B, int64_t L, int32_t channels,
+                         const int32_t* d_chunks, int32_t n_chunks, int64_t max_len,
+                         const float* d_noise, const float* d_noise_max, void* stream);
+/* DropFreq's filtering (:994-1007) = convolve1d(x, taps, padding = pad) of
+ * signal_processing.py:157-277: out[b][t] = sum_k taps[k] x[b][t + k - pad], x zero outside
+ * [0, L) (conv1d, no kernel flip); x, out [B, L]; n_taps <= 1024. */
+SBFE_API int sbfe_wav_fir(const float* d_x, int64_t B, int64_t L, const float* d_taps, int32_t n_taps,
+                 int32_t pad, float* d_out, void* stream);
+/* DoClip (:1176-1228): out = clamp(x, -value, value) over n floats; in place when d_out == d_x. */
+SBFE_API int sbfe_wav_clip(const float* d_x, int64_t n, float value, float* d_out, void* stream);
+/* Resample._perform_resample (:600-665), Kaldi's LinearResample: output sample n * phases + i =
+ * sum_k d_weights[i][k] x[d_first[i] + n * in_stride + k] (x zero outside [0, L)), k < width;
+ * x [B, L] -> out [B, L_out].  Weights and first indices: Resample._indices_and_weights (:740-820). */
+SBFE_API int sbfe_wav_resample(const float* d_x, int64_t B, int64_t L, const float* d_weights,
+                      const int32_t* d_first, int32_t phases, int32_t in_stride, int32_t width,
+                      int64_t L_out, float* d_out, void* stream);
+
 /* mean over n floats as a device scalar (x.mean() of augment.py:196); two small launches,
  * double accumulation, workspace of sbfe_mean_workspace_bytes() bytes. */
 SBFE_API int64_t sbfe_mean_workspace_bytes(void);

@@ -7,10 +7,12 @@ Deltas, ContextWindow, InputNormalization}`` (and, next to the path,
 behind a C ABI (include/sbfe.h).  See DESIGN.md / INTEGRATION.md.
 """
 from .dataio import RaggedBatch  # noqa: F401
-from .lobes.augment import SpecAugment  # noqa: F401
+from .lobes.augment import SpecAugment, TimeDomainSpecAugment  # noqa: F401
 from .lobes.features import MFCC, Fbank, pair  # noqa: F401
 from .processing.features import (  # noqa: F401
     DCT, ISTFT, STFT, ContextWindow, Deltas, Filterbank, InputNormalization, spectral_magnitude)
+from .processing.speech_augmentation import (  # noqa: F401
+    DoClip, DropChunk, DropFreq, Resample, SpeedPerturb)
 
 __version__ = "0.1.0"
 
@@ -43,7 +45,13 @@ def install():
     try:  # the step after the path (lobes/augment.py pulls in torchaudio; optional)
         aug = importlib.import_module("speechbrain.lobes.augment")
         aug.SpecAugment = here.SpecAugment
-        patched.append("speechbrain.lobes.augment.SpecAugment")
+        aug.TimeDomainSpecAugment = here.TimeDomainSpecAugment
+        patched += ["speechbrain.lobes.augment.SpecAugment",
+                    "speechbrain.lobes.augment.TimeDomainSpecAugment"]
+        sa = importlib.import_module("speechbrain.processing.speech_augmentation")
+        for name in ("DropChunk", "DropFreq", "DoClip", "Resample", "SpeedPerturb"):
+            setattr(sa, name, getattr(here, name))
+            patched.append("speechbrain.processing.speech_augmentation." + name)
     except Exception:
         pass
     normalization.register_checkpoint_hooks_if_available()

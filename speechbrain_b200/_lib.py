@@ -76,6 +76,10 @@ SIGNATURES = {
     "sbfe_norm_speaker_update": (C.c_int, [_P, _P, _I64, _I32, _P, _P, _P, _P, _P, _P, _P, _P]),
     "sbfe_specaugment_forward": (C.c_int, [_P, _I64, _I64, _I32, _I32, _I32, _I32, _P, _P, _I32, _P,
                                            _P, _I32, _P, _F, _P, _P]),
+    "sbfe_wav_drop_chunks": (C.c_int, [_P, _I64, _I64, _I32, _P, _I32, _I64, _P, _P, _P]),
+    "sbfe_wav_fir": (C.c_int, [_P, _I64, _I64, _P, _I32, _I32, _P, _P]),
+    "sbfe_wav_clip": (C.c_int, [_P, _I64, _F, _P, _P]),
+    "sbfe_wav_resample": (C.c_int, [_P, _I64, _I64, _P, _P, _I32, _I32, _I32, _I64, _P, _P]),
     "sbfe_mean_workspace_bytes": (_I64, []),
     "sbfe_mean": (C.c_int, [_P, _I64, _P, _P, _I64, _P]),
 }

@@ -49,6 +49,12 @@ static bool desc_ok(const sbfe_fbank_desc* d, bool need_mel) {
 int launch_specaugment(const float*, int64_t, int64_t, int, int, int, int, const int64_t*,
                        const int64_t*, int, const int64_t*, const int64_t*, int, const float*, float,
                        float*, cudaStream_t);
+int launch_drop_chunks(float*, int64_t, int, const int32_t*, int, int64_t, const float*, const float*,
+                       cudaStream_t);
+int launch_fir_same(const float*, int64_t, int64_t, const float*, int, int, float*, cudaStream_t);
+int launch_clip(const float*, int64_t, float, float*, cudaStream_t);
+int launch_resample(const float*, int64_t, int64_t, const float*, const int32_t*, int, int, int,
+                    int64_t, float*, cudaStream_t);
 int64_t mean_workspace_bytes();
 int launch_mean(const float*, int64_t, float*, void*, int64_t, cudaStream_t);
 int launch_norm_speaker_update(const float*, const float*, int64_t, int, const int32_t*,
@@ -299,6 +305,42 @@ int sbfe_specaugment_forward(const float* d_x, int64_t B, int64_t T, int32_t F, 
   if (!d_x || !d_out) return SBFE_E_INVAL;
   return launch_specaugment(d_x, B, T, F, warp_c, warp_w, warp_mode, d_fpos, d_flen, n_fmask,
                             d_tpos, d_tlen, n_tmask, d_fill, fill, d_out, (cudaStream_t)stream);
+}
+
+int sbfe_wav_drop_chunks(float* d_out, int64_t B, int64_t L, int32_t channels,
+                         const int32_t* d_chunks, int32_t n_chunks, int64_t max_len,
+                         const float* d_noise, const float* d_noise_max, void* stream) {
+  if (B < 0 || L < 0 || channels < 1 || n_chunks < 0 || (d_noise != nullptr) != (d_noise_max != nullptr))
+    return SBFE_E_INVAL;
+  if (B == 0 || L == 0 || n_chunks == 0) return 0;
+  if (!d_out || !d_chunks) return SBFE_E_INVAL;
+  return launch_drop_chunks(d_out, L, channels, d_chunks, n_chunks, max_len, d_noise, d_noise_max,
+                            (cudaStream_t)stream);
+}
+
+int sbfe_wav_fir(const float* d_x, int64_t B, int64_t L, const float* d_taps, int32_t n_taps,
+                 int32_t pad, float* d_out, void* stream) {
+  if (B < 0 || L < 0) return SBFE_E_INVAL;
+  if (B == 0 || L == 0) return 0;
+  if (!d_x || !d_taps || !d_out || d_x == d_out) return SBFE_E_INVAL;
+  return launch_fir_same(d_x, B, L, d_taps, n_taps, pad, d_out, (cudaStream_t)stream);
+}
+
+int sbfe_wav_clip(const float* d_x, int64_t n, float value, float* d_out, void* stream) {
+  if (n < 0 || !(value >= 0.f)) return SBFE_E_INVAL;
+  if (n == 0) return 0;
+  if (!d_x || !d_out) return SBFE_E_INVAL;
+  return launch_clip(d_x, n, value, d_out, (cudaStream_t)stream);
+}
+
+int sbfe_wav_resample(const float* d_x, int64_t B, int64_t L, const float* d_weights,
+                      const int32_t* d_first, int32_t phases, int32_t in_stride, int32_t width,
+                      int64_t L_out, float* d_out, void* stream) {
+  if (B < 0 || L < 0 || L_out < 0) return SBFE_E_INVAL;
+  if (B == 0 || L_out == 0) return 0;
+  if (!d_x || !d_weights || !d_first || !d_out) return SBFE_E_INVAL;
+  return launch_resample(d_x, B, L, d_weights, d_first, phases, in_stride, width, L_out, d_out,
+                         (cudaStream_t)stream);
 }
 
 int64_t sbfe_mean_workspace_bytes(void) { return mean_workspace_bytes(); }

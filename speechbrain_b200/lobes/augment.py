@@ -11,7 +11,37 @@ import torch
 from .. import ops
 from .._jit import traceable
 
-__all__ = ["SpecAugment"]
+from ..processing.speech_augmentation import DropChunk, DropFreq, SpeedPerturb
+
+__all__ = ["SpecAugment", "TimeDomainSpecAugment"]
+
+
+class TimeDomainSpecAugment(torch.nn.Module):
+    """Speed perturbation -> frequency drop -> chunk drop on ``[batch, time]`` waveforms;
+    reference: lobes/augment.py:204-299 (same constructor, same order, same draws)."""
+
+    def __init__(self, perturb_prob=1.0, drop_freq_prob=1.0, drop_chunk_prob=1.0,
+                 speeds=[95, 100, 105], sample_rate=16000, drop_freq_count_low=0,
+                 drop_freq_count_high=3, drop_chunk_count_low=0, drop_chunk_count_high=5,
+                 drop_chunk_length_low=1000, drop_chunk_length_high=2000,
+                 drop_chunk_noise_factor=0):
+        super().__init__()
+        self.speed_perturb = SpeedPerturb(perturb_prob=perturb_prob, orig_freq=sample_rate,
+                                          speeds=speeds)
+        self.drop_freq = DropFreq(drop_prob=drop_freq_prob, drop_count_low=drop_freq_count_low,
+                                  drop_count_high=drop_freq_count_high)
+        self.drop_chunk = DropChunk(drop_prob=drop_chunk_prob, drop_count_low=drop_chunk_count_low,
+                                    drop_count_high=drop_chunk_count_high,
+                                    drop_length_low=drop_chunk_length_low,
+                                    drop_length_high=drop_chunk_length_high,
+                                    noise_factor=drop_chunk_noise_factor)
+
+    def forward(self, waveforms, lengths):
+        with torch.no_grad():
+            waveforms = self.speed_perturb(waveforms)
+            waveforms = self.drop_freq(waveforms)
+            waveforms = self.drop_chunk(waveforms, lengths)
+        return waveforms
 
 
 class SpecAugment(torch.nn.Module):

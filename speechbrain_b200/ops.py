@@ -469,3 +469,49 @@ def specaugment_forward(x, warp=None, warp_mode="bicubic", freq_masks=None, time
                                              _ptr(fpos), _ptr(flen), nf, _ptr(tpos), _ptr(tlen),
                                              nt, _ptr(d_fill), f_fill, _ptr(out), _stream()))
     return mark_written(out) if out is x else out
+
+
+# ---- time-domain augmentation (csrc/timedomain.cu; processing/speech_augmentation.py) ----------
+def wav_drop_chunks(out, chunks, noise=None, noise_max=None):
+    """Zero (or noise-fill) ``chunks`` = [(utterance, start, length, noise offset), ...] of
+    ``out`` [B, L] in place (sbfe_wav_drop_chunks); chunks of one call must not overlap inside an
+    utterance."""
+    B, L = out.shape
+    tab = torch.tensor(chunks, dtype=torch.int32).reshape(-1, 4)
+    max_len = int(tab[:, 2].max()) if tab.numel() else 0
+    d_tab = tab.to(out.device, non_blocking=True)
+    with torch.cuda.device(out.device):
+        check(lib().sbfe_wav_drop_chunks(_ptr(out), B, L, 1, _ptr(d_tab), tab.shape[0], max_len,
+                                         _ptr(noise), _ptr(noise_max), _stream()))
+    return mark_written(out)
+
+
+def wav_fir(x, taps, pad):
+    """out[b][t] = sum_k taps[k] x[b][t + k - pad] with zero padding (sbfe_wav_fir)."""
+    B, L = x.shape
+    out = torch.empty_like(x)
+    taps = taps.to(device=x.device, dtype=torch.float32).contiguous()
+    with torch.cuda.device(x.device):
+        check(lib().sbfe_wav_fir(_ptr(x), B, L, _ptr(taps), taps.numel(), int(pad), _ptr(out),
+                                 _stream()))
+    return out
+
+
+def wav_clip(x, value):
+    """clamp(x, -value, value) into a new tensor (sbfe_wav_clip)."""
+    out = torch.empty_like(x)
+    with torch.cuda.device(x.device):
+        check(lib().sbfe_wav_clip(_ptr(x), x.numel(), float(value), _ptr(out), _stream()))
+    return out
+
+
+def wav_resample(x, weights, first, in_stride, n_out):
+    """Polyphase resampling of x [B, L] -> [B, n_out] (sbfe_wav_resample); weights [P, W] float32
+    and first [P] int32 on x's device."""
+    B, L = x.shape
+    out = torch.empty((B, n_out), dtype=torch.float32, device=x.device)
+    P, W = weights.shape
+    with torch.cuda.device(x.device):
+        check(lib().sbfe_wav_resample(_ptr(x), B, L, _ptr(weights), _ptr(first), P, int(in_stride), W,
+                                      n_out, _ptr(out), _stream()))
+    return out
