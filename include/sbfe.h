@@ -100,8 +100,8 @@ SBFE_API int64_t sbfe_fbank_workspace_bytes(const sbfe_fbank_desc* desc, int64_t
  *  (a) d_tile_stats == NULL: out holds the dB values WITHOUT the
  *      per-utterance top_db clamp; d_utt_max[b] (zeroed by the caller first; may be NULL) receives
  *      the key of max_{t,m} out[b] for a later clamp (sbfe_post_forward).  top_db is ignored.
- *  (b) tile records, only where sbfe_fbank_tile_frames(desc) = R > 0 (fused n_fft 400 / hop 160
- *      kernel): d_tile_stats = [B][ceil(T/R)] records of W = sbfe_fbank_tile_stats_floats(desc)
+ *  (b) tile records, only where sbfe_fbank_tile_frames(desc) = R > 0 (the fused n_fft 400 and
+ *      n_fft 512 kernels, hop 160): d_tile_stats = [B][ceil(T/R)] records of W = sbfe_fbank_tile_stats_floats(desc)
  *      = 3*M + 4 words.  When the call's work completes, out IS top_db-clamped
  *      (x = max(x, max_b - top_db), features.py:706-710, the maximum taken over all T frames of
  *      the padded utterance; top_db < 0: no clamp), and record j of utterance b holds
@@ -124,7 +124,7 @@ SBFE_API int sbfe_fbank_forward(const sbfe_fbank_desc* desc, const float* d_wav,
  * valid samples: utterance b = d_packed[d_offsets[b] .. + d_nsamples[b]) (offsets multiples of
  * 4 samples for 16-byte aligned rows), d_nsamples[b] <= L.  Result = sbfe_fbank_forward on the
  * zero-padded [B, L] batch, bit for bit; the padding is never materialised (the copy engine of
- * the fused kernel zero-fills).  Only where sbfe_fbank_tile_frames(desc) != 0, else
+ * the fused kernel zero-fills).  Only where sbfe_fbank_ragged_supported(desc) != 0, else
  * SBFE_E_INVAL. */
 SBFE_API int sbfe_fbank_forward_ragged(const sbfe_fbank_desc* desc, const float* d_packed,
                               const int64_t* d_offsets, const int32_t* d_nsamples, int64_t B,
@@ -144,6 +144,8 @@ SBFE_API int sbfe_fbank_forward_ragged_pcm16(const sbfe_fbank_desc* desc, const 
                                     void* stream);
 
 SBFE_API int32_t sbfe_fbank_tile_frames(const sbfe_fbank_desc* desc);
+/* 1 where sbfe_fbank_forward_ragged[_pcm16] take this configuration (fused n_fft 400 / hop 160). */
+SBFE_API int32_t sbfe_fbank_ragged_supported(const sbfe_fbank_desc* desc);
 SBFE_API int32_t sbfe_fbank_tile_stats_floats(const sbfe_fbank_desc* desc);
 
 /* InputNormalization statistics (features.py:1020-1031, 1120-1145; same contract as

@@ -54,6 +54,7 @@ SIGNATURES = {
     "sbfe_fbank_forward_ragged_pcm16": (C.c_int, [_DESC, _P, _P, _P, _I64, _I64, _F, _P, _P, _P, _F,
                                                   _P]),
     "sbfe_fbank_tile_frames": (_I32, [_DESC]),
+    "sbfe_fbank_ragged_supported": (_I32, [_DESC]),
     "sbfe_fbank_tile_stats_floats": (_I32, [_DESC]),
     "sbfe_norm_stats_tiles": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, _I32, _F, _P, _I32, _F, _P,
                                         _P, _P]),

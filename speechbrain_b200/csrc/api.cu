@@ -16,6 +16,9 @@ int launch_norm_sentence_tiles(const float*, const float*, int64_t, int64_t, int
 int64_t istft_workspace_bytes(int64_t, int64_t, int);
 int launch_istft(const float*, int64_t, int64_t, int, int, const float*, int, int64_t, float*, void*,
                  int64_t, cudaStream_t);
+bool fbank512_supported(const sbfe_fbank_desc*);
+int launch_fbank512(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
+                    sbfe_maxkey_t*, float*, float, cudaStream_t);
 bool fbank_pow2_supported(const sbfe_fbank_desc*);
 bool mel_dense_mma(const sbfe_fbank_desc*);
 int launch_fbank_pow2(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
@@ -92,13 +95,18 @@ int64_t sbfe_num_frames(int64_t n_samples, int32_t hop) {
 
 int64_t sbfe_fbank_workspace_bytes(const sbfe_fbank_desc* d, int64_t B, int64_t L) {
   if (!d || d->hop < 1 || B < 0 || L < 0) return SBFE_E_INVAL;
-  if (!mel_dense_mma(d) && (fused_ok(d) || fbank_pow2_supported(d))) return 0;
+  if (!mel_dense_mma(d) && (fused_ok(d) || fbank512_supported(d) || fbank_pow2_supported(d))) return 0;
   return B * (1 + L / d->hop) * (int64_t)(d->n_fft / 2 + 1) * (int64_t)sizeof(float);
 }
 
 int32_t sbfe_fbank_tile_frames(const sbfe_fbank_desc* d) {
-  // a dense filterbank goes through the tensor-core projection, not the fused kernel
-  return (d && desc_ok(d, true) && fbank400_v3_supported(d) && !mel_dense_mma(d)) ? 32 : 0;
+  // a dense filterbank goes through the tensor-core projection, not the fused kernels
+  return (d && desc_ok(d, true) && (fbank400_v3_supported(d) || fbank512_supported(d)) &&
+          !mel_dense_mma(d)) ? 32 : 0;
+}
+
+int32_t sbfe_fbank_ragged_supported(const sbfe_fbank_desc* d) {
+  return (d && desc_ok(d, true) && fbank400_v3_supported(d) && !mel_dense_mma(d)) ? 1 : 0;
 }
 
 int32_t sbfe_fbank_tile_stats_floats(const sbfe_fbank_desc* d) {
@@ -117,6 +125,8 @@ int sbfe_fbank_forward(const sbfe_fbank_desc* d, const float* d_wav, int64_t B, 
   if (fbank400_v3_supported(d) && !mel_dense_mma(d))
     return launch_fbank400_v3(d, d_wav, 0, 1.f, nullptr, nullptr, B, L, wav_stride, d_out, d_utt_max,
                               d_tile_stats, top_db, s);
+  if (fbank512_supported(d) && !mel_dense_mma(d))
+    return launch_fbank512(d, d_wav, B, L, wav_stride, d_out, d_utt_max, d_tile_stats, top_db, s);
   if (d_tile_stats) return SBFE_E_INVAL;  // only where sbfe_fbank_tile_frames() != 0
   // dense (gaussian) filterbank: power spectrum to the workspace, projection on the tensor cores
   if (!mel_dense_mma(d)) {
@@ -137,7 +147,7 @@ int sbfe_fbank_forward_ragged(const sbfe_fbank_desc* d, const float* d_packed,
   if (!desc_ok(d, true) || B < 0 || L < 0) return SBFE_E_INVAL;
   if (B == 0) return 0;
   if (!d_packed || !d_offsets || !d_nsamples || !d_out) return SBFE_E_INVAL;
-  if (!sbfe_fbank_tile_frames(d)) return SBFE_E_INVAL;  // pad on the device and use sbfe_fbank_forward
+  if (!sbfe_fbank_ragged_supported(d)) return SBFE_E_INVAL;  // pad on the device and use sbfe_fbank_forward
   return launch_fbank400_v3(d, d_packed, 0, 1.f, d_offsets, d_nsamples, B, L, 0, d_out, d_utt_max,
                             d_tile_stats, top_db, (cudaStream_t)stream);
 }
@@ -151,7 +161,7 @@ int sbfe_fbank_forward_ragged_pcm16(const sbfe_fbank_desc* d, const int16_t* d_p
     return SBFE_E_INVAL;
   if (B == 0) return 0;
   if (!d_packed || !d_offsets || !d_nsamples || !d_out) return SBFE_E_INVAL;
-  if (!sbfe_fbank_tile_frames(d)) return SBFE_E_INVAL;  // convert on the device and use sbfe_fbank_forward
+  if (!sbfe_fbank_ragged_supported(d)) return SBFE_E_INVAL;  // convert on the device and use sbfe_fbank_forward
   return launch_fbank400_v3(d, d_packed, 1, scale, d_offsets, d_nsamples, B, L, 0, d_out, d_utt_max,
                             d_tile_stats, top_db, (cudaStream_t)stream);
 }

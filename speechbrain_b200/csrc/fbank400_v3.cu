@@ -838,4 +838,23 @@ int launch_fbank400_v3(const sbfe_fbank_desc* d, const void* wav, int pcm16, flo
   return rc;
 }
 
+// the clamp launch of mode (b) for any kernel that emits the same 32-frame tile records
+int launch_clamp_tiles(const sbfe_fbank_desc* d, int64_t B, int64_t T, float* out, const float* tile_stats,
+                       float top_db, cudaStream_t stream) {
+  using namespace v3;
+  Params prm = {};
+  prm.db = DbParams{d->multiplier * 0.30102999566398120f, d->amin, d->db_offset, d->floor_db,
+                    d->log_mel};
+  prm.n_mels = d->n_mels;
+  prm.T = T;
+  prm.out = out;
+  prm.tile_stats = const_cast<float*>(tile_stats);
+  prm.top_db = top_db;
+  const int64_t tiles = (T + kTile - 1) / kTile;
+  if (tiles * B > 0x7fffffff) return SBFE_E_TOOBIG;
+  prm.tiles_per_utt = (unsigned)tiles;
+  prm.n_tiles = (unsigned)(tiles * B);
+  return launch_pdl(pick_clamp(d->n_mels), dim3(prm.n_tiles), dim3(kClampThreads), 0, stream, prm);
+}
+
 }  // namespace sbfe

@@ -198,6 +198,43 @@ SBFE_HD void stage2_k10(const T (&y)[20], cx<T> (&C)[10]) {
   dft10(c, C);
 }
 
+
+// ---- radix-4 butterfly, forward (W4 = -i), in place: y_q = sum_m a_m W4^(m q) ---------------------
+template <class T>
+SBFE_HD void radix4(cx<T>& a0, cx<T>& a1, cx<T>& a2, cx<T>& a3) {
+  const T s02r = a0.re + a2.re, s02i = a0.im + a2.im, d02r = a0.re - a2.re, d02i = a0.im - a2.im;
+  const T s13r = a1.re + a3.re, s13i = a1.im + a3.im, d13r = a1.re - a3.re, d13i = a1.im - a3.im;
+  a0 = cx<T>{s02r + s13r, s02i + s13i};
+  a2 = cx<T>{s02r - s13r, s02i - s13i};
+  a1 = cx<T>{d02r + d13i, d02i - d13r};   // (a0 - a2) - i (a1 - a3)
+  a3 = cx<T>{d02r - d13i, d02i + d13r};   // (a0 - a2) + i (a1 - a3)
+}
+
+// ---- complex 16-point DFT (4 x 4 Cooley-Tukey), natural order in and out: X[k] = out[k] --------
+// n = j + 4 m, k = q + 4 r:  W16^(nk) = W16^(jq) W4^(jr) W4^(mq).  144 adds + 8 twiddle products.
+template <class T>
+SBFE_HD void dft16(const cx<T> (&in)[16], cx<T> (&X)[16]) {
+  constexpr float c1 = 0.92387953251128674f, s1 = 0.38268343236508977f, h = 0.70710678118654752f;
+  cx<T> a[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) a[i] = in[i];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) radix4(a[j], a[j + 4], a[j + 8], a[j + 12]);   // a[j + 4 q] = b[j][q]
+  a[5] = cmuls(a[5], c1, -s1);                       // W16^1
+  a[9] = cmuls(a[9], h, -h);                         // W16^2
+  a[13] = cmuls(a[13], s1, -c1);                     // W16^3
+  a[6] = cmuls(a[6], h, -h);                         // W16^2
+  a[10] = cx<T>{a[10].im, -a[10].re};                // W16^4 = -i
+  a[14] = cmuls(a[14], -h, -h);                      // W16^6
+  a[7] = cmuls(a[7], s1, -c1);                       // W16^3
+  a[11] = cmuls(a[11], -h, -h);                      // W16^6
+  a[15] = cmuls(a[15], -c1, s1);                     // W16^9
+#pragma unroll
+  for (int q = 0; q < 4; ++q) radix4(a[4 * q], a[4 * q + 1], a[4 * q + 2], a[4 * q + 3]);
+#pragma unroll
+  for (int k = 0; k < 16; ++k) X[k] = a[4 * (k & 3) + (k >> 2)];             // a[4 q + r] = X[q + 4 r]
+}
+
 // bin (0..200) that output j of a stage-2 unit lands in (mirrored above 200)
 SBFE_HD int stage2_bin(int k1, int h, int j) {
   const int k = k1 + 20 * (2 * j + h);

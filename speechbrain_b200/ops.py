@@ -178,7 +178,7 @@ class TileStats:
 def ragged_supported(tables, device):
     """True when sbfe_fbank_forward_ragged can take this configuration."""
     desc, _ = tables.on(device)
-    return int(lib().sbfe_fbank_tile_frames(C.byref(desc))) > 0
+    return int(lib().sbfe_fbank_ragged_supported(C.byref(desc))) > 0
 
 
 def fbank_forward(tables, wav, tile_stats=False, top_db=80.0):

@@ -162,6 +162,39 @@ def test_cfg2_full_size_vs_oracle(sb):
     _check_sentence_norm(out.cpu().numpy(), ref64, lens)
 
 
+def test_nfft512_full_size_vs_oracle_and_generic_path(sb):
+    """Fbank(n_fft=512) on the cfg2 batch through the fused 512-point kernel (fbank512.cu: 16 x 16
+    complex FFT + untangle in registers, tile records, clamp launch, one-launch normalisation)
+    against the float64 oracle, and against the library's generic Stockham path on a batch slice."""
+    import os
+
+    import bench
+
+    wav_t, lens_t = bench.synth_batch(3, "cpu")
+    wav, lens = wav_t.numpy(), lens_t.numpy()
+    fb = sb.Fbank(n_mels=80, n_fft=512)
+    feats = fb(wav_t.cuda())
+    assert getattr(feats, "_sbfe_tile_stats", None) is not None      # the fused kernel took it
+    got = feats.cpu().numpy()
+    assert got.shape == (32, 1601, 80)
+    consts = (fb.compute_fbanks.f_central.numpy(), fb.compute_fbanks.band.numpy())
+    kw = dict(n_mels=80, n_fft=512, mel_params=consts, window=fb.compute_STFT.window.numpy())
+    sl = [0, 13, 31]
+    ref64 = onp.fbank(wav[sl], dtype=np.float64, **kw)
+    ref32 = onp.fbank(wav[sl], dtype=np.float32, **kw)
+    _protocol_full(got[sl], ref64, ref32)
+    # STFT(n_fft=512) is the Stockham kernel: an independent implementation inside the library
+    st = sb.STFT(sample_rate=16000, n_fft=512)(wav_t[sl].cuda())
+    power = (st ** 2).sum(-1)
+    mel = torch.matmul(power, fb.compute_fbanks.fbank_matrix().cuda())
+    x_db = 10 * torch.log10(torch.clamp(mel, min=1e-10))
+    x_db = torch.maximum(x_db, x_db.amax(dim=(1, 2), keepdim=True) - 80.0)
+    assert float((feats[sl] - x_db).abs().max()) < 2e-3
+    out = sb.InputNormalization(norm_type="sentence")(feats, lens_t.cuda())
+    full64 = onp.fbank(wav[:4], dtype=np.float64, **kw)
+    _check_sentence_norm(out[:4].cpu().numpy(), full64, lens[:4])
+
+
 def test_cfg3_full_size_vs_oracle(sb):
     """64 x 4 s MFCC: 23 mel -> 20 DCT -> deltas -> context 5+5 = 660."""
     wav = gc.synth_wav(703, 64, 64000)
