@@ -179,9 +179,21 @@ SBFE_API int sbfe_norm_sentence_tiles(const float* d_x, const float* d_lengths, 
                              int32_t flags, void* d_out, void* stream);
 
 /* STFT.forward for [B, L] input (processing/features.py:133-188):
- * out [B, T, bins, 2] (re, im), or, with power_only != 0, [B, T, bins] = re^2+im^2. */
+ * out [B, T, bins, 2] (re, im), or, with power_only != 0, [B, T, bins] = re^2+im^2.
+ * flags select torch.stft's other modes (STFT.__init__ :101-112):
+ *   SBFE_STFT_NO_CENTER  center=False: frame t starts at t * hop, T = 1 + (L - n_fft) / hop
+ *                        (0 when L < n_fft); default: frame t is centred on t * hop, T = 1 + L / hop
+ *   SBFE_STFT_REFLECT    pad_mode="reflect" instead of zeros (centred only; needs L > n_fft / 2)
+ *   SBFE_STFT_TWOSIDED   onesided=False: bins = n_fft (X[n_fft - k] = conj X[k]) instead of
+ *                        n_fft / 2 + 1
+ * sbfe_stft_frames gives T for the same flags. */
+#define SBFE_STFT_NO_CENTER 1
+#define SBFE_STFT_REFLECT 2
+#define SBFE_STFT_TWOSIDED 4
+SBFE_API int64_t sbfe_stft_frames(const sbfe_fbank_desc* desc, int64_t L, int32_t flags);
 SBFE_API int sbfe_stft_forward(const sbfe_fbank_desc* desc, const float* d_wav, int64_t B, int64_t L,
-                      int64_t wav_stride, float* d_out, int32_t power_only, void* stream);
+                      int64_t wav_stride, float* d_out, int32_t power_only, int32_t flags,
+                      void* stream);
 
 /* ---- next row: ISTFT.forward (processing/features.py:283-324) = torch.istft
  * for one-sided spectra: d_spec [B, T, n_fft/2 + 1, 2] -> d_out [B, out_len].  Per frame the

@@ -60,7 +60,8 @@ SIGNATURES = {
                                         _P, _P]),
     "sbfe_norm_sentence_tiles": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, _I32, _F, _P, _I32, _F,
                                            _I32, _P, _P]),
-    "sbfe_stft_forward": (C.c_int, [_DESC, _P, _I64, _I64, _I64, _P, _I32, _P]),
+    "sbfe_stft_frames": (_I64, [_DESC, _I64, _I32]),
+    "sbfe_stft_forward": (C.c_int, [_DESC, _P, _I64, _I64, _I64, _P, _I32, _I32, _P]),
     "sbfe_istft_workspace_bytes": (_I64, [_I64, _I64, _I32]),
     "sbfe_istft_forward": (C.c_int, [_P, _I64, _I64, _I32, _I32, _P, _I32, _I64, _P, _P, _I64, _P]),
     "sbfe_spectral_magnitude": (C.c_int, [_P, _I64, _F, _I32, _F, _P, _P]),

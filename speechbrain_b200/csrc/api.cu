@@ -23,8 +23,9 @@ bool fbank_pow2_supported(const sbfe_fbank_desc*);
 bool mel_dense_mma(const sbfe_fbank_desc*);
 int launch_fbank_pow2(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
                       sbfe_maxkey_t*, cudaStream_t);
+int64_t stft_frames(const sbfe_fbank_desc*, int64_t, int);
 int launch_stft_generic(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
-                        int, cudaStream_t);
+                        int, int, cudaStream_t);
 int launch_spectral_magnitude(const float*, int64_t, float, int, float, float*, cudaStream_t);
 int launch_mel_db(const sbfe_fbank_desc*, const float*, int64_t, int64_t, float*, sbfe_maxkey_t*,
                   cudaStream_t);
@@ -135,7 +136,7 @@ int sbfe_fbank_forward(const sbfe_fbank_desc* d, const float* d_wav, int64_t B, 
       return launch_fbank_pow2(d, d_wav, B, L, wav_stride, d_out, d_utt_max, s);
   }
   if (!d_ws || ws_bytes < sbfe_fbank_workspace_bytes(d, B, L)) return SBFE_E_NOSPACE;
-  int rc = launch_stft_generic(d, d_wav, B, L, wav_stride, (float*)d_ws, 1, s);
+  int rc = launch_stft_generic(d, d_wav, B, L, wav_stride, (float*)d_ws, 1, 0, s);
   if (rc) return rc;
   return launch_mel_db(d, (const float*)d_ws, B, 1 + L / d->hop, d_out, d_utt_max, s);
 }
@@ -181,12 +182,23 @@ int sbfe_istft_forward(const float* d_spec, int64_t B, int64_t T, int32_t n_fft,
                       (cudaStream_t)stream);
 }
 
+int64_t sbfe_stft_frames(const sbfe_fbank_desc* d, int64_t L, int32_t flags) {
+  if (!desc_ok(d, false) || L < 0) return SBFE_E_INVAL;
+  return stft_frames(d, L, flags);
+}
+
 int sbfe_stft_forward(const sbfe_fbank_desc* d, const float* d_wav, int64_t B, int64_t L,
-                      int64_t wav_stride, float* d_out, int32_t power_only, void* stream) {
-  if (!desc_ok(d, false) || B < 0 || L < 0 || wav_stride < L) return SBFE_E_INVAL;
+                      int64_t wav_stride, float* d_out, int32_t power_only, int32_t flags,
+                      void* stream) {
+  if (!desc_ok(d, false) || B < 0 || L < 0 || wav_stride < L || (flags & ~7)) return SBFE_E_INVAL;
+  // reflection needs the mirror image inside the signal (torch.stft raises otherwise); reflect
+  // without centring pads nothing
+  if ((flags & SBFE_STFT_REFLECT) && !(flags & SBFE_STFT_NO_CENTER) && L <= d->n_fft / 2)
+    return SBFE_E_INVAL;
   if (B == 0) return 0;
   if ((!d_wav && L > 0) || !d_out) return SBFE_E_INVAL;
-  return launch_stft_generic(d, d_wav, B, L, wav_stride, d_out, power_only, (cudaStream_t)stream);
+  return launch_stft_generic(d, d_wav, B, L, wav_stride, d_out, power_only, flags,
+                             (cudaStream_t)stream);
 }
 
 int sbfe_spectral_magnitude(const float* d_stft, int64_t n, float power, int32_t take_log,

@@ -12,6 +12,17 @@
 
 namespace sbfe {
 
+// sample g of a signal of L samples under torch.stft's padding: zeros, or (pad_mode="reflect")
+// the mirror image about the first / last sample (processing/features.py:161-172)
+__device__ __forceinline__ float padded_sample(const float* __restrict__ w, int64_t g, int64_t L,
+                                               int reflect) {
+  if (reflect) {
+    if (g < 0) g = -g;
+    if (g >= L) g = 2 * (L - 1) - g;
+  }
+  return (g >= 0 && g < L) ? __ldg(w + g) : 0.f;
+}
+
 constexpr int kGenFrames = 4;     // frames per CTA
 constexpr int kGenThreads = 256;
 
@@ -19,7 +30,8 @@ constexpr int kGenThreads = 256;
 __global__ void __launch_bounds__(kGenThreads)
 stft_generic_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, int64_t T,
                     const float* __restrict__ window, int n_fft, int hop,
-                    float* __restrict__ out, int power_only, unsigned tiles) {
+                    float* __restrict__ out, int power_only, unsigned tiles, int start, int reflect,
+                    int twosided) {
   extern __shared__ __align__(16) float smem[];
   float2* s_cs = reinterpret_cast<float2*>(smem);
   float* s_fr = smem + 2 * n_fft;
@@ -34,8 +46,8 @@ stft_generic_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride
   }
   for (int i = threadIdx.x; i < kGenFrames * n_fft; i += kGenThreads) {
     const int f = i / n_fft, n = i - f * n_fft;
-    const int64_t g = (t0 + f) * hop - n_fft / 2 + n;
-    s_fr[i] = (g >= 0 && g < L) ? __ldg(w + g) * __ldg(window + n) : 0.f;
+    const int64_t g = (t0 + f) * hop + start + n;
+    s_fr[i] = padded_sample(w, g, L, reflect) * __ldg(window + n);
   }
   __syncthreads();
   for (int p = threadIdx.x; p < kGenFrames * bins; p += kGenThreads) {
@@ -51,11 +63,15 @@ stft_generic_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride
       idx += k;
       if (idx >= n_fft) idx -= n_fft;
     }
-    const int64_t o = ((b * T + t0 + f) * bins + k);
+    const int obins = twosided ? n_fft : bins;
+    const int64_t o = ((b * T + t0 + f) * obins + k);
     if (power_only) {
       out[o] = re * re + im * im;
+      if (twosided && k > 0 && k < n_fft - k) out[o + n_fft - 2 * k] = re * re + im * im;
     } else {
       reinterpret_cast<float2*>(out)[o] = make_float2(re, im);
+      if (twosided && k > 0 && k < n_fft - k)   // X[n_fft - k] = conj X[k]
+        reinterpret_cast<float2*>(out)[o + n_fft - 2 * k] = make_float2(re, -im);
     }
   }
 }
@@ -115,7 +131,8 @@ template <int MODE>
 __global__ void __launch_bounds__(kGenThreads)
 stft_pow2_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, int64_t T,
                  const float* __restrict__ window, int n_fft, const FftPlan plan, int hop,
-                 float* __restrict__ out, int power_only, unsigned tiles, const MelArgs mel) {
+                 float* __restrict__ out, int power_only, unsigned tiles, const MelArgs mel,
+                 int start, int reflect, int twosided) {
   constexpr bool MEL = MODE == 1, INV = MODE == 2;
   extern __shared__ __align__(16) float smem[];
   const int M = n_fft >> 1;
@@ -157,11 +174,11 @@ stft_pow2_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, i
   // division, no per-element window load
   for (int n = threadIdx.x; n < M && !INV; n += kGenThreads) {
     const float w0 = __ldg(window + 2 * n), w1 = __ldg(window + 2 * n + 1);
-    int64_t g = t0 * hop - n_fft / 2 + 2 * n;
+    int64_t g = t0 * hop + start + 2 * n;
 #pragma unroll 4
     for (int f = 0; f < kPow2Frames; ++f, g += hop) {
-      const float x0 = (g >= 0 && g < L) ? __ldg(w + g) * w0 : 0.f;
-      const float x1 = (g + 1 >= 0 && g + 1 < L) ? __ldg(w + g + 1) * w1 : 0.f;
+      const float x0 = padded_sample(w, g, L, reflect) * w0;
+      const float x1 = padded_sample(w, g + 1, L, reflect) * w1;
       s_a[f * M + n] = make_float2(x0, x1);
     }
   }
@@ -277,11 +294,15 @@ stft_pow2_kernel(const float* __restrict__ wav, int64_t L, int64_t wav_stride, i
         reinterpret_cast<float*>(dst)[f * bins + k] = re * re + im * im;  // idle buffer: [frame][bins]
         continue;
       }
-      const int64_t o = ((b * T + t0 + f) * bins + k);
+      const int obins = twosided ? n_fft : bins;
+      const int64_t o = ((b * T + t0 + f) * obins + k);
       if (power_only) {
         out[o] = re * re + im * im;
+        if (twosided && k > 0 && k < M) out[o + n_fft - 2 * k] = re * re + im * im;
       } else {
         reinterpret_cast<float2*>(out)[o] = make_float2(re, im);
+        if (twosided && k > 0 && k < M)   // X[n_fft - k] = conj X[k]
+          reinterpret_cast<float2*>(out)[o + n_fft - 2 * k] = make_float2(re, -im);
       }
     }
   }
@@ -338,7 +359,8 @@ int launch_fbank_pow2(const sbfe_fbank_desc* d, const float* wav, int64_t B, int
                        d->log_mel},
               utt_max};
   stft_pow2_kernel<1><<<(unsigned)(tiles * B), kGenThreads, smem, stream>>>(
-      wav, L, wav_stride, T, d->d_window, d->n_fft, plan, d->hop, out, 1, (unsigned)tiles, mel);
+      wav, L, wav_stride, T, d->d_window, d->n_fft, plan, d->hop, out, 1, (unsigned)tiles, mel,
+      -d->n_fft / 2, 0, 0);
   return check_last();
 }
 
@@ -357,13 +379,23 @@ int launch_irfft_frames(const float* spec, int64_t n_frames, int n_fft, const fl
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
   stft_pow2_kernel<2><<<(unsigned)tiles, kGenThreads, smem, stream>>>(
-      spec, 0, 0, n_frames, window, n_fft, plan, 1, frames, 0, (unsigned)tiles, MelArgs{});
+      spec, 0, 0, n_frames, window, n_fft, plan, 1, frames, 0, (unsigned)tiles, MelArgs{}, 0, 0, 0);
   return check_last();
 }
 
+// flags (include/sbfe.h): SBFE_STFT_NO_CENTER 1, SBFE_STFT_REFLECT 2, SBFE_STFT_TWOSIDED 4
+int64_t stft_frames(const sbfe_fbank_desc* d, int64_t L, int flags) {
+  if (flags & 1) return L < d->n_fft ? 0 : 1 + (L - d->n_fft) / d->hop;
+  return 1 + L / d->hop;
+}
+
 int launch_stft_generic(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64_t L,
-                        int64_t wav_stride, float* out, int power_only, cudaStream_t stream) {
-  const int64_t T = 1 + L / d->hop;
+                        int64_t wav_stride, float* out, int power_only, int flags,
+                        cudaStream_t stream) {
+  const int64_t T = stft_frames(d, L, flags);
+  if (T == 0) return 0;
+  const int start = (flags & 1) ? 0 : -d->n_fft / 2;
+  const int reflect = (flags & 2) ? 1 : 0, twosided = (flags & 4) ? 1 : 0;
   const int64_t tiles = (T + kGenFrames - 1) / kGenFrames;
   if (tiles * B > 0x7fffffff) return SBFE_E_TOOBIG;
   if (d->n_fft > 4096) return SBFE_E_TOOBIG;
@@ -378,7 +410,7 @@ int launch_stft_generic(const sbfe_fbank_desc* d, const float* wav, int64_t B, i
     if (e2 != cudaSuccess) return (int)e2;
     stft_pow2_kernel<0><<<(unsigned)(tiles2 * B), kGenThreads, smem2, stream>>>(
         wav, L, wav_stride, T, d->d_window, d->n_fft, plan, d->hop, out, power_only, (unsigned)tiles2,
-        MelArgs{});
+        MelArgs{}, start, reflect, twosided);
     return check_last();
   }
   const size_t smem = (size_t)(2 + kGenFrames) * d->n_fft * sizeof(float);
@@ -386,7 +418,8 @@ int launch_stft_generic(const sbfe_fbank_desc* d, const float* wav, int64_t B, i
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
   stft_generic_kernel<<<(unsigned)(tiles * B), kGenThreads, smem, stream>>>(
-      wav, L, wav_stride, T, d->d_window, d->n_fft, d->hop, out, power_only, (unsigned)tiles);
+      wav, L, wav_stride, T, d->d_window, d->n_fft, d->hop, out, power_only, (unsigned)tiles, start,
+      reflect, twosided);
   return check_last();
 }
 

@@ -57,6 +57,9 @@ class _Lobe(torch.nn.Module):
             mel = fb.tables()  # re-drawn per call when the reference would jitter
             st = self.compute_STFT
             st._check_supported()
+            if not st._default_mode():   # the lobes build their STFT with the defaults (:107-112)
+                raise NotImplementedError("Fbank / MFCC run the default STFT mode (center=True, "
+                                          "pad_mode='constant', onesided=True)")
             win = st.window.detach().float().cpu()
             if st.normalized_stft:
                 win = win * (float(st.n_fft) ** -0.5)

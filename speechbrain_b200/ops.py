@@ -280,17 +280,23 @@ def norm_sentence_tiles(x, lengths, ts, mean_norm=True, std_norm=True, eps=1e-10
     return mark_written(out)
 
 
-def stft_forward(tables, wav, power_only=False):
-    """wav [B, L] -> [B, T, bins, 2] (or [B, T, bins] power).  sbfe_stft_forward."""
+def stft_forward(tables, wav, power_only=False, center=True, reflect=False, onesided=True):
+    """wav [B, L] -> [B, T, bins, 2] (or [B, T, bins] power).  sbfe_stft_forward; the keyword
+    flags are torch.stft's center / pad_mode="reflect" / onesided."""
     wav = _wav2d(wav)
     B, L = wav.shape
-    T = 1 + L // tables.hop
+    flags = (0 if center else 1) | (2 if reflect and center else 0) | (0 if onesided else 4)
     desc, _ = tables.on(wav.device)
-    shape = (B, T, tables.bins) if power_only else (B, T, tables.bins, 2)
+    T = int(lib().sbfe_stft_frames(C.byref(desc), L, flags))
+    if T <= 0 and not center:
+        raise RuntimeError("STFT(center=False) needs at least n_fft = %d samples, got %d"
+                           % (tables.n_fft, L))
+    bins = tables.bins if onesided else tables.n_fft
+    shape = (B, T, bins) if power_only else (B, T, bins, 2)
     out = torch.empty(shape, dtype=torch.float32, device=wav.device)
     with torch.cuda.device(wav.device):
         check(lib().sbfe_stft_forward(C.byref(desc), _ptr(wav), B, L, L, _ptr(out),
-                                      int(power_only), _stream()))
+                                      int(power_only), flags, _stream()))
     return out
 
 

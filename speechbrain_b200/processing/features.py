@@ -24,8 +24,8 @@ class STFT(torch.nn.Module):
     """Short-term Fourier transform; reference: processing/features.py:50-188.
 
     ``[B, L]`` -> ``[B, T, n_fft//2+1, 2]``; ``[B, L, C]`` -> ``[B, T, F, 2, C]``.
-    Supported natively: ``center=True``, ``pad_mode="constant"``, ``onesided=True``
-    (the only combination any recipe uses); anything else raises.
+    ``center`` True / False, ``pad_mode`` "constant" / "reflect" and ``onesided`` True / False are
+    all native (torch.stft's other pad modes, "replicate" / "circular", raise).
     """
 
     def __init__(self, sample_rate, win_length=25, hop_length=10, n_fft=400,
@@ -45,11 +45,14 @@ class STFT(torch.nn.Module):
         self._tables = None
 
     def _check_supported(self):
-        if not (self.center and self.pad_mode == "constant" and self.onesided):
+        if self.pad_mode not in ("constant", "reflect"):
             raise NotImplementedError(
-                "speechbrain_b200.STFT implements center=True, pad_mode='constant', "
-                "onesided=True (got center=%r, pad_mode=%r, onesided=%r)"
-                % (self.center, self.pad_mode, self.onesided))
+                "speechbrain_b200.STFT implements pad_mode 'constant' and 'reflect' (got %r)"
+                % (self.pad_mode,))
+
+    def _default_mode(self):
+        """The combination every recipe uses (and the fused Fbank / MFCC kernels implement)."""
+        return bool(self.center) and self.pad_mode == "constant" and bool(self.onesided)
 
     def tables(self):
         if self._tables is None:
@@ -65,10 +68,14 @@ class STFT(torch.nn.Module):
         if x.dim() == 3:  # [B, L, C] -> [B*C, L]   (processing/features.py:143-146)
             b, l, c = x.shape
             flat = x.transpose(1, 2).reshape(b * c, l)
-            out = ops.stft_forward(self.tables(), flat)  # [B*C, T, F, 2]
+            out = ops.stft_forward(self.tables(), flat, **self._mode())  # [B*C, T, F, 2]
             out = out.reshape(b, c, out.shape[1], out.shape[2], 2)
             return out.permute(0, 2, 3, 4, 1)  # [B, T, F, 2, C]    (:175-183)
-        return ops.stft_forward(self.tables(), x)
+        return ops.stft_forward(self.tables(), x, **self._mode())
+
+    def _mode(self):
+        return {"center": bool(self.center), "reflect": self.pad_mode == "reflect",
+                "onesided": bool(self.onesided)}
 
 
 class ISTFT(torch.nn.Module):
