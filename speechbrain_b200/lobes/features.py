@@ -35,10 +35,6 @@ class _Lobe(torch.nn.Module):
     def _make_common(self, requires_grad, sample_rate, f_min, f_max, n_fft, n_mels, filter_shape,
                      param_change_factor, param_rand_factor, left_frames, right_frames, win_length,
                      hop_length):
-        if requires_grad:
-            raise NotImplementedError(
-                "requires_grad=True (learnable filterbank) needs a backward pass; the B200 "
-                "frontend is forward-only - use the reference class for that")
         if f_max is None:
             f_max = sample_rate / 2
         self.compute_STFT = STFT(sample_rate=sample_rate, n_fft=n_fft, win_length=win_length,
@@ -78,6 +74,17 @@ class _Lobe(torch.nn.Module):
                 "input the reference sums over the channel axis, lobes/features.py:138-139)")
         fb = self.compute_fbanks
         ctx = self.context and self.context_window.context_len > 1
+        if not fb.freeze:
+            # requires_grad=True (next row N4): learnable centres / bands.  Power spectrum from the
+            # STFT kernel, then the Filterbank module's autograd-aware forward; the waveform gets
+            # no gradient, and the DCT / deltas / context stages have no backward pass here
+            if dct is not None or self.deltas or ctx:
+                raise NotImplementedError(
+                    "requires_grad=True is built for plain Fbank features (deltas=False, "
+                    "context=False); MFCC / deltas / context have no backward pass")
+            self.compute_STFT._check_supported()
+            spec = ops.stft_forward(self.compute_STFT.tables(), ops._wav2d(wav.detach()), power_only=True)
+            return fb(spec)
         if dct is None and not self.deltas and not ctx and fb.log_mel:
             # plain log-mel: ONE launch.  The fused kernel finishes each utterance itself (top_db
             # clamp, per-tile moments); a following InputNormalization gets its statistics from

@@ -344,6 +344,47 @@ def filterbank_forward(tables, spec):
     return out, utt_max
 
 
+_DENSE_TABLES = {}
+
+
+def filterbank_forward_dense(spec, mat, log_mel=True, multiplier=10.0, amin=1e-10, db_multiplier=0.0):
+    """Filterbank projection with a dense DEVICE matrix ``mat`` [bins, M] (a learnable filterbank
+    rebuilds it every step: no host copy, no sparsity scan): spec [B, T, bins] -> (dB or linear
+    mel [B, T, M] without the top_db clamp, utt_max keys).  Same entry point as filterbank_forward
+    with a descriptor whose tables describe the full matrix, which routes to the tensor-core
+    kernel (sbfe.h: mel_precision)."""
+    _require_cuda(spec, "spectrogram")
+    spec = _f32c(spec, "spectrogram")
+    B, T, bins = spec.shape
+    M = mat.shape[1]
+    if mat.shape[0] != bins:
+        raise ValueError("filterbank matrix has %d rows, spectrogram has %d bins" % (mat.shape[0], bins))
+    wt = mat.t().contiguous().float()                      # [M][bins]: filter m = row m
+    key = (spec.device, bins, M)
+    idx = _DENSE_TABLES.get(key)
+    if idx is None:
+        idx = (torch.zeros(M, dtype=torch.int32, device=spec.device),
+               torch.full((M,), bins, dtype=torch.int32, device=spec.device),
+               (torch.arange(M, dtype=torch.int32, device=spec.device) * bins).contiguous())
+        _DENSE_TABLES[key] = idx
+    tab = FrontendTables(2 * (bins - 1), 1, torch.ones(2 * (bins - 1)), None, log_mel, multiplier,
+                         amin, db_multiplier)
+    desc = FbankDesc()
+    desc.n_fft, desc.hop, desc.n_mels, desc.log_mel = tab.n_fft, 1, M, int(bool(log_mel))
+    desc.multiplier, desc.amin = tab.multiplier, tab.amin
+    desc.db_offset, desc.floor_db = tab.db_offset, tab.floor_db
+    desc.h_window = desc.d_window = wt.data_ptr()          # not used by the projection
+    desc.d_mel_start, desc.d_mel_count = idx[0].data_ptr(), idx[1].data_ptr()
+    desc.d_mel_offset, desc.d_mel_weight = idx[2].data_ptr(), wt.data_ptr()
+    desc.mel_nnz, desc.mel_pad4, desc.mel_precision = M * bins, 0, 0
+    out = torch.empty((B, T, M), dtype=torch.float32, device=spec.device)
+    utt_max = torch.zeros((B,), dtype=torch.int32, device=spec.device)
+    with torch.cuda.device(spec.device):
+        check(lib().sbfe_filterbank_forward(C.byref(desc), _ptr(spec), B, T, _ptr(out), _ptr(utt_max),
+                                            _stream()))
+    return out, utt_max
+
+
 def post_forward(x, utt_max=None, top_db=80.0, dct=None, deltas=False, delta_window=5,
                  context=False, left=0, right=0, inplace=False):
     """clamp -> DCT -> deltas -> context window (sbfe_post_forward)."""

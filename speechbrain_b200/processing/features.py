@@ -185,10 +185,6 @@ class Filterbank(torch.nn.Module):
         self.param_change_factor = param_change_factor
         self.param_rand_factor = param_rand_factor
         self.multiplier = 10 if self.power_spectrogram == 2 else 20
-        if not freeze:
-            raise NotImplementedError(
-                "learnable filterbanks (freeze=False / requires_grad=True) need a backward "
-                "pass; the B200 frontend is forward-only - keep the reference class for that")
         if self.f_min >= self.f_max:  # the reference only logs this (:457-462)
             logger.error("Require f_min: %f < f_max: %f", self.f_min, self.f_max)
         # mel-spaced centres and bands in float32, as the reference builds them (:464-488)
@@ -197,6 +193,10 @@ class Filterbank(torch.nn.Module):
         band = hz[1:] - hz[:-1]
         self.band = band[:-1]
         self.f_central = hz[1:-1]
+        if not self.freeze:  # learnable centres / bands, stored scaled like the reference (:476-482)
+            self.f_central = torch.nn.Parameter(
+                self.f_central / (self.sample_rate * self.param_change_factor))
+            self.band = torch.nn.Parameter(self.band / (self.sample_rate * self.param_change_factor))
         all_freqs = torch.linspace(0, self.sample_rate // 2, self.n_stft)
         self.all_freqs_mat = all_freqs.repeat(self.f_central.shape[0], 1)
         self._tables = None
@@ -222,9 +222,18 @@ class Filterbank(torch.nn.Module):
             return inside.float().t()
         return torch.exp(-0.5 * ((freqs - f_central_mat) / (band_mat / 2.0)) ** 2).t()
 
+    def _host_params(self):
+        """f_central / band in Hz on the host (a learnable filterbank stores them scaled)."""
+        fc, bw = self.f_central.detach().float().cpu(), self.band.detach().float().cpu()
+        if not self.freeze:
+            k = self.sample_rate * self.param_change_factor * self.param_change_factor
+            fc, bw = fc * k, bw * k
+        return fc, bw
+
     def _build_tables(self, jitter=None):
-        fc = self.f_central.float().cpu().unsqueeze(1).expand(-1, self.n_stft)
-        bw = self.band.float().cpu().unsqueeze(1).expand(-1, self.n_stft)
+        fc, bw = self._host_params()
+        fc = fc.unsqueeze(1).expand(-1, self.n_stft)
+        bw = bw.unsqueeze(1).expand(-1, self.n_stft)
         if jitter is not None:
             fc, bw = fc * jitter[0], bw * jitter[1]
         mat = self._create_fbank_matrix(fc, bw)
@@ -244,9 +253,31 @@ class Filterbank(torch.nn.Module):
 
     def fbank_matrix(self):
         """Dense ``[n_stft, n_mels]`` matrix (host), for inspection/tests."""
-        fc = self.f_central.float().cpu().unsqueeze(1).expand(-1, self.n_stft)
-        bw = self.band.float().cpu().unsqueeze(1).expand(-1, self.n_stft)
-        return self._create_fbank_matrix(fc, bw)
+        fc, bw = self._host_params()
+        return self._create_fbank_matrix(fc.unsqueeze(1).expand(-1, self.n_stft),
+                                         bw.unsqueeze(1).expand(-1, self.n_stft))
+
+    def _learnable_forward(self, spectrogram):
+        """freeze=False (:512-522, 534-551): the matrix is rebuilt from the parameters with torch
+        ops on their device (so autograd reaches f_central / band), the projection + dB + top_db
+        clamp run through the kernels (dense matrix: the tensor-core projection), and
+        ``_FilterbankGrad`` supplies the backward pass."""
+        dev = spectrogram.device
+        k = self.sample_rate * self.param_change_factor * self.param_change_factor
+        fc = (self.f_central.to(dev) * k).unsqueeze(1).expand(-1, self.n_stft)
+        bw = (self.band.to(dev) * k).unsqueeze(1).expand(-1, self.n_stft)
+        freqs = self.all_freqs_mat.to(dev)
+        if self.filter_shape == "triangular":
+            # the reference's op sequence (:603-612): torch.max / torch.min split the gradient at
+            # ties (a bin exactly on a filter's edge: f_min, f_max), clamp / minimum would not
+            slope = (freqs - fc) / bw
+            zero = torch.zeros(1, device=dev)
+            mat = torch.max(zero, torch.min(slope + 1.0, -slope + 1.0)).t()
+        elif self.filter_shape == "rectangular":
+            mat = (freqs.ge(fc - bw) & freqs.le(fc + bw)).float().t()
+        else:
+            mat = torch.exp(-0.5 * ((freqs - fc) / (bw / 2.0)) ** 2).t()
+        return _FilterbankGrad.apply(spectrogram, mat, self)
 
     @traceable()
     def forward(self, spectrogram):
@@ -254,9 +285,12 @@ class Filterbank(torch.nn.Module):
         if len(sp_shape) == 4:  # [B, T, F, C] -> [B*C, T, F]     (:541-545)
             spectrogram = spectrogram.permute(0, 3, 1, 2).reshape(
                 sp_shape[0] * sp_shape[3], sp_shape[1], sp_shape[2])
-        fbanks, utt_max = ops.filterbank_forward(self.tables(), spectrogram)
-        if self.log_mel:
-            fbanks = ops.post_forward(fbanks, utt_max, self.top_db, inplace=True)
+        if not self.freeze:
+            fbanks = self._learnable_forward(spectrogram)
+        else:
+            fbanks, utt_max = ops.filterbank_forward(self.tables(), spectrogram)
+            if self.log_mel:
+                fbanks = ops.post_forward(fbanks, utt_max, self.top_db, inplace=True)
         if len(sp_shape) == 4:  # (:553-558)
             fbanks = fbanks.reshape(sp_shape[0], sp_shape[3], fbanks.shape[1], fbanks.shape[2])
             fbanks = fbanks.permute(0, 2, 3, 1)
@@ -274,6 +308,54 @@ class Filterbank(torch.nn.Module):
             self._identity[f] = tab
         x_db, utt_max = ops.filterbank_forward(tab, x3)
         return ops.post_forward(x_db, utt_max, self.top_db, inplace=True).reshape(shape)
+
+
+class _FilterbankGrad(torch.autograd.Function):
+    """Learnable filterbank (next row N4): y = top_db_clamp(dB(spec @ W)).
+
+    Forward: the library's kernels on a dense device matrix (``ops.filterbank_forward_dense``:
+    tensor-core projection, then the clamp).  Backward (what autograd derives for the reference's
+    op chain, :548, 701-712): g_mel = g_y * multiplier / ln 10 / mel where mel > amin and y was
+    not clamped; the clamp's floor = utterance maximum - top_db also carries gradient - the sum of
+    g_y over an utterance's clamped elements goes to its maximum element(s), as ``amax`` /
+    ``torch.max`` do; g_spec = g_mel @ W^T and g_W = spec^T @ g_mel are plain library GEMMs."""
+
+    @staticmethod
+    def forward(ctx, spec, mat, mod):
+        spec = spec.float().contiguous()
+        y, utt_max = ops.filterbank_forward_dense(spec, mat.detach(), mod.log_mel, mod.multiplier,
+                                                  mod.amin, mod.db_multiplier)
+        raw = y
+        if mod.log_mel:
+            y = ops.post_forward(raw, utt_max, mod.top_db)
+        ctx.save_for_backward(spec, mat.detach(), raw, y)
+        ctx.cfg = (mod.log_mel, float(mod.multiplier), float(mod.amin), float(mod.db_multiplier))
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        spec, mat, raw, y = ctx.saved_tensors
+        log_mel, mult, amin, db_mul = ctx.cfg
+        g = g.contiguous()
+        if log_mel:
+            B = raw.shape[0]
+            clamped = raw < y                                   # raised to the floor
+            top = raw.reshape(B, -1).amax(dim=1).reshape(B, 1, 1)
+            is_max = raw == top
+            g_floor = (g * clamped).reshape(B, -1).sum(dim=1).reshape(B, 1, 1)
+            g_raw = torch.where(clamped, torch.zeros_like(g), g)
+            g_raw = g_raw + is_max * (g_floor / is_max.reshape(B, -1).sum(dim=1).reshape(B, 1, 1))
+            # raw = mult * log10(max(mel, amin)) - mult * db_mul  ->  mel from raw where mel > amin
+            mel = torch.pow(10.0, (raw + mult * db_mul) / mult)
+            above = raw > (mult * math.log10(amin) - mult * db_mul)
+            g_mel = torch.where(above, g_raw * (mult / math.log(10.0)) / mel, torch.zeros_like(g))
+        else:
+            g_mel = g
+        g_spec = torch.matmul(g_mel, mat.t()) if ctx.needs_input_grad[0] else None
+        g_mat = None
+        if ctx.needs_input_grad[1]:
+            g_mat = torch.matmul(spec.reshape(-1, spec.shape[-1]).t(), g_mel.reshape(-1, g_mel.shape[-1]))
+        return g_spec, g_mat, None
 
 
 class DCT(torch.nn.Module):

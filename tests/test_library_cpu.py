@@ -87,8 +87,7 @@ def test_drop_in_surface():
     assert list(inspect.signature(n.forward).parameters)[:2] == ["x", "lengths"]
     with pytest.raises(ValueError):
         sb.DCT(input_size=10, n_out=20)
-    with pytest.raises(NotImplementedError):
-        sb.Fbank(requires_grad=True)
+    assert not sb.Fbank(requires_grad=True).compute_fbanks.freeze   # learnable: tests/test_learnable.py
 
 
 def test_cpu_tensors_are_refused():
