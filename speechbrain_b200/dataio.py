@@ -92,8 +92,10 @@ class RaggedBatch:
                            mv(self.lengths), self.scale)
 
     def to_padded(self):
-        """Materialise the zero-padded ``[B, L]`` tensor (fallback / tests)."""
-        out = torch.zeros((self.batch_size, self.max_len), dtype=torch.float32, device=self.device)
-        for i, (o, n) in enumerate(zip(self.offsets.tolist(), self.nsamples.tolist())):
-            out[i, :n] = self.packed[o:o + n]      # int16 -> float32 is exact
+        """Materialise the zero-padded ``[B, L]`` tensor (configurations without a ragged kernel,
+        tests): one gather on the batch's device, nothing is read back to the host."""
+        idx = torch.arange(self.max_len, device=self.device).unsqueeze(0)
+        live = idx < self.nsamples.to(torch.int64).unsqueeze(1)
+        src = (self.offsets.unsqueeze(1) + idx).clamp_(max=max(self.packed.numel() - 1, 0))
+        out = torch.where(live, self.packed[src].to(torch.float32), 0.0)   # int16 -> float32 is exact
         return out * self.scale if self.packed.dtype == torch.int16 else out
