@@ -42,7 +42,7 @@ for name, B, L, F, make in cfgs():
     torch.manual_seed(1234 + rank)
     fe, norm = make()
     if norm is not None and norm.norm_type == "sentence":
-        sb.pair(fe, norm)   # the recipe-side declaration: features go straight into the normaliser
+        pass   # unmodified recipe flow: nothing to declare (round 1 paired the modules here)
     T = 1 + L // 160
     n_in = max(2, min(8, int(300e6 // (4 * B * L)) + 1))  # rotate over > L2 worth of input
     pool = [torch.randn(B, L, device=dev) * 0.1 for _ in range(n_in)]

@@ -74,6 +74,20 @@ static bool fused_ok(const sbfe_fbank_desc* d) {
 
 using namespace sbfe;
 
+#ifdef SBFE_EXP_TIMELINE
+namespace sbfe {
+int tl_sync_v3(unsigned long long*, int);
+int tl_sync_norm(unsigned long long*, int);
+}
+// kernels 0, 1 (producer, clamp) live in fbank400_v3.cu, 2, 3 (normalisation) in norm.cu
+extern "C" __attribute__((visibility("default"))) int sbfe_exp_timeline(unsigned long long* h_out, int reset) {
+  unsigned long long a[24], b[24];
+  int rc = sbfe::tl_sync_v3(a, reset) | sbfe::tl_sync_norm(b, reset);
+  for (int i = 0; i < 24; ++i) h_out[i] = i < 6 ? a[i] : b[i];
+  return rc;
+}
+#endif
+
 extern "C" {
 
 int sbfe_abi_version(void) { return SBFE_ABI_VERSION; }

@@ -102,6 +102,38 @@ __device__ __forceinline__ void pdl_launch_dependents() {
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 
+#ifdef SBFE_EXP_TIMELINE
+// experiment build (profiles/exp_timeline.sh): per kernel id, min start / min wait-return / max end
+// of its CTAs in %globaltimer ns; one copy of the stamps per translation unit
+static __device__ unsigned long long g_timeline[3 * 8];
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void tl_mark(int kernel, int what) {
+  if (threadIdx.x == 0) {
+    if (what < 2) atomicMin(&g_timeline[3 * kernel + what], gtimer());
+    else atomicMax(&g_timeline[3 * kernel + 2], gtimer());
+  }
+}
+#define SBFE_TL(kernel, what) tl_mark(kernel, what)
+// host side of one translation unit's copy: read (and optionally re-arm) the stamps
+#define SBFE_TL_DEFINE_SYNC(name)                                                             \
+  int name(unsigned long long* h_out, int reset) {                                            \
+    cudaDeviceSynchronize();                                                                  \
+    cudaError_t e = cudaMemcpyFromSymbol(h_out, g_timeline, sizeof(unsigned long long) * 24); \
+    if (reset) {                                                                              \
+      unsigned long long init[24];                                                            \
+      for (int i = 0; i < 24; ++i) init[i] = (i % 3 == 2) ? 0ull : ~0ull;                     \
+      cudaMemcpyToSymbol(g_timeline, init, sizeof(init));                                     \
+    }                                                                                         \
+    return (int)e;                                                                            \
+  }
+#else
+#define SBFE_TL(kernel, what)
+#endif
+
 // SBFE_PDL=0 in the environment turns the launch attribute off (plain stream order).
 inline bool pdl_enabled() {
   static const int on = [] {

@@ -279,7 +279,9 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
     const int r = tid / ((kPRows - kBins) * kTile), i = tid - r * (kPRows - kBins) * kTile;
     s_a[r * kRegionA + kBins * kTile + i] = 0.f;
   }
+  SBFE_TL(0, 0);
   pdl_wait();  // from here on the waveform is read and out / tile records are written
+  SBFE_TL(0, 1);
   // (utterance, first frame) of the tile in flight: one division per tile, carried over
   unsigned nb = tile / prm.tiles_per_utt;
   unsigned nj = tile - nb * prm.tiles_per_utt;               // tile index inside the utterance
@@ -698,6 +700,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
     // the barrier at the top of the next iteration orders these s_o reads before its stage 1
   }
   cp_async_wait<0>();
+  SBFE_TL(0, 2);
 }
 
 // grid = n_tiles CTAs of kClampThreads: one tile each (the refills spread over the SMs, one wave).
@@ -708,7 +711,9 @@ constexpr int kClampThreads = 128;
 
 template <int MC>
 __global__ void __launch_bounds__(kClampThreads) clamp_tiles_kernel(const __grid_constant__ Params prm) {
+  SBFE_TL(1, 0);
   pdl_wait();
+  SBFE_TL(1, 1);
   pdl_launch_dependents();
   const int M = MC > 0 ? MC : prm.n_mels;
   const int tid = threadIdx.x;
@@ -731,10 +736,11 @@ __global__ void __launch_bounds__(kClampThreads) clamp_tiles_kernel(const __grid
   key = __reduce_max_sync(0xffffffffu, key);
   if ((tid & 31) == 0 && key) atomicMax(&s_key, key);
   __syncthreads();
-  if (s_key == 0u) return;
+  if (s_key == 0u) { SBFE_TL(1, 2); return; }
   const float floor_b = max_key_decode(s_key) - prm.top_db;
-  if (__syncthreads_or(mn < floor_b) == 0) return;
+  if (__syncthreads_or(mn < floor_b) == 0) { SBFE_TL(1, 2); return; }
   clamp_tile<MC, kClampThreads>(prm, b, j, floor_b, (flags & 1u) != 0u, tid);
+  SBFE_TL(1, 2);
 }
 
 constexpr int kMaxSmem = 110 * 1024;  // two CTAs per SM
@@ -856,5 +862,9 @@ int launch_clamp_tiles(const sbfe_fbank_desc* d, int64_t B, int64_t T, float* ou
   prm.n_tiles = (unsigned)(tiles * B);
   return launch_pdl(pick_clamp(d->n_mels), dim3(prm.n_tiles), dim3(kClampThreads), 0, stream, prm);
 }
+
+#ifdef SBFE_EXP_TIMELINE
+SBFE_TL_DEFINE_SYNC(tl_sync_v3)
+#endif
 
 }  // namespace sbfe

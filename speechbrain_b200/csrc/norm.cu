@@ -294,9 +294,11 @@ __global__ void __launch_bounds__(kTileNormThreads, 2)
 norm_sentence_tiles_kernel(const float* x, const float* __restrict__ lengths, int T, int F,
                            int tile, int tiles, const float* tile_stats, float top_db,
                            int mean_norm, int std_norm, float eps, void* out, unsigned chunks) {
+  SBFE_TL(2, 0);
   if (!BESIDE_CLAMP) {
     pdl_wait();
     pdl_launch_dependents();
+    SBFE_TL(2, 1);
   }
   extern __shared__ __align__(16) float s_dyn[];   // mean[F] | std[F] | 3 * blockDim scratch
   __shared__ unsigned s_key;
@@ -343,6 +345,7 @@ norm_sentence_tiles_kernel(const float* x, const float* __restrict__ lengths, in
     if ((threadIdx.x & 31) == 0 && key) atomicMax(&s_key, key);
     __syncthreads();
     if (s_key) floor_b = max_key_decode(s_key) - top_db;
+    SBFE_TL(4, 0);   // keys + first records arrived, floor known
     Moments acc{0.f, 0.f, 0.f};
     if (live) {
       const int whole = (n >= T) ? tiles : n / tile;
@@ -393,6 +396,7 @@ norm_sentence_tiles_kernel(const float* x, const float* __restrict__ lengths, in
         merge(acc, (float)c, pivot + mloc, fmaxf(fmaf(-mloc, s1, s2), 0.f));
       }
     }
+    SBFE_TL(5, 0);   // per-thread merges (all records, cut rows) done
     s_red[threadIdx.x] = acc.n;
     s_red[kTileNormThreads + threadIdx.x] = acc.mean;
     s_red[2 * kTileNormThreads + threadIdx.x] = acc.m2;
@@ -425,9 +429,11 @@ norm_sentence_tiles_kernel(const float* x, const float* __restrict__ lengths, in
       else v1[k] = __ldcg(xb + i);
     }
   }
+  SBFE_TL(3, 0);          // statistics done, vectors requested
   if (BESIDE_CLAMP) {   // nothing has been written so far
     pdl_wait();
     pdl_launch_dependents();
+    SBFE_TL(2, 1);
   }
   int col = i0 % FV;
   const int dcol = kTileNormThreads % FV;
@@ -451,6 +457,7 @@ norm_sentence_tiles_kernel(const float* x, const float* __restrict__ lengths, in
     col += dcol;
     while (col >= FV) col -= FV;
   }
+  SBFE_TL(2, 2);
 }
 
 // grid = ceil(F / 32) CTAs of 32 columns x 8 utterance groups
@@ -746,5 +753,9 @@ int launch_norm_speaker_update(const float* mean, const float* stdv, int64_t B, 
   return launch_pdl(norm_speaker_update_kernel, dim3((F + 127) / 128), dim3(128), 0, stream, mean,
                     stdv, (int)B, F, row, mode, weight, tab_mean, tab_std, out_mean, out_std);
 }
+
+#ifdef SBFE_EXP_TIMELINE
+SBFE_TL_DEFINE_SYNC(tl_sync_norm)
+#endif
 
 }  // namespace sbfe
