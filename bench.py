@@ -375,23 +375,31 @@ def time_cfg5(dev, world, rank, steps, barrier, max_over_ranks):
                world, "NCCL all-reduce (sum) of 2F+1 = 161 floats per step" if world > 1
                else "single rank: nothing to reduce")}
     ms_by = {}
-    for sync in ([False, True] if world > 1 else [False]):
-        fb = sb.Fbank(n_mels=N_MELS)
-        norm = sb.InputNormalization(norm_type="global", sync_stats=sync).train()
-        for i in range(3):
-            norm(fb(pool[i & 1][0]), pool[i & 1][1], epoch=0)
-        barrier()
-        e0.record()
-        for i in range(steps):
-            y = norm(fb(pool[i & 1][0]), pool[i & 1][1], epoch=0)
-        e1.record()
-        torch.cuda.synchronize()
-        barrier()
-        ms = max_over_ranks(e0.elapsed_time(e1))
-        ms_by[sync] = ms / steps
-        key = "with_sync" if sync else "no_sync"
-        out[key] = {"value": world * B5 * S5 * steps / (ms / 1e3), "ms_per_step": ms / steps,
-                    "count": norm.count, "checksum": float(y[0, 0, :4].sum())}
+    mods = {}
+    # the two variants alternate (no sync, sync, no sync, sync) and each keeps its faster pass: a
+    # single pass per variant makes the later one look faster (allocator, clocks, L2 warm)
+    for rep in range(2):
+        for sync in ([False, True] if world > 1 else [False]):
+            if sync not in mods:
+                mods[sync] = (sb.Fbank(n_mels=N_MELS),
+                              sb.InputNormalization(norm_type="global", sync_stats=sync).train())
+            fb, norm = mods[sync]
+            for i in range(3 if rep == 0 else 1):
+                norm(fb(pool[i & 1][0]), pool[i & 1][1], epoch=0)
+            barrier()
+            e0.record()
+            for i in range(steps):
+                y = norm(fb(pool[i & 1][0]), pool[i & 1][1], epoch=0)
+            e1.record()
+            torch.cuda.synchronize()
+            barrier()
+            ms = max_over_ranks(e0.elapsed_time(e1))
+            if sync in ms_by and ms / steps >= ms_by[sync]:
+                continue
+            ms_by[sync] = ms / steps
+            key = "with_sync" if sync else "no_sync"
+            out[key] = {"value": world * B5 * S5 * steps / (ms / 1e3), "ms_per_step": ms / steps,
+                        "count": norm.count, "checksum": float(y[0, 0, :4].sum())}
     if True in ms_by:
         out["exposed_allreduce_us_per_step"] = (ms_by[True] - ms_by[False]) * 1e3
         out["value"] = out["with_sync"]["value"]
