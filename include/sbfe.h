@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define SBFE_ABI_VERSION 10
+#define SBFE_ABI_VERSION 11
 
 #if defined(__GNUC__)
 #define SBFE_API __attribute__((visibility("default")))
@@ -109,7 +109,8 @@ SBFE_API int64_t sbfe_fbank_workspace_bytes(const sbfe_fbank_desc* desc, int64_t
  *        [M, 2M)   M2    } the clamp (M2 = sum of squared deviations),
  *        [2M, 3M)  the column minima of tile j before the clamp: a column whose minimum is not
  *                  below the utterance's floor was not changed by the clamp, its moments hold,
- *        [3M]      max key of tile j, [3M+1] flags (bit 0: the tile's input was all zero).
+ *        [3M]      max key of tile j, [3M+1] flags (bit 0: the tile's input was all zero),
+ *        [3M+2], [3M+3] zero (small counters of the consumers; never above any key).
  *      sbfe_norm_stats_tiles / sbfe_norm_sentence_tiles turn these into InputNormalization
  *      statistics for any valid length: 2 M floats per R frames instead of a pass over out.
  *      The clamp is a second, small kernel launched by this call (it reads the records only
@@ -170,12 +171,18 @@ SBFE_API int sbfe_norm_stats_tiles(const float* d_x, const float* d_lengths, int
  *   first, like every other kernel of the library.  Results are identical either way.
  *   SBFE_OUT_BF16 - d_out is a bfloat16 [B, T, F] tensor (must not be d_x): the opt-in
  *   reduced-precision output, rounded to nearest even from the float32 result, i.e. relative
- *   error <= 2^-8 of each normalised value (stated bound; the statistics stay float32). */
+ *   error <= 2^-8 of each normalised value (stated bound; the statistics stay float32).
+ * In place, the rows the statistics are read from (the tile the length cuts, tiles with values
+ * below the floor) are written by the CTA of the utterance that finishes its statistics last: the
+ * CTAs count themselves in word 3F + 3 of the utterance's first record (zero from the producer,
+ * zero again when the call completes) - the one reason d_tile_stats is not const; two in-place
+ * calls must not share records concurrently.  Out of place needs none of this and is the faster
+ * call (about 6 us per 32 x 16 s batch). */
 #define SBFE_BESIDE_CLAMP 1
 #define SBFE_OUT_BF16 2
 SBFE_API int sbfe_norm_sentence_tiles(const float* d_x, const float* d_lengths, int64_t B, int64_t T,
                              int32_t F, int32_t mean_norm, int32_t std_norm, float eps,
-                             const float* d_tile_stats, int32_t tile_frames, float top_db,
+                             float* d_tile_stats, int32_t tile_frames, float top_db,
                              int32_t flags, void* d_out, void* stream);
 
 /* STFT.forward for [B, L] input (processing/features.py:133-188):

@@ -40,8 +40,8 @@ for beside in (True, False):
         h.sbfe_exp_timeline(buf, 0)
         v = list(buf)
         t0 = v[1]                            # producer's wait-return = start of the step's work
-        rows.append([(v[3 * k + i] - t0) / 1e3 for k in range(6) for i in range(3)])
-    med = [sorted(r[i] for r in rows)[len(rows) // 2] for i in range(18)]
+        rows.append([(v[3 * k + i] - t0) / 1e3 for k in range(8) for i in range(3)])
+    med = [sorted(r[i] for r in rows)[len(rows) // 2] for i in range(24)]
     print("beside_clamp=%s   (us after the producer's wait returned; median of 20 single-step graphs)" % beside)
     for k in range(3):
         print("  %-10s first CTA in %7.2f   first wait-return %7.2f   last CTA out %7.2f"

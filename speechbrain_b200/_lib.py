@@ -86,7 +86,7 @@ SIGNATURES = {
     "sbfe_mean": (C.c_int, [_P, _I64, _P, _P, _I64, _P]),
 }
 
-ABI_VERSION = 10
+ABI_VERSION = 11
 _lock = threading.Lock()
 _lib = None
 

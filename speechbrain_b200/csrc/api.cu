@@ -12,7 +12,7 @@ int launch_fbank400_v3(const sbfe_fbank_desc*, const void*, int, float, const in
 int launch_norm_stats_tiles(const float*, const float*, int64_t, int64_t, int, int, int, float,
                             const float*, int, float, float*, float*, cudaStream_t);
 int launch_norm_sentence_tiles(const float*, const float*, int64_t, int64_t, int, int, int, float,
-                               const float*, int, float, int, int, void*, cudaStream_t);
+                               float*, int, float, int, int, void*, cudaStream_t);
 int64_t istft_workspace_bytes(int64_t, int64_t, int);
 int launch_istft(const float*, int64_t, int64_t, int, int, const float*, int, int64_t, float*, void*,
                  int64_t, cudaStream_t);
@@ -256,7 +256,7 @@ int sbfe_norm_stats_tiles(const float* d_x, const float* d_lengths, int64_t B, i
 
 int sbfe_norm_sentence_tiles(const float* d_x, const float* d_lengths, int64_t B, int64_t T,
                              int32_t F, int32_t mean_norm, int32_t std_norm, float eps,
-                             const float* d_tile_stats, int32_t tile_frames, float top_db,
+                             float* d_tile_stats, int32_t tile_frames, float top_db,
                              int32_t flags, void* d_out, void* stream) {
   if (B < 0 || T < 0 || F < 0 || tile_frames < 1) return SBFE_E_INVAL;
   if (B == 0 || F == 0) return 0;

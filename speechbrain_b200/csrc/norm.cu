@@ -292,19 +292,34 @@ constexpr int kSentSpec = 4;     // records per thread and batch
 template <int VEC, bool BESIDE_CLAMP, bool BF16OUT>
 __global__ void __launch_bounds__(kTileNormThreads, 2)
 norm_sentence_tiles_kernel(const float* x, const float* __restrict__ lengths, int T, int F,
-                           int tile, int tiles, const float* tile_stats, float top_db,
-                           int mean_norm, int std_norm, float eps, void* out, unsigned chunks) {
+                           int tile, int tiles, float* tile_stats, float top_db,
+                           int mean_norm, int std_norm, float eps, void* out, unsigned chunks,
+                           int inplace) {
   SBFE_TL(2, 0);
   if (!BESIDE_CLAMP) {
     pdl_wait();
     pdl_launch_dependents();
     SBFE_TL(2, 1);
   }
-  extern __shared__ __align__(16) float s_dyn[];   // mean[F] | std[F] | 3 * blockDim scratch
-  __shared__ unsigned s_key;
+  extern __shared__ __align__(16) float s_dyn[];   // mean[F] | std[F] | 3 * blockDim scratch | bitmask
+  __shared__ unsigned s_key, s_ticket;
   float* s_mean = s_dyn;
   float* s_std = s_dyn + F;
   float* s_red = s_dyn + 2 * F;
+  // IN PLACE with more than one CTA per utterance: tiles whose rows are READ for the statistics
+  // (the tile the length cuts, tiles with a column below the floor) - see the end of the kernel
+  unsigned* s_held = reinterpret_cast<unsigned*>(s_red + 3 * kTileNormThreads);
+#ifdef SBFE_EXP_NOGUARD   // experiment build: shows that tests/test_gpu_r2.py catches the race
+  const bool guard = false;
+#else
+  const bool guard = inplace != 0 && chunks > 1;
+#endif
+  unsigned* const arrivals =
+      reinterpret_cast<unsigned*>(tile_stats + (size_t)(blockIdx.x / chunks) * tiles * tile_rec_words(F)) +
+      3 * F + 3;
+  bool held_any = false;
+  if (guard)
+    for (int i = threadIdx.x; i < (tiles + 31) / 32; i += kTileNormThreads) s_held[i] = 0u;
   const unsigned b = blockIdx.x / chunks;
   const int c0 = blockIdx.x - b * chunks;
   const float* xb = x + (size_t)b * T * F;
@@ -366,8 +381,13 @@ norm_sentence_tiles_kernel(const float* x, const float* __restrict__ lengths, in
             // a record below the floor (values the clamp changes, inside the valid part: rare)
             // is not used - its moments may be the clamp kernel's or the producer's
             float2 mq = make_float2(pm[k], pq[k]);
-            if (pn[k] < floor_b)
+            if (pn[k] < floor_b) {
               mq = column_moments_clamped(xb + (size_t)j * tile * F + col, F, cnt, floor_b);
+              if (guard) {
+                atomicOr(&s_held[j >> 5], 1u << (j & 31));
+                held_any = true;
+              }
+            }
             merge(acc, (float)cnt, mq.x, mq.y);
           }
         }
@@ -382,6 +402,10 @@ norm_sentence_tiles_kernel(const float* x, const float* __restrict__ lengths, in
             pn[k] = __ldcg(tsb + j * rec + 2 * F);
           }
         }
+      }
+      if (guard && ncut > 0 && threadIdx.x == 0) {
+        atomicOr(&s_held[whole >> 5], 1u << (whole & 31));
+        held_any = true;
       }
       if (grp < ncut) {
         pivot = fmaxf(pivot, floor_b);
@@ -400,7 +424,9 @@ norm_sentence_tiles_kernel(const float* x, const float* __restrict__ lengths, in
     s_red[threadIdx.x] = acc.n;
     s_red[kTileNormThreads + threadIdx.x] = acc.mean;
     s_red[2 * kTileNormThreads + threadIdx.x] = acc.m2;
-    __syncthreads();
+    __syncthreads();   // every thread's reads of x for the statistics are complete
+    unsigned ticket = 0u;
+    if (guard && threadIdx.x == 0) ticket = atomicAdd(arrivals, 1u);   // in flight during the merge below
     if (threadIdx.x < F) {
       for (int g = 1; g < G; ++g)
         merge(acc, s_red[g * F + col], s_red[kTileNormThreads + g * F + col],
@@ -412,8 +438,23 @@ norm_sentence_tiles_kernel(const float* x, const float* __restrict__ lengths, in
       s_mean[col] = mean_norm ? m : 0.f;
       s_std[col] = std_norm ? sd : 1.f;
     }
-    __syncthreads();
+    if (guard && threadIdx.x == 0) {
+      if (ticket == chunks - 1) *arrivals = 0u;
+      s_ticket = ticket;
+    }
+    held_any = __syncthreads_or(held_any) != 0;   // block-uniform from here on (false without guard)
   }
+  const bool last = held_any && s_ticket == chunks - 1;
+
+  // ---- in place, rows that the statistics READ: the CTAs of an utterance all read them, and
+  // one of them owns them in the pass below - it must not overwrite them while a sibling (a later
+  // wave of the grid, a slower SM) still computes its statistics.  Every CTA draws a ticket AFTER
+  // its own statistics (word 3F + 3 of the utterance's first record: zero from the producer,
+  // zero again afterwards); nobody stores the held tiles in the pass below; the CTA that drew the
+  // last ticket - every sibling has finished reading - normalises them itself.  (A sibling's
+  // reads are complete when it draws: their values went into its statistics; the last CTA's
+  // stores depend on the ticket it drew: no fences.)  The ticket is drawn between the two
+  // barriers of the column merge: its round trip costs no barrier of its own.
   // ---- (max(x, floor) - mean) / std over the CTA's share of the utterance: all loads first
   const int FV = F / VEC;
   const int nvec = T * FV;                         // < 2^30 (launcher)
@@ -430,17 +471,80 @@ norm_sentence_tiles_kernel(const float* x, const float* __restrict__ lengths, in
     }
   }
   SBFE_TL(3, 0);          // statistics done, vectors requested
+  // which of them this thread stores (bit k): inside the utterance and, in place, not in a held
+  // tile - worked out while the loads are in flight
+  const int row0 = i0 / FV, col0 = i0 - row0 * FV;
+  const int drow = kTileNormThreads / FV, dcol = kTileNormThreads - drow * FV;
+  unsigned live8 = 0u;
+  {
+    const int tshift = (tile & (tile - 1)) == 0 ? __ffs(tile) - 1 : -1;
+    int r = row0, c = col0;
+#pragma unroll
+    for (int k = 0; k < kSentIters; ++k) {
+      bool mine = i0 + k * kTileNormThreads < nvec;
+      if (held_any && mine) {
+        const int j = tshift >= 0 ? r >> tshift : r / tile;
+        mine = ((s_held[j >> 5] >> (j & 31)) & 1u) == 0u;
+      }
+      live8 |= (mine ? 1u : 0u) << k;
+      r += drow;
+      c += dcol;
+      if (c >= FV) {
+        c -= FV;
+        ++r;
+      }
+    }
+  }
   if (BESIDE_CLAMP) {   // nothing has been written so far
     pdl_wait();
     pdl_launch_dependents();
     SBFE_TL(2, 1);
   }
-  int col = i0 % FV;
-  const int dcol = kTileNormThreads % FV;
+  if (last) {   // the held tiles (a few of the utterance): their loads join the ones in flight
+    for (int j = 0; j < tiles; ++j) {
+      if (((s_held[j >> 5] >> (j & 31)) & 1u) == 0u) continue;
+      const int r_lo = j * tile;
+      const int cnt = (T - r_lo < tile ? T - r_lo : tile) * FV;   // vectors of the tile
+      const int v0 = r_lo * FV;
+      constexpr int kBatch = 2;                                    // loads first, then the stores
+      for (int e0 = threadIdx.x; e0 < cnt; e0 += kBatch * kTileNormThreads) {
+        float4 h4[VEC == 4 ? kBatch : 1];
+        float h1[VEC == 4 ? 1 : kBatch];
+#pragma unroll
+        for (int k = 0; k < kBatch; ++k) {
+          const int e = e0 + k * kTileNormThreads;
+          if (e < cnt) {
+            if (VEC == 4) h4[k] = __ldcg(reinterpret_cast<const float4*>(xb) + v0 + e);
+            else h1[k] = __ldcg(xb + v0 + e);
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < kBatch; ++k) {
+          const int e = e0 + k * kTileNormThreads;
+          if (e < cnt) {
+            const int c = e % FV;
+            if (VEC == 4) {
+              const float4 mm = *reinterpret_cast<const float4*>(s_mean + 4 * c);
+              const float4 ss = *reinterpret_cast<const float4*>(s_std + 4 * c);
+              float4 r;
+              r.x = (fmaxf(h4[k].x, floor_b) - mm.x) / ss.x;
+              r.y = (fmaxf(h4[k].y, floor_b) - mm.y) / ss.y;
+              r.z = (fmaxf(h4[k].z, floor_b) - mm.z) / ss.z;
+              r.w = (fmaxf(h4[k].w, floor_b) - mm.w) / ss.w;
+              store4<BF16OUT>(out, ob / 4 + (size_t)(v0 + e), r);
+            } else {
+              store1<BF16OUT>(out, ob + (size_t)(v0 + e), (fmaxf(h1[k], floor_b) - s_mean[c]) / s_std[c]);
+            }
+          }
+        }
+      }
+    }
+  }
+  int col = col0;
 #pragma unroll
   for (int k = 0; k < kSentIters; ++k) {
     const int i = i0 + k * kTileNormThreads;
-    if (i < nvec) {
+    if ((live8 >> k) & 1u) {
       if (VEC == 4) {
         const float4 mm = *reinterpret_cast<const float4*>(s_mean + 4 * col);
         const float4 ss = *reinterpret_cast<const float4*>(s_std + 4 * col);
@@ -455,7 +559,7 @@ norm_sentence_tiles_kernel(const float* x, const float* __restrict__ lengths, in
       }
     }
     col += dcol;
-    while (col >= FV) col -= FV;
+    if (col >= FV) col -= FV;
   }
   SBFE_TL(2, 2);
 }
@@ -673,7 +777,7 @@ int launch_norm_apply(const float* x, int64_t B, int64_t T, int F, const float* 
 
 // sentence normalisation from the tile records, one launch
 int launch_norm_sentence_tiles(const float* x, const float* lengths, int64_t B, int64_t T, int F,
-                               int mean_norm, int std_norm, float eps, const float* tile_stats,
+                               int mean_norm, int std_norm, float eps, float* tile_stats,
                                int tile, float top_db, int beside_clamp, int out_bf16, void* out,
                                cudaStream_t stream) {
   if (B == 0 || T == 0 || F == 0) return 0;
@@ -686,7 +790,9 @@ int launch_norm_sentence_tiles(const float* x, const float* lengths, int64_t B, 
   const int64_t chunks = (nvec + per_cta - 1) / per_cta;
   if (chunks * B > 0x7fffffff) return SBFE_E_TOOBIG;
   if (F > kTileNormThreads || nvec > 0x3fffffff) return SBFE_E_TOOBIG;
-  const size_t smem = ((size_t)2 * F + 3 * kTileNormThreads) * sizeof(float);
+  const bool inplace = out == static_cast<const void*>(x) && !out_bf16;
+  const size_t smem = ((size_t)2 * F + 3 * kTileNormThreads + (inplace ? (tiles + 31) / 32 : 0)) * sizeof(float);
+  if (smem > 48 * 1024) return SBFE_E_TOOBIG;
   // the flag presumes that call's last launch was its clamp kernel: there is none without a top_db
   const bool beside = beside_clamp != 0 && top_db >= 0.f && pdl_enabled();
   using Kern = decltype(&norm_sentence_tiles_kernel<4, true, false>);
@@ -698,7 +804,7 @@ int launch_norm_sentence_tiles(const float* x, const float* lengths, int64_t B, 
   Kern k = table[(out_bf16 ? 4 : 0) + (beside ? 2 : 0) + (vec ? 1 : 0)];
   return launch_pdl(k, dim3((unsigned)(chunks * B)), dim3(kTileNormThreads), smem, stream, x, lengths,
                     (int)T, F, tile, tiles, tile_stats, top_db >= 0.f ? top_db : INFINITY, mean_norm,
-                    std_norm, eps, out, (unsigned)chunks);
+                    std_norm, eps, out, (unsigned)chunks, inplace ? 1 : 0);
 }
 
 // ---- speaker mode (processing/features.py:1037-1081): running per-speaker statistics ---------

@@ -30,6 +30,14 @@ def sync_payload(cur, group=None):
     return cur
 
 
+def _swappable(x):
+    """x owns its whole storage and nothing tracks it: x.set_(y) is then indistinguishable from
+    an in-place write for whoever holds x (views of x made earlier keep the old values)."""
+    return (x._base is None and not x.requires_grad and x.storage_offset() == 0
+            and x.untyped_storage().nbytes() == x.numel() * x.element_size()
+            and (not x.is_inference() or torch.is_inference_mode_enabled()))
+
+
 class InputNormalization(torch.nn.Module):
     """Mean / variance normalisation: ``sentence``, ``speaker``, ``batch`` or
     ``global`` statistics, same arguments and state as the reference.
@@ -104,6 +112,16 @@ class InputNormalization(torch.nn.Module):
             # the version check above is the statement SBFE_BESIDE_CLAMP asks for: nothing this
             # package or torch launched has written x since Fbank returned it (same stream)
             beside = ts.stream == torch.cuda.current_stream(x.device).cuda_stream
+            if self.output_dtype in (None, torch.float32) and _swappable(x):
+                # The kernel writes a fresh tensor and x takes over its storage: for the caller x
+                # IS normalised when the call returns, like the reference's x[snt_id] = ... - but
+                # no CTA overwrites rows that another CTA of the utterance still reads for its
+                # statistics (the tile the length cuts, clamped tiles), which the truly in-place
+                # launch below has to order with tickets (csrc/norm.cu) at ~6 us per cfg2 step
+                y = ops.norm_sentence_tiles(x, lengths, ts, self.mean_norm, self.std_norm, self.eps,
+                                            beside_clamp=beside)
+                x.set_(y)
+                return x
             return ops.norm_sentence_tiles(x, lengths, ts, self.mean_norm, self.std_norm, self.eps,
                                            out=x, beside_clamp=beside, out_dtype=self.output_dtype)
         if ts is not None:

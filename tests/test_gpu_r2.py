@@ -253,3 +253,40 @@ def test_cfg5_shard_vs_oracle(sb):
         np.testing.assert_allclose(gn.glob_mean.cpu().numpy(), ref.glob_mean, rtol=1e-5, atol=2e-5)
         np.testing.assert_allclose(gn.glob_std.cpu().numpy(), ref.glob_std, rtol=2e-5, atol=2e-5)
     assert gn.count == ref.count == 2
+
+
+@pytest.mark.parametrize("n_fft", [400, 512])
+def test_sentence_norm_in_place_reads_before_it_writes(sb, n_fft):
+    """In place, the CTAs of an utterance all READ the rows the statistics need (the tile the
+    length cuts, tiles with values below the top_db floor) and one of them owns those rows in
+    the normalisation pass: with more CTAs than the GPU holds at once (400 here) a CTA of a later
+    wave must still see them un-normalised.  Ragged lengths, silence and near-silence make both
+    kinds of rows; in place (after the call and beside its clamp launch) == out of place, bitwise,
+    and == the reference's formula (processing/features.py:1020-1035) on the clamped features."""
+    from speechbrain_b200 import ops
+
+    torch.manual_seed(5)
+    B, L = 200, 64000
+    wav = torch.randn(B, L, device="cuda") * 0.1
+    wav[::3, 20000:30000] = 0.0                       # digital silence: constant tiles
+    wav[1::3, 40000:52000] *= 1e-6                    # below the floor: clamped columns
+    lens = (0.3 + 0.7 * torch.rand(B, device="cuda")).clamp(max=1.0)
+    lens[:4] = 1.0
+    fb = sb.Fbank(n_mels=80, n_fft=n_fft)
+    tab = fb._frontend_tables()
+    for round_ in range(3):
+        feats, _, ts = ops.fbank_forward(tab, wav, tile_stats=True, top_db=80.0)
+        want = ops.norm_sentence_tiles(feats, lens, ts)
+        keep = feats.clone()
+        got = ops.norm_sentence_tiles(feats, lens, ts, out=feats)
+        assert got.data_ptr() == feats.data_ptr()
+        assert torch.equal(got, want), round_
+        feats2, _, ts2 = ops.fbank_forward(tab, wav, tile_stats=True, top_db=80.0)
+        got2 = ops.norm_sentence_tiles(feats2, lens, ts2, out=feats2, beside_clamp=True)
+        assert torch.equal(got2, want), round_
+    T = keep.shape[1]
+    n = torch.round(lens * T).long().clamp(max=T)
+    for b in (0, 1, 2, 3, 17, 101, 199):
+        v = keep[b, : int(n[b])]
+        ref = (keep[b] - v.mean(0)) / v.std(0).clamp(min=1e-10)
+        assert torch.allclose(want[b], ref, rtol=1e-4, atol=2e-4), b
