@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "libsbfe.so")
-SOURCES = ["api.cu", "fbank400.cu", "fbank400_v3.cu", "fbank512.cu", "generic.cu", "post.cu", "norm.cu", "augment.cu", "istft.cu", "timedomain.cu"]
+SOURCES = ["api.cu", "fbank400.cu", "fbank400_v3.cu", "fbank512.cu", "generic.cu", "post.cu", "norm.cu", "augment.cu", "istft.cu", "timedomain.cu", "mel_umma.cu"]
 HEADERS = ["common.cuh", "fft_codelets.cuh", "fft_packed.cuh", os.path.join("..", "..", "include", "sbfe.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -656,6 +656,23 @@ mel_mma_kernel(const float* __restrict__ spec, int64_t rows_total, int64_t T, in
 }
 
 // dense enough for the tensor-core kernel, and its weights + two frame tiles fit in shared memory
+bool mel_umma_ok(const sbfe_fbank_desc* d);          // mel_umma.cu
+int launch_mel_umma(const sbfe_fbank_desc*, const float*, int64_t, int64_t, float*, sbfe_maxkey_t*,
+                    cudaStream_t);
+
+// does this filterbank count as dense?  SBFE_MEL_MMA = 0: never, 2: always (experiments, tests)
+static bool mel_dense_rule(const sbfe_fbank_desc* d) {
+  const int bins = d->n_fft / 2 + 1;
+  const char* sw = getenv("SBFE_MEL_MMA");
+  if (sw != nullptr && sw[0] == '0') return false;
+  if (sw != nullptr && sw[0] == '2') return true;
+  // where a fused n_fft = 400 kernel takes the configuration its sparse loops win unless the
+  // matrix is really dense (gaussian-80 at 18 % stored weights: 96 us fused against STFT +
+  // projection on the cfg2 batch); elsewhere (n_fft 512 ...) 10 % is enough
+  const int density = fbank400_supported(d) ? kMmaDensity : kMmaDensitySlowPath;
+  return (int64_t)density * d->mel_nnz >= (int64_t)bins * d->n_mels;
+}
+
 static bool mel_mma_ok(const sbfe_fbank_desc* d, size_t* smem_out, int* nbuf_out = nullptr) {
   const int bins = d->n_fft / 2 + 1;
   const int kpad = (bins + 7) & ~7, npad = (d->n_mels + 31) & ~31;   // 4 column groups x NT x 8
@@ -667,25 +684,22 @@ static bool mel_mma_ok(const sbfe_fbank_desc* d, size_t* smem_out, int* nbuf_out
   }
   if (nbuf_out) *nbuf_out = nbuf;
   if (smem_out) *smem_out = smem;
-  const char* sw = getenv("SBFE_MEL_MMA");          // 0: never, 2: whenever it fits (experiments)
-  if (sw != nullptr && sw[0] == '0') return false;
   if (npad > 8 * kMmaColGroups * kMmaMaxNT || smem > 220 * 1024) return false;
-  if (sw != nullptr && sw[0] == '2') return true;
-  // where a fused n_fft = 400 kernel takes the configuration its sparse loops win unless the
-  // matrix is really dense (gaussian-80 at 18 % stored weights: 96 us fused against STFT +
-  // projection = 91 + 40 us on the cfg2 batch); elsewhere (n_fft 512 ...) 10 % is enough
-  const int density = fbank400_supported(d) ? kMmaDensity : kMmaDensitySlowPath;
-  return (int64_t)density * d->mel_nnz >= (int64_t)bins * d->n_mels;
+  return mel_dense_rule(d);
 }
 
 // Fbank with a dense filterbank = STFT power spectrum (workspace) + the tensor-core projection
-bool mel_dense_mma(const sbfe_fbank_desc* d) { return mel_mma_ok(d, nullptr); }
+bool mel_dense_mma(const sbfe_fbank_desc* d) {
+  return (mel_dense_rule(d) && mel_umma_ok(d)) || mel_mma_ok(d, nullptr);
+}
 
 int launch_mel_db(const sbfe_fbank_desc* d, const float* spec, int64_t B, int64_t T, float* out,
                   sbfe_maxkey_t* utt_max, cudaStream_t stream) {
   if (B == 0 || T == 0) return 0;
   size_t smem_mma = 0;
   int nbuf = 2;
+  // dense: tcgen05 + TMEM (mel_umma.cu) where its stages fit, else the warp-level mma.sync kernel
+  if (mel_dense_rule(d) && mel_umma_ok(d)) return launch_mel_umma(d, spec, B, T, out, utt_max, stream);
   if (mel_mma_ok(d, &smem_mma, &nbuf)) {
     const int bins = d->n_fft / 2 + 1;
     const int kpad = (bins + 7) & ~7, npad = (d->n_mels + 31) & ~31;
