@@ -220,7 +220,10 @@ __device__ __forceinline__ void clamp_tile(const Params& prm, unsigned b, unsign
 #endif
 // MC > 0: n_mels is the compile-time constant MC (every M-dependent index, walk and trip count
 // folds away: the recipes' 80 / 40 / 23 filters); MC == 0: any n_mels at run time
-template <bool PCM16, int MC>
+// POWER: the kernel is the STFT + spectral_magnitude(power=1) of the default mode (features.py:
+// 133-188, 327-356): the tile [32 frames][201 bins] of the power spectrum leaves through the same
+// output path, no filterbank (M = 201, no tables, no records)
+template <bool PCM16, int MC, bool POWER = false>
 __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(const __grid_constant__ Params prm) {
   extern __shared__ __align__(16) float smem[];
   float* s_a = smem;                       // 2 x [staged waveform | P[bin][32]]
@@ -229,7 +232,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
   float* s_tt = s_tw + kTabW;              // [n2][20]: (re, im) of W400^(k1*n2), k1 = 1..9, 2 pad
   float* s_t2 = s_tt + kTabTw;             // [h][20]
   int2* s_meta = reinterpret_cast<int2*>(s_t2 + kTabT2);
-  const int M = MC > 0 ? MC : prm.n_mels;
+  const int M = POWER ? kBins : (MC > 0 ? MC : prm.n_mels);
   float* s_w = reinterpret_cast<float*>(s_meta) + ((2 * M + 3) & ~3);  // 16-byte aligned
 
   __shared__ unsigned s_tile_key;  // max key of the current tile (tile records)
@@ -252,7 +255,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
     const float c0 = kTw400[tid], c1 = second ? kTw400[tid + kThreads] : 0.f;
     const float t2 = tid < kTabT2 ? kT2[tid] : 0.f;
     int ms = 0, mc = 0, mo = 0;
-    if (tid < M) {
+    if (!POWER && tid < M) {
       ms = __ldg(prm.mel_start + tid);
       mc = __ldg(prm.mel_count + tid);
       mo = __ldg(prm.mel_offset + tid);
@@ -267,11 +270,11 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
     put_w(tid, w0, c0);
     if (second) put_w(tid + kThreads, w1, c1);
     if (tid < kTabT2) s_t2[tid] = t2;
-    if (tid < M) s_meta[tid] = make_int2(ms | (mc << 16), mo);
+    if (!POWER && tid < M) s_meta[tid] = make_int2(ms | (mc << 16), mo);
     if (tid < prm.mel_nnz) s_w[tid] = g0;
     if (tid + kThreads < prm.mel_nnz) s_w[tid + kThreads] = g1;
   }
-  for (int m = tid + kThreads; m < M; m += kThreads)       // more than 320 filters
+  for (int m = tid + kThreads; !POWER && m < M; m += kThreads)       // more than 320 filters
     s_meta[m] = make_int2(__ldg(prm.mel_start + m) | (__ldg(prm.mel_count + m) << 16),
                           __ldg(prm.mel_offset + m));
   for (int i = tid + 2 * kThreads; i < prm.mel_nnz; i += kThreads) s_w[i] = __ldg(prm.mel_weight + i);
@@ -323,7 +326,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
   };
   int planG[4], planW[4], planP[4];
   __syncthreads();   // s_meta is complete
-  mel_plan(0, planG, planW, planP);
+  if (!POWER) mel_plan(0, planG, planW, planP);
 
 #pragma unroll 1
   for (int it = 0; tile < prm.n_tiles; ++it, tile += gridDim.x) {
@@ -524,7 +527,11 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
     continue;
 #endif
     // ---- stage 3: sparse mel projection + dB -> output tile [32][M] in smem -----------------
-    {
+    if constexpr (POWER) {
+      // P[bin][32] -> tile [frame][bin], pitch 201: a warp reads 32 consecutive words of one bin
+      // and writes 32 distinct banks (201 = 9 mod 32)
+      for (int i = tid; i < kBins * kTile; i += kThreads) s_o[(i & (kTile - 1)) * opitch + (i >> 5)] = s_p[i];
+    } else {
       float vmax0 = -INFINITY, vmax1 = -INFINITY;
       const float2* pp0 = reinterpret_cast<const float2*>(s_p) + p;
       // four filters (m, m+20, m+40, m+60) in flight per thread: their loads and FMA chains
@@ -775,16 +782,16 @@ bool fbank400_v3_supported(const sbfe_fbank_desc* d) {
          v3::smem_floats(d->n_mels, d->mel_nnz) * sizeof(float) <= (size_t)v3::kMaxSmem;
 }
 
-int launch_fbank400_v3(const sbfe_fbank_desc* d, const void* wav, int pcm16, float scale,
-                       const int64_t* offsets, const int32_t* nsamples, int64_t B, int64_t L,
-                       int64_t wav_stride, float* out, sbfe_maxkey_t* utt_max, float* tile_stats,
-                       float top_db, cudaStream_t stream) {
+static int launch_v3(const sbfe_fbank_desc* d, const void* wav, int pcm16, float scale,
+                     const int64_t* offsets, const int32_t* nsamples, int64_t B, int64_t L,
+                     int64_t wav_stride, float* out, sbfe_maxkey_t* utt_max, float* tile_stats,
+                     float top_db, bool power, cudaStream_t stream) {
   using namespace v3;
   Params prm;
   prm.db = DbParams{d->multiplier * 0.30102999566398120f, d->amin, d->db_offset, d->floor_db,
-                    d->log_mel};
-  prm.n_mels = d->n_mels;
-  prm.mel_nnz = d->mel_nnz;
+                    power ? 0 : d->log_mel};
+  prm.n_mels = power ? kBins : d->n_mels;
+  prm.mel_nnz = power ? 0 : d->mel_nnz;
   prm.L = L;
   prm.wav_stride = wav_stride;
   prm.T = 1 + L / kHop;
@@ -805,7 +812,7 @@ int launch_fbank400_v3(const sbfe_fbank_desc* d, const void* wav, int pcm16, flo
   if (tiles * B > 0x7fffffff || prm.T > 0x7fffffff) return SBFE_E_TOOBIG;
   prm.tiles_per_utt = (unsigned)tiles;
   prm.n_tiles = (unsigned)(tiles * B);
-  const size_t smem = smem_floats(d->n_mels, d->mel_nnz) * sizeof(float);
+  const size_t smem = smem_floats(prm.n_mels, prm.mel_nnz) * sizeof(float);
   // once per device and process: the opt-in to > 48 KB of dynamic shared memory and the number
   // of these CTAs an SM holds.  The cache is a lock-free per-device word whose only transition is
   // 0 -> the value after idempotent calls: no call depends on another call's state (sbfe.h).
@@ -829,6 +836,16 @@ int launch_fbank400_v3(const sbfe_fbank_desc* d, const void* wav, int pcm16, flo
                                                             (size_t)kMaxSmem);
         if (e == cudaSuccess && n < per_sm) per_sm = n;
       }
+    {
+      int n = 0;
+      if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(fbank400_v3_kernel<false, 0, true>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem);
+      if (e == cudaSuccess)
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fbank400_v3_kernel<false, 0, true>, kThreads,
+                                                          (size_t)kMaxSmem);
+      if (e == cudaSuccess && n < per_sm) per_sm = n;
+    }
     if (e != cudaSuccess) return (int)e;
     if (per_sm < 1) return (int)cudaErrorLaunchOutOfResources;
     if (cached) per_sm_cache[dev].store(per_sm, std::memory_order_release);
@@ -836,12 +853,32 @@ int launch_fbank400_v3(const sbfe_fbank_desc* d, const void* wav, int pcm16, flo
   // persistent: every CTA strides over the tiles
   const unsigned cap = (unsigned)(per_sm * sms);
   const unsigned grid = prm.n_tiles < cap ? prm.n_tiles : cap;
-  int rc = launch_pdl(pick_kernel(pcm16, d->n_mels), dim3(grid), dim3(kThreads), (size_t)smem, stream,
-                      prm);
-  if (rc == 0 && tile_stats != nullptr && prm.top_db < INFINITY) {
+  KernelFn kern = power ? fbank400_v3_kernel<false, 0, true> : pick_kernel(pcm16, d->n_mels);
+  int rc = launch_pdl(kern, dim3(grid), dim3(kThreads), (size_t)smem, stream, prm);
+  if (rc == 0 && !power && tile_stats != nullptr && prm.top_db < INFINITY) {
     rc = launch_pdl(pick_clamp(d->n_mels), dim3(prm.n_tiles), dim3(kClampThreads), 0, stream, prm);
   }
   return rc;
+}
+
+int launch_fbank400_v3(const sbfe_fbank_desc* d, const void* wav, int pcm16, float scale,
+                       const int64_t* offsets, const int32_t* nsamples, int64_t B, int64_t L,
+                       int64_t wav_stride, float* out, sbfe_maxkey_t* utt_max, float* tile_stats,
+                       float top_db, cudaStream_t stream) {
+  return launch_v3(d, wav, pcm16, scale, offsets, nsamples, B, L, wav_stride, out, utt_max, tile_stats,
+                   top_db, false, stream);
+}
+
+// STFT + power spectrum of the default mode (centre, zero padding, one-sided) at n_fft 400 / hop
+// 160: the fused kernel's transform with the [32 frames][201 bins] tile as its output
+bool stft400_power_supported(const sbfe_fbank_desc* d) {
+  return d->n_fft == 400 && d->hop == v3::kHop &&
+         v3::smem_floats(v3::kBins, 0) * sizeof(float) <= (size_t)v3::kMaxSmem;
+}
+int launch_stft400_power(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64_t L,
+                         int64_t wav_stride, float* out, cudaStream_t stream) {
+  return launch_v3(d, wav, 0, 1.f, nullptr, nullptr, B, L, wav_stride, out, nullptr, nullptr, -1.f, true,
+                   stream);
 }
 
 // the clamp launch of mode (b) for any kernel that emits the same 32-frame tile records

@@ -110,7 +110,9 @@ __device__ __forceinline__ void stage_tile(const Params& prm, unsigned b, unsign
   }
 }
 
-template <int MC>
+// POWER: STFT + spectral_magnitude(power=1) of the default mode - the [32 frames][257 bins] tile of
+// the power spectrum is the output (M = 257, no filterbank, no records); see fbank400_v3.cu
+template <int MC, bool POWER = false>
 __global__ void __launch_bounds__(kThreads, 2) fbank512_kernel(const __grid_constant__ Params prm) {
   extern __shared__ __align__(16) float smem[];
   float* s_a = smem;                       // staged waveform, later P[bin][32]
@@ -119,7 +121,7 @@ __global__ void __launch_bounds__(kThreads, 2) fbank512_kernel(const __grid_cons
   float* s_tw = s_win + kTabW;             // [n2][k1] (re, im) of W256^(n2 k1)
   float* s_ut = s_tw + kTabTw;             // [k] (cos, sin)(2 pi k / 512)
   int2* s_meta = reinterpret_cast<int2*>(s_ut + kTabUt);
-  const int M = MC > 0 ? MC : prm.n_mels;
+  const int M = POWER ? kBins : (MC > 0 ? MC : prm.n_mels);
   float* s_w = reinterpret_cast<float*>(s_meta) + ((2 * M + 3) & ~3);
 
   __shared__ unsigned s_tile_key;
@@ -140,7 +142,7 @@ __global__ void __launch_bounds__(kThreads, 2) fbank512_kernel(const __grid_cons
     sincospif(2.0f * (float)i / (float)kNfft, &sn, &cs);
     reinterpret_cast<float2*>(s_ut)[i] = make_float2(cs, sn);
   }
-  for (int m = tid; m < M; m += kThreads)
+  for (int m = tid; !POWER && m < M; m += kThreads)
     s_meta[m] = make_int2(__ldg(prm.mel_start + m) | (__ldg(prm.mel_count + m) << 16),
                           __ldg(prm.mel_offset + m));
   for (int i = tid; i < prm.mel_nnz; i += kThreads) s_w[i] = __ldg(prm.mel_weight + i);
@@ -171,7 +173,7 @@ __global__ void __launch_bounds__(kThreads, 2) fbank512_kernel(const __grid_cons
   };
   int planG[4], planW[4], planP[4];
   __syncthreads();   // tables are complete
-  mel_plan(0, planG, planW, planP);
+  if (!POWER) mel_plan(0, planG, planW, planP);
 
 #pragma unroll 1
   for (unsigned tile = blockIdx.x; tile < prm.n_tiles; tile += gridDim.x) {
@@ -264,7 +266,10 @@ __global__ void __launch_bounds__(kThreads, 2) fbank512_kernel(const __grid_cons
     __syncthreads();
 
     // ---- stage 3: sparse mel projection + dB -> output tile [32][M] in smem ---------------------
-    {
+    if constexpr (POWER) {
+      // P[bin][32] -> tile [frame][bin], pitch 257 (odd): conflict-free reads and writes
+      for (int i = tid; i < kBins * kTile; i += kThreads) s_o[(i & (kTile - 1)) * opitch + (i >> 5)] = s_a[i];
+    } else {
       float vmax0 = -INFINITY, vmax1 = -INFINITY;
       const float2* pp0 = reinterpret_cast<const float2*>(s_a) + p;
 #pragma unroll 1
@@ -421,15 +426,15 @@ bool fbank512_supported(const sbfe_fbank_desc* d) {
 int launch_clamp_tiles(const sbfe_fbank_desc* d, int64_t B, int64_t T, float* out, const float* tile_stats,
                        float top_db, cudaStream_t stream);
 
-int launch_fbank512(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64_t L,
-                    int64_t wav_stride, float* out, sbfe_maxkey_t* utt_max, float* tile_stats,
-                    float top_db, cudaStream_t stream) {
+static int launch_512(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64_t L,
+                      int64_t wav_stride, float* out, sbfe_maxkey_t* utt_max, float* tile_stats,
+                      float top_db, bool power, cudaStream_t stream) {
   using namespace v512;
   Params prm;
   prm.db = DbParams{d->multiplier * 0.30102999566398120f, d->amin, d->db_offset, d->floor_db,
-                    d->log_mel};
-  prm.n_mels = d->n_mels;
-  prm.mel_nnz = d->mel_nnz;
+                    power ? 0 : d->log_mel};
+  prm.n_mels = power ? kBins : d->n_mels;
+  prm.mel_nnz = power ? 0 : d->mel_nnz;
   prm.L = L;
   prm.wav_stride = wav_stride;
   prm.T = 1 + L / kHop;
@@ -446,7 +451,7 @@ int launch_fbank512(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64
   if (tiles * B > 0x7fffffff || prm.T > 0x7fffffff) return SBFE_E_TOOBIG;
   prm.tiles_per_utt = (unsigned)tiles;
   prm.n_tiles = (unsigned)(tiles * B);
-  const size_t smem = smem_floats(d->n_mels, d->mel_nnz) * sizeof(float);
+  const size_t smem = smem_floats(prm.n_mels, prm.mel_nnz) * sizeof(float);
   static std::atomic<int> per_sm_cache[64];   // 0 -> value, idempotent (see fbank400_v3.cu)
   int dev = 0, sms = 0;
   cudaError_t e = cudaGetDevice(&dev);
@@ -464,16 +469,43 @@ int launch_fbank512(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, pick_kernel(mc), kThreads, (size_t)kMaxSmem);
       if (e == cudaSuccess && n < per_sm) per_sm = n;
     }
+    {
+      int n = 0;
+      if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(fbank512_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 kMaxSmem);
+      if (e == cudaSuccess)
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fbank512_kernel<0, true>, kThreads,
+                                                          (size_t)kMaxSmem);
+      if (e == cudaSuccess && n < per_sm) per_sm = n;
+    }
     if (e != cudaSuccess) return (int)e;
     if (per_sm < 1) return (int)cudaErrorLaunchOutOfResources;
     if (cached) per_sm_cache[dev].store(per_sm, std::memory_order_release);
   }
   const unsigned cap = (unsigned)(per_sm * sms);
   const unsigned grid = prm.n_tiles < cap ? prm.n_tiles : cap;
-  int rc = launch_pdl(pick_kernel(d->n_mels), dim3(grid), dim3(kThreads), (size_t)smem, stream, prm);
-  if (rc == 0 && tile_stats != nullptr && top_db >= 0.f)
+  KernelFn kern = power ? fbank512_kernel<0, true> : pick_kernel(d->n_mels);
+  int rc = launch_pdl(kern, dim3(grid), dim3(kThreads), (size_t)smem, stream, prm);
+  if (rc == 0 && !power && tile_stats != nullptr && top_db >= 0.f)
     rc = launch_clamp_tiles(d, B, prm.T, out, tile_stats, top_db, stream);
   return rc;
+}
+
+int launch_fbank512(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64_t L,
+                    int64_t wav_stride, float* out, sbfe_maxkey_t* utt_max, float* tile_stats,
+                    float top_db, cudaStream_t stream) {
+  return launch_512(d, wav, B, L, wav_stride, out, utt_max, tile_stats, top_db, false, stream);
+}
+
+// STFT + power spectrum of the default mode at n_fft 512 / hop 160 (see fbank400_v3.cu)
+bool stft512_power_supported(const sbfe_fbank_desc* d) {
+  return d->n_fft == v512::kNfft && d->hop == v512::kHop &&
+         v512::smem_floats(v512::kBins, 0) * sizeof(float) <= (size_t)v512::kMaxSmem;
+}
+int launch_stft512_power(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64_t L,
+                         int64_t wav_stride, float* out, cudaStream_t stream) {
+  return launch_512(d, wav, B, L, wav_stride, out, nullptr, nullptr, -1.f, true, stream);
 }
 
 }  // namespace sbfe

@@ -389,11 +389,24 @@ int64_t stft_frames(const sbfe_fbank_desc* d, int64_t L, int flags) {
   return 1 + L / d->hop;
 }
 
+bool stft400_power_supported(const sbfe_fbank_desc* d);   // fbank400_v3.cu
+int launch_stft400_power(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
+                         cudaStream_t);
+bool stft512_power_supported(const sbfe_fbank_desc* d);   // fbank512.cu
+int launch_stft512_power(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
+                         cudaStream_t);
+
 int launch_stft_generic(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64_t L,
                         int64_t wav_stride, float* out, int power_only, int flags,
                         cudaStream_t stream) {
   const int64_t T = stft_frames(d, L, flags);
   if (T == 0) return 0;
+  // the recipes' transforms (n_fft 400 / 512, hop 160, default mode), power only: the fused
+  // kernels' FFTs (SBFE_STFT400_OFF: the Stockham kernel below, for the tests' cross-check)
+  if (power_only && flags == 0 && getenv("SBFE_STFT400_OFF") == nullptr) {
+    if (stft400_power_supported(d)) return launch_stft400_power(d, wav, B, L, wav_stride, out, stream);
+    if (stft512_power_supported(d)) return launch_stft512_power(d, wav, B, L, wav_stride, out, stream);
+  }
   const int start = (flags & 1) ? 0 : -d->n_fft / 2;
   const int reflect = (flags & 2) ? 1 : 0, twosided = (flags & 4) ? 1 : 0;
   const int64_t tiles = (T + kGenFrames - 1) / kGenFrames;
@@ -501,7 +514,7 @@ constexpr int kMmaRows = 64;       // frames per tile
 constexpr int kMmaThreads = 512;   // 16 warps = 4 row groups of 16 x 4 column groups
 constexpr int kMmaColGroups = 4;
 constexpr int kMmaMaxNT = 4;       // n-tiles of 8 filters per warp: M <= 128
-constexpr int kMmaDensity = 2;     // stored weights >= 1 / kMmaDensity of the matrix: "dense"
+constexpr int kMmaDensity = 5;          // n_fft 400: dense path from 1/5 stored weights (see mel_dense_rule)
 constexpr int kMmaDensitySlowPath = 10;
 bool fbank400_supported(const sbfe_fbank_desc* d);   // fbank400.cu
 
@@ -666,9 +679,10 @@ static bool mel_dense_rule(const sbfe_fbank_desc* d) {
   const char* sw = getenv("SBFE_MEL_MMA");
   if (sw != nullptr && sw[0] == '0') return false;
   if (sw != nullptr && sw[0] == '2') return true;
-  // where a fused n_fft = 400 kernel takes the configuration its sparse loops win unless the
-  // matrix is really dense (gaussian-80 at 18 % stored weights: 96 us fused against STFT +
-  // projection on the cfg2 batch); elsewhere (n_fft 512 ...) 10 % is enough
+  // where a fused n_fft = 400 kernel takes the configuration, its sparse loops cost about
+  // 36 us + 0.02 us per stored weight on the cfg2 batch (triangular-80: 44 us, gaussian-80 at 18 %
+  // stored weights: 96 us) against 92 us for power STFT + tcgen05 projection whatever the
+  // density: the dense path from 1/5 on; elsewhere (n_fft 512 ...) 10 % is enough
   const int density = fbank400_supported(d) ? kMmaDensity : kMmaDensitySlowPath;
   return (int64_t)density * d->mel_nnz >= (int64_t)bins * d->n_mels;
 }

@@ -59,3 +59,39 @@ def test_error_behaviour_of_the_modes():
     fb.compute_STFT = sb.STFT(sample_rate=16000, center=False)
     with pytest.raises(NotImplementedError):
         fb(torch.zeros(2, 4000).cuda())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("B,L", [(3, 16000 + 53), (2, 5119), (1, 160 * 33), (2, 160), (32, 64000)])
+@pytest.mark.parametrize("normalized", [False, True])
+@pytest.mark.parametrize("n_fft", [400, 512])
+def test_power_spectrum_of_the_default_mode_uses_the_fused_transform(B, L, normalized, n_fft):
+    """power_only STFT at n_fft 400 / 512, hop 160 (default mode) runs the fused kernels'
+    transforms (csrc/fbank400_v3.cu, fbank512.cu: POWER); same numbers as the Stockham kernel it replaces and as
+    torch.stft in float64 (features.py:133-188 + spectral_magnitude power=1, :327-356).
+    Tolerance: 3e-6 of the frame's largest bin (fp32 FFT of 400 points)."""
+    import speechbrain_b200 as sb
+    from speechbrain_b200 import ops
+
+    torch.manual_seed(L)
+    wav = torch.randn(B, L, device="cuda") * 0.1
+    wav[0, L // 2:] = 0.0                                  # a zero tail: all-zero tiles
+    st = sb.STFT(sample_rate=16000, n_fft=n_fft, normalized_stft=normalized)
+    tab = st.tables()
+    got = ops.stft_forward(tab, wav, power_only=True)
+    os.environ["SBFE_STFT400_OFF"] = "1"
+    try:
+        old = ops.stft_forward(tab, wav, power_only=True)
+    finally:
+        del os.environ["SBFE_STFT400_OFF"]
+    win = torch.hamming_window(400, device="cuda", dtype=torch.float64)
+    ref = torch.stft(wav.double(), n_fft, 160, 400, win, center=True, pad_mode="constant",
+                     normalized=normalized, onesided=True, return_complex=True)
+    ref = (ref.real ** 2 + ref.imag ** 2).transpose(1, 2)
+    assert got.shape == old.shape == ref.shape == (B, 1 + L // 160, n_fft // 2 + 1)
+    scale = ref.amax(dim=2, keepdim=True).clamp(min=1e-30)
+    err_new = float(((got.double() - ref).abs() / scale).max())
+    err_old = float(((old.double() - ref).abs() / scale).max())
+    assert err_new <= 3e-6, (err_new, err_old)
+    assert err_old <= 3e-6, (err_new, err_old)
+    assert bool((got[0, L // 320 + 4:] == 0).all())        # zeros in, exact zeros out
