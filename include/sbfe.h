@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define SBFE_ABI_VERSION 11
+#define SBFE_ABI_VERSION 12
 
 #if defined(__GNUC__)
 #define SBFE_API __attribute__((visibility("default")))
@@ -338,6 +338,23 @@ SBFE_API int sbfe_wav_fir(const float* d_x, int64_t B, int64_t L, const float* d
                  int32_t pad, float* d_out, void* stream);
 /* DoClip (:1176-1228): out = clamp(x, -value, value) over n floats; in place when d_out == d_x. */
 SBFE_API int sbfe_wav_clip(const float* d_x, int64_t n, float value, float* d_out, void* stream);
+/* AddNoise with white noise (csv_file = None; :126-168): the caller draws snr_db [B] and the noise
+ * [B, L] with the reference's torch.rand / torch.randn_like calls.
+ *   sbfe_wav_abs_sums   d_partials [B][sbfe_wav_abs_chunks(L)]: sums of |x| per 16384 samples (the
+ *                       numerator of compute_amplitude, signal_processing.py:51-56, which sums the
+ *                       whole padded row); the consumer adds them in index order
+ *   sbfe_wav_add_noise  out = x * (1 - f) + (f * amp) * noise, f = 1 / (10^(snr_db / 20) + 1),
+ *                       amp = sum|x| / (d_lengths[b] * L), rounded like the reference's three eager
+ *                       ops; in place when d_out == d_x; d_absmax (NULL, or [B] zeroed by the
+ *                       caller) receives the bits of max |out[b]| for normalize = True
+ *   sbfe_wav_peak_normalize  x[b] /= max(absmax[b], 1)  (:164-168) */
+SBFE_API int64_t sbfe_wav_abs_chunks(int64_t L);
+SBFE_API int sbfe_wav_abs_sums(const float* d_x, int64_t B, int64_t L, float* d_partials, void* stream);
+SBFE_API int sbfe_wav_add_noise(const float* d_x, const float* d_noise, int64_t B, int64_t L,
+                       const float* d_partials, const float* d_lengths, const float* d_snr_db,
+                       float* d_out, uint32_t* d_absmax, void* stream);
+SBFE_API int sbfe_wav_peak_normalize(float* d_x, int64_t B, int64_t L, const uint32_t* d_absmax,
+                            void* stream);
 /* Resample._perform_resample (:600-665), Kaldi's LinearResample: output sample n * phases + i =
  * sum_k d_weights[i][k] x[d_first[i] + n * in_stride + k] (x zero outside [0, L)), k < width;
  * x [B, L] -> out [B, L_out].  Weights and first indices: Resample._indices_and_weights (:740-820). */

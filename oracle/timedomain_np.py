@@ -8,6 +8,8 @@ to the samples:
                 (as DropFreq.forward applies it, speech_augmentation.py:1003-1007)
   clip          DoClip.forward             speech_augmentation.py:1222-1226
   resample      Resample._perform_resample speech_augmentation.py:600-665
+  add_noise     AddNoise.forward (white)   speech_augmentation.py:126-168 (+ compute_amplitude,
+                dB_to_amplitude: signal_processing.py:51-56, 355-372)
 Pinned on outputs of the unmodified reference modules (tests/golden/timedomain_golden.npz,
 tests/make_golden_timedomain.py) in tests/test_timedomain.py.
 """
@@ -64,3 +66,22 @@ def resample(x, weights, first, in_stride, n_out, dtype=np.float64):
             ok = (g >= 0) & (g < L)
             out[:, o[ok]] += w[i, k] * x[:, g[ok]]
     return out
+
+
+def add_noise(x, noise, lengths, snr_db, normalize=False):
+    """x, noise [B, L] float32; lengths [B] relative; snr_db [B].  The reference's float32 ops in
+    its order: amp = sum|x| / (lengths * L); f = 1 / (10^(snr/20) + 1); y = x * (1 - f);
+    y += (f * amp) * noise; normalize: y / max(max|y|, 1)."""
+    f32 = np.float32
+    x = np.asarray(x, dtype=f32)
+    noise = np.asarray(noise, dtype=f32)
+    B, L = x.shape
+    ln = (np.asarray(lengths, dtype=f32) * f32(L)).reshape(B, 1)
+    amp = np.abs(x).sum(axis=1, keepdims=True, dtype=np.float64).astype(f32) / ln
+    snr = np.asarray(snr_db, dtype=f32).reshape(B, 1)
+    f = (f32(1) / (np.power(f32(10), snr / f32(20), dtype=f32) + f32(1))).astype(f32)
+    y = x * (f32(1) - f)
+    y = y + (f * amp) * noise
+    if normalize:
+        y = y / np.maximum(np.abs(y).max(axis=1, keepdims=True), f32(1))
+    return y.astype(f32)

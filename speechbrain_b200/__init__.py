@@ -12,7 +12,7 @@ from .lobes.features import MFCC, Fbank, pair  # noqa: F401
 from .processing.features import (  # noqa: F401
     DCT, ISTFT, STFT, ContextWindow, Deltas, Filterbank, InputNormalization, spectral_magnitude)
 from .processing.speech_augmentation import (  # noqa: F401
-    DoClip, DropChunk, DropFreq, Resample, SpeedPerturb)
+    AddNoise, DoClip, DropChunk, DropFreq, Resample, SpeedPerturb)
 
 __version__ = "0.1.0"
 

@@ -81,12 +81,16 @@ SIGNATURES = {
     "sbfe_wav_drop_chunks": (C.c_int, [_P, _I64, _I64, _I32, _P, _I32, _I64, _P, _P, _P]),
     "sbfe_wav_fir": (C.c_int, [_P, _I64, _I64, _P, _I32, _I32, _P, _P]),
     "sbfe_wav_clip": (C.c_int, [_P, _I64, _F, _P, _P]),
+    "sbfe_wav_abs_chunks": (_I64, [_I64]),
+    "sbfe_wav_abs_sums": (C.c_int, [_P, _I64, _I64, _P, _P]),
+    "sbfe_wav_add_noise": (C.c_int, [_P, _P, _I64, _I64, _P, _P, _P, _P, _P, _P]),
+    "sbfe_wav_peak_normalize": (C.c_int, [_P, _I64, _I64, _P, _P]),
     "sbfe_wav_resample": (C.c_int, [_P, _I64, _I64, _P, _P, _I32, _I32, _I32, _I64, _P, _P]),
     "sbfe_mean_workspace_bytes": (_I64, []),
     "sbfe_mean": (C.c_int, [_P, _I64, _P, _P, _I64, _P]),
 }
 
-ABI_VERSION = 11
+ABI_VERSION = 12
 _lock = threading.Lock()
 _lib = None
 

@@ -57,6 +57,11 @@ int launch_drop_chunks(float*, int64_t, int, const int32_t*, int, int64_t, const
                        cudaStream_t);
 int launch_fir_same(const float*, int64_t, int64_t, const float*, int, int, float*, cudaStream_t);
 int launch_clip(const float*, int64_t, float, float*, cudaStream_t);
+int64_t abs_chunks(int64_t);
+int launch_abs_sums(const float*, int64_t, int64_t, float*, cudaStream_t);
+int launch_add_noise(const float*, const float*, int64_t, int64_t, const float*, const float*, const float*,
+                     float*, unsigned*, cudaStream_t);
+int launch_peak_normalize(float*, int64_t, int64_t, const unsigned*, cudaStream_t);
 int launch_resample(const float*, int64_t, int64_t, const float*, const int32_t*, int, int, int,
                     int64_t, float*, cudaStream_t);
 int64_t mean_workspace_bytes();
@@ -367,6 +372,32 @@ int sbfe_wav_clip(const float* d_x, int64_t n, float value, float* d_out, void* 
   if (n == 0) return 0;
   if (!d_x || !d_out) return SBFE_E_INVAL;
   return launch_clip(d_x, n, value, d_out, (cudaStream_t)stream);
+}
+
+int64_t sbfe_wav_abs_chunks(int64_t L) { return L < 0 ? SBFE_E_INVAL : abs_chunks(L); }
+
+int sbfe_wav_abs_sums(const float* d_x, int64_t B, int64_t L, float* d_partials, void* stream) {
+  if (B < 0 || L < 0) return SBFE_E_INVAL;
+  if (B == 0 || L == 0) return 0;
+  if (!d_x || !d_partials) return SBFE_E_INVAL;
+  return launch_abs_sums(d_x, B, L, d_partials, (cudaStream_t)stream);
+}
+
+int sbfe_wav_add_noise(const float* d_x, const float* d_noise, int64_t B, int64_t L,
+                       const float* d_partials, const float* d_lengths, const float* d_snr_db,
+                       float* d_out, uint32_t* d_absmax, void* stream) {
+  if (B < 0 || L < 0) return SBFE_E_INVAL;
+  if (B == 0 || L == 0) return 0;
+  if (!d_x || !d_noise || !d_partials || !d_lengths || !d_snr_db || !d_out) return SBFE_E_INVAL;
+  return launch_add_noise(d_x, d_noise, B, L, d_partials, d_lengths, d_snr_db, d_out, d_absmax,
+                          (cudaStream_t)stream);
+}
+
+int sbfe_wav_peak_normalize(float* d_x, int64_t B, int64_t L, const uint32_t* d_absmax, void* stream) {
+  if (B < 0 || L < 0) return SBFE_E_INVAL;
+  if (B == 0 || L == 0) return 0;
+  if (!d_x || !d_absmax) return SBFE_E_INVAL;
+  return launch_peak_normalize(d_x, B, L, d_absmax, (cudaStream_t)stream);
 }
 
 int sbfe_wav_resample(const float* d_x, int64_t B, int64_t L, const float* d_weights,

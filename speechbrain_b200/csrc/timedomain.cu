@@ -176,4 +176,114 @@ int launch_resample(const float* x, int64_t B, int64_t L, const float* w, const 
                     L, w, first, P, S, W, L_out, out);
 }
 
+// ---- AddNoise with white noise (speech_augmentation.py:126-168) --------------------------------
+// compute_amplitude (signal_processing.py:51-56) sums |x| over the WHOLE padded row and divides by
+// the valid length; partial sums of kAbsChunk samples, added in a fixed order by the consumer
+// (deterministic: no float atomics).
+constexpr int kAbsChunk = 16384;
+
+__global__ void __launch_bounds__(kTdThreads)
+abs_sums_kernel(const float* __restrict__ x, int64_t L, float* __restrict__ partials, int chunks) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int64_t b = blockIdx.y;
+  const int64_t lo = (int64_t)blockIdx.x * kAbsChunk;
+  const int64_t hi = lo + kAbsChunk < L ? lo + kAbsChunk : L;
+  const float* xb = x + b * L;
+  float acc = 0.f;
+  for (int64_t i = lo + threadIdx.x; i < hi; i += kTdThreads) acc += fabsf(__ldg(xb + i));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  __shared__ float s_part[kTdThreads / 32];
+  if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < kTdThreads / 32; ++w) t += s_part[w];
+    partials[b * chunks + blockIdx.x] = t;
+  }
+}
+
+// out = x * (1 - f) + (f * amp) * noise, three roundings like the reference's eager ops
+// (noisy *= 1 - f; noisy += new_noise_amplitude * white_noise), f = 1 / (10^(snr / 20) + 1),
+// amp = sum|x| / (lengths * L); absmax[b] (uint bits of max |out|, zeroed by the caller) for
+// normalize=True
+__global__ void __launch_bounds__(kTdThreads)
+add_noise_kernel(const float* __restrict__ x, const float* __restrict__ noise, int64_t L,
+                 const float* __restrict__ partials, int chunks, const float* __restrict__ lengths,
+                 const float* __restrict__ snr, float* __restrict__ out, unsigned* absmax) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int64_t b = blockIdx.y;
+  __shared__ float s_keep, s_namp;
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int c = 0; c < chunks; ++c) t += partials[b * chunks + c];
+    const float amp = t / (__ldg(lengths + b) * (float)L);
+    const float f = 1.f / (powf(10.f, __ldg(snr + b) / 20.f) + 1.f);
+    s_keep = 1.f - f;
+    s_namp = f * amp;
+  }
+  __syncthreads();
+  const float keep = s_keep, namp = s_namp;
+  const float* xb = x + b * L;
+  const float* nb = noise + b * L;
+  float* ob = out + b * L;
+  float mx = 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * kTdThreads + threadIdx.x; i < L; i += (int64_t)gridDim.x * kTdThreads) {
+    const float v = __fadd_rn(__fmul_rn(__ldg(xb + i), keep), __fmul_rn(namp, __ldg(nb + i)));
+    ob[i] = v;
+    mx = fmaxf(mx, fabsf(v));
+  }
+  if (absmax != nullptr) {
+    const unsigned k = __reduce_max_sync(0xffffffffu, __float_as_uint(mx));   // non-negative floats order as uints
+    if ((threadIdx.x & 31) == 0 && k) atomicMax(absmax + b, k);
+  }
+}
+
+// normalize=True (:164-168): x / clamp(absmax, min = 1)
+__global__ void __launch_bounds__(kTdThreads)
+peak_normalize_kernel(float* x, int64_t L, const unsigned* __restrict__ absmax) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int64_t b = blockIdx.y;
+  const float d = fmaxf(__uint_as_float(__ldg(absmax + b)), 1.f);
+  if (d == 1.f) return;
+  float* xb = x + b * L;
+  for (int64_t i = (int64_t)blockIdx.x * kTdThreads + threadIdx.x; i < L; i += (int64_t)gridDim.x * kTdThreads)
+    xb[i] = xb[i] / d;
+}
+
+int64_t abs_chunks(int64_t L) { return (L + kAbsChunk - 1) / kAbsChunk; }
+
+int launch_abs_sums(const float* x, int64_t B, int64_t L, float* partials, cudaStream_t stream) {
+  if (B == 0 || L == 0) return 0;
+  const int64_t chunks = abs_chunks(L);
+  if (B > 65535 || chunks > 0x7fffffff) return SBFE_E_TOOBIG;
+  return launch_pdl(abs_sums_kernel, dim3((unsigned)chunks, (unsigned)B), dim3(kTdThreads), 0, stream, x, L,
+                    partials, (int)chunks);
+}
+
+int launch_add_noise(const float* x, const float* noise, int64_t B, int64_t L, const float* partials,
+                     const float* lengths, const float* snr, float* out, unsigned* absmax,
+                     cudaStream_t stream) {
+  if (B == 0 || L == 0) return 0;
+  const int64_t chunks = abs_chunks(L);
+  if (B > 65535 || chunks > 0x7fffffff) return SBFE_E_TOOBIG;
+  int64_t bx = (L + 4 * kTdThreads - 1) / (4 * kTdThreads);
+  if (bx > 148 * 8) bx = 148 * 8;
+  return launch_pdl(add_noise_kernel, dim3((unsigned)bx, (unsigned)B), dim3(kTdThreads), 0, stream, x, noise,
+                    L, partials, (int)chunks, lengths, snr, out, absmax);
+}
+
+int launch_peak_normalize(float* x, int64_t B, int64_t L, const unsigned* absmax, cudaStream_t stream) {
+  if (B == 0 || L == 0) return 0;
+  if (B > 65535) return SBFE_E_TOOBIG;
+  int64_t bx = (L + 4 * kTdThreads - 1) / (4 * kTdThreads);
+  if (bx > 148 * 8) bx = 148 * 8;
+  return launch_pdl(peak_normalize_kernel, dim3((unsigned)bx, (unsigned)B), dim3(kTdThreads), 0, stream, x, L,
+                    absmax);
+}
+
+
 }  // namespace sbfe

@@ -552,6 +552,28 @@ def wav_clip(x, value):
     return out
 
 
+def wav_add_noise(x, noise, lengths, snr_db, normalize=False):
+    """AddNoise's arithmetic for a drawn noise tensor (sbfe_wav_abs_sums + sbfe_wav_add_noise
+    [+ sbfe_wav_peak_normalize]): x, noise [B, L], lengths (relative) and snr_db [B] on the device;
+    returns a new tensor."""
+    B, L = x.shape
+    out = torch.empty_like(x)
+    if B == 0 or L == 0:
+        return out
+    L_ = lib()
+    chunks = int(L_.sbfe_wav_abs_chunks(L))
+    partials = torch.empty((B, chunks), dtype=torch.float32, device=x.device)
+    absmax = torch.zeros(B, dtype=torch.int32, device=x.device) if normalize else None
+    with torch.cuda.device(x.device):
+        check(L_.sbfe_wav_abs_sums(_ptr(x), B, L, _ptr(partials), _stream()))
+        check(L_.sbfe_wav_add_noise(_ptr(x), _ptr(noise), B, L, _ptr(partials), _ptr(lengths),
+                                    _ptr(snr_db), _ptr(out), _ptr(absmax) if normalize else None,
+                                    _stream()))
+        if normalize:
+            check(L_.sbfe_wav_peak_normalize(_ptr(out), B, L, _ptr(absmax), _stream()))
+    return out
+
+
 def wav_resample(x, weights, first, in_stride, n_out):
     """Polyphase resampling of x [B, L] -> [B, n_out] (sbfe_wav_resample); weights [P, W] float32
     and first [P] int32 on x's device."""

@@ -9,8 +9,10 @@ the data movement is one kernel each (csrc/timedomain.cu) instead of per-sentenc
 slice assignments and, for the resampler, five ATen calls per polyphase branch.
 
 Waveforms are ``[batch, time]`` float32 on a CUDA device (``[batch, time, 1]`` is accepted and
-returned as such); multi-channel input raises ``NotImplementedError``.  Not built: ``AddNoise``,
-``AddReverb``, ``AddBabble`` (they need the reference's CSV data loaders, SURVEY.md 8 out of scope).
+returned as such); multi-channel input raises ``NotImplementedError``.  ``AddNoise`` (:30-290)
+is built for its white-noise mode (``csv_file=None``); with a CSV of noise files it raises, as do
+``AddReverb`` / ``AddBabble``, which are not built: they sit on the reference's CSV data loaders
+(out of scope).
 """
 import math
 
@@ -18,7 +20,7 @@ import torch
 
 from .. import ops
 
-__all__ = ["DropChunk", "DropFreq", "DoClip", "Resample", "SpeedPerturb"]
+__all__ = ["AddNoise", "DropChunk", "DropFreq", "DoClip", "Resample", "SpeedPerturb"]
 
 
 def _as_2d(waveforms, who):
@@ -29,6 +31,49 @@ def _as_2d(waveforms, who):
     if waveforms.dim() != 2:
         raise NotImplementedError("%s takes [batch, time] (or [batch, time, 1]) waveforms" % who)
     return waveforms, False
+
+
+class AddNoise(torch.nn.Module):
+    """Mixes white noise into the batch at a random SNR; reference :30-168 (``csv_file=None``).
+
+    Same constructor; same draws in the same order - ``torch.rand(1)`` for ``mix_prob``,
+    ``torch.rand(B, 1, device=...)`` for the SNRs, ``torch.randn_like(waveforms)`` for the noise - so
+    a seeded run on the same device mixes the same noise.  The amplitude of every signal, the
+    scaling, the mix and the optional peak normalisation are two or three launches
+    (csrc/timedomain.cu) instead of ~15 ATen ops over the batch."""
+
+    def __init__(self, csv_file=None, csv_keys=None, sorting="random", num_workers=0, snr_low=0,
+                 snr_high=0, pad_noise=False, mix_prob=1.0, start_index=None, normalize=False,
+                 replacements={}, noise_sample_rate=16000, clean_sample_rate=16000):
+        super().__init__()
+        if csv_file is not None:
+            raise NotImplementedError(
+                "speechbrain_b200.AddNoise mixes white noise (csv_file=None); noise files go "
+                "through the reference's CSV data loader, which is outside this package")
+        self.csv_file = csv_file
+        self.csv_keys = csv_keys
+        self.sorting = sorting
+        self.num_workers = num_workers
+        self.snr_low = snr_low
+        self.snr_high = snr_high
+        self.pad_noise = pad_noise
+        self.mix_prob = mix_prob
+        self.start_index = start_index
+        self.normalize = normalize
+        self.replacements = replacements
+
+    def forward(self, waveforms, lengths):
+        x, was3 = _as_2d(waveforms, "AddNoise")
+        x = x.float().contiguous()
+        if torch.rand(1) > self.mix_prob:                       # :131-132
+            out = x.clone()
+            return out.unsqueeze(2) if was3 else out
+        snr = torch.rand(len(x), 1, device=x.device)            # :138-139
+        snr = snr * (self.snr_high - self.snr_low) + self.snr_low
+        noise = torch.randn_like(x)                             # :148
+        lengths = lengths.to(device=x.device, dtype=torch.float32).contiguous()
+        out = ops.wav_add_noise(x, noise, lengths, snr.reshape(-1).contiguous(), self.normalize)
+        return out.unsqueeze(2) if was3 else out
 
 
 class DropChunk(torch.nn.Module):
