@@ -15,7 +15,7 @@ ncu --set full --import-source on --clock-control none -k regex:"fbank400_v3|nor
   python profiles/prof_norm.py >> $O/r2f_prof.log 2>&1
 PROF_PADDED=0 ncu --set full --import-source on --clock-control none -k regex:fbank400_v3 -s 2 -c 1 -f -o $O/r2f_fbank_unpadded \
   python profiles/prof_fbank.py 4 >> $O/r2f_prof.log 2>&1
-ncu --set full --clock-control none -k regex:"fbank512|mel_mma" -s 2 -c 2 -f -o $O/r2f_other python profiles/prof_other.py >> $O/r2f_prof.log 2>&1
+ncu --set full --clock-control none -k regex:"fbank512|mel_umma|mel_mma" -s 3 -c 3 -f -o $O/r2f_other python profiles/prof_other.py >> $O/r2f_prof.log 2>&1
 python profiles/stepbench.py > $O/r2f_stepbench.txt 2>&1
 python profiles/configs_bench.py --json $O/r2f_configs.json > $O/r2f_configs.txt 2>&1
 (python profiles/istft_bench.py; python profiles/nfft512_bench.py; python profiles/gaussian_bench.py) > $O/r2f_general.txt 2>&1
