@@ -55,6 +55,7 @@ constexpr int kPRows = 204;          // power rows incl. 3 zero rows for padded 
 constexpr int kRegionA = kPRows * kTile;                          // >= padded span (5428)
 constexpr int kRegionE = 200 * kPairs * 4;                        // exchange, float4 entries
 constexpr int kTabW = 400, kTabTw = 400, kTabT2 = 40;
+constexpr float kImSign = 1.f;       // COMPLEX: sign that turns stage 2's imaginary parts into torch.stft's
 
 struct Params {
   DbParams db;
@@ -223,7 +224,10 @@ __device__ __forceinline__ void clamp_tile(const Params& prm, unsigned b, unsign
 // POWER: the kernel is the STFT + spectral_magnitude(power=1) of the default mode (features.py:
 // 133-188, 327-356): the tile [32 frames][201 bins] of the power spectrum leaves through the same
 // output path, no filterbank (M = 201, no tables, no records)
-template <bool PCM16, int MC, bool POWER = false>
+// COMPLEX: the STFT itself, out [B, T, 201, 2].  Stage 2 writes X[k] = (re, im) of its frame pair IN
+// PLACE over the exchange entries its own warp has just read (a warp's 20 rows hold exactly its 20
+// bins x 16 pairs), rotated inside the row so that the store pass below reads them conflict-free.
+template <bool PCM16, int MC, bool POWER = false, bool COMPLEX = false>
 __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(const __grid_constant__ Params prm) {
   extern __shared__ __align__(16) float smem[];
   float* s_a = smem;                       // 2 x [staged waveform | P[bin][32]]
@@ -232,8 +236,9 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
   float* s_tt = s_tw + kTabW;              // [n2][20]: (re, im) of W400^(k1*n2), k1 = 1..9, 2 pad
   float* s_t2 = s_tt + kTabTw;             // [h][20]
   int2* s_meta = reinterpret_cast<int2*>(s_t2 + kTabT2);
-  const int M = POWER ? kBins : (MC > 0 ? MC : prm.n_mels);
+  const int M = COMPLEX ? 2 * kBins : (POWER ? kBins : (MC > 0 ? MC : prm.n_mels));   // floats per output row
   float* s_w = reinterpret_cast<float*>(s_meta) + ((2 * M + 3) & ~3);  // 16-byte aligned
+  int* s_row = reinterpret_cast<int*>(s_meta);   // COMPLEX: exchange row that holds bin k
 
   __shared__ unsigned s_tile_key;  // max key of the current tile (tile records)
   const int tid = threadIdx.x;
@@ -255,7 +260,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
     const float c0 = kTw400[tid], c1 = second ? kTw400[tid + kThreads] : 0.f;
     const float t2 = tid < kTabT2 ? kT2[tid] : 0.f;
     int ms = 0, mc = 0, mo = 0;
-    if (!POWER && tid < M) {
+    if (!POWER && !COMPLEX && tid < M) {
       ms = __ldg(prm.mel_start + tid);
       mc = __ldg(prm.mel_count + tid);
       mo = __ldg(prm.mel_offset + tid);
@@ -270,11 +275,11 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
     put_w(tid, w0, c0);
     if (second) put_w(tid + kThreads, w1, c1);
     if (tid < kTabT2) s_t2[tid] = t2;
-    if (!POWER && tid < M) s_meta[tid] = make_int2(ms | (mc << 16), mo);
+    if (!POWER && !COMPLEX && tid < M) s_meta[tid] = make_int2(ms | (mc << 16), mo);
     if (tid < prm.mel_nnz) s_w[tid] = g0;
     if (tid + kThreads < prm.mel_nnz) s_w[tid + kThreads] = g1;
   }
-  for (int m = tid + kThreads; !POWER && m < M; m += kThreads)       // more than 320 filters
+  for (int m = tid + kThreads; !POWER && !COMPLEX && m < M; m += kThreads)       // more than 320 filters
     s_meta[m] = make_int2(__ldg(prm.mel_start + m) | (__ldg(prm.mel_count + m) << 16),
                           __ldg(prm.mel_offset + m));
   for (int i = tid + 2 * kThreads; i < prm.mel_nnz; i += kThreads) s_w[i] = __ldg(prm.mel_weight + i);
@@ -326,7 +331,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
   };
   int planG[4], planW[4], planP[4];
   __syncthreads();   // s_meta is complete
-  if (!POWER) mel_plan(0, planG, planW, planP);
+  if (!POWER && !COMPLEX) mel_plan(0, planG, planW, planP);
 
 #pragma unroll 1
   for (int it = 0; tile < prm.n_tiles; ++it, tile += gridDim.x) {
@@ -479,6 +484,19 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
         cx<f2> C[10];
         stage2_half(a, sigma, tr, ti, C);
         // bin of output j: k = k1 + 20h + 40j, mirrored above 200
+        if constexpr (COMPLEX) {
+          __syncwarp();   // every lane of the warp has read its exchange entries: the rows are free
+#pragma unroll
+          for (int j = 0; j < 10; ++j) {
+            const int kk = k1 + 20 * h + 40 * j;
+            const int bin = j < 5 ? kk : kNfft - kk;          // X[400 - k] = conj X[k]
+            const float sg = (j < 5 ? 1.f : -1.f) * kImSign;
+            const int row = (10 * h + j) * 10 + k1;
+            s_e4[row * kPairs + ((p + row) & (kPairs - 1))] =
+                make_float4(C[j].re.v.x, sg * C[j].im.v.x, C[j].re.v.y, sg * C[j].im.v.y);
+            if (p == 0) s_row[bin] = row;
+          }
+        } else {
         float2* pr = prow + (k1 + 20 * h) * kPairs;
 #pragma unroll
         for (int j = 0; j < 10; ++j) {
@@ -491,6 +509,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
           const f2 pw = fmat(C[j].im, C[j].im, f2{__fmul2_rn(C[j].re.v, C[j].re.v)});
           pm[-40 * j * kPairs] = pw.v;
         }
+        }
       } else {
         const float4* src = s_e4 + p;
         f2 y[20];
@@ -499,23 +518,48 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
           const float4 q = src[n2 * 10 * kPairs];
           y[n2] = h ? mk2(q.z, q.w) : mk2(q.x, q.y);
         }
+        if constexpr (COMPLEX) __syncwarp();   // both halves have read rows 20 n2: they are free
         if (h == 0) {  // k1 = 0: bins 20*k2
           const float none[20] = {};
           cx<f2> X[11];
           rdft20<false>(y, none, X);
+          if constexpr (COMPLEX) {
+            // bins 0 and 200 are real: they share row 0 as (X0, X200) of the two frames
+            s_e4[p] = make_float4(X[0].re.v.x, X[10].re.v.x, X[0].re.v.y, X[10].re.v.y);
+#pragma unroll
+            for (int k2 = 1; k2 <= 9; ++k2) {
+              const int row = k2 * 10;
+              s_e4[row * kPairs + ((p + row) & (kPairs - 1))] = make_float4(
+                  X[k2].re.v.x, kImSign * X[k2].im.v.x, X[k2].re.v.y, kImSign * X[k2].im.v.y);
+              if (p == 0) s_row[20 * k2] = row;
+            }
+          } else {
           prow[0] = __fmul2_rn(X[0].re.v, X[0].re.v);
           prow[200 * kPairs] = __fmul2_rn(X[10].re.v, X[10].re.v);
 #pragma unroll
           for (int k2 = 1; k2 <= 9; ++k2)
             prow[20 * k2 * kPairs] =
                 fmat(X[k2].im, X[k2].im, f2{__fmul2_rn(X[k2].re.v, X[k2].re.v)}).v;
+          }
         } else {  // k1 = 10: bins 10 + 20*k2
           cx<f2> C[10];
           stage2_k10(y, C);
+          if constexpr (COMPLEX) {
+#pragma unroll
+            for (int j = 0; j < 10; ++j) {
+              const int bin = j < 5 ? 10 + 40 * j : 390 - 40 * j;
+              const float sg = (j < 5 ? 1.f : -1.f) * kImSign;
+              const int row = (10 + j) * 10;
+              s_e4[row * kPairs + ((p + row) & (kPairs - 1))] =
+                  make_float4(C[j].re.v.x, sg * C[j].im.v.x, C[j].re.v.y, sg * C[j].im.v.y);
+              if (p == 0) s_row[bin] = row;
+            }
+          } else {
 #pragma unroll
           for (int j = 0; j < 10; ++j) {
             const int bin = j < 5 ? 10 + 40 * j : 390 - 40 * j;
             prow[bin * kPairs] = fmat(C[j].im, C[j].im, f2{__fmul2_rn(C[j].re.v, C[j].re.v)}).v;
+          }
           }
         }
       }
@@ -526,6 +570,28 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
     if (s_p[tid] == 1.2345e-30f) prm.out[0] = 1.f;
     continue;
 #endif
+    if constexpr (COMPLEX) {
+      // ---- store pass: frame t = row of 201 (re, im) pairs, 8-byte stores, lanes over bins.
+      // Entry of bin k, pair q: row s_row[k], slot (q + row) & 15 - 16 consecutive bins of a warp
+      // sit in 16 different slots
+      const int64_t left = prm.T - t0;
+      const int nvalid = left < kTile ? (int)left : kTile;
+      float2* o2 = reinterpret_cast<float2*>(prm.out) + (b * prm.T + t0) * kBins;
+      for (int i = tid; i < nvalid * kBins; i += kThreads) {
+        const int t = i / kBins, k = i - t * kBins;
+        const int q = t >> 1, odd = t & 1;
+        float2 v;
+        if (k == 0 || k == kNfft / 2) {
+          const float4 e = s_e4[q];
+          v = make_float2(k == 0 ? (odd ? e.z : e.x) : (odd ? e.w : e.y), 0.f);
+        } else {
+          const int row = s_row[k];
+          v = reinterpret_cast<const float2*>(s_e4 + row * kPairs + ((q + row) & (kPairs - 1)))[odd];
+        }
+        o2[i] = v;
+      }
+      continue;   // the barrier at the top of the next iteration orders these reads before its stage 1
+    }
     // ---- stage 3: sparse mel projection + dB -> output tile [32][M] in smem -----------------
     if constexpr (POWER) {
       // P[bin][32] -> tile [frame][bin], pitch 201: a warp reads 32 consecutive words of one bin
@@ -785,12 +851,12 @@ bool fbank400_v3_supported(const sbfe_fbank_desc* d) {
 static int launch_v3(const sbfe_fbank_desc* d, const void* wav, int pcm16, float scale,
                      const int64_t* offsets, const int32_t* nsamples, int64_t B, int64_t L,
                      int64_t wav_stride, float* out, sbfe_maxkey_t* utt_max, float* tile_stats,
-                     float top_db, bool power, cudaStream_t stream) {
+                     float top_db, int power, cudaStream_t stream) {   // power: 1 = |X|^2, 2 = X
   using namespace v3;
   Params prm;
   prm.db = DbParams{d->multiplier * 0.30102999566398120f, d->amin, d->db_offset, d->floor_db,
                     power ? 0 : d->log_mel};
-  prm.n_mels = power ? kBins : d->n_mels;
+  prm.n_mels = power == 2 ? 2 * kBins : (power ? kBins : d->n_mels);
   prm.mel_nnz = power ? 0 : d->mel_nnz;
   prm.L = L;
   prm.wav_stride = wav_stride;
@@ -845,6 +911,13 @@ static int launch_v3(const sbfe_fbank_desc* d, const void* wav, int pcm16, float
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fbank400_v3_kernel<false, 0, true>, kThreads,
                                                           (size_t)kMaxSmem);
       if (e == cudaSuccess && n < per_sm) per_sm = n;
+      if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(fbank400_v3_kernel<false, 0, false, true>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem);
+      if (e == cudaSuccess)
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fbank400_v3_kernel<false, 0, false, true>,
+                                                          kThreads, (size_t)kMaxSmem);
+      if (e == cudaSuccess && n < per_sm) per_sm = n;
     }
     if (e != cudaSuccess) return (int)e;
     if (per_sm < 1) return (int)cudaErrorLaunchOutOfResources;
@@ -853,7 +926,8 @@ static int launch_v3(const sbfe_fbank_desc* d, const void* wav, int pcm16, float
   // persistent: every CTA strides over the tiles
   const unsigned cap = (unsigned)(per_sm * sms);
   const unsigned grid = prm.n_tiles < cap ? prm.n_tiles : cap;
-  KernelFn kern = power ? fbank400_v3_kernel<false, 0, true> : pick_kernel(pcm16, d->n_mels);
+  KernelFn kern = power == 2 ? fbank400_v3_kernel<false, 0, false, true>
+                             : (power ? fbank400_v3_kernel<false, 0, true> : pick_kernel(pcm16, d->n_mels));
   int rc = launch_pdl(kern, dim3(grid), dim3(kThreads), (size_t)smem, stream, prm);
   if (rc == 0 && !power && tile_stats != nullptr && prm.top_db < INFINITY) {
     rc = launch_pdl(pick_clamp(d->n_mels), dim3(prm.n_tiles), dim3(kClampThreads), 0, stream, prm);
@@ -866,19 +940,20 @@ int launch_fbank400_v3(const sbfe_fbank_desc* d, const void* wav, int pcm16, flo
                        int64_t wav_stride, float* out, sbfe_maxkey_t* utt_max, float* tile_stats,
                        float top_db, cudaStream_t stream) {
   return launch_v3(d, wav, pcm16, scale, offsets, nsamples, B, L, wav_stride, out, utt_max, tile_stats,
-                   top_db, false, stream);
+                   top_db, 0, stream);
 }
 
 // STFT + power spectrum of the default mode (centre, zero padding, one-sided) at n_fft 400 / hop
 // 160: the fused kernel's transform with the [32 frames][201 bins] tile as its output
 bool stft400_power_supported(const sbfe_fbank_desc* d) {
   return d->n_fft == 400 && d->hop == v3::kHop &&
-         v3::smem_floats(v3::kBins, 0) * sizeof(float) <= (size_t)v3::kMaxSmem;
+         v3::smem_floats(2 * v3::kBins, 0) * sizeof(float) <= (size_t)v3::kMaxSmem;
 }
+// complex != 0: out [B, T, 201, 2]; else the power spectrum [B, T, 201]
 int launch_stft400_power(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64_t L,
-                         int64_t wav_stride, float* out, cudaStream_t stream) {
-  return launch_v3(d, wav, 0, 1.f, nullptr, nullptr, B, L, wav_stride, out, nullptr, nullptr, -1.f, true,
-                   stream);
+                         int64_t wav_stride, float* out, int complex, cudaStream_t stream) {
+  return launch_v3(d, wav, 0, 1.f, nullptr, nullptr, B, L, wav_stride, out, nullptr, nullptr, -1.f,
+                   complex ? 2 : 1, stream);
 }
 
 // the clamp launch of mode (b) for any kernel that emits the same 32-frame tile records
