@@ -41,6 +41,7 @@ constexpr int kHop = 160;
 constexpr int kNfft = 512;
 constexpr int kHalf = kNfft / 2;                       // complex FFT size
 constexpr int kBins = kHalf + 1;
+constexpr float kImSign = 1.f;   // COMPLEX: sign that turns the untangle's imaginary parts into torch.stft's
 constexpr int kSpan = (kTile - 1) * kHop + kNfft;      // 5472 samples per tile
 constexpr int kChunks = kSpan / 2;                     // 8-byte cp.async chunks
 constexpr int kCpIters = (kChunks + kThreads - 1) / kThreads;
@@ -112,7 +113,13 @@ __device__ __forceinline__ void stage_tile(const Params& prm, unsigned b, unsign
 
 // POWER: STFT + spectral_magnitude(power=1) of the default mode - the [32 frames][257 bins] tile of
 // the power spectrum is the output (M = 257, no filterbank, no records); see fbank400_v3.cu
-template <int MC, bool POWER = false>
+// COMPLEX: the STFT itself, out [B, T, 257, 2].  The untangle works on PAIRS (k, 256 - k): the
+// thread that owns Z[k], k = k1 + 16 k2 with k2 < 8, reads the partner Z[256 - k] (a row with
+// k2 >= 8 of unit 16 - k1) and writes X[k] AND X[256 - k] in place - every exchange row is then read
+// and written by one half-warp only, so the entries can be rotated inside their row (slot (p + k) &
+// 15, one __syncwarp between a row's reads and writes) for the conflict-free store pass of
+// fbank400_v3.cu.
+template <int MC, bool POWER = false, bool COMPLEX = false>
 __global__ void __launch_bounds__(kThreads, 2) fbank512_kernel(const __grid_constant__ Params prm) {
   extern __shared__ __align__(16) float smem[];
   float* s_a = smem;                       // staged waveform, later P[bin][32]
@@ -121,7 +128,7 @@ __global__ void __launch_bounds__(kThreads, 2) fbank512_kernel(const __grid_cons
   float* s_tw = s_win + kTabW;             // [n2][k1] (re, im) of W256^(n2 k1)
   float* s_ut = s_tw + kTabTw;             // [k] (cos, sin)(2 pi k / 512)
   int2* s_meta = reinterpret_cast<int2*>(s_ut + kTabUt);
-  const int M = POWER ? kBins : (MC > 0 ? MC : prm.n_mels);
+  const int M = COMPLEX ? 2 * kBins : (POWER ? kBins : (MC > 0 ? MC : prm.n_mels));   // floats per output row
   float* s_w = reinterpret_cast<float*>(s_meta) + ((2 * M + 3) & ~3);
 
   __shared__ unsigned s_tile_key;
@@ -142,7 +149,7 @@ __global__ void __launch_bounds__(kThreads, 2) fbank512_kernel(const __grid_cons
     sincospif(2.0f * (float)i / (float)kNfft, &sn, &cs);
     reinterpret_cast<float2*>(s_ut)[i] = make_float2(cs, sn);
   }
-  for (int m = tid; !POWER && m < M; m += kThreads)
+  for (int m = tid; !POWER && !COMPLEX && m < M; m += kThreads)
     s_meta[m] = make_int2(__ldg(prm.mel_start + m) | (__ldg(prm.mel_count + m) << 16),
                           __ldg(prm.mel_offset + m));
   for (int i = tid; i < prm.mel_nnz; i += kThreads) s_w[i] = __ldg(prm.mel_weight + i);
@@ -173,7 +180,7 @@ __global__ void __launch_bounds__(kThreads, 2) fbank512_kernel(const __grid_cons
   };
   int planG[4], planW[4], planP[4];
   __syncthreads();   // tables are complete
-  if (!POWER) mel_plan(0, planG, planW, planP);
+  if (!POWER && !COMPLEX) mel_plan(0, planG, planW, planP);
 
 #pragma unroll 1
   for (unsigned tile = blockIdx.x; tile < prm.n_tiles; tile += gridDim.x) {
@@ -239,6 +246,58 @@ __global__ void __launch_bounds__(kThreads, 2) fbank512_kernel(const __grid_cons
     }
     __syncthreads();
 
+    if constexpr (COMPLEX) {
+      // ---- untangle in pairs, X in place (see the head of the kernel); X = (S - i W D) / 2 --------
+      const float2* ut = reinterpret_cast<const float2*>(s_ut);
+      const unsigned half_mask = h ? 0xffff0000u : 0x0000ffffu;   // a unit = one half-warp
+      auto put = [&](int k, const f2 xr, const f2 xi) {
+        s_e4[k * kPairs + ((p + k) & (kPairs - 1))] =
+            make_float4(0.5f * xr.v.x, kImSign * 0.5f * xi.v.x, 0.5f * xr.v.y, kImSign * 0.5f * xi.v.y);
+      };
+#pragma unroll
+      for (int k2 = 0; k2 < 8; ++k2) {
+        const int k = k1 + 16 * k2;
+        if (k == 0) {          // X[0] = Re Z0 + Im Z0 and X[256] = Re Z0 - Im Z0 share row 0 (both real)
+          const f2 x0 = Z[0].re + Z[0].im, xn = Z[0].re - Z[0].im;
+          s_e4[p] = make_float4(x0.v.x, xn.v.x, x0.v.y, xn.v.y);   // row 0 is nobody's partner row
+          continue;
+        }
+        const int kp = kHalf - k;
+        const float4 q = s_e4[kp * kPairs + p];             // Z[256 - k]; its conjugate is (br, -bi)
+        __syncwarp(half_mask);                              // the half-warp has read the row: it is free
+        const f2 br = mk2(q.x, q.y), bi = mk2(q.z, q.w);
+        const f2 sr = Z[k2].re + br, si = Z[k2].im - bi;
+        const f2 dr = Z[k2].re - br, di = Z[k2].im + bi;
+        const float2 cs = ut[k];                            // V = W D, W = (c, -s)
+        const f2 vr = fmas(dr, cs.x, muls(di, cs.y)), vi = fmas(di, cs.x, muls(dr, -cs.y));
+        put(k, sr + vi, si - vr);                           // X[k]       = (S - i V) / 2
+        put(kp, sr - vi, mk2(0.f, 0.f) - si - vr);          // X[256 - k] = (conj S - i conj V) / 2
+      }
+      if (k1 == 0) {           // k = 128 is its own partner
+        const f2 sr = Z[8].re + Z[8].re, si = mk2(0.f, 0.f), di = Z[8].im + Z[8].im;
+        const float2 cs = ut[128];                          // D = (0, 2 Im Z): V = W D
+        const f2 vr = muls(di, cs.y), vi = muls(di, cs.x);
+        put(128, sr + vi, si - vr);                         // row 128: read by nobody (Z[8] is in registers)
+      }
+      __syncthreads();
+      // ---- store pass: frame t = row of 257 (re, im) pairs, 8-byte stores, lanes over bins -------
+      const int64_t left = prm.T - t0;
+      const int nvalid = left < kTile ? (int)left : kTile;
+      float2* o2 = reinterpret_cast<float2*>(prm.out) + (b * prm.T + t0) * kBins;
+      for (int i = tid; i < nvalid * kBins; i += kThreads) {
+        const int t = i / kBins, k = i - t * kBins;
+        const int q = t >> 1, odd = t & 1;
+        float2 v;
+        if (k == 0 || k == kHalf) {
+          const float4 e = s_e4[q];
+          v = make_float2(k == 0 ? (odd ? e.z : e.x) : (odd ? e.w : e.y), 0.f);
+        } else {
+          v = reinterpret_cast<const float2*>(s_e4 + k * kPairs + ((q + k) & (kPairs - 1)))[odd];
+        }
+        o2[i] = v;
+      }
+      continue;   // the barrier behind the next tile's staging orders these reads before its stage 1
+    }
     // ---- untangle + power: bins k1 + 16 k2 (and 256 from Z[0]) --------------------------------
     {
       float2* prow = reinterpret_cast<float2*>(s_a) + p;   // row stride = 16 float2
@@ -428,12 +487,12 @@ int launch_clamp_tiles(const sbfe_fbank_desc* d, int64_t B, int64_t T, float* ou
 
 static int launch_512(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64_t L,
                       int64_t wav_stride, float* out, sbfe_maxkey_t* utt_max, float* tile_stats,
-                      float top_db, bool power, cudaStream_t stream) {
+                      float top_db, int power, cudaStream_t stream) {   // power: 1 = |X|^2, 2 = X
   using namespace v512;
   Params prm;
   prm.db = DbParams{d->multiplier * 0.30102999566398120f, d->amin, d->db_offset, d->floor_db,
                     power ? 0 : d->log_mel};
-  prm.n_mels = power ? kBins : d->n_mels;
+  prm.n_mels = power == 2 ? 2 * kBins : (power ? kBins : d->n_mels);
   prm.mel_nnz = power ? 0 : d->mel_nnz;
   prm.L = L;
   prm.wav_stride = wav_stride;
@@ -451,7 +510,7 @@ static int launch_512(const sbfe_fbank_desc* d, const float* wav, int64_t B, int
   if (tiles * B > 0x7fffffff || prm.T > 0x7fffffff) return SBFE_E_TOOBIG;
   prm.tiles_per_utt = (unsigned)tiles;
   prm.n_tiles = (unsigned)(tiles * B);
-  const size_t smem = smem_floats(prm.n_mels, prm.mel_nnz) * sizeof(float);
+  const size_t smem = smem_floats(power == 2 ? 0 : prm.n_mels, prm.mel_nnz) * sizeof(float);   // COMPLEX: no tables
   static std::atomic<int> per_sm_cache[64];   // 0 -> value, idempotent (see fbank400_v3.cu)
   int dev = 0, sms = 0;
   cudaError_t e = cudaGetDevice(&dev);
@@ -478,6 +537,13 @@ static int launch_512(const sbfe_fbank_desc* d, const float* wav, int64_t B, int
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fbank512_kernel<0, true>, kThreads,
                                                           (size_t)kMaxSmem);
       if (e == cudaSuccess && n < per_sm) per_sm = n;
+      if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(fbank512_kernel<0, false, true>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem);
+      if (e == cudaSuccess)
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fbank512_kernel<0, false, true>, kThreads,
+                                                          (size_t)kMaxSmem);
+      if (e == cudaSuccess && n < per_sm) per_sm = n;
     }
     if (e != cudaSuccess) return (int)e;
     if (per_sm < 1) return (int)cudaErrorLaunchOutOfResources;
@@ -485,7 +551,8 @@ static int launch_512(const sbfe_fbank_desc* d, const float* wav, int64_t B, int
   }
   const unsigned cap = (unsigned)(per_sm * sms);
   const unsigned grid = prm.n_tiles < cap ? prm.n_tiles : cap;
-  KernelFn kern = power ? fbank512_kernel<0, true> : pick_kernel(d->n_mels);
+  KernelFn kern = power == 2 ? fbank512_kernel<0, false, true>
+                             : (power ? fbank512_kernel<0, true> : pick_kernel(d->n_mels));
   int rc = launch_pdl(kern, dim3(grid), dim3(kThreads), (size_t)smem, stream, prm);
   if (rc == 0 && !power && tile_stats != nullptr && top_db >= 0.f)
     rc = launch_clamp_tiles(d, B, prm.T, out, tile_stats, top_db, stream);
@@ -495,7 +562,7 @@ static int launch_512(const sbfe_fbank_desc* d, const float* wav, int64_t B, int
 int launch_fbank512(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64_t L,
                     int64_t wav_stride, float* out, sbfe_maxkey_t* utt_max, float* tile_stats,
                     float top_db, cudaStream_t stream) {
-  return launch_512(d, wav, B, L, wav_stride, out, utt_max, tile_stats, top_db, false, stream);
+  return launch_512(d, wav, B, L, wav_stride, out, utt_max, tile_stats, top_db, 0, stream);
 }
 
 // STFT + power spectrum of the default mode at n_fft 512 / hop 160 (see fbank400_v3.cu)
@@ -503,9 +570,10 @@ bool stft512_power_supported(const sbfe_fbank_desc* d) {
   return d->n_fft == v512::kNfft && d->hop == v512::kHop &&
          v512::smem_floats(v512::kBins, 0) * sizeof(float) <= (size_t)v512::kMaxSmem;
 }
+// complex != 0: out [B, T, 257, 2]; else the power spectrum [B, T, 257]
 int launch_stft512_power(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64_t L,
-                         int64_t wav_stride, float* out, cudaStream_t stream) {
-  return launch_512(d, wav, B, L, wav_stride, out, nullptr, nullptr, -1.f, true, stream);
+                         int64_t wav_stride, float* out, int complex, cudaStream_t stream) {
+  return launch_512(d, wav, B, L, wav_stride, out, nullptr, nullptr, -1.f, complex ? 2 : 1, stream);
 }
 
 }  // namespace sbfe

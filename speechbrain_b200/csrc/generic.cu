@@ -393,7 +393,7 @@ bool stft400_power_supported(const sbfe_fbank_desc* d);   // fbank400_v3.cu
 int launch_stft400_power(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*, int,
                          cudaStream_t);
 bool stft512_power_supported(const sbfe_fbank_desc* d);   // fbank512.cu
-int launch_stft512_power(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*,
+int launch_stft512_power(const sbfe_fbank_desc*, const float*, int64_t, int64_t, int64_t, float*, int,
                          cudaStream_t);
 
 int launch_stft_generic(const sbfe_fbank_desc* d, const float* wav, int64_t B, int64_t L,
@@ -404,10 +404,10 @@ int launch_stft_generic(const sbfe_fbank_desc* d, const float* wav, int64_t B, i
   // the recipes' transforms (n_fft 400 / 512, hop 160, default mode), power only: the fused
   // kernels' FFTs (SBFE_STFT400_OFF: the Stockham kernel below, for the tests' cross-check)
   if (flags == 0 && getenv("SBFE_STFT400_OFF") == nullptr) {
-    if (stft400_power_supported(d))   // n_fft 400: power spectrum or the complex STFT itself
+    if (stft400_power_supported(d))   // power spectrum or the complex STFT itself
       return launch_stft400_power(d, wav, B, L, wav_stride, out, power_only ? 0 : 1, stream);
-    if (power_only && stft512_power_supported(d))
-      return launch_stft512_power(d, wav, B, L, wav_stride, out, stream);
+    if (stft512_power_supported(d))
+      return launch_stft512_power(d, wav, B, L, wav_stride, out, power_only ? 0 : 1, stream);
   }
   const int start = (flags & 1) ? 0 : -d->n_fft / 2;
   const int reflect = (flags & 2) ? 1 : 0, twosided = (flags & 4) ? 1 : 0;

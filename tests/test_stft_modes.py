@@ -100,16 +100,17 @@ def test_power_spectrum_of_the_default_mode_uses_the_fused_transform(B, L, norma
 @pytest.mark.gpu
 @pytest.mark.parametrize("B,L", [(3, 16000 + 53), (2, 5119), (1, 160 * 33), (2, 160), (32, 64000)])
 @pytest.mark.parametrize("normalized", [False, True])
-def test_complex_stft_of_the_default_mode_uses_the_fused_transform(B, L, normalized):
-    """STFT.forward at n_fft 400 / hop 160 (default mode; features.py:133-188) = the fused kernel's
-    transform with a complex store pass (csrc/fbank400_v3.cu, COMPLEX): against torch.stft in
+@pytest.mark.parametrize("n_fft", [400, 512])
+def test_complex_stft_of_the_default_mode_uses_the_fused_transform(B, L, normalized, n_fft):
+    """STFT.forward at n_fft 400 / 512, hop 160 (default mode; features.py:133-188) = the fused kernels'
+    transforms with a complex store pass (csrc/fbank400_v3.cu, fbank512.cu: COMPLEX): against torch.stft in
     float64 and the Stockham kernel it replaces.  Tolerance: 2e-6 of the frame's largest |X[k]|."""
     import speechbrain_b200 as sb
 
     torch.manual_seed(L + 1)
     wav = torch.randn(B, L, device="cuda") * 0.1
     wav[0, L // 2:] = 0.0
-    st = sb.STFT(sample_rate=16000, normalized_stft=normalized)
+    st = sb.STFT(sample_rate=16000, n_fft=n_fft, normalized_stft=normalized)
     got = st(wav)
     os.environ["SBFE_STFT400_OFF"] = "1"
     try:
@@ -117,14 +118,14 @@ def test_complex_stft_of_the_default_mode_uses_the_fused_transform(B, L, normali
     finally:
         del os.environ["SBFE_STFT400_OFF"]
     win = torch.hamming_window(400, device="cuda", dtype=torch.float64)
-    ref = torch.stft(wav.double(), 400, 160, 400, win, center=True, pad_mode="constant",
+    ref = torch.stft(wav.double(), n_fft, 160, 400, win, center=True, pad_mode="constant",
                      normalized=normalized, onesided=True, return_complex=True)
-    ref = torch.view_as_real(ref).transpose(1, 2)                  # [B, T, 201, 2]
-    assert got.shape == old.shape == ref.shape == (B, 1 + L // 160, 201, 2)
+    ref = torch.view_as_real(ref).transpose(1, 2)                  # [B, T, bins, 2]
+    assert got.shape == old.shape == ref.shape == (B, 1 + L // 160, n_fft // 2 + 1, 2)
     scale = ref.pow(2).sum(-1).sqrt().amax(dim=2, keepdim=True).unsqueeze(-1).clamp(min=1e-30)
     err_new = float(((got.double() - ref).abs() / scale).max())
     err_old = float(((old.double() - ref).abs() / scale).max())
     assert err_new <= 2e-6, (err_new, err_old)
     assert err_old <= 2e-6, (err_new, err_old)
     assert bool((got[0, L // 320 + 4:] == 0).all())
-    assert bool((got[..., 0, 1] == 0).all()) and bool((got[..., 200, 1] == 0).all())   # real bins
+    assert bool((got[..., 0, 1] == 0).all()) and bool((got[..., n_fft // 2, 1] == 0).all())   # real bins
