@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define SBFE_ABI_VERSION 12
+#define SBFE_ABI_VERSION 13
 
 #if defined(__GNUC__)
 #define SBFE_API __attribute__((visibility("default")))
@@ -336,6 +336,12 @@ SBFE_API int sbfe_wav_drop_chunks(float* d_out, int64_t B, int64_t L, int32_t ch
  * [0, L) (conv1d, no kernel flip); x, out [B, L]; n_taps <= 1024. */
 SBFE_API int sbfe_wav_fir(const float* d_x, int64_t B, int64_t L, const float* d_taps, int32_t n_taps,
                  int32_t pad, float* d_out, void* stream);
+/* DropFreq's composite filter (:977-1001, notch_filter of signal_processing.py:373-430) built on
+ * the device from the drawn frequencies: h_freqs is a HOST array of n_freqs <= 16 normalised
+ * frequencies (copied into the launch's arguments), filter_len odd <= 255; d_taps [filter_len] is
+ * what sbfe_wav_fir takes (pad = filter_len / 2). */
+SBFE_API int sbfe_wav_notch_taps(const float* h_freqs, int32_t n_freqs, float width, int32_t filter_len,
+                        float* d_taps, void* stream);
 /* DoClip (:1176-1228): out = clamp(x, -value, value) over n floats; in place when d_out == d_x. */
 SBFE_API int sbfe_wav_clip(const float* d_x, int64_t n, float value, float* d_out, void* stream);
 /* AddNoise with white noise (csv_file = None; :126-168): the caller draws snr_db [B] and the noise

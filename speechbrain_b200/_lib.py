@@ -81,6 +81,7 @@ SIGNATURES = {
     "sbfe_wav_drop_chunks": (C.c_int, [_P, _I64, _I64, _I32, _P, _I32, _I64, _P, _P, _P]),
     "sbfe_wav_fir": (C.c_int, [_P, _I64, _I64, _P, _I32, _I32, _P, _P]),
     "sbfe_wav_clip": (C.c_int, [_P, _I64, _F, _P, _P]),
+    "sbfe_wav_notch_taps": (C.c_int, [_P, _I32, _F, _I32, _P, _P]),
     "sbfe_wav_abs_chunks": (_I64, [_I64]),
     "sbfe_wav_abs_sums": (C.c_int, [_P, _I64, _I64, _P, _P]),
     "sbfe_wav_add_noise": (C.c_int, [_P, _P, _I64, _I64, _P, _P, _P, _P, _P, _P]),
@@ -90,7 +91,7 @@ SIGNATURES = {
     "sbfe_mean": (C.c_int, [_P, _I64, _P, _P, _I64, _P]),
 }
 
-ABI_VERSION = 12
+ABI_VERSION = 13
 _lock = threading.Lock()
 _lib = None
 

@@ -57,6 +57,7 @@ int launch_drop_chunks(float*, int64_t, int, const int32_t*, int, int64_t, const
                        cudaStream_t);
 int launch_fir_same(const float*, int64_t, int64_t, const float*, int, int, float*, cudaStream_t);
 int launch_clip(const float*, int64_t, float, float*, cudaStream_t);
+int launch_notch_taps(const float*, int, float, int, float*, cudaStream_t);
 int64_t abs_chunks(int64_t);
 int launch_abs_sums(const float*, int64_t, int64_t, float*, cudaStream_t);
 int launch_add_noise(const float*, const float*, int64_t, int64_t, const float*, const float*, const float*,
@@ -372,6 +373,12 @@ int sbfe_wav_clip(const float* d_x, int64_t n, float value, float* d_out, void* 
   if (n == 0) return 0;
   if (!d_x || !d_out) return SBFE_E_INVAL;
   return launch_clip(d_x, n, value, d_out, (cudaStream_t)stream);
+}
+
+int sbfe_wav_notch_taps(const float* h_freqs, int32_t n_freqs, float width, int32_t filter_len,
+                        float* d_taps, void* stream) {
+  if ((n_freqs > 0 && !h_freqs) || !d_taps) return SBFE_E_INVAL;
+  return launch_notch_taps(h_freqs, n_freqs, width, filter_len, d_taps, (cudaStream_t)stream);
 }
 
 int64_t sbfe_wav_abs_chunks(int64_t L) { return L < 0 ? SBFE_E_INVAL : abs_chunks(L); }

@@ -176,6 +176,64 @@ int launch_resample(const float* x, int64_t B, int64_t L, const float* w, const 
                     L, w, first, P, S, W, L_out, out);
 }
 
+// ---- DropFreq's composite band-reject filter on the device (speech_augmentation.py:977-1001 +
+// notch_filter, signal_processing.py:373-430): the reference builds it with ~40 small ATen ops per
+// call; here one CTA does it from the drawn frequencies (kernel arguments: no copy).
+// Per frequency f: low-pass = sinc(3 f x) * blackman, normalised to sum 1; high-pass =
+// sinc(3 (f + 2 w) x) * blackman, normalised to sum -1, + 1 at the centre; notch = their sum; the
+// running filter is cross-correlated with it (conv1d, zero padding = half the length).
+constexpr int kNotchMaxFreq = 16;
+constexpr int kNotchMaxLen = 255;
+struct NotchFreqs { float f[kNotchMaxFreq]; };
+
+__global__ void __launch_bounds__(256)
+notch_taps_kernel(const NotchFreqs fr, int n, float width, int len, float* __restrict__ taps) {
+  pdl_wait();
+  pdl_launch_dependents();
+  __shared__ float s_cur[kNotchMaxLen], s_notch[kNotchMaxLen], s_lo[kNotchMaxLen], s_hi[kNotchMaxLen];
+  __shared__ float s_sum[2];
+  const int t = threadIdx.x, pad = len / 2;
+  if (t < len) s_cur[t] = t == pad ? 1.f : 0.f;
+  for (int j = 0; j < n; ++j) {
+    const float f = fr.f[j] + width;                 // notch_freq += notch_width
+    if (t < len) {
+      const float x = (float)(t - pad);
+      const float w = 0.42f - 0.5f * cosf(6.283185307179586f * (float)t / (float)len) +
+                      0.08f * cosf(12.566370614359172f * (float)t / (float)len);   // periodic blackman
+      const float a = 3.f * (f - width) * x, b = 3.f * (f + width) * x;
+      s_lo[t] = (t == pad ? 1.f : sinf(a) / a) * w;
+      s_hi[t] = (t == pad ? 1.f : sinf(b) / b) * w;
+    }
+    __syncthreads();
+    if (t < 2) {                                      // fixed order: deterministic
+      const float* v = t == 0 ? s_lo : s_hi;
+      float acc = 0.f;
+      for (int i = 0; i < len; ++i) acc += v[i];
+      s_sum[t] = acc;
+    }
+    __syncthreads();
+    if (t < len) s_notch[t] = s_lo[t] / s_sum[0] + (s_hi[t] / -s_sum[1] + (t == pad ? 1.f : 0.f));
+    __syncthreads();
+    float acc = 0.f;
+    if (t < len)
+      for (int k = 0; k < len; ++k) {
+        const int i = t + k - pad;
+        if (i >= 0 && i < len) acc = fmaf(s_cur[i], s_notch[k], acc);
+      }
+    __syncthreads();
+    if (t < len) s_cur[t] = acc;
+    __syncthreads();
+  }
+  if (t < len) taps[t] = s_cur[t];
+}
+
+int launch_notch_taps(const float* h_freqs, int n, float width, int len, float* taps, cudaStream_t stream) {
+  if (n < 0 || n > kNotchMaxFreq || len < 1 || len > kNotchMaxLen || (len & 1) == 0) return SBFE_E_INVAL;
+  NotchFreqs fr = {};
+  for (int j = 0; j < n; ++j) fr.f[j] = h_freqs[j];
+  return launch_pdl(notch_taps_kernel, dim3(1), dim3(256), 0, stream, fr, n, width, len, taps);
+}
+
 // ---- AddNoise with white noise (speech_augmentation.py:126-168) --------------------------------
 // compute_amplitude (signal_processing.py:51-56) sums |x| over the WHOLE padded row and divides by
 // the valid length; partial sums of kAbsChunk samples, added in a fixed order by the consumer

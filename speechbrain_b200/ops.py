@@ -544,6 +544,17 @@ def wav_fir(x, taps, pad):
     return out
 
 
+def wav_notch_taps(freqs, width, filter_len, device):
+    """DropFreq's composite band-reject taps [filter_len] on ``device`` from the drawn
+    frequencies (a short python list; sbfe_wav_notch_taps: they travel as launch arguments)."""
+    taps = torch.empty(filter_len, dtype=torch.float32, device=device)
+    arr = (C.c_float * max(len(freqs), 1))(*freqs)
+    with torch.cuda.device(device):
+        check(lib().sbfe_wav_notch_taps(arr, len(freqs), float(width), int(filter_len), _ptr(taps),
+                                        _stream()))
+    return taps
+
+
 def wav_clip(x, value):
     """clamp(x, -value, value) into a new tensor (sbfe_wav_clip)."""
     out = torch.empty_like(x)

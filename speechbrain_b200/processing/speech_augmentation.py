@@ -107,13 +107,14 @@ class DropChunk(torch.nn.Module):
         utterance that has one.  ``h_valid``: valid samples per utterance (python ints);
         ``noise_draw(n)`` is called once per chunk where the reference draws its noise."""
         drop_times = torch.randint(low=self.drop_count_low, high=self.drop_count_high + 1,
-                                   size=(len(h_valid),))
+                                   size=(len(h_valid),)).tolist()
         rounds, noise_at = [], 0
         for i in range(len(h_valid)):
-            k = int(drop_times[i])
+            k = drop_times[i]
             if k == 0:
                 continue
-            length = torch.randint(low=self.drop_length_low, high=self.drop_length_high + 1, size=(k,))
+            length = torch.randint(low=self.drop_length_low, high=self.drop_length_high + 1,
+                                   size=(k,)).tolist()
             start_min = self.drop_start
             if start_min < 0:
                 start_min += h_valid[i]
@@ -122,15 +123,15 @@ class DropChunk(torch.nn.Module):
                 start_max = h_valid[i]
             if start_max < 0:
                 start_max += h_valid[i]
-            start_max = max(0, start_max - int(length.max()))
-            start = torch.randint(low=start_min, high=start_max + 1, size=(k,))
+            start_max = max(0, start_max - max(length))
+            start = torch.randint(low=start_min, high=start_max + 1, size=(k,)).tolist()
             for j in range(k):
                 if len(rounds) <= j:
                     rounds.append([])
-                rounds[j].append((i, int(start[j]), int(length[j]), noise_at))
+                rounds[j].append((i, start[j], length[j], noise_at))
                 if noise_draw is not None:
-                    noise_draw(int(length[j]))
-                    noise_at += int(length[j])
+                    noise_draw(length[j])
+                    noise_at += length[j]
         return rounds
 
     def forward(self, waveforms, lengths):
@@ -202,11 +203,19 @@ class DropFreq(torch.nn.Module):
         self.drop_width = drop_width
         self.drop_prob = drop_prob
 
-    def _draw_filter(self):
-        """The composite taps [filter_length] (host) for this call's draws (:977-1001)."""
+    def _draw_frequencies(self):
+        """This call's notch frequencies (host; the reference's draws, :977-983)."""
         drop_count = torch.randint(low=self.drop_count_low, high=self.drop_count_high + 1, size=(1,))
         drop_range = self.drop_freq_high - self.drop_freq_low
-        drop_frequency = torch.rand(drop_count) * drop_range + self.drop_freq_low
+        return torch.rand(drop_count) * drop_range + self.drop_freq_low
+
+    def _draw_filter(self):
+        """Draws + the composite taps built on the HOST (what the tests' reference replay uses;
+        forward() builds them on the device)."""
+        return self._filter_from(self._draw_frequencies())
+
+    def _filter_from(self, drop_frequency):
+        """The composite taps [filter_length] with the reference's op chain (:984-1001), host."""
         filter_length = 101
         pad = filter_length // 2
         drop_filter = torch.zeros(1, 1, filter_length)
@@ -222,8 +231,12 @@ class DropFreq(torch.nn.Module):
         done = (lambda t: t.unsqueeze(2)) if squeeze else (lambda t: t)
         if torch.rand(1) > self.drop_prob:
             return done(wav.clone())
-        taps, pad = self._draw_filter()
-        return done(ops.wav_fir(wav, taps.to(wav.device), pad))
+        freqs = self._draw_frequencies().tolist()
+        if len(freqs) > 16:        # sbfe_wav_notch_taps takes up to 16 notches per call
+            taps, pad = self._filter_from(torch.tensor(freqs))
+            return done(ops.wav_fir(wav, taps.to(wav.device), pad))
+        taps = ops.wav_notch_taps(freqs, self.drop_width, 101, wav.device)
+        return done(ops.wav_fir(wav, taps, 50))
 
 
 class DoClip(torch.nn.Module):
