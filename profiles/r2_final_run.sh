@@ -18,7 +18,7 @@ PROF_PADDED=0 ncu --set full --import-source on --clock-control none -k regex:fb
 ncu --set full --clock-control none -k regex:"fbank512|mel_umma|mel_mma" -s 3 -c 3 -f -o $O/r2f_other python profiles/prof_other.py >> $O/r2f_prof.log 2>&1
 python profiles/stepbench.py > $O/r2f_stepbench.txt 2>&1
 python profiles/configs_bench.py --json $O/r2f_configs.json > $O/r2f_configs.txt 2>&1
-(python profiles/istft_bench.py; python profiles/nfft512_bench.py; python profiles/gaussian_bench.py) > $O/r2f_general.txt 2>&1
+(python profiles/istft_bench.py; python profiles/stft_bench.py; python profiles/nfft512_bench.py; python profiles/gaussian_bench.py; python profiles/tdbench.py) > $O/r2f_general.txt 2>&1
 bash profiles/exp_timeline.sh > $O/r2f_timeline.txt 2>&1
 cat $O/r2f_tests.txt $O/r2f_stepbench.txt $O/r2f_configs.txt $O/r2f_general.txt $O/r2f_timeline.txt
 tail -c 600 $O/r2f_bench.json
