@@ -202,8 +202,11 @@ def frontend_step(fb, norm, wav, lengths):
     return norm(fb(wav), lengths)
 
 
-def time_device_resident(fb, norm, pool, steps, warmup, use_graph):
-    """K steps with inputs already in HBM; returns elapsed ms (CUDA events)."""
+def time_device_resident(fb, norm, pool, steps, warmup, use_graph, n_streams=1):
+    """K steps with inputs already in HBM; returns (run_steps, outs).  n_streams > 1: inside the
+    group graph consecutive steps - independent batches - alternate between streams, so that the
+    bandwidth-bound normalisation tail of batch i runs under the issue-bound FFT kernel of batch
+    i + 1 (every step still runs start to end on one stream)."""
     stream = torch.cuda.current_stream()
     outs = [None] * len(pool)
     if use_graph:
@@ -223,11 +226,29 @@ def time_device_resident(fb, norm, pool, steps, warmup, use_graph):
         # the same steps, one per pool slot, back to back in ONE graph: consecutive steps then
         # run without the host's graph-launch gap between them (what the frontend sees inside
         # a captured training step, where the model's kernels follow immediately)
-        group = torch.cuda.CUDAGraph()
-        group_outs = []
-        with torch.cuda.graph(group):
-            for wav, lens in pool:
-                group_outs.append(frontend_step(fb, norm, wav, lens))
+        lanes = [torch.cuda.Stream() for _ in range(n_streams - 1)]
+
+        def capture(slots):
+            g, g_outs = torch.cuda.CUDAGraph(), []
+            with torch.cuda.graph(g):
+                main = torch.cuda.current_stream()
+                fork = torch.cuda.Event()
+                fork.record(main)
+                for s in lanes:
+                    s.wait_event(fork)
+                for i, (wav, lens) in enumerate(slots):
+                    s = main if i % n_streams == 0 else lanes[i % n_streams - 1]
+                    with torch.cuda.stream(s):
+                        g_outs.append(frontend_step(fb, norm, wav, lens))
+                for s in lanes:
+                    join = torch.cuda.Event()
+                    join.record(s)
+                    main.wait_event(join)
+            return g, g_outs
+
+        group, group_outs = capture(pool)
+        rest = steps % len(pool)           # the remainder of the timed steps: one more graph
+        tail, tail_outs = capture(pool[:rest]) if rest > 1 else (None, None)
 
         def run(i):
             graphs[i % len(pool)].replay()
@@ -238,10 +259,14 @@ def time_device_resident(fb, norm, pool, steps, warmup, use_graph):
                 if n - i >= len(pool):
                     group.replay()
                     i += len(pool)
+                elif tail is not None and n - i == rest:
+                    tail.replay()
+                    i += rest
                 else:
                     graphs[i % len(pool)].replay()
                     i += 1
         run_steps.keep = group_outs
+        run_steps.keep_tail = tail_outs
     else:
         def run(i):
             wav, lens = pool[i % len(pool)]
@@ -417,6 +442,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of CUDA graphs")
+    ap.add_argument("--streams", type=int, default=2,
+                    help="streams the consecutive (independent) steps of a graph alternate between")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-cfg5", action="store_true", help="skip the cfg5 (global norm + all-reduce) leg")
     ap.add_argument("--e2e-padded", action="store_true",
@@ -472,7 +499,22 @@ def main():
     lens_dev = pool[0][1]
 
     # ---- device-resident throughput: exactly K timed steps -------------------
-    run_steps, outs = time_device_resident(fb, norm, pool, args.steps, args.warmup, not args.no_graph)
+    n_streams = 1 if args.no_graph else max(1, args.streams)
+    # the same steps on ONE stream first (reported beside the headline as run.one_stream)
+    one_ms = None
+    if n_streams > 1:
+        run1, outs1 = time_device_resident(fb, norm, pool, args.steps, args.warmup, True, 1)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        run1(args.steps)
+        e1.record()
+        torch.cuda.synchronize()
+        one_ms = max_over_ranks(e0.elapsed_time(e1))
+        ref_outs = [o.clone() for o in run1.keep]
+        del run1, outs1
+    run_steps, outs = time_device_resident(fb, norm, pool, args.steps, args.warmup, not args.no_graph,
+                                           n_streams)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     with ClockSampler(local) as clocks:
@@ -483,6 +525,16 @@ def main():
     barrier()
     ms = max_over_ranks(e0.elapsed_time(e1))
     value = world * AUDIO_S_PER_STEP * args.steps / (ms / 1e3)
+    one_stream = None
+    if one_ms is not None:
+        same = all(torch.equal(torch.nan_to_num(a), torch.nan_to_num(b))
+                   for a, b in zip(run_steps.keep, ref_outs))
+        one_stream = {"ms_per_step": one_ms / args.steps,
+                      "value": world * AUDIO_S_PER_STEP * args.steps / (one_ms / 1e3),
+                      "outputs_identical": bool(same),
+                      "note": "the same %d steps with every step on ONE stream (each batch waits for the "
+                              "previous batch's normalisation)" % args.steps}
+        del ref_outs
 
     # ---- dominant kernel alone -> roofline ------------------------------------
     k_ms = kernel_only_ms(fb, pool, reps=max(4, args.steps // POOL))
@@ -532,7 +584,13 @@ def main():
         "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": CONFIG,
-        "run": {"launch": "eager" if args.no_graph else "CUDA graphs: %d consecutive steps (one per pool slot) per graph, remainder one step per graph" % POOL,
+        "run": {"launch": "eager" if args.no_graph else
+                          "CUDA graphs: %d consecutive steps (one per pool slot) per graph, the remainder in "
+                          "one more graph; inside a graph the steps - independent batches - alternate between %d "
+                          "streams (every step runs start to end on one stream), so the bandwidth-bound "
+                          "normalisation of batch i overlaps the issue-bound FFT kernel of batch i + 1"
+                          % (POOL, n_streams),
+                "streams": n_streams, "one_stream": one_stream,
                 "parallelism": "utterance-sharded x%d, no collective on this config (sentence "
                                "statistics are per utterance); the path's one collective is "
                                "measured in the cfg5 key" % world,
