@@ -18,8 +18,24 @@ for i in range(8):
 fb, norm = sb.Fbank(n_mels=80), sb.InputNormalization(norm_type="sentence")
 
 
+from speechbrain_b200 import ops
+tab = fb._frontend_tables()
+VARIANT = int(os.environ.get("VARIANT", "0"))
+
+
 def step(w):
-    return norm(fb(w), lens)
+    if VARIANT == 0:      # the modules: one-launch normalisation beside the clamp
+        return norm(fb(w), lens)
+    if VARIANT == 3:      # the FFT kernel alone (records, no clamp launch)
+        return ops.fbank_forward(tab, w, tile_stats=True, top_db=None)[0]
+    feats, _, ts = ops.fbank_forward(tab, w, tile_stats=True, top_db=80.0)
+    if VARIANT == 4:      # + the clamp launch
+        return feats
+    if VARIANT == 1:      # statistics kernel (one CTA per utterance) + streaming apply: fewer CTA-slots held
+        m, sd = ops.norm_stats_tiles(feats, lens, ts)
+        return ops.norm_apply(feats, m, sd, per_utt=True)
+    m, sd = ops.norm_stats_tiles(feats, lens, ts)
+    return ops.norm_apply(feats, m, sd, per_utt=True, out=feats)
 
 
 def bench(n_streams):
