@@ -44,8 +44,11 @@ change of the round, assembled by `profiles/make_r2_final_md.py`; raw artefacts:
 `r2_final_bench_reference.json`, `r2_final_launches.csv`, `r2_configs.json` (2 GPUs: `r2_bench_2gpu.json`).
 GPU tests of the same pass: {read('r2f_tests.txt').strip().splitlines()[-1]}
 
-`bench.py` ({d['steps']} steps, 8 per CUDA graph, the unmodified recipe flow `normalize(compute_features(wavs), wav_lens)`):
-**{d['ms_per_step'] * 1e3:.2f} us/step = {d['value'] / 1e6:.2f} M audio-s/s** ({d['gpu_launches'] // d['steps']} launches per step); dominant
+`bench.py` ({d['steps']} steps, 8 per CUDA graph, the unmodified recipe flow `normalize(compute_features(wavs), wav_lens)`,
+consecutive independent batches alternating between {d['run'].get('streams', 1)} streams inside a graph):
+**{d['ms_per_step'] * 1e3:.2f} us/step = {d['value'] / 1e6:.2f} M audio-s/s** ({d['gpu_launches'] // d['steps']} launches per step;
+with every step on ONE stream: {(d['run'].get('one_stream') or {}).get('ms_per_step', 0) * 1e3:.2f} us/step = {(d['run'].get('one_stream') or {}).get('value', 0) / 1e6:.2f} M audio-s/s,
+outputs identical: {(d['run'].get('one_stream') or {}).get('outputs_identical')}); dominant
 kernel alone {ro['us_per_launch']:.2f} us = {ro['achieved']:.0f} GB/s = **{100 * ro['frac']:.1f} % of the measured HBM peak** ({ro['peak']} GB/s),
 whole step {100 * ro['step_frac']:.1f} %; end to end from pinned host memory {d['e2e']['value'] / 1e6:.3f} M audio-s/s (PCIe-bound),
 {d['e2e_pcm16']['value'] / 1e6:.2f} M with int16 PCM in, {d['e2e_pcm16'].get('bf16_out', {}).get('value', 0) / 1e6:.2f} M with int16 PCM in + bfloat16 features out;
