@@ -776,11 +776,13 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
   SBFE_TL(0, 2);
 }
 
-// grid = n_tiles CTAs of kClampThreads: one tile each (the refills spread over the SMs, one wave).
+// grid = B x ceil(tiles / 4) CTAs of kClampThreads, four tiles each (the keys are read once per CTA).
 // The utterance's keys and the tile's own column minima / flags are requested together (one
 // round trip); a tile with nothing below the floor costs nothing else.  The kernel lets its
 // successor start right after its own wait: sbfe_norm_sentence_tiles runs beside it (norm.cu).
 constexpr int kClampThreads = 128;
+
+constexpr int kClampTilesPerCta = 2;
 
 template <int MC>
 __global__ void __launch_bounds__(kClampThreads) clamp_tiles_kernel(const __grid_constant__ Params prm) {
@@ -791,10 +793,10 @@ __global__ void __launch_bounds__(kClampThreads) clamp_tiles_kernel(const __grid
   const int M = MC > 0 ? MC : prm.n_mels;
   const int tid = threadIdx.x;
   const int tiles = (int)prm.tiles_per_utt;
-  const unsigned b = blockIdx.x / prm.tiles_per_utt, j = blockIdx.x - b * prm.tiles_per_utt;
+  const unsigned groups = (prm.tiles_per_utt + kClampTilesPerCta - 1) / kClampTilesPerCta;
+  const unsigned b = blockIdx.x / groups, j0 = (blockIdx.x - b * groups) * kClampTilesPerCta;
   const size_t rec = tile_rec_words(M);
   const float* tsb = prm.tile_stats + (size_t)b * tiles * rec;
-  const float* ts = tsb + (size_t)j * rec;
   __shared__ unsigned s_key;
   if (tid == 0) s_key = 0u;
   unsigned key = 0u;
@@ -802,17 +804,30 @@ __global__ void __launch_bounds__(kClampThreads) clamp_tiles_kernel(const __grid
     const unsigned k = __ldg(reinterpret_cast<const unsigned*>(tsb) + (size_t)i * rec + 3 * M);
     key = k > key ? k : key;
   }
-  float mn = INFINITY;
-  for (int m = tid; m < M; m += kClampThreads) mn = fminf(mn, __ldg(ts + 2 * M + m));
-  const unsigned flags = __ldg(reinterpret_cast<const unsigned*>(ts) + 3 * M + 1);
+  // the CTA's tiles: column minima and flags requested with the keys (one round trip)
+  float mn[kClampTilesPerCta];
+  unsigned flags[kClampTilesPerCta];
+#pragma unroll
+  for (int q = 0; q < kClampTilesPerCta; ++q) {
+    mn[q] = INFINITY;
+    flags[q] = 0u;
+    if (j0 + q < prm.tiles_per_utt) {
+      const float* ts = tsb + (size_t)(j0 + q) * rec;
+      for (int m = tid; m < M; m += kClampThreads) mn[q] = fminf(mn[q], __ldg(ts + 2 * M + m));
+      flags[q] = __ldg(reinterpret_cast<const unsigned*>(ts) + 3 * M + 1);
+    }
+  }
   __syncthreads();
   key = __reduce_max_sync(0xffffffffu, key);
   if ((tid & 31) == 0 && key) atomicMax(&s_key, key);
   __syncthreads();
   if (s_key == 0u) { SBFE_TL(1, 2); return; }
   const float floor_b = max_key_decode(s_key) - prm.top_db;
-  if (__syncthreads_or(mn < floor_b) == 0) { SBFE_TL(1, 2); return; }
-  clamp_tile<MC, kClampThreads>(prm, b, j, floor_b, (flags & 1u) != 0u, tid);
+#pragma unroll
+  for (int q = 0; q < kClampTilesPerCta; ++q) {
+    if (__syncthreads_or(mn[q] < floor_b) == 0) continue;    // block-uniform (also past the last tile: inf)
+    clamp_tile<MC, kClampThreads>(prm, b, j0 + q, floor_b, (flags[q] & 1u) != 0u, tid);
+  }
   SBFE_TL(1, 2);
 }
 
@@ -930,7 +945,7 @@ static int launch_v3(const sbfe_fbank_desc* d, const void* wav, int pcm16, float
                              : (power ? fbank400_v3_kernel<false, 0, true> : pick_kernel(pcm16, d->n_mels));
   int rc = launch_pdl(kern, dim3(grid), dim3(kThreads), (size_t)smem, stream, prm);
   if (rc == 0 && !power && tile_stats != nullptr && prm.top_db < INFINITY) {
-    rc = launch_pdl(pick_clamp(d->n_mels), dim3(prm.n_tiles), dim3(kClampThreads), 0, stream, prm);
+    rc = launch_pdl(pick_clamp(d->n_mels), dim3((unsigned)(((prm.tiles_per_utt + kClampTilesPerCta - 1) / kClampTilesPerCta) * (prm.n_tiles / prm.tiles_per_utt))), dim3(kClampThreads), 0, stream, prm);
   }
   return rc;
 }
@@ -972,7 +987,7 @@ int launch_clamp_tiles(const sbfe_fbank_desc* d, int64_t B, int64_t T, float* ou
   if (tiles * B > 0x7fffffff) return SBFE_E_TOOBIG;
   prm.tiles_per_utt = (unsigned)tiles;
   prm.n_tiles = (unsigned)(tiles * B);
-  return launch_pdl(pick_clamp(d->n_mels), dim3(prm.n_tiles), dim3(kClampThreads), 0, stream, prm);
+  return launch_pdl(pick_clamp(d->n_mels), dim3((unsigned)(((prm.tiles_per_utt + kClampTilesPerCta - 1) / kClampTilesPerCta) * (prm.n_tiles / prm.tiles_per_utt))), dim3(kClampThreads), 0, stream, prm);
 }
 
 #ifdef SBFE_EXP_TIMELINE
