@@ -17,6 +17,7 @@ PROF_PADDED=0 ncu --set full --import-source on --clock-control none -k regex:fb
   python profiles/prof_fbank.py 4 >> $O/r2f_prof.log 2>&1
 ncu --set full --clock-control none -k regex:"fbank512|mel_umma|mel_mma" -s 3 -c 3 -f -o $O/r2f_other python profiles/prof_other.py >> $O/r2f_prof.log 2>&1
 python profiles/stepbench.py > $O/r2f_stepbench.txt 2>&1
+(for v in 3 4 0; do echo "variant $v (3: FFT kernel alone, 4: + clamp launch, 0: the whole step)"; VARIANT=$v python profiles/twostream.py; done) >> $O/r2f_stepbench.txt 2>&1
 python profiles/configs_bench.py --json $O/r2f_configs.json > $O/r2f_configs.txt 2>&1
 (python profiles/istft_bench.py; python profiles/stft_bench.py; python profiles/nfft512_bench.py; python profiles/gaussian_bench.py; python profiles/tdbench.py) > $O/r2f_general.txt 2>&1
 bash profiles/exp_timeline.sh > $O/r2f_timeline.txt 2>&1
