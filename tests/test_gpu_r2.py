@@ -319,3 +319,51 @@ def test_normalisation_divides_exactly(sb):
     one = ops.norm_sentence_tiles(feats, lens, ts)
     m, s = ops.norm_stats_tiles(feats, lens, ts)
     assert torch.equal(one, (feats - m[:, None, :]) / s[:, None, :])
+
+
+def test_independent_batches_on_two_streams_match_the_single_stream_run(sb):
+    """bench.py alternates consecutive batches between two streams (the normalisation of one
+    batch then runs under the FFT kernel of the next).  Every step runs start to end on one
+    stream, which is what the tile-record hand-over and SBFE_BESIDE_CLAMP need; eager and inside
+    one CUDA graph the outputs are bitwise those of the single-stream run."""
+    torch.manual_seed(9)
+    B, L = 16, 96000
+    lens = torch.linspace(0.55, 1.0, B, device="cuda")
+    pool = []
+    for i in range(6):
+        w = torch.randn(B, L, device="cuda") * 0.1
+        w[i % B, 30000:41000] = 0.0
+        for b in range(B):
+            w[b, int(round(float(lens[b]) * L)):] = 0
+        pool.append(w)
+    fb, norm = sb.Fbank(n_mels=80), sb.InputNormalization(norm_type="sentence")
+    want = [norm(fb(w), lens).clone() for w in pool]
+    torch.cuda.synchronize()
+    lanes = [torch.cuda.Stream(), torch.cuda.Stream()]
+    for s in lanes:
+        s.wait_stream(torch.cuda.current_stream())
+    got = []
+    for i, w in enumerate(pool):                      # eager
+        with torch.cuda.stream(lanes[i % 2]):
+            got.append(norm(fb(w), lens))
+    torch.cuda.synchronize()
+    for a, b in zip(got, want):
+        assert torch.equal(a, b)
+    g, keep = torch.cuda.CUDAGraph(), []
+    with torch.cuda.graph(g):                         # one graph, two parallel chains
+        main = torch.cuda.current_stream()
+        side = lanes[0]
+        fork = torch.cuda.Event()
+        fork.record(main)
+        side.wait_event(fork)
+        for i, w in enumerate(pool):
+            with torch.cuda.stream(main if i % 2 == 0 else side):
+                keep.append(norm(fb(w), lens))
+        join = torch.cuda.Event()
+        join.record(side)
+        main.wait_event(join)
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    for a, b in zip(keep, want):
+        assert torch.equal(a, b)

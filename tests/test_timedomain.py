@@ -170,3 +170,21 @@ def test_dropchunk_noise_mode_and_three_dim_input(sb):
     assert y3.shape == (6, 20000, 1)
     with pytest.raises(NotImplementedError):
         sb.DropFreq()(torch.zeros(2, 100, 2).cuda())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("count", [0, 5, 20])
+def test_dropfreq_filter_built_on_the_device_matches_the_host_chain(sb, count):
+    """0 notches (identity filter), a few (sbfe_wav_notch_taps: frequencies as launch arguments)
+    and more than the 16 that call takes (host-built taps): the module against the host chain of
+    the reference's ops + the numpy FIR."""
+    x = gt.wav(31, 3, 6000).cuda()
+    mod = sb.DropFreq(drop_count_low=count, drop_count_high=count)
+    torch.manual_seed(400 + count)
+    y = mod(x.clone())
+    torch.manual_seed(400 + count)
+    assert not torch.rand(1) > mod.drop_prob
+    taps, pad = mod._draw_filter()
+    want = otd.fir_same(x.cpu().numpy(), taps.numpy(), pad).astype(np.float32)
+    tol = 2e-6 * max(1, count)
+    assert np.abs(y.cpu().numpy() - want).max() <= tol, np.abs(y.cpu().numpy() - want).max()
