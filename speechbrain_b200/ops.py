@@ -42,8 +42,39 @@ def _f32c(t, name):
     return t.contiguous()
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def _stream():
+    """The current stream of the current device as a raw pointer (one C call where available:
+    the eager step is host-bound, torch.cuda.current_stream() costs ~4 us per use)."""
+    if _raw_stream is not None:
+        return C.c_void_p(_raw_stream(torch.cuda.current_device()))
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def stream_id(device):
+    """The raw handle (int) of ``device``'s current stream."""
+    with _on_device(device):
+        return _stream().value or 0
+
+
+class _on_device:
+    """`with _on_device(d)` only when d is not already current (the common case costs
+    ~8 us of context management per call otherwise)."""
+    __slots__ = ("ctx",)
+
+    def __init__(self, device):
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        self.ctx = None if idx == torch.cuda.current_device() else torch.cuda.device(idx)
+
+    def __enter__(self):
+        if self.ctx is not None:
+            self.ctx.__enter__()
+
+    def __exit__(self, *a):
+        if self.ctx is not None:
+            self.ctx.__exit__(*a)
 
 
 def _ptr(t):
@@ -205,19 +236,27 @@ def fbank_forward(tables, wav, tile_stats=False, top_db=80.0):
     desc, _ = tables.on(wav.device)
     out = torch.empty((B, T, tables.n_mels), dtype=torch.float32, device=wav.device)
     L_ = lib()
-    ws_bytes = L_.sbfe_fbank_workspace_bytes(C.byref(desc), B, L)
+    info = tables.__dict__.setdefault("_call_info", {})     # per (device, B, L): library answers
+    key = (wav.device.index, B, L)
+    hit = info.get(key)
+    if hit is None:
+        if len(info) > 64:
+            info.clear()
+        fr = int(L_.sbfe_fbank_tile_frames(C.byref(desc)))
+        hit = info[key] = (int(L_.sbfe_fbank_workspace_bytes(C.byref(desc), B, L)), fr,
+                           int(L_.sbfe_fbank_tile_stats_floats(C.byref(desc))) if fr > 0 else 0)
+    ws_bytes, frames_, words = hit
     ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=wav.device) if ws_bytes > 0 else None
     ts, frames = None, 0
     if tile_stats and B > 0:
-        frames = int(L_.sbfe_fbank_tile_frames(C.byref(desc)))
+        frames = frames_
         if frames > 0:
-            words = int(L_.sbfe_fbank_tile_stats_floats(C.byref(desc)))
             ts = torch.empty((B, (T + frames - 1) // frames, words), dtype=torch.float32,
                              device=wav.device)
     # with tile records the utterance maximum travels in the records: no atomics, no memset
     utt_max = None if ts is not None else torch.zeros((B,), dtype=torch.int32, device=wav.device)
     db = -1.0 if top_db is None else float(top_db)
-    with torch.cuda.device(wav.device):
+    with _on_device(wav.device):
         if ragged is not None and wav.dtype == torch.int16:
             check(L_.sbfe_fbank_forward_ragged_pcm16(C.byref(desc), _ptr(wav), _ptr(ragged.offsets),
                                                      _ptr(ragged.nsamples), B, L, ragged.scale,
@@ -234,7 +273,7 @@ def fbank_forward(tables, wav, tile_stats=False, top_db=80.0):
         rec = None
         if ts is not None:
             rec = TileStats(ts, frames, top_db)
-            rec.stream = torch.cuda.current_stream(wav.device).cuda_stream
+            rec.stream = stream_id(wav.device)
         return out, utt_max, rec
     return out, utt_max
 
@@ -252,7 +291,7 @@ def norm_stats_tiles(x, lengths, ts, mean_norm=True, std_norm=True, eps=1e-10):
     tile the valid length cuts; no pass over x).  sbfe_norm_stats_tiles."""
     B, T, F = x.shape
     lengths, mean, std = _stats_out(x, lengths)
-    with torch.cuda.device(x.device):
+    with _on_device(x.device):
         check(lib().sbfe_norm_stats_tiles(_ptr(x), _ptr(lengths), B, T, F, int(bool(mean_norm)),
                                           int(bool(std_norm)), float(eps), _ptr(ts.stats), ts.frames,
                                           -1.0 if ts.top_db is None else float(ts.top_db),
@@ -271,7 +310,7 @@ def norm_sentence_tiles(x, lengths, ts, mean_norm=True, std_norm=True, eps=1e-10
     bf16 = out_dtype == torch.bfloat16
     if out is None or bf16:   # a bfloat16 result (sbfe.h: SBFE_OUT_BF16) is always a new tensor
         out = torch.empty_like(x, dtype=torch.bfloat16 if bf16 else None)
-    with torch.cuda.device(x.device):
+    with _on_device(x.device):
         check(lib().sbfe_norm_sentence_tiles(_ptr(x), _ptr(lengths), B, T, F, int(bool(mean_norm)),
                                              int(bool(std_norm)), float(eps), _ptr(ts.stats),
                                              ts.frames, -1.0 if ts.top_db is None else float(ts.top_db),
@@ -294,7 +333,7 @@ def stft_forward(tables, wav, power_only=False, center=True, reflect=False, ones
     bins = tables.bins if onesided else tables.n_fft
     shape = (B, T, bins) if power_only else (B, T, bins, 2)
     out = torch.empty(shape, dtype=torch.float32, device=wav.device)
-    with torch.cuda.device(wav.device):
+    with _on_device(wav.device):
         check(lib().sbfe_stft_forward(C.byref(desc), _ptr(wav), B, L, L, _ptr(out),
                                       int(power_only), flags, _stream()))
     return out
@@ -311,7 +350,7 @@ def istft_forward(spec, n_fft, hop, window, center, out_len):
     L_ = lib()
     ws = torch.empty((max(int(L_.sbfe_istft_workspace_bytes(B, T, n_fft)), 16),), dtype=torch.uint8,
                      device=spec.device)
-    with torch.cuda.device(spec.device):
+    with _on_device(spec.device):
         check(L_.sbfe_istft_forward(_ptr(spec), B, T, int(n_fft), int(hop), _ptr(window),
                                     int(bool(center)), int(out_len), _ptr(out), _ptr(ws), ws.numel(),
                                     _stream()))
@@ -323,7 +362,7 @@ def spectral_magnitude(stft, power=1, log=False, eps=1e-14):
     if stft.shape[-1] != 2:
         raise ValueError("last dimension must hold (re, im)")
     out = torch.empty(stft.shape[:-1], dtype=torch.float32, device=stft.device)
-    with torch.cuda.device(stft.device):
+    with _on_device(stft.device):
         check(lib().sbfe_spectral_magnitude(_ptr(stft), out.numel(), float(power), int(bool(log)),
                                             float(eps), _ptr(out), _stream()))
     return out
@@ -338,7 +377,7 @@ def filterbank_forward(tables, spec):
     desc, _ = tables.on(spec.device)
     out = torch.empty((B, T, tables.n_mels), dtype=torch.float32, device=spec.device)
     utt_max = torch.zeros((B,), dtype=torch.int32, device=spec.device)
-    with torch.cuda.device(spec.device):
+    with _on_device(spec.device):
         check(lib().sbfe_filterbank_forward(C.byref(desc), _ptr(spec), B, T, _ptr(out),
                                             _ptr(utt_max), _stream()))
     return out, utt_max
@@ -379,7 +418,7 @@ def filterbank_forward_dense(spec, mat, log_mel=True, multiplier=10.0, amin=1e-1
     desc.mel_nnz, desc.mel_pad4, desc.mel_precision = M * bins, 0, 0
     out = torch.empty((B, T, M), dtype=torch.float32, device=spec.device)
     utt_max = torch.zeros((B,), dtype=torch.int32, device=spec.device)
-    with torch.cuda.device(spec.device):
+    with _on_device(spec.device):
         check(lib().sbfe_filterbank_forward(C.byref(desc), _ptr(spec), B, T, _ptr(out), _ptr(utt_max),
                                             _stream()))
     return out, utt_max
@@ -395,7 +434,7 @@ def post_forward(x, utt_max=None, top_db=80.0, dct=None, deltas=False, delta_win
     F_out = F0 * (3 if deltas == 1 or deltas is True else 1) * ((left + right + 1) if context else 1)
     out = x if (inplace and pure_clamp) else torch.empty((B, T, F_out), dtype=torch.float32,
                                                          device=x.device)
-    with torch.cuda.device(x.device):
+    with _on_device(x.device):
         check(lib().sbfe_post_forward(_ptr(x), B, T, F, _ptr(utt_max), float(top_db), _ptr(dct),
                                       int(F0 if dct is not None else 0), int(deltas),
                                       int(delta_window), int(bool(context)), int(left), int(right),
@@ -412,7 +451,7 @@ def norm_stats(x, lengths, mean_norm=True, std_norm=True, eps=1e-10, utt_max=Non
     L_ = lib()
     ws_bytes = L_.sbfe_norm_workspace_bytes(B, T, F)
     ws = torch.empty((max(ws_bytes, 16),), dtype=torch.uint8, device=x.device)
-    with torch.cuda.device(x.device):
+    with _on_device(x.device):
         check(L_.sbfe_norm_stats(_ptr(x), _ptr(lengths), B, T, F, int(bool(mean_norm)),
                                  int(bool(std_norm)), float(eps), _ptr(utt_max), float(top_db),
                                  _ptr(mean), _ptr(std), _ptr(ws), ws_bytes, _stream()))
@@ -423,14 +462,14 @@ def norm_reduce(mean, std):
     """[B,F] stats -> [2F+1] payload {sum mean, sum std, B} (all-reduce-able)."""
     B, F = mean.shape
     cur = torch.empty((2 * F + 1,), dtype=torch.float32, device=mean.device)
-    with torch.cuda.device(mean.device):
+    with _on_device(mean.device):
         check(lib().sbfe_norm_reduce(_ptr(mean), _ptr(std), B, F, _ptr(cur), _stream()))
     return cur
 
 
 def norm_update(cur, glob_mean, glob_std, first, weight):
     F = glob_mean.numel()
-    with torch.cuda.device(cur.device):
+    with _on_device(cur.device):
         check(lib().sbfe_norm_update(_ptr(cur), F, int(bool(first)), float(weight),
                                      _ptr(glob_mean), _ptr(glob_std), _stream()))
 
@@ -440,7 +479,7 @@ def norm_speaker_update(mean, std, row, mode, weight, table_mean, table_std):
     normalise with; updates the table rows in place."""
     B, F = mean.shape
     out_m, out_s = torch.empty_like(mean), torch.empty_like(std)
-    with torch.cuda.device(mean.device):
+    with _on_device(mean.device):
         check(lib().sbfe_norm_speaker_update(_ptr(mean), _ptr(std), B, F, _ptr(row), _ptr(mode),
                                              _ptr(weight), _ptr(table_mean), _ptr(table_std),
                                              _ptr(out_m), _ptr(out_s), _stream()))
@@ -454,7 +493,7 @@ def norm_apply(x, mean, std, per_utt, out=None, utt_max=None, top_db=80.0, out_d
     bf16 = out_dtype == torch.bfloat16
     if out is None or bf16:
         out = torch.empty_like(x, dtype=torch.bfloat16 if bf16 else None)
-    with torch.cuda.device(x.device):
+    with _on_device(x.device):
         check(lib().sbfe_norm_apply(_ptr(x), B, T, F, _ptr(mean), _ptr(std), int(bool(per_utt)),
                                     _ptr(utt_max), float(top_db), 2 if bf16 else 0, _ptr(out),
                                     _stream()))
@@ -478,7 +517,7 @@ def tensor_mean(x):
     L_ = lib()
     ws = torch.empty((int(L_.sbfe_mean_workspace_bytes()),), dtype=torch.uint8, device=x.device)
     out = torch.empty((1,), dtype=torch.float32, device=x.device)
-    with torch.cuda.device(x.device):
+    with _on_device(x.device):
         check(L_.sbfe_mean(_ptr(x), x.numel(), _ptr(out), _ptr(ws), ws.numel(), _stream()))
     return out
 
@@ -511,7 +550,7 @@ def specaugment_forward(x, warp=None, warp_mode="bicubic", freq_masks=None, time
     d_fill, f_fill = (fill, 0.0) if isinstance(fill, torch.Tensor) else (None, float(fill))
     out = torch.empty_like(x) if warp is not None else x
     c, w = (int(warp[0]), int(warp[1])) if warp is not None else (-1, -1)
-    with torch.cuda.device(x.device):
+    with _on_device(x.device):
         check(lib().sbfe_specaugment_forward(_ptr(x), B, T, F, c, w, modes.get(warp_mode, 0),
                                              _ptr(fpos), _ptr(flen), nf, _ptr(tpos), _ptr(tlen),
                                              nt, _ptr(d_fill), f_fill, _ptr(out), _stream()))
@@ -527,7 +566,7 @@ def wav_drop_chunks(out, chunks, noise=None, noise_max=None):
     tab = torch.tensor(chunks, dtype=torch.int32).reshape(-1, 4)
     max_len = int(tab[:, 2].max()) if tab.numel() else 0
     d_tab = tab.to(out.device, non_blocking=True)
-    with torch.cuda.device(out.device):
+    with _on_device(out.device):
         check(lib().sbfe_wav_drop_chunks(_ptr(out), B, L, 1, _ptr(d_tab), tab.shape[0], max_len,
                                          _ptr(noise), _ptr(noise_max), _stream()))
     return mark_written(out)
@@ -538,7 +577,7 @@ def wav_fir(x, taps, pad):
     B, L = x.shape
     out = torch.empty_like(x)
     taps = taps.to(device=x.device, dtype=torch.float32).contiguous()
-    with torch.cuda.device(x.device):
+    with _on_device(x.device):
         check(lib().sbfe_wav_fir(_ptr(x), B, L, _ptr(taps), taps.numel(), int(pad), _ptr(out),
                                  _stream()))
     return out
@@ -549,7 +588,7 @@ def wav_notch_taps(freqs, width, filter_len, device):
     frequencies (a short python list; sbfe_wav_notch_taps: they travel as launch arguments)."""
     taps = torch.empty(filter_len, dtype=torch.float32, device=device)
     arr = (C.c_float * max(len(freqs), 1))(*freqs)
-    with torch.cuda.device(device):
+    with _on_device(device):
         check(lib().sbfe_wav_notch_taps(arr, len(freqs), float(width), int(filter_len), _ptr(taps),
                                         _stream()))
     return taps
@@ -558,7 +597,7 @@ def wav_notch_taps(freqs, width, filter_len, device):
 def wav_clip(x, value):
     """clamp(x, -value, value) into a new tensor (sbfe_wav_clip)."""
     out = torch.empty_like(x)
-    with torch.cuda.device(x.device):
+    with _on_device(x.device):
         check(lib().sbfe_wav_clip(_ptr(x), x.numel(), float(value), _ptr(out), _stream()))
     return out
 
@@ -575,7 +614,7 @@ def wav_add_noise(x, noise, lengths, snr_db, normalize=False):
     chunks = int(L_.sbfe_wav_abs_chunks(L))
     partials = torch.empty((B, chunks), dtype=torch.float32, device=x.device)
     absmax = torch.zeros(B, dtype=torch.int32, device=x.device) if normalize else None
-    with torch.cuda.device(x.device):
+    with _on_device(x.device):
         check(L_.sbfe_wav_abs_sums(_ptr(x), B, L, _ptr(partials), _stream()))
         check(L_.sbfe_wav_add_noise(_ptr(x), _ptr(noise), B, L, _ptr(partials), _ptr(lengths),
                                     _ptr(snr_db), _ptr(out), _ptr(absmax) if normalize else None,
@@ -591,7 +630,7 @@ def wav_resample(x, weights, first, in_stride, n_out):
     B, L = x.shape
     out = torch.empty((B, n_out), dtype=torch.float32, device=x.device)
     P, W = weights.shape
-    with torch.cuda.device(x.device):
+    with _on_device(x.device):
         check(lib().sbfe_wav_resample(_ptr(x), B, L, _ptr(weights), _ptr(first), P, int(in_stride), W,
                                       n_out, _ptr(out), _stream()))
     return out

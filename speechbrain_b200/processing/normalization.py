@@ -111,7 +111,7 @@ class InputNormalization(torch.nn.Module):
             # statistics + normalisation in one library call, in place (:1020-1035)
             # the version check above is the statement SBFE_BESIDE_CLAMP asks for: nothing this
             # package or torch launched has written x since Fbank returned it (same stream)
-            beside = ts.stream == torch.cuda.current_stream(x.device).cuda_stream
+            beside = ts.stream == ops.stream_id(x.device)
             if self.output_dtype in (None, torch.float32) and _swappable(x):
                 # The kernel writes a fresh tensor and x takes over its storage: for the caller x
                 # IS normalised when the call returns, like the reference's x[snt_id] = ... - but
