@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define SBFE_ABI_VERSION 13
+#define SBFE_ABI_VERSION 14
 
 #if defined(__GNUC__)
 #define SBFE_API __attribute__((visibility("default")))
@@ -361,6 +361,13 @@ SBFE_API int sbfe_wav_add_noise(const float* d_x, const float* d_noise, int64_t 
                        float* d_out, uint32_t* d_absmax, void* stream);
 SBFE_API int sbfe_wav_peak_normalize(float* d_x, int64_t B, int64_t L, const uint32_t* d_absmax,
                             void* stream);
+/* AddBabble.forward (:861-906): babble[b] = x[b-1] + ... + x[b-speakers] (rows modulo B, added in
+ * that order), out = x * (1 - f) + babble * (f * amp / (bamp + 1e-14)) with amp = sum|x[b]| /
+ * (d_lengths[b] * L), bamp = sum|babble[b]| / max_s(d_lengths[b-s] * L), f as in
+ * sbfe_wav_add_noise.  d_partials: scratch of 2 * B * sbfe_wav_abs_chunks(L) floats; d_out must not
+ * be d_x (every row is read by `speakers` other rows). */
+SBFE_API int sbfe_wav_add_babble(const float* d_x, int64_t B, int64_t L, int32_t speakers, float* d_partials,
+                        const float* d_lengths, const float* d_snr_db, float* d_out, void* stream);
 /* Resample._perform_resample (:600-665), Kaldi's LinearResample: output sample n * phases + i =
  * sum_k d_weights[i][k] x[d_first[i] + n * in_stride + k] (x zero outside [0, L)), k < width;
  * x [B, L] -> out [B, L_out].  Weights and first indices: Resample._indices_and_weights (:740-820). */

@@ -10,6 +10,7 @@ to the samples:
   resample      Resample._perform_resample speech_augmentation.py:600-665
   add_noise     AddNoise.forward (white)   speech_augmentation.py:126-168 (+ compute_amplitude,
                 dB_to_amplitude: signal_processing.py:51-56, 355-372)
+  add_babble    AddBabble.forward          speech_augmentation.py:861-906
 Pinned on outputs of the unmodified reference modules (tests/golden/timedomain_golden.npz,
 tests/make_golden_timedomain.py) in tests/test_timedomain.py.
 """
@@ -85,3 +86,25 @@ def add_noise(x, noise, lengths, snr_db, normalize=False):
     if normalize:
         y = y / np.maximum(np.abs(y).max(axis=1, keepdims=True), f32(1))
     return y.astype(f32)
+
+
+def add_babble(x, lengths, snr_db, speakers):
+    """x [B, L] float32; lengths [B] relative; snr_db [B].  The reference's float32 ops in its
+    order: babble = roll(x, 1) + roll(x, 2) + ... (in place, in that order); babble_len = the
+    running maximum of the rolled lengths; scale = (f amp) / (sum|babble| / babble_len + 1e-14)."""
+    f32 = np.float32
+    x = np.asarray(x, dtype=f32)
+    B, L = x.shape
+    ln = (np.asarray(lengths, dtype=f32) * f32(L)).reshape(B, 1)
+    amp = np.abs(x).sum(axis=1, keepdims=True, dtype=np.float64).astype(f32) / ln
+    snr = np.asarray(snr_db, dtype=f32).reshape(B, 1)
+    f = (f32(1) / (np.power(f32(10), snr / f32(20), dtype=f32) + f32(1))).astype(f32)
+    y = x * (f32(1) - f)
+    babble = np.roll(x, 1, axis=0).copy()
+    blen = np.roll(ln, 1, axis=0)
+    for i in range(1, speakers):
+        babble = babble + np.roll(x, 1 + i, axis=0)
+        blen = np.maximum(blen, np.roll(blen, 1, axis=0))
+    bamp = np.abs(babble).sum(axis=1, keepdims=True, dtype=np.float64).astype(f32) / blen
+    babble = babble * ((f * amp) / (bamp + f32(1e-14)))
+    return (y + babble).astype(f32)

@@ -12,7 +12,7 @@ from .lobes.features import MFCC, Fbank, pair  # noqa: F401
 from .processing.features import (  # noqa: F401
     DCT, ISTFT, STFT, ContextWindow, Deltas, Filterbank, InputNormalization, spectral_magnitude)
 from .processing.speech_augmentation import (  # noqa: F401
-    AddNoise, DoClip, DropChunk, DropFreq, Resample, SpeedPerturb)
+    AddBabble, AddNoise, DoClip, DropChunk, DropFreq, Resample, SpeedPerturb)
 
 __version__ = "0.1.0"
 
@@ -49,7 +49,7 @@ def install():
         patched += ["speechbrain.lobes.augment.SpecAugment",
                     "speechbrain.lobes.augment.TimeDomainSpecAugment"]
         sa = importlib.import_module("speechbrain.processing.speech_augmentation")
-        for name in ("DropChunk", "DropFreq", "DoClip", "Resample", "SpeedPerturb"):
+        for name in ("DropChunk", "DropFreq", "DoClip", "Resample", "SpeedPerturb", "AddBabble"):
             setattr(sa, name, getattr(here, name))
             patched.append("speechbrain.processing.speech_augmentation." + name)
     except Exception:

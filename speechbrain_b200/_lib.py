@@ -86,12 +86,13 @@ SIGNATURES = {
     "sbfe_wav_abs_sums": (C.c_int, [_P, _I64, _I64, _P, _P]),
     "sbfe_wav_add_noise": (C.c_int, [_P, _P, _I64, _I64, _P, _P, _P, _P, _P, _P]),
     "sbfe_wav_peak_normalize": (C.c_int, [_P, _I64, _I64, _P, _P]),
+    "sbfe_wav_add_babble": (C.c_int, [_P, _I64, _I64, _I32, _P, _P, _P, _P, _P]),
     "sbfe_wav_resample": (C.c_int, [_P, _I64, _I64, _P, _P, _I32, _I32, _I32, _I64, _P, _P]),
     "sbfe_mean_workspace_bytes": (_I64, []),
     "sbfe_mean": (C.c_int, [_P, _I64, _P, _P, _I64, _P]),
 }
 
-ABI_VERSION = 13
+ABI_VERSION = 14
 _lock = threading.Lock()
 _lib = None
 

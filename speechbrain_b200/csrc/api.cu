@@ -63,6 +63,8 @@ int launch_abs_sums(const float*, int64_t, int64_t, float*, cudaStream_t);
 int launch_add_noise(const float*, const float*, int64_t, int64_t, const float*, const float*, const float*,
                      float*, unsigned*, cudaStream_t);
 int launch_peak_normalize(float*, int64_t, int64_t, const unsigned*, cudaStream_t);
+int launch_add_babble(const float*, int64_t, int64_t, int, float*, float*, const float*, const float*, float*,
+                      cudaStream_t);
 int launch_resample(const float*, int64_t, int64_t, const float*, const int32_t*, int, int, int,
                     int64_t, float*, cudaStream_t);
 int64_t mean_workspace_bytes();
@@ -398,6 +400,15 @@ int sbfe_wav_add_noise(const float* d_x, const float* d_noise, int64_t B, int64_
   if (!d_x || !d_noise || !d_partials || !d_lengths || !d_snr_db || !d_out) return SBFE_E_INVAL;
   return launch_add_noise(d_x, d_noise, B, L, d_partials, d_lengths, d_snr_db, d_out, d_absmax,
                           (cudaStream_t)stream);
+}
+
+int sbfe_wav_add_babble(const float* d_x, int64_t B, int64_t L, int32_t speakers, float* d_partials,
+                        const float* d_lengths, const float* d_snr_db, float* d_out, void* stream) {
+  if (B < 0 || L < 0 || speakers < 1) return SBFE_E_INVAL;
+  if (B == 0 || L == 0) return 0;
+  if (!d_x || !d_partials || !d_lengths || !d_snr_db || !d_out || d_out == d_x) return SBFE_E_INVAL;
+  return launch_add_babble(d_x, B, L, speakers, d_partials, d_partials + B * abs_chunks(L), d_lengths,
+                           d_snr_db, d_out, (cudaStream_t)stream);
 }
 
 int sbfe_wav_peak_normalize(float* d_x, int64_t B, int64_t L, const uint32_t* d_absmax, void* stream) {

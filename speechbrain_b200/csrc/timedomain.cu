@@ -344,4 +344,97 @@ int launch_peak_normalize(float* x, int64_t B, int64_t L, const unsigned* absmax
 }
 
 
+// ---- AddBabble (speech_augmentation.py:861-906): the batch's own signals as babble noise --------
+// babble[b] = x[b-1] + x[b-2] + ... + x[b-S] (rows modulo B, added in that order like the
+// reference's in-place roll-and-add), scaled to the drawn SNR against x[b].  Two passes: the sums
+// of |babble| per 16384 samples (fixed-order partials, like abs_sums_kernel), then the mix, which
+// recomputes the babble from the S rows (the batch sits in L2).
+__device__ __forceinline__ float babble_at(const float* __restrict__ x, int64_t B, int64_t L, int64_t b,
+                                           int S, int64_t i) {
+  int64_t r = b - 1 < 0 ? b - 1 + B : b - 1;
+  float acc = __ldg(x + r * L + i);
+  for (int s = 1; s < S; ++s) {
+    r = r - 1 < 0 ? r - 1 + B : r - 1;
+    acc = __fadd_rn(acc, __ldg(x + r * L + i));
+  }
+  return acc;
+}
+
+__global__ void __launch_bounds__(kTdThreads)
+babble_abs_sums_kernel(const float* __restrict__ x, int64_t B, int64_t L, int S,
+                       float* __restrict__ partials, int chunks) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int64_t b = blockIdx.y;
+  const int64_t lo = (int64_t)blockIdx.x * kAbsChunk;
+  const int64_t hi = lo + kAbsChunk < L ? lo + kAbsChunk : L;
+  float acc = 0.f;
+  for (int64_t i = lo + threadIdx.x; i < hi; i += kTdThreads) acc += fabsf(babble_at(x, B, L, b, S, i));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  __shared__ float s_part[kTdThreads / 32];
+  if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < kTdThreads / 32; ++w) t += s_part[w];
+    partials[b * chunks + blockIdx.x] = t;
+  }
+}
+
+// out = x * (1 - f) + babble * (f * amp / (bamp + 1e-14)): amp = sum|x[b]| / (len[b] L),
+// bamp = sum|babble[b]| / max_{s = 1..S} (len[b - s] L), f = 1 / (10^(snr / 20) + 1)
+__global__ void __launch_bounds__(kTdThreads)
+add_babble_kernel(const float* __restrict__ x, int64_t B, int64_t L, int S,
+                  const float* __restrict__ clean_partials, const float* __restrict__ babble_partials,
+                  int chunks, const float* __restrict__ lengths, const float* __restrict__ snr,
+                  float* __restrict__ out) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int64_t b = blockIdx.y;
+  __shared__ float s_keep, s_scale;
+  if (threadIdx.x == 0) {
+    float tc = 0.f, tb = 0.f;
+    for (int c = 0; c < chunks; ++c) {
+      tc += clean_partials[b * chunks + c];
+      tb += babble_partials[b * chunks + c];
+    }
+    const float amp = tc / (__ldg(lengths + b) * (float)L);
+    float blen = 0.f;
+    int64_t r = b;
+    for (int s = 0; s < S; ++s) {
+      r = r - 1 < 0 ? r - 1 + B : r - 1;
+      blen = fmaxf(blen, __ldg(lengths + r) * (float)L);
+    }
+    const float bamp = tb / blen;
+    const float f = 1.f / (powf(10.f, __ldg(snr + b) / 20.f) + 1.f);
+    s_keep = 1.f - f;
+    s_scale = (f * amp) / (bamp + 1e-14f);
+  }
+  __syncthreads();
+  const float keep = s_keep, scale = s_scale;
+  const float* xb = x + b * L;
+  float* ob = out + b * L;
+  for (int64_t i = (int64_t)blockIdx.x * kTdThreads + threadIdx.x; i < L; i += (int64_t)gridDim.x * kTdThreads)
+    ob[i] = __fadd_rn(__fmul_rn(__ldg(xb + i), keep), __fmul_rn(babble_at(x, B, L, b, S, i), scale));
+}
+
+int launch_add_babble(const float* x, int64_t B, int64_t L, int S, float* clean_partials,
+                      float* babble_partials, const float* lengths, const float* snr, float* out,
+                      cudaStream_t stream) {
+  if (B == 0 || L == 0) return 0;
+  const int64_t chunks = abs_chunks(L);
+  if (B > 65535 || chunks > 0x7fffffff || S < 1) return SBFE_E_INVAL;
+  int rc = launch_abs_sums(x, B, L, clean_partials, stream);
+  if (rc) return rc;
+  rc = launch_pdl(babble_abs_sums_kernel, dim3((unsigned)chunks, (unsigned)B), dim3(kTdThreads), 0, stream, x,
+                  B, L, S, babble_partials, (int)chunks);
+  if (rc) return rc;
+  int64_t bx = (L + 4 * kTdThreads - 1) / (4 * kTdThreads);
+  if (bx > 148 * 8) bx = 148 * 8;
+  return launch_pdl(add_babble_kernel, dim3((unsigned)bx, (unsigned)B), dim3(kTdThreads), 0, stream, x, B, L, S,
+                    (const float*)clean_partials, (const float*)babble_partials, (int)chunks, lengths, snr,
+                    out);
+}
+
 }  // namespace sbfe

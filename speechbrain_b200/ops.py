@@ -624,6 +624,22 @@ def wav_add_noise(x, noise, lengths, snr_db, normalize=False):
     return out
 
 
+def wav_add_babble(x, lengths, snr_db, speakers):
+    """AddBabble's arithmetic (sbfe_wav_add_babble): x [B, L], lengths (relative) and snr_db [B] on
+    the device; returns a new tensor."""
+    B, L = x.shape
+    out = torch.empty_like(x)
+    if B == 0 or L == 0:
+        return out
+    L_ = lib()
+    chunks = int(L_.sbfe_wav_abs_chunks(L))
+    partials = torch.empty((2, B, chunks), dtype=torch.float32, device=x.device)
+    with _on_device(x.device):
+        check(L_.sbfe_wav_add_babble(_ptr(x), B, L, int(speakers), _ptr(partials), _ptr(lengths),
+                                     _ptr(snr_db), _ptr(out), _stream()))
+    return out
+
+
 def wav_resample(x, weights, first, in_stride, n_out):
     """Polyphase resampling of x [B, L] -> [B, n_out] (sbfe_wav_resample); weights [P, W] float32
     and first [P] int32 on x's device."""

@@ -10,9 +10,9 @@ slice assignments and, for the resampler, five ATen calls per polyphase branch.
 
 Waveforms are ``[batch, time]`` float32 on a CUDA device (``[batch, time, 1]`` is accepted and
 returned as such); multi-channel input raises ``NotImplementedError``.  ``AddNoise`` (:30-290)
-is built for its white-noise mode (``csv_file=None``); with a CSV of noise files it raises, as do
-``AddReverb`` / ``AddBabble``, which are not built: they sit on the reference's CSV data loaders
-(out of scope).
+is built for its white-noise mode (``csv_file=None``; with a CSV of noise files it raises) and
+``AddBabble`` (:824-906) in full; ``AddReverb`` is not built: it sits on the reference's CSV data
+loader (out of scope).
 """
 import math
 
@@ -20,7 +20,7 @@ import torch
 
 from .. import ops
 
-__all__ = ["AddNoise", "DropChunk", "DropFreq", "DoClip", "Resample", "SpeedPerturb"]
+__all__ = ["AddNoise", "AddBabble", "DropChunk", "DropFreq", "DoClip", "Resample", "SpeedPerturb"]
 
 
 def _as_2d(waveforms, who):
@@ -73,6 +73,31 @@ class AddNoise(torch.nn.Module):
         noise = torch.randn_like(x)                             # :148
         lengths = lengths.to(device=x.device, dtype=torch.float32).contiguous()
         out = ops.wav_add_noise(x, noise, lengths, snr.reshape(-1).contiguous(), self.normalize)
+        return out.unsqueeze(2) if was3 else out
+
+
+class AddBabble(torch.nn.Module):
+    """Babble noise from the batch's own signals; reference :824-906.  Same constructor, same
+    draws (``torch.rand(1)``, ``torch.rand(B, 1, device=...)``); the rolls, sums, amplitudes and
+    the mix are three launches (csrc/timedomain.cu) instead of ~25 ATen ops over the batch."""
+
+    def __init__(self, speaker_count=3, snr_low=0, snr_high=0, mix_prob=1):
+        super().__init__()
+        self.speaker_count = speaker_count
+        self.snr_low = snr_low
+        self.snr_high = snr_high
+        self.mix_prob = mix_prob
+
+    def forward(self, waveforms, lengths):
+        x, was3 = _as_2d(waveforms, "AddBabble")
+        x = x.float().contiguous()
+        if torch.rand(1) > self.mix_prob:                       # :881-882
+            out = x.clone()
+            return out.unsqueeze(2) if was3 else out
+        snr = torch.rand(len(x), 1, device=x.device)            # :886-887
+        snr = snr * (self.snr_high - self.snr_low) + self.snr_low
+        lengths = lengths.to(device=x.device, dtype=torch.float32).contiguous()
+        out = ops.wav_add_babble(x, lengths, snr.reshape(-1).contiguous(), self.speaker_count)
         return out.unsqueeze(2) if was3 else out
 
 

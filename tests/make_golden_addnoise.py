@@ -1,5 +1,6 @@
 """Generate ``tests/golden/addnoise_golden.npz``: the UNMODIFIED reference ``AddNoise`` in its
-white-noise mode (``/root/reference``, speechbrain/processing/speech_augmentation.py:30-168) on CPU
+white-noise mode and ``AddBabble`` (``/root/reference``, speechbrain/processing/speech_augmentation.py:30-168,
+824-906) on CPU
 under ``torch.manual_seed(seed)``.
 
     python tests/make_golden_addnoise.py
@@ -28,6 +29,15 @@ CASES = {
 }
 
 
+# AddBabble: name: (kwargs, input (seed, B, L, gain), run seed)
+BABBLE = {
+    "babble_default": ({}, (31, 5, 8000, 0.1), 301),
+    "babble_snr_range": ({"speaker_count": 2, "snr_low": 5, "snr_high": 20}, (32, 4, 5003, 0.2), 302),
+    "babble_wraps": ({"speaker_count": 5, "snr_low": -5, "snr_high": 5}, (33, 3, 3000, 0.1), 303),
+    "babble_skipped": ({"mix_prob": 0.0}, (34, 2, 1000, 0.1), 304),
+}
+
+
 def wav(seed, B, L, gain):
     g = torch.Generator().manual_seed(seed)
     x = torch.randn(B, L, generator=g) * gain
@@ -45,6 +55,13 @@ def main():
     for name, (kw, (s, B, L, gain), seed) in CASES.items():
         x, lens = wav(s, B, L, gain)
         mod = ref_sa.AddNoise(**kw)
+        torch.manual_seed(seed)
+        y = mod(x.clone(), lens)
+        out[name + "/out"] = y.numpy()
+        print("%-18s %s max |y| %.3f" % (name, tuple(y.shape), float(y.abs().max())))
+    for name, (kw, (s, B, L, gain), seed) in BABBLE.items():
+        x, lens = wav(s, B, L, gain)
+        mod = ref_sa.AddBabble(**kw)
         torch.manual_seed(seed)
         y = mod(x.clone(), lens)
         out[name + "/out"] = y.numpy()

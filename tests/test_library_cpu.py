@@ -21,7 +21,7 @@ def test_library_exports_every_declared_symbol():
     assert declared and declared == set(_lib.SIGNATURES)
     for name in declared:
         assert getattr(handle, name) is not None
-    assert handle.sbfe_abi_version() == _lib.ABI_VERSION == 13
+    assert handle.sbfe_abi_version() == _lib.ABI_VERSION == 14
     assert handle.sbfe_num_frames(16000, 160) == 101
     assert handle.sbfe_error_string(-1).decode().startswith("sbfe")
 
