@@ -29,7 +29,8 @@ mods = [("DropChunk", sb.DropChunk(), True), ("DropFreq", sb.DropFreq(), False),
         ("Resample 16k -> 15.2k", sb.Resample(16000, 15200), False),
         ("SpeedPerturb [95, 100, 105]", sb.SpeedPerturb(16000), False),
         ("AddNoise (white, snr 0..15)", sb.AddNoise(snr_low=0, snr_high=15), True),
+        ("AddBabble (3 speakers, snr 0..15)", sb.AddBabble(snr_low=0, snr_high=15), True),
         ("TimeDomainSpecAugment", sb.TimeDomainSpecAugment(), True)]
 for name, m, with_len in mods:
     us = timed((lambda: m(wav, lens)) if with_len else (lambda: m(wav)))
-    print("%-30s %8.1f us per call   (read + write once at the HBM peak: %.1f us)" % (name, us, BYTES / 6553.3e3))
+    print("%-34s %8.1f us per call   (read + write once at the HBM peak: %.1f us)" % (name, us, BYTES / 6553.3e3))
