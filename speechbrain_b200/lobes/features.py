@@ -3,10 +3,12 @@
 Same constructors, sub-module names (``compute_STFT``, ``compute_fbanks``,
 ``compute_dct``, ``compute_deltas``, ``context_window``), ``state_dict`` keys and
 ``[batch, time, features]`` output as the reference (speechbrain/lobes/features.py:
-22-281), but ``forward`` is one or two kernel launches instead of a chain of 15-25
-ATen ops:
-  plain log-mel   sbfe_fbank_forward (finisher mode): wav -> final, clamped log-mel
-  otherwise       sbfe_fbank_forward  wav -> un-clamped log-mel + per-utterance max
+22-281), but ``forward`` is one library call (two kernel launches) instead of a chain of
+15-25 ATen ops:
+  plain log-mel   sbfe_fbank_forward, mode (b): wav -> log-mel + per-tile records, then the
+                  top_db clamp launch; the records ride on the returned tensor for a
+                  following InputNormalization (processing/normalization.py)
+  otherwise       sbfe_fbank_forward, mode (a): wav -> un-clamped log-mel + per-utterance max
                   sbfe_post_forward   top_db clamp [-> DCT] [-> deltas] [-> context window]
 """
 import torch
@@ -22,9 +24,9 @@ def pair(compute_features, normalizer):
     """Kept for source compatibility with round-1 recipes: a no-op.
 
     It used to declare that the features go straight into ``normalizer`` so that the top_db
-    clamp could be deferred to it.  The fused kernel now finishes every utterance itself (every
-    CTA clamps the tiles it produced once their utterance is complete, csrc/fbank400_v3.cu), so an
-    unmodified recipe - ``normalize(compute_features(wavs), wav_lens)`` - already gets the
+    clamp could be deferred to it.  ``sbfe_fbank_forward`` now clamps itself (a second, small
+    launch of the same call, csrc/fbank400_v3.cu) and the normalisation runs beside that launch,
+    so an unmodified recipe - ``normalize(compute_features(wavs), wav_lens)`` - already gets the
     shortest chain and the tensor ``compute_features`` returns is always final."""
     if not isinstance(compute_features, _Lobe):
         raise TypeError("pair() takes a speechbrain_b200 Fbank / MFCC")
@@ -86,9 +88,9 @@ class _Lobe(torch.nn.Module):
             spec = ops.stft_forward(self.compute_STFT.tables(), ops._wav2d(wav.detach()), power_only=True)
             return fb(spec)
         if dct is None and not self.deltas and not ctx and fb.log_mel:
-            # plain log-mel: ONE launch.  The fused kernel finishes each utterance itself (top_db
-            # clamp, per-tile moments); a following InputNormalization gets its statistics from
-            # the records handed over on the returned tensor instead of a pass over it
+            # plain log-mel: ONE library call (fused kernel + its clamp launch).  A following
+            # InputNormalization gets its statistics from the per-tile records handed over on the
+            # returned tensor instead of a pass over it
             feats, utt_max, ts = ops.fbank_forward(self._frontend_tables(), wav, tile_stats=True,
                                                    top_db=fb.top_db)
             if ts is not None:
