@@ -396,7 +396,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
               ts[M + m] = 0.f;
               ts[2 * M + m] = v;
             }
-            // word 1 of the keys: flags, bit 0 = constant tile (the finisher refills it unread)
+            // word 1 of the keys: flags, bit 0 = constant tile (the clamp launch refills it unread)
             if (tid < kTileKeys)
               reinterpret_cast<unsigned*>(ts)[3 * M + tid] = tid == 0 ? key : (tid == 1 ? 1u : 0u);
           }
@@ -721,7 +721,7 @@ __global__ void __launch_bounds__(kThreads, SBFE_EXP_MINB) fbank400_v3_kernel(co
     }
     // ---- per-tile column statistics (un-clamped values) for InputNormalization --------------------
     // mean / M2 (sum of squared deviations) / min over the tile's existing frames, so that the
-    // normalisation needs no second pass over the features (norm.cu: prefix_stats_block, after finish_utterance)
+    // normalisation needs no second pass over the features (norm.cu: tile_stats_block, norm_sentence_tiles_kernel)
     if (prm.tile_stats != nullptr) {
       if (tid < kTileKeys)
         reinterpret_cast<unsigned*>(prm.tile_stats)[(size_t)tile * tile_rec_words(M) + 3 * M + tid] =

@@ -1,6 +1,6 @@
 """Multi-rank GPU test of the path's one collective (BASELINE.json configs[4]):
 two ranks each run Fbank(80) + InputNormalization("global", sync_stats=True) on THEIR (uneven)
-shard for three training steps - the real kernels (fused Fbank with finisher, norm_stats_tiles,
+shard for three training steps - the real kernels (fused Fbank with tile records + clamp launch, norm_stats_tiles,
 norm_reduce, norm_update, norm_apply) and a real all-reduce of the 161-float payload: NCCL with
 one rank per GPU when the box has two GPUs, else both ranks on cuda:0 over gloo.  Every rank's
 output must equal its slice of the ORACLE (numpy, float64 features) run single-process on the
